@@ -1,0 +1,162 @@
+/*
+ * stgcn_b200 -- C-ABI of the B200-native ST-GCN block path.
+ *
+ * The reference (nagyrajmund/st-gcn) has no FFI layer: its hot path is the
+ * Python class SpatialTemporalConv (src/network/st_graphconv.py:4-109) calling
+ * stock torch modules.  This header is the boundary a maintainer binds instead
+ * (ctypes stub in INTEGRATION.md): plain pointers and sizes, no torch types.
+ *
+ * Conventions
+ *   - every data pointer is a DEVICE pointer owned by the caller (PyTorch);
+ *     the library never allocates or frees caller-visible memory;
+ *   - activations are channels-last: x[n][t][v][c] (logical (N,C,T,V) with
+ *     torch.channels_last strides), element type given by StgcnBlockDesc.dtype;
+ *   - parameters and parameter gradients are fp32 in the reference's
+ *     state_dict layouts (st_graphconv.py:28,34,41-46,129,136);
+ *   - all launches go to the cudaStream_t passed in (as void*), no host sync,
+ *     no allocation: CUDA-graph capturable;
+ *   - return value 0 = ok, negative = error; stgcn_last_error() gives the text.
+ *     There is no CPU fallback: unsupported input is an error.
+ */
+#ifndef STGCN_B200_H_
+#define STGCN_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define STGCN_OK 0
+#define STGCN_ERR_INVALID (-1)
+#define STGCN_ERR_UNSUPPORTED (-2)
+#define STGCN_ERR_CUDA (-3)
+#define STGCN_ERR_WORKSPACE (-4)
+
+enum { STGCN_F32 = 0, STGCN_BF16 = 1 };
+enum { STGCN_RES_NONE = 0, STGCN_RES_IDENTITY = 1, STGCN_RES_CONV = 2 };
+/* StgcnBlockDesc.flags */
+enum {
+  STGCN_FLAG_FORCE_SIMT = 1,     /* bf16 storage but CUDA-core GEMMs (debug / A-B) */
+};
+
+/* One SpatialTemporalConv call: replaces SpatialTemporalConv.__init__ arguments
+ * (st_graphconv.py:9) + the runtime shape of forward's f_in (st_graphconv.py:85). */
+typedef struct StgcnBlockDesc {
+  int32_t n;          /* batch (persons folded in), f_in.shape[0]            */
+  int32_t c_in;       /* C_in                                                 */
+  int32_t c_out;      /* C_out                                                */
+  int32_t t;          /* input frames T                                       */
+  int32_t v;          /* joints V = A.shape[1]  (<= 32)                       */
+  int32_t k;          /* partitions K = A.shape[0] (<= 4)                     */
+  int32_t gamma;      /* temporal kernel size (odd, <= 15)                    */
+  int32_t stride;     /* temporal stride (1 or 2)                             */
+  int32_t pad;        /* temporal zero padding                                */
+  int32_t dtype;      /* STGCN_F32 | STGCN_BF16 : activation storage type     */
+  int32_t training;   /* module.training: batch statistics + running update   */
+  int32_t residual;   /* STGCN_RES_*  (st_graphconv.py:23-28)                 */
+  int32_t flags;
+  float dropout_p;    /* nn.Dropout p, 0 = none (st_graphconv.py:53-58)       */
+  float bn_eps;       /* 1e-5                                                 */
+  float bn_momentum;  /* 0.1                                                  */
+  uint64_t seed;      /* Philox seed / offset for dropout                     */
+  uint64_t offset;
+} StgcnBlockDesc;
+
+/* Parameters and buffers, named like the reference's state_dict. */
+typedef struct StgcnBlockParams {
+  const float* bn1_weight;  const float* bn1_bias;      /* batch_n.*    (C_in)  */
+  float* bn1_running_mean;  float* bn1_running_var;     /* updated in training  */
+  int64_t* bn1_num_batches_tracked;
+  const float* A;                                       /* spatialConv.A (K,V,V) */
+  const float* W;                                       /* spatialConv.W.weight (K*C_out, C_in) */
+  const float* W_bias;                                  /* spatialConv.W.bias (K*C_out) */
+  const float* Wt;                                      /* temporalConv.weight (C_out,C_out,gamma) */
+  const float* Wt_bias;                                 /* temporalConv.bias (C_out) */
+  const float* bn2_weight;  const float* bn2_bias;      /* batch_n_2.*  (C_out) */
+  float* bn2_running_mean;  float* bn2_running_var;
+  int64_t* bn2_num_batches_tracked;
+  const float* Wr;                                      /* apply_residual.weight (C_out,C_in) or NULL */
+  const float* Wr_bias;                                 /* apply_residual.bias (C_out) or NULL */
+} StgcnBlockParams;
+
+/* Parameter gradients (fp32, overwritten).  Same shapes as the parameters. */
+typedef struct StgcnBlockGrads {
+  float* bn1_weight; float* bn1_bias;
+  float* A;
+  float* W; float* W_bias;
+  float* Wt; float* Wt_bias;
+  float* bn2_weight; float* bn2_bias;
+  float* Wr; float* Wr_bias;
+} StgcnBlockGrads;
+
+/* T_out = (T + 2*pad - gamma)/stride + 1 */
+int32_t stgcn_block_t_out(const StgcnBlockDesc* desc);
+
+/* Bytes of the `saved` buffer forward fills for backward (0 when not training
+ * is still valid: eval-mode backward is supported and saves the same tensors). */
+size_t stgcn_block_saved_bytes(const StgcnBlockDesc* desc);
+
+/* Scratch bytes needed by forward (backward=0) or backward (backward=1). */
+size_t stgcn_block_workspace_bytes(const StgcnBlockDesc* desc, int32_t backward);
+
+/* SpatialTemporalConv.forward (st_graphconv.py:85-109), both the default path
+ * (:97-100) and residual_block (:60-82), trailing ReLU (:105) and dropout (:108).
+ *   x (n,t,v,c_in) -> y (n,t_out,v,c_out); saved may be NULL when no backward
+ *   will follow. */
+int32_t stgcn_block_forward(const StgcnBlockDesc* desc, const void* x, const StgcnBlockParams* params,
+                            void* y, void* saved, void* workspace, size_t workspace_bytes, void* stream);
+
+/* Autograd of the above (reference: torch autograd over st_graphconv.py:85-109).
+ *   dy (n,t_out,v,c_out) -> dx (n,t,v,c_in) (may be NULL: first block) + grads. */
+int32_t stgcn_block_backward(const StgcnBlockDesc* desc, const void* x, const void* y,
+                             const StgcnBlockParams* params, const void* saved, const void* dy,
+                             void* dx, const StgcnBlockGrads* grads,
+                             void* workspace, size_t workspace_bytes, void* stream);
+
+/* SpatialConv.forward alone (st_graphconv.py:139-152), for the SpatialConv
+ * module: x (n,t,v,c_in) -> out (n,t,v,c_out); no BN, no activation. */
+size_t stgcn_spatial_workspace_bytes(const StgcnBlockDesc* desc, int32_t backward);
+int32_t stgcn_spatial_forward(const StgcnBlockDesc* desc, const void* x, const float* A, const float* W,
+                              const float* W_bias, void* out, void* workspace, size_t workspace_bytes,
+                              void* stream);
+int32_t stgcn_spatial_backward(const StgcnBlockDesc* desc, const void* x, const float* A, const float* W,
+                               const float* W_bias, const void* dout, void* dx, float* dA, float* dW,
+                               float* dW_bias, void* workspace, size_t workspace_bytes, void* stream);
+
+/* Head of L_STGCN.forward (lightning_model.py:105-107): global average pool
+ * over (T,V) + Linear(C, classes).  feat (n,t,v,c) -> logits (n,classes) fp32. */
+int32_t stgcn_head_forward(int32_t dtype, int32_t n, int32_t t, int32_t v, int32_t c, int32_t classes,
+                           const void* feat, const float* fc_weight, const float* fc_bias,
+                           float* pooled /* (n,c) */, float* logits, void* stream);
+int32_t stgcn_head_backward(int32_t dtype, int32_t n, int32_t t, int32_t v, int32_t c, int32_t classes,
+                            const float* pooled, const float* fc_weight, const float* dlogits,
+                            void* dfeat, float* dfc_weight, float* dfc_bias, void* stream);
+
+/* Layout helpers: fp32 (n,t,v,c) <-> dtype (n,t,v,c) casts on device. */
+int32_t stgcn_cast(int32_t src_dtype, int32_t dst_dtype, const void* src, void* dst, size_t count, void* stream);
+
+/* tcgen05 implicit-GEMM engine exposed for unit tests:
+ *   out[r][n] = sum_tap sum_c in[row(r,tap)][c] * w[tap][n][c]   (bf16 in, fp32 accumulate, bf16 out)
+ * in (nb,t_in,v,c) ; w (taps,n_out,c) bf16 ; out (nb,t_out,v,n_out) bf16;
+ * input frame for output frame j and tap i:  j*stride - pad + i  (zero outside). */
+int32_t stgcn_umma_conv_gemm(int32_t nb, int32_t t_in, int32_t t_out, int32_t v, int32_t c, int32_t n_out,
+                             int32_t taps, int32_t stride, int32_t pad, const void* in, const void* w,
+                             const float* bias, void* out, void* stream);
+
+/* tcgen05 descriptor probe (tests only): mode 0 = K-major A with a start address shifted by row_off rows,
+ * mode 1 = MN-major A (a_rows x 128) and B (64 x 64): D[m][n] = sum_k A[k+row_off][m]*B[k][n]. d: 128x64 fp32.
+ * base_off < 0 leaves the descriptor's base-offset field 0. */
+int32_t stgcn_umma_probe(int32_t mode, int32_t row_off, int32_t base_off, int32_t a_rows, const void* a,
+                         const void* b, float* d, void* stream);
+
+/* Number of CUDA kernels this library has launched in this process (bench's gpu_launches). */
+uint64_t stgcn_launch_count(void);
+const char* stgcn_last_error(void);
+const char* stgcn_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif  /* STGCN_B200_H_ */

@@ -1,0 +1,311 @@
+// K-partition adjacency aggregation on CUDA cores (generic path: any V<=32,
+// K<=4, any C).  Reference: the einsum 'kvw,nkctw->nctv' at
+// st_graphconv.py:150, applied on the C_in side of the 1x1 convolution
+// (aggregation and channel mixing commute):
+//     XA[f, v, k*C + c] = sum_w A[k,v,w] * h[f, w, c],   h = act(a*x + b)
+// so that S = XA . W2 is a single GEMM with reduction K*C_in.  The adjacency
+// (K,V,V) lives in shared memory, each frame tile is staged in shared memory
+// once, outputs are written channel-contiguous.
+#include "kernels.cuh"
+
+namespace stgcn {
+
+constexpr int kAggThreads = 256;
+constexpr int kVP = 32;   // padded joint count in shared memory
+
+// ---------------------------------------------------------------------------
+// forward aggregation
+// ---------------------------------------------------------------------------
+template <class T>
+__global__ void __launch_bounds__(kAggThreads) agg_fwd_kernel(const T* __restrict__ x, long long frames, int V, int C, int K,
+                                                              const float* __restrict__ A, const float* __restrict__ aff_a,
+                                                              const float* __restrict__ aff_b, int relu, int FB,
+                                                              T* __restrict__ xa) {
+  extern __shared__ float sm[];
+  float* As = sm;                         // [K][V][kVP]
+  float* hs = sm + K * V * kVP;           // [FB][V][C]
+  for (int i = threadIdx.x; i < K * V * kVP; i += blockDim.x) {
+    int w = i % kVP, kv = i / kVP;
+    As[i] = w < V ? A[kv * V + w] : 0.f;
+  }
+  const int KC = K * C;
+  for (long long f0 = (long long)blockIdx.x * FB; f0 < frames; f0 += (long long)gridDim.x * FB) {
+    int nf = (int)min((long long)FB, frames - f0);
+    __syncthreads();
+    const T* xp = x + f0 * V * C;
+    for (int i = threadIdx.x; i < nf * V * C; i += blockDim.x) {
+      float t = ldf(xp + i);
+      if (aff_a) { int c = i % C; t = fmaf(aff_a[c], t, aff_b[c]); }
+      if (relu) t = fmaxf(t, 0.f);
+      hs[i] = t;
+    }
+    __syncthreads();
+    // work item = (frame_local, k, c): 25 staged inputs in registers, V outputs
+    for (int it = threadIdx.x; it < nf * KC; it += blockDim.x) {
+      int c = it % C, k = (it / C) % K, fl = it / KC;
+      float h[kVP];
+#pragma unroll
+      for (int w = 0; w < kVP; ++w) h[w] = w < V ? hs[(fl * V + w) * C + c] : 0.f;
+      T* op = xa + ((f0 + fl) * V) * KC + k * C + c;
+      const float* Ak = As + k * V * kVP;
+      for (int v = 0; v < V; ++v) {
+        const float4* ar = reinterpret_cast<const float4*>(Ak + v * kVP);
+        float acc = 0.f;
+#pragma unroll
+        for (int q = 0; q < kVP / 4; ++q) {
+          float4 a4 = ar[q];
+          acc = fmaf(a4.x, h[4 * q], acc); acc = fmaf(a4.y, h[4 * q + 1], acc);
+          acc = fmaf(a4.z, h[4 * q + 2], acc); acc = fmaf(a4.w, h[4 * q + 3], acc);
+        }
+        stf(op + (size_t)v * KC, acc);
+      }
+    }
+  }
+}
+
+static int agg_fb(int V, int C, int K) {
+  int fb = kAggThreads / (K * C);
+  if (fb < 1) fb = 1;
+  // keep the staged frames under ~64 KB
+  while (fb > 1 && (size_t)fb * V * C * 4 > 64 * 1024) --fb;
+  return fb;
+}
+
+template <class T>
+int32_t launch_agg_fwd(const T* x, long long frames, int V, int C, int K, const float* A, const float* a, const float* b,
+                       int relu, T* xa, cudaStream_t st) {
+  if (V > kVP || K > 4) { set_error("agg: V=%d K=%d unsupported (V<=32, K<=4)", V, K); return STGCN_ERR_UNSUPPORTED; }
+  int FB = agg_fb(V, C, K);
+  size_t smem = ((size_t)K * V * kVP + (size_t)FB * V * C) * sizeof(float);
+  if (smem > 200 * 1024) { set_error("agg: C=%d too large for shared staging", C); return STGCN_ERR_UNSUPPORTED; }
+  static bool attr_f = false, attr_b = false;
+  bool& attr = std::is_same<T, float>::value ? attr_f : attr_b;
+  if (!attr) { cudaFuncSetAttribute(agg_fwd_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024); attr = true; }
+  int blocks = (int)std::min<long long>((frames + FB - 1) / FB, 148 * 4);
+  agg_fwd_kernel<T><<<blocks, kAggThreads, smem, st>>>(x, frames, V, C, K, A, a, b, relu, FB, xa);
+  STGCN_CHECK_LAUNCH("agg_fwd");
+  return STGCN_OK;
+}
+template int32_t launch_agg_fwd<float>(const float*, long long, int, int, int, const float*, const float*, const float*, int, float*, cudaStream_t);
+template int32_t launch_agg_fwd<bf16>(const bf16*, long long, int, int, int, const float*, const float*, const float*, int, bf16*, cudaStream_t);
+
+// ---------------------------------------------------------------------------
+// transposed aggregation:  dh[f,w,c] = sum_k sum_v A[k,v,w] * dxa[f,v,k*C+c]
+// optionally masked by the ReLU of h = a*x+b (residual path, st_graphconv.py:74)
+// ---------------------------------------------------------------------------
+template <class T>
+__global__ void __launch_bounds__(kAggThreads) agg_bwd_kernel(const T* __restrict__ dxa, long long frames, int V, int C, int K,
+                                                              const float* __restrict__ A, const T* __restrict__ x,
+                                                              const float* __restrict__ aff_a, const float* __restrict__ aff_b,
+                                                              int relu, T* __restrict__ dh) {
+  extern __shared__ float sm[];
+  float* At = sm;                         // [K][W=V][kVP over v]  (transposed)
+  for (int i = threadIdx.x; i < K * V * kVP; i += blockDim.x) {
+    int v = i % kVP, kw = i / kVP, w = kw % V, k = kw / V;
+    At[i] = v < V ? A[(k * V + v) * V + w] : 0.f;
+  }
+  __syncthreads();
+  const int KC = K * C;
+  const long long items = frames * C;
+  for (long long it = (long long)blockIdx.x * blockDim.x + threadIdx.x; it < items; it += (long long)gridDim.x * blockDim.x) {
+    int c = (int)(it % C);
+    long long f = it / C;
+    float acc[kVP];
+#pragma unroll
+    for (int w = 0; w < kVP; ++w) acc[w] = 0.f;
+    for (int k = 0; k < K; ++k) {
+      float g[kVP];
+#pragma unroll
+      for (int v = 0; v < kVP; ++v) g[v] = v < V ? ldf(dxa + (f * V + v) * KC + k * C + c) : 0.f;
+      const float* Ak = At + k * V * kVP;
+#pragma unroll
+      for (int w = 0; w < kVP; ++w) {
+        if (w < V) {
+          const float4* ar = reinterpret_cast<const float4*>(Ak + w * kVP);
+          float s = acc[w];
+#pragma unroll
+          for (int q = 0; q < kVP / 4; ++q) {
+            float4 a4 = ar[q];
+            s = fmaf(a4.x, g[4 * q], s); s = fmaf(a4.y, g[4 * q + 1], s);
+            s = fmaf(a4.z, g[4 * q + 2], s); s = fmaf(a4.w, g[4 * q + 3], s);
+          }
+          acc[w] = s;
+        }
+      }
+    }
+#pragma unroll
+    for (int w = 0; w < kVP; ++w) {
+      if (w < V) {
+        float r = acc[w];
+        if (relu) {
+          float xv = ldf(x + (f * V + w) * C + c);
+          if (!(fmaf(aff_a[c], xv, aff_b[c]) > 0.f)) r = 0.f;
+        }
+        stf(dh + (f * V + w) * C + c, r);
+      }
+    }
+  }
+}
+
+template <class T>
+int32_t launch_agg_bwd(const T* dxa, long long frames, int V, int C, int K, const float* A, const T* x, const float* a,
+                       const float* b, int relu, T* dh, cudaStream_t st) {
+  if (V > kVP || K > 4) { set_error("agg_bwd: V=%d K=%d unsupported", V, K); return STGCN_ERR_UNSUPPORTED; }
+  size_t smem = (size_t)K * V * kVP * sizeof(float);
+  int blocks = (int)std::min<long long>((frames * C + kAggThreads - 1) / kAggThreads, 148 * 8);
+  agg_bwd_kernel<T><<<blocks, kAggThreads, smem, st>>>(dxa, frames, V, C, K, A, x, a, b, relu, dh);
+  STGCN_CHECK_LAUNCH("agg_bwd");
+  return STGCN_OK;
+}
+template int32_t launch_agg_bwd<float>(const float*, long long, int, int, int, const float*, const float*, const float*, const float*, int, float*, cudaStream_t);
+template int32_t launch_agg_bwd<bf16>(const bf16*, long long, int, int, int, const float*, const bf16*, const float*, const float*, int, bf16*, cudaStream_t);
+
+// ---------------------------------------------------------------------------
+// adjacency gradient (the "dA-mask" of the north star; in this reference the
+// trained leaf is spatialConv.A, st_graphconv.py:129):
+//     dA[k,v,w] += sum_f sum_c dxa[f,v,k*C+c] * h[f,w,c]
+// One CTA walks a strip of frames, keeps the K*V*V accumulators in registers
+// (8 per thread) and flushes them with one atomicAdd each at the end.
+// ---------------------------------------------------------------------------
+constexpr int kDaPer = 8;   // accumulators per thread: 256*8 = 2048 >= 4*... see host check
+
+template <class T>
+__global__ void __launch_bounds__(kAggThreads) agg_dA_kernel(const T* __restrict__ dxa, const T* __restrict__ x, long long frames,
+                                                             int V, int C, int K, const float* __restrict__ aff_a,
+                                                             const float* __restrict__ aff_b, int relu, int CC,
+                                                             float* __restrict__ dA) {
+  extern __shared__ float sm[];
+  const int KV = K * V;
+  float* hs = sm;                          // [V][CC+1]
+  float* gs = sm + V * (CC + 1);           // [K*V][CC+1]
+  const int nout = K * V * V;
+  float acc[kDaPer];
+  int okv[kDaPer], ow[kDaPer];
+#pragma unroll
+  for (int j = 0; j < kDaPer; ++j) {
+    acc[j] = 0.f;
+    int o = threadIdx.x + j * kAggThreads;
+    okv[j] = o < nout ? o / V : -1;
+    ow[j] = o < nout ? o % V : 0;
+  }
+  const int KC = K * C;
+  for (long long f = blockIdx.x; f < frames; f += gridDim.x) {
+    for (int c0 = 0; c0 < C; c0 += CC) {
+      int cc = min(CC, C - c0);
+      __syncthreads();
+      for (int i = threadIdx.x; i < V * cc; i += blockDim.x) {
+        int c = i % cc, w = i / cc;
+        float t = ldf(x + (f * V + w) * C + c0 + c);
+        if (aff_a) t = fmaf(aff_a[c0 + c], t, aff_b[c0 + c]);
+        if (relu) t = fmaxf(t, 0.f);
+        hs[w * (CC + 1) + c] = t;
+      }
+      for (int i = threadIdx.x; i < KV * cc; i += blockDim.x) {
+        int c = i % cc, kv = i / cc, k = kv / V, v = kv % V;
+        gs[kv * (CC + 1) + c] = ldf(dxa + (f * V + v) * KC + k * C + c0 + c);
+      }
+      __syncthreads();
+#pragma unroll
+      for (int j = 0; j < kDaPer; ++j) {
+        if (okv[j] >= 0) {
+          const float* gp = gs + okv[j] * (CC + 1);
+          const float* hp = hs + ow[j] * (CC + 1);
+          float s = acc[j];
+          for (int c = 0; c < cc; ++c) s = fmaf(gp[c], hp[c], s);
+          acc[j] = s;
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < kDaPer; ++j)
+    if (okv[j] >= 0) atomicAdd(dA + okv[j] * V + ow[j], acc[j]);
+}
+
+template <class T>
+int32_t launch_agg_dA(const T* dxa, const T* x, long long frames, int V, int C, int K, const float* a, const float* b,
+                      int relu, float* dA, cudaStream_t st) {
+  if (K * V * V > kDaPer * kAggThreads) { set_error("agg_dA: K*V*V=%d too large", K * V * V); return STGCN_ERR_UNSUPPORTED; }
+  int CC = std::min(C, 64);
+  size_t smem = (size_t)(V + K * V) * (CC + 1) * sizeof(float);
+  int blocks = (int)std::min<long long>(frames, 148 * 4);
+  agg_dA_kernel<T><<<blocks, kAggThreads, smem, st>>>(dxa, x, frames, V, C, K, a, b, relu, CC, dA);
+  STGCN_CHECK_LAUNCH("agg_dA");
+  return STGCN_OK;
+}
+template int32_t launch_agg_dA<float>(const float*, const float*, long long, int, int, int, const float*, const float*, int, float*, cudaStream_t);
+template int32_t launch_agg_dA<bf16>(const bf16*, const bf16*, long long, int, int, int, const float*, const float*, int, float*, cudaStream_t);
+
+// ---------------------------------------------------------------------------
+// per-joint column sums  t1[v][c] = sum_f ds[f,v,c]   (feeds dW_bias and the
+// bias part of dA).  grid.y tiles the V*C axis, grid.x strips of frames.
+// ---------------------------------------------------------------------------
+template <class T>
+__global__ void __launch_bounds__(256) vcolsum_kernel(const T* __restrict__ ds, long long frames, int VC, float* __restrict__ t1) {
+  int e = blockIdx.y * 256 + threadIdx.x;
+  if (e >= VC) return;
+  float s = 0.f;
+  for (long long f = blockIdx.x; f < frames; f += gridDim.x) s += ldf(ds + f * VC + e);
+  atomicAdd(t1 + e, s);
+}
+template <class T>
+int32_t launch_vcolsum(const T* ds, long long frames, int V, int C, float* t1, cudaStream_t st) {
+  int VC = V * C;
+  dim3 grid((unsigned)std::min<long long>(frames, 64), (unsigned)cdiv(VC, 256));
+  vcolsum_kernel<T><<<grid, 256, 0, st>>>(ds, frames, VC, t1);
+  STGCN_CHECK_LAUNCH("vcolsum");
+  return STGCN_OK;
+}
+template int32_t launch_vcolsum<float>(const float*, long long, int, int, float*, cudaStream_t);
+template int32_t launch_vcolsum<bf16>(const bf16*, long long, int, int, float*, cudaStream_t);
+
+// bias2d[v][co] = sum_k rowsum_k[v] * bias[k*Co+co]   (bias of W passes through A, st_graphconv.py:148-150)
+__global__ void bias2d_kernel(const float* __restrict__ A, const float* __restrict__ bias, int K, int V, int Co,
+                              float* __restrict__ out) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= V * Co) return;
+  int co = i % Co, v = i / Co;
+  float s = 0.f;
+  for (int k = 0; k < K; ++k) {
+    float rs = 0.f;
+    for (int w = 0; w < V; ++w) rs += A[(k * V + v) * V + w];
+    s = fmaf(rs, bias[k * Co + co], s);
+  }
+  out[i] = s;
+}
+int32_t launch_bias2d(const float* A, const float* bias, int K, int V, int Co, float* out, cudaStream_t st) {
+  bias2d_kernel<<<cdiv(V * Co, 128), 128, 0, st>>>(A, bias, K, V, Co, out);
+  STGCN_CHECK_LAUNCH("bias2d");
+  return STGCN_OK;
+}
+
+// dbias[k*Co+co] = sum_v t1[v][co]*rowsum_k[v] ;  dA[k,v,w] += sum_co t1[v][co]*bias[k*Co+co]
+__global__ void spatial_bias_grads_kernel(const float* __restrict__ t1, const float* __restrict__ A, const float* __restrict__ bias,
+                                          int K, int V, int Co, float* __restrict__ dbias, float* __restrict__ dA) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < K * Co) {
+    int co = i % Co, k = i / Co;
+    float s = 0.f;
+    for (int v = 0; v < V; ++v) {
+      float rs = 0.f;
+      for (int w = 0; w < V; ++w) rs += A[(k * V + v) * V + w];
+      s = fmaf(t1[v * Co + co], rs, s);
+    }
+    if (dbias) dbias[i] = s;
+  }
+  if (dA && i < K * V) {
+    int v = i % V, k = i / V;
+    float s = 0.f;
+    for (int co = 0; co < Co; ++co) s = fmaf(t1[v * Co + co], bias[k * Co + co], s);
+    for (int w = 0; w < V; ++w) dA[(k * V + v) * V + w] += s;
+  }
+}
+int32_t launch_spatial_bias_grads(const float* t1, const float* A, const float* bias, int K, int V, int Co, float* dbias,
+                                  float* dA, cudaStream_t st) {
+  int n = std::max(K * Co, K * V);
+  spatial_bias_grads_kernel<<<cdiv(n, 128), 128, 0, st>>>(t1, A, bias, K, V, Co, dbias, dA);
+  STGCN_CHECK_LAUNCH("spatial_bias_grads");
+  return STGCN_OK;
+}
+
+}  // namespace stgcn

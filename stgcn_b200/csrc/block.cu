@@ -1,0 +1,467 @@
+// Host-side kernel chains of one ST-GCN block + the C-ABI entry points.
+// Reference semantics: SpatialTemporalConv.forward (st_graphconv.py:85-109),
+// residual_block (:60-82), SpatialConv.forward (:139-152); backward = what
+// torch autograd derives for those.
+#include <stdarg.h>
+#include <string.h>
+
+#include "kernels.cuh"
+
+namespace stgcn {
+
+std::atomic<uint64_t> g_launches{0};
+static thread_local char g_err[512] = "";
+void set_error(const char* fmt, ...) {
+  va_list ap; va_start(ap, fmt); vsnprintf(g_err, sizeof(g_err), fmt, ap); va_end(ap);
+}
+
+// ---- bump allocator over caller-provided device memory ---------------------
+struct Arena {
+  char* base; size_t cap; size_t off = 0; bool dry;
+  Arena(void* b, size_t c) : base((char*)b), cap(c), dry(b == nullptr) {}
+  template <class U> U* get(size_t count) {
+    size_t bytes = align_up(count * sizeof(U), 256);
+    size_t o = off; off += bytes;
+    if (dry) return reinterpret_cast<U*>((uintptr_t)256);   // never dereferenced
+    return reinterpret_cast<U*>(base + o);
+  }
+  bool ok() const { return dry || off <= cap; }
+};
+
+struct Dims {
+  int n, ci, co, t, to, v, k, gamma, stride, pad;
+  long long rows_in, rows_out, frames_in;
+};
+static Dims dims_of(const StgcnBlockDesc& d) {
+  Dims m;
+  m.n = d.n; m.ci = d.c_in; m.co = d.c_out; m.t = d.t; m.v = d.v; m.k = d.k; m.gamma = d.gamma; m.stride = d.stride; m.pad = d.pad;
+  m.to = (d.t + 2 * d.pad - d.gamma) / d.stride + 1;
+  m.rows_in = (long long)d.n * d.t * d.v; m.rows_out = (long long)d.n * m.to * d.v; m.frames_in = (long long)d.n * d.t;
+  return m;
+}
+
+static int32_t validate(const StgcnBlockDesc* d) {
+  if (!d) { set_error("null descriptor"); return STGCN_ERR_INVALID; }
+  if (d->n < 1 || d->c_in < 1 || d->c_out < 1 || d->t < 1 || d->v < 1 || d->k < 1) { set_error("non-positive dimension"); return STGCN_ERR_INVALID; }
+  if (d->v > 32 || d->k > 4) { set_error("V=%d K=%d unsupported (V<=32, K<=4)", d->v, d->k); return STGCN_ERR_UNSUPPORTED; }
+  if (d->gamma < 1 || d->gamma > 15 || d->stride < 1 || d->pad < 0) { set_error("bad temporal conv geometry"); return STGCN_ERR_INVALID; }
+  if (d->t + 2 * d->pad < d->gamma) { set_error("T=%d too short for gamma=%d pad=%d", d->t, d->gamma, d->pad); return STGCN_ERR_INVALID; }
+  if (d->dtype != STGCN_F32 && d->dtype != STGCN_BF16) { set_error("dtype %d unsupported", d->dtype); return STGCN_ERR_UNSUPPORTED; }
+  if (d->dropout_p < 0.f || d->dropout_p >= 1.f) { set_error("dropout_p out of range"); return STGCN_ERR_INVALID; }
+  if (d->residual == STGCN_RES_IDENTITY && (d->c_in != d->c_out || d->stride != 1)) { set_error("identity residual needs C_in==C_out, stride 1"); return STGCN_ERR_INVALID; }
+  if (d->residual == STGCN_RES_IDENTITY) {
+    int to = (d->t + 2 * d->pad - d->gamma) / d->stride + 1;
+    if (to != d->t) { set_error("identity residual needs T_out==T"); return STGCN_ERR_INVALID; }
+  }
+  if (d->residual < 0 || d->residual > 2) { set_error("bad residual mode"); return STGCN_ERR_INVALID; }
+  return STGCN_OK;
+}
+
+// saved-for-backward layout
+template <class T> struct Saved { float* stats1; float* stats2; T* S; T* U; };
+template <class T> static Saved<T> carve_saved(Arena& a, const StgcnBlockDesc& d, const Dims& m) {
+  Saved<T> s;
+  s.stats1 = a.get<float>(4 * m.ci);
+  s.stats2 = a.get<float>(4 * m.co);
+  s.S = a.get<T>(m.rows_in * m.co);
+  s.U = d.residual == STGCN_RES_NONE ? a.get<T>(m.rows_out * m.co) : nullptr;
+  return s;
+}
+
+// ---- GEMM dispatch: tcgen05 engine for bf16 when the shape fits, else CUDA cores ----
+template <class T> struct Engine {
+  const StgcnBlockDesc& d; Arena& ws; cudaStream_t st;
+  bool want_umma() const { return std::is_same<T, bf16>::value && !(d.flags & STGCN_FLAG_FORCE_SIMT); }
+  int32_t gemm(const ConvGeom& g, const T* in, const float* wsrc, const WIndex& wi, const GemmEpilogue& ep, T* out) {
+    if (want_umma() && umma_conv_gemm_supported(g)) {
+      bf16* wp = ws.template get<bf16>((size_t)g.taps * g.n_out * g.c);
+      if (ws.dry) return STGCN_OK;
+      if (!ws.ok()) { set_error("workspace too small"); return STGCN_ERR_WORKSPACE; }
+      STGCN_TRY(launch_pack_weights<bf16>(wsrc, wi, g.taps, g.n_out, g.c, wp, st));
+      return launch_conv_gemm_umma(g, reinterpret_cast<const bf16*>(in), wp, ep, reinterpret_cast<bf16*>(out), st);
+    }
+    float* wp = ws.template get<float>((size_t)g.taps * g.n_out * g.c);
+    if (ws.dry) return STGCN_OK;
+    if (!ws.ok()) { set_error("workspace too small"); return STGCN_ERR_WORKSPACE; }
+    STGCN_TRY(launch_pack_weights<float>(wsrc, wi, g.taps, g.n_out, g.c, wp, st));
+    return launch_conv_gemm_simt<T>(g, in, wp, ep, out, st);
+  }
+};
+
+static ConvGeom geom(int nb, int t_in, int t_out, int v, int c, int n_out, int taps, int stride, int pad, int dgrad) {
+  ConvGeom g; g.nb = nb; g.t_in = t_in; g.t_out = t_out; g.v = v; g.c = c; g.n_out = n_out; g.taps = taps; g.stride = stride; g.pad = pad; g.dgrad = dgrad;
+  return g;
+}
+static WIndex widx(int ndiv, long long snh, long long snl, int cdiv_, long long sch, long long scl, long long st) {
+  WIndex w; w.ndiv = ndiv; w.snh = snh; w.snl = snl; w.cdiv = cdiv_; w.sch = sch; w.scl = scl; w.st = st; return w;
+}
+constexpr int kNoDiv = 1 << 30;
+
+// ---------------------------------------------------------------------------
+// spatial graph convolution:  S = sum_k (A_k h) W_k^T + bias through A
+// ---------------------------------------------------------------------------
+template <class T>
+static int32_t spatial_fwd(Engine<T>& e, const Dims& m, const T* x, const float* aff_a, const float* aff_b, int relu1,
+                           const float* A, const float* W, const float* Wb, T* S) {
+  Arena& ws = e.ws;
+  T* XA = ws.template get<T>(m.rows_in * m.k * m.ci);
+  float* b2d = ws.template get<float>((size_t)m.v * m.co);
+  if (!ws.dry) {
+    if (!ws.ok()) return STGCN_ERR_WORKSPACE;
+    STGCN_TRY(launch_agg_fwd<T>(x, m.frames_in, m.v, m.ci, m.k, A, aff_a, aff_b, relu1, XA, e.st));
+    STGCN_TRY(launch_bias2d(A, Wb, m.k, m.v, m.co, b2d, e.st));
+  }
+  GemmEpilogue ep; ep.bias2d = b2d;
+  // W2[n=co][c=k*Ci+ci] = W[(k*Co+co)*Ci + ci]
+  WIndex wi = widx(kNoDiv, 0, m.ci, m.ci, (long long)m.co * m.ci, 1, 0);
+  return e.gemm(geom(m.n, m.t, m.t, m.v, m.k * m.ci, m.co, 1, 1, 0, 0), XA, W, wi, ep, S);
+}
+
+// gradients of the above given dS; dx_pre = d/d(h) masked by relu1 (NOT yet through the BN)
+template <class T>
+static int32_t spatial_bwd(Engine<T>& e, const Dims& m, const T* x, const float* aff_a, const float* aff_b, int relu1,
+                           const float* A, const float* W, const float* Wb, const T* dS, T* dh, float* dA, float* dW, float* dWb) {
+  Arena& ws = e.ws;
+  const int KCi = m.k * m.ci;
+  T* XA = ws.template get<T>(m.rows_in * KCi);
+  T* dXA = ws.template get<T>(m.rows_in * KCi);
+  float* t1 = ws.template get<float>((size_t)m.v * m.co);
+  if (!ws.dry) {
+    if (!ws.ok()) return STGCN_ERR_WORKSPACE;
+    STGCN_TRY(launch_agg_fwd<T>(x, m.frames_in, m.v, m.ci, m.k, A, aff_a, aff_b, relu1, XA, e.st));
+    cudaMemsetAsync(dW, 0, sizeof(float) * (size_t)m.k * m.co * m.ci, e.st);
+    cudaMemsetAsync(dA, 0, sizeof(float) * (size_t)m.k * m.v * m.v, e.st);
+    cudaMemsetAsync(t1, 0, sizeof(float) * (size_t)m.v * m.co, e.st);
+    ConvGeom gw = geom(m.n, m.t, m.t, m.v, KCi, m.co, 1, 1, 0, 0);
+    STGCN_TRY(launch_wgrad_simt<T>(gw, dS, XA, widx(kNoDiv, 0, m.ci, m.ci, (long long)m.co * m.ci, 1, 0), dW, e.st));
+    STGCN_TRY(launch_vcolsum<T>(dS, m.frames_in, m.v, m.co, t1, e.st));
+  }
+  // dXA = dS . W2 : packed [n=k*Ci+ci][c=co] = W[(k*Co+co)*Ci+ci]
+  GemmEpilogue ep;
+  WIndex wiT = widx(m.ci, (long long)m.co * m.ci, 1, kNoDiv, 0, m.ci, 0);
+  STGCN_TRY(e.gemm(geom(m.n, m.t, m.t, m.v, m.co, KCi, 1, 1, 0, 0), dS, W, wiT, ep, dXA));
+  if (ws.dry) return STGCN_OK;
+  STGCN_TRY(launch_agg_dA<T>(dXA, x, m.frames_in, m.v, m.ci, m.k, aff_a, aff_b, relu1, dA, e.st));
+  STGCN_TRY(launch_spatial_bias_grads(t1, A, Wb, m.k, m.v, m.co, dWb, dA, e.st));
+  if (dh) STGCN_TRY(launch_agg_bwd<T>(dXA, m.frames_in, m.v, m.ci, m.k, A, x, aff_a, aff_b, relu1, dh, e.st));
+  return STGCN_OK;
+}
+
+// ---------------------------------------------------------------------------
+// block forward
+// ---------------------------------------------------------------------------
+template <class T>
+static int32_t block_forward_t(const StgcnBlockDesc& d, const T* x, const StgcnBlockParams& P, T* y, void* saved_mem,
+                               Arena& ws, cudaStream_t st) {
+  const Dims m = dims_of(d);
+  Arena sv(saved_mem, ~(size_t)0);
+  Saved<T> S;
+  const bool keep = saved_mem != nullptr || ws.dry;
+  if (saved_mem) S = carve_saved<T>(sv, d, m);
+  else { S.stats1 = ws.get<float>(4 * m.ci); S.stats2 = ws.get<float>(4 * m.co); S.S = ws.get<T>(m.rows_in * m.co); S.U = nullptr; }
+  float* partials = ws.get<float>(stat_partials_bytes(std::max(m.ci, m.co)) / sizeof(float));
+  Engine<T> e{d, ws, st};
+  const bool res = d.residual != STGCN_RES_NONE;
+  const int relu1 = res ? 1 : 0;
+  int nblk = 0;
+  if (!ws.dry) {
+    if (!ws.ok()) { set_error("workspace too small"); return STGCN_ERR_WORKSPACE; }
+    if (d.training) {
+      STGCN_TRY(launch_colstats<T>(x, m.rows_in, m.ci, partials, &nblk, st));
+      STGCN_TRY(launch_bn_finalize(partials, nblk, m.ci, (double)m.rows_in, P.bn1_weight, P.bn1_bias, P.bn1_running_mean,
+                                   P.bn1_running_var, (long long*)P.bn1_num_batches_tracked, d.bn_eps, d.bn_momentum, S.stats1, st));
+    } else {
+      STGCN_TRY(launch_bn_eval_coeffs(m.ci, P.bn1_weight, P.bn1_bias, P.bn1_running_mean, P.bn1_running_var, d.bn_eps, S.stats1, st));
+    }
+  }
+  STGCN_TRY(spatial_fwd<T>(e, m, x, S.stats1 + 2 * m.ci, S.stats1 + 3 * m.ci, relu1, P.A, P.W, P.W_bias, S.S));
+
+  // temporal weights: packed [tap][n=co][c=ci] = Wt[(co*Co+ci)*gamma + tap]
+  const WIndex wiT = widx(kNoDiv, 0, (long long)m.co * m.gamma, kNoDiv, 0, m.gamma, 1);
+  const ConvGeom gt = geom(m.n, m.t, m.to, m.v, m.co, m.co, m.gamma, m.stride, m.pad, 0);
+  if (!res) {
+    if (d.training || keep) {
+      T* U = S.U ? S.U : ws.get<T>(m.rows_out * m.co);
+      GemmEpilogue ep; ep.bias = P.Wt_bias;
+      STGCN_TRY(e.gemm(gt, S.S, P.Wt, wiT, ep, U));
+      if (ws.dry) return STGCN_OK;
+      if (!ws.ok()) { set_error("workspace too small"); return STGCN_ERR_WORKSPACE; }
+      if (d.training) {
+        STGCN_TRY(launch_colstats<T>(U, m.rows_out, m.co, partials, &nblk, st));
+        STGCN_TRY(launch_bn_finalize(partials, nblk, m.co, (double)m.rows_out, P.bn2_weight, P.bn2_bias, P.bn2_running_mean,
+                                     P.bn2_running_var, (long long*)P.bn2_num_batches_tracked, d.bn_eps, d.bn_momentum, S.stats2, st));
+      } else {
+        STGCN_TRY(launch_bn_eval_coeffs(m.co, P.bn2_weight, P.bn2_bias, P.bn2_running_mean, P.bn2_running_var, d.bn_eps, S.stats2, st));
+      }
+      const float p = d.training ? d.dropout_p : 0.f;
+      return launch_affine_act<T>(U, m.rows_out, m.co, S.stats2 + 2 * m.co, S.stats2 + 3 * m.co, 1, p, d.seed, d.offset, y, st);
+    }
+    // inference: BN2 + ReLU folded into the temporal GEMM's epilogue, U never exists
+    if (!ws.dry) STGCN_TRY(launch_bn_eval_coeffs(m.co, P.bn2_weight, P.bn2_bias, P.bn2_running_mean, P.bn2_running_var, d.bn_eps, S.stats2, st));
+    GemmEpilogue ep; ep.bias = P.Wt_bias; ep.scale = S.stats2 + 2 * m.co; ep.shift = S.stats2 + 3 * m.co; ep.relu = 1;
+    return e.gemm(gt, S.S, P.Wt, wiT, ep, y);
+  }
+  // residual block: BN2 + ReLU sit between the spatial and the temporal conv
+  T* P2 = ws.get<T>(m.rows_in * m.co);
+  if (!ws.dry) {
+    if (!ws.ok()) { set_error("workspace too small"); return STGCN_ERR_WORKSPACE; }
+    if (d.training) {
+      STGCN_TRY(launch_colstats<T>(S.S, m.rows_in, m.co, partials, &nblk, st));
+      STGCN_TRY(launch_bn_finalize(partials, nblk, m.co, (double)m.rows_in, P.bn2_weight, P.bn2_bias, P.bn2_running_mean,
+                                   P.bn2_running_var, (long long*)P.bn2_num_batches_tracked, d.bn_eps, d.bn_momentum, S.stats2, st));
+    } else {
+      STGCN_TRY(launch_bn_eval_coeffs(m.co, P.bn2_weight, P.bn2_bias, P.bn2_running_mean, P.bn2_running_var, d.bn_eps, S.stats2, st));
+    }
+    STGCN_TRY(launch_affine_act<T>(S.S, m.rows_in, m.co, S.stats2 + 2 * m.co, S.stats2 + 3 * m.co, 1, 0.f, 0, 0, P2, st));
+  }
+  const void* resid = x;
+  if (d.residual == STGCN_RES_CONV) {
+    GemmEpilogue er; er.bias = P.Wr_bias;
+    STGCN_TRY(e.gemm(geom(m.n, m.t, m.to, m.v, m.ci, m.co, 1, m.stride, 0, 0), x, P.Wr, widx(kNoDiv, 0, m.ci, kNoDiv, 0, 1, 0), er, y));
+    resid = y;
+  }
+  GemmEpilogue ep; ep.bias = P.Wt_bias; ep.residual = resid; ep.relu = 1;
+  if (d.training) { ep.dropout_p = d.dropout_p; ep.seed = d.seed; ep.offset = d.offset; }
+  return e.gemm(gt, P2, P.Wt, wiT, ep, y);
+}
+
+// ---------------------------------------------------------------------------
+// block backward
+// ---------------------------------------------------------------------------
+template <class T>
+static int32_t block_backward_t(const StgcnBlockDesc& d, const T* x, const T* y, const StgcnBlockParams& P, const void* saved_mem,
+                                const T* dy, T* dx, const StgcnBlockGrads& G, Arena& ws, cudaStream_t st) {
+  const Dims m = dims_of(d);
+  Arena sv(const_cast<void*>(saved_mem), ~(size_t)0);
+  Saved<T> S = carve_saved<T>(sv, d, m);
+  float* partials = ws.get<float>(stat_partials_bytes(std::max(m.ci, m.co)) / sizeof(float));
+  float* sums1 = ws.get<float>(2 * m.ci);
+  float* sums2 = ws.get<float>(2 * m.co);
+  T* dU = ws.get<T>(m.rows_out * m.co);
+  T* dTin = ws.get<T>(m.rows_in * m.co);
+  T* dh = ws.get<T>(m.rows_in * m.ci);
+  Engine<T> e{d, ws, st};
+  const bool res = d.residual != STGCN_RES_NONE;
+  const int relu1 = res ? 1 : 0;
+  const float p = d.training ? d.dropout_p : 0.f;
+  int nblk = 0;
+  const T* tin = S.S;
+  T* P2 = res ? ws.get<T>(m.rows_in * m.co) : nullptr;
+  T* dS = res ? ws.get<T>(m.rows_in * m.co) : dTin;
+  if (!ws.dry) {
+    if (!ws.ok()) { set_error("workspace too small"); return STGCN_ERR_WORKSPACE; }
+    if (!res) {
+      STGCN_TRY(launch_bn_bwd_reduce<T>(dy, S.U, S.stats2, m.rows_out, m.co, 1, p, d.seed, d.offset, partials, &nblk, st));
+      STGCN_TRY(launch_bn_bwd_finalize(partials, nblk, m.co, sums2, G.bn2_weight, G.bn2_bias, st));
+      STGCN_TRY(launch_bn_bwd_apply<T>(dy, S.U, S.stats2, sums2, m.rows_out, m.co, 1, d.training, p, d.seed, d.offset, dU, st));
+      if (d.training) cudaMemsetAsync(G.Wt_bias, 0, sizeof(float) * m.co, st);   // a bias before a batch-stat BN has zero gradient
+      else STGCN_TRY(launch_colsum<T>(dU, m.rows_out, m.co, partials, G.Wt_bias, st));
+    } else {
+      STGCN_TRY(launch_relu_bwd<T>(dy, y, m.rows_out * m.co, p, dU, st));
+      STGCN_TRY(launch_colsum<T>(dU, m.rows_out, m.co, partials, G.Wt_bias, st));
+      STGCN_TRY(launch_affine_act<T>(S.S, m.rows_in, m.co, S.stats2 + 2 * m.co, S.stats2 + 3 * m.co, 1, 0.f, 0, 0, P2, st));
+      tin = P2;
+    }
+    cudaMemsetAsync(G.Wt, 0, sizeof(float) * (size_t)m.co * m.co * m.gamma, st);
+    STGCN_TRY(launch_wgrad_simt<T>(geom(m.n, m.t, m.to, m.v, m.co, m.co, m.gamma, m.stride, m.pad, 0), dU, tin,
+                                   widx(kNoDiv, 0, (long long)m.co * m.gamma, kNoDiv, 0, m.gamma, 1), G.Wt, st));
+  }
+  // temporal dgrad: packed [tap][n=ci][c=co] = Wt[(co*Co+ci)*gamma + tap]
+  {
+    GemmEpilogue ep;
+    STGCN_TRY(e.gemm(geom(m.n, m.to, m.t, m.v, m.co, m.co, m.gamma, m.stride, m.pad, 1), dU, P.Wt,
+                     widx(kNoDiv, 0, m.gamma, kNoDiv, 0, (long long)m.co * m.gamma, 1), ep, dTin));
+  }
+  if (res && !ws.dry) {
+    STGCN_TRY(launch_bn_bwd_reduce<T>(dTin, S.S, S.stats2, m.rows_in, m.co, 1, 0.f, 0, 0, partials, &nblk, st));
+    STGCN_TRY(launch_bn_bwd_finalize(partials, nblk, m.co, sums2, G.bn2_weight, G.bn2_bias, st));
+    STGCN_TRY(launch_bn_bwd_apply<T>(dTin, S.S, S.stats2, sums2, m.rows_in, m.co, 1, d.training, 0.f, 0, 0, dS, st));
+  }
+  STGCN_TRY(spatial_bwd<T>(e, m, x, S.stats1 + 2 * m.ci, S.stats1 + 3 * m.ci, relu1, P.A, P.W, P.W_bias, dS, dh, G.A, G.W, G.W_bias));
+  if (!ws.dry) {
+    STGCN_TRY(launch_bn_bwd_reduce<T>(dh, x, S.stats1, m.rows_in, m.ci, 0, 0.f, 0, 0, partials, &nblk, st));
+    STGCN_TRY(launch_bn_bwd_finalize(partials, nblk, m.ci, sums1, G.bn1_weight, G.bn1_bias, st));
+    if (dx) STGCN_TRY(launch_bn_bwd_apply<T>(dh, x, S.stats1, sums1, m.rows_in, m.ci, 0, d.training, 0.f, 0, 0, dx, st));
+  }
+  if (d.residual == STGCN_RES_IDENTITY) {
+    if (!ws.dry && dx) STGCN_TRY(launch_add_inplace<T>(dx, dU, (size_t)m.rows_in * m.ci, st));
+  } else if (d.residual == STGCN_RES_CONV) {
+    if (!ws.dry) {
+      cudaMemsetAsync(G.Wr, 0, sizeof(float) * (size_t)m.co * m.ci, st);
+      STGCN_TRY(launch_wgrad_simt<T>(geom(m.n, m.t, m.to, m.v, m.ci, m.co, 1, m.stride, 0, 0), dU, x,
+                                     widx(kNoDiv, 0, m.ci, kNoDiv, 0, 1, 0), G.Wr, st));
+      cudaMemcpyAsync(G.Wr_bias, G.Wt_bias, sizeof(float) * m.co, cudaMemcpyDeviceToDevice, st);
+    }
+    if (dx) {
+      GemmEpilogue ep; ep.accumulate = 1;
+      STGCN_TRY(e.gemm(geom(m.n, m.to, m.t, m.v, m.co, m.ci, 1, m.stride, 0, 1), dU, P.Wr, widx(kNoDiv, 0, 1, kNoDiv, 0, m.ci, 0), ep, dx));
+    }
+  }
+  if (!ws.ok()) { set_error("workspace too small"); return STGCN_ERR_WORKSPACE; }
+  return STGCN_OK;
+}
+
+// ---------------------------------------------------------------------------
+// SpatialConv alone (module SpatialConv, st_graphconv.py:111-152)
+// ---------------------------------------------------------------------------
+template <class T>
+static int32_t spatial_only_fwd(const StgcnBlockDesc& d, const T* x, const float* A, const float* W, const float* Wb, T* out,
+                                Arena& ws, cudaStream_t st) {
+  const Dims m = dims_of(d);
+  Engine<T> e{d, ws, st};
+  STGCN_TRY(spatial_fwd<T>(e, m, x, nullptr, nullptr, 0, A, W, Wb, out));
+  if (!ws.ok()) { set_error("workspace too small"); return STGCN_ERR_WORKSPACE; }
+  return STGCN_OK;
+}
+template <class T>
+static int32_t spatial_only_bwd(const StgcnBlockDesc& d, const T* x, const float* A, const float* W, const float* Wb, const T* dout,
+                                T* dx, float* dA, float* dW, float* dWb, Arena& ws, cudaStream_t st) {
+  const Dims m = dims_of(d);
+  Engine<T> e{d, ws, st};
+  STGCN_TRY(spatial_bwd<T>(e, m, x, nullptr, nullptr, 0, A, W, Wb, dout, dx, dA, dW, dWb));
+  if (!ws.ok()) { set_error("workspace too small"); return STGCN_ERR_WORKSPACE; }
+  return STGCN_OK;
+}
+
+}  // namespace stgcn
+
+// ===========================================================================
+// C ABI
+// ===========================================================================
+using namespace stgcn;
+
+extern "C" {
+
+int32_t stgcn_block_t_out(const StgcnBlockDesc* d) { return d ? (d->t + 2 * d->pad - d->gamma) / d->stride + 1 : -1; }
+
+size_t stgcn_block_saved_bytes(const StgcnBlockDesc* d) {
+  if (validate(d) != STGCN_OK) return 0;
+  Arena a(nullptr, 0);
+  Dims m = dims_of(*d);
+  if (d->dtype == STGCN_F32) carve_saved<float>(a, *d, m); else carve_saved<bf16>(a, *d, m);
+  return a.off;
+}
+
+size_t stgcn_block_workspace_bytes(const StgcnBlockDesc* d, int32_t backward) {
+  if (validate(d) != STGCN_OK) return 0;
+  StgcnBlockParams P; memset(&P, 0, sizeof(P));
+  StgcnBlockGrads G; memset(&G, 0, sizeof(G));
+  Arena dry(nullptr, 0);   // dry arena: the chain only records its allocation plan, nothing is launched
+  int32_t rc;
+  if (d->dtype == STGCN_F32)
+    rc = backward ? block_backward_t<float>(*d, nullptr, nullptr, P, nullptr, nullptr, (float*)256, G, dry, 0)
+                  : block_forward_t<float>(*d, nullptr, P, nullptr, nullptr, dry, 0);
+  else
+    rc = backward ? block_backward_t<bf16>(*d, nullptr, nullptr, P, nullptr, nullptr, (bf16*)256, G, dry, 0)
+                  : block_forward_t<bf16>(*d, nullptr, P, nullptr, nullptr, dry, 0);
+  if (rc != STGCN_OK) return 0;
+  return dry.off + 256;
+}
+
+static int32_t check_ptrs(const void* a, const void* b, const void* c) {
+  if (!a || !b || !c) { set_error("null pointer argument"); return STGCN_ERR_INVALID; }
+  return STGCN_OK;
+}
+
+int32_t stgcn_block_forward(const StgcnBlockDesc* d, const void* x, const StgcnBlockParams* P, void* y, void* saved,
+                            void* workspace, size_t workspace_bytes, void* stream) {
+  STGCN_TRY(validate(d));
+  STGCN_TRY(check_ptrs(x, P, y));
+  if (!workspace) { set_error("null workspace"); return STGCN_ERR_WORKSPACE; }
+  if (d->residual == STGCN_RES_CONV && (!P->Wr || !P->Wr_bias)) { set_error("conv residual needs Wr / Wr_bias"); return STGCN_ERR_INVALID; }
+  Arena ws(workspace, workspace_bytes);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (d->dtype == STGCN_F32) return block_forward_t<float>(*d, (const float*)x, *P, (float*)y, saved, ws, st);
+  return block_forward_t<bf16>(*d, (const bf16*)x, *P, (bf16*)y, saved, ws, st);
+}
+
+int32_t stgcn_block_backward(const StgcnBlockDesc* d, const void* x, const void* y, const StgcnBlockParams* P, const void* saved,
+                             const void* dy, void* dx, const StgcnBlockGrads* G, void* workspace, size_t workspace_bytes,
+                             void* stream) {
+  STGCN_TRY(validate(d));
+  STGCN_TRY(check_ptrs(x, P, dy));
+  STGCN_TRY(check_ptrs(saved, G, y));
+  if (!workspace) { set_error("null workspace"); return STGCN_ERR_WORKSPACE; }
+  Arena ws(workspace, workspace_bytes);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (d->dtype == STGCN_F32)
+    return block_backward_t<float>(*d, (const float*)x, (const float*)y, *P, saved, (const float*)dy, (float*)dx, *G, ws, st);
+  return block_backward_t<bf16>(*d, (const bf16*)x, (const bf16*)y, *P, saved, (const bf16*)dy, (bf16*)dx, *G, ws, st);
+}
+
+size_t stgcn_spatial_workspace_bytes(const StgcnBlockDesc* d, int32_t backward) {
+  if (validate(d) != STGCN_OK) return 0;
+  Arena dry(nullptr, 0);
+  int32_t rc;
+  if (d->dtype == STGCN_F32)
+    rc = backward ? spatial_only_bwd<float>(*d, nullptr, nullptr, nullptr, nullptr, nullptr, (float*)256, nullptr, nullptr, nullptr, dry, 0)
+                  : spatial_only_fwd<float>(*d, nullptr, nullptr, nullptr, nullptr, nullptr, dry, 0);
+  else
+    rc = backward ? spatial_only_bwd<bf16>(*d, nullptr, nullptr, nullptr, nullptr, nullptr, (bf16*)256, nullptr, nullptr, nullptr, dry, 0)
+                  : spatial_only_fwd<bf16>(*d, nullptr, nullptr, nullptr, nullptr, nullptr, dry, 0);
+  if (rc != STGCN_OK) return 0;
+  return dry.off + 256;
+}
+
+int32_t stgcn_spatial_forward(const StgcnBlockDesc* d, const void* x, const float* A, const float* W, const float* Wb, void* out,
+                              void* workspace, size_t workspace_bytes, void* stream) {
+  STGCN_TRY(validate(d));
+  STGCN_TRY(check_ptrs(x, A, W));
+  STGCN_TRY(check_ptrs(Wb, out, workspace));
+  Arena ws(workspace, workspace_bytes);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (d->dtype == STGCN_F32) return spatial_only_fwd<float>(*d, (const float*)x, A, W, Wb, (float*)out, ws, st);
+  return spatial_only_fwd<bf16>(*d, (const bf16*)x, A, W, Wb, (bf16*)out, ws, st);
+}
+
+int32_t stgcn_spatial_backward(const StgcnBlockDesc* d, const void* x, const float* A, const float* W, const float* Wb,
+                               const void* dout, void* dx, float* dA, float* dW, float* dWb, void* workspace,
+                               size_t workspace_bytes, void* stream) {
+  STGCN_TRY(validate(d));
+  STGCN_TRY(check_ptrs(x, A, W));
+  STGCN_TRY(check_ptrs(Wb, dout, workspace));
+  STGCN_TRY(check_ptrs(dA, dW, dWb));
+  Arena ws(workspace, workspace_bytes);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (d->dtype == STGCN_F32)
+    return spatial_only_bwd<float>(*d, (const float*)x, A, W, Wb, (const float*)dout, (float*)dx, dA, dW, dWb, ws, st);
+  return spatial_only_bwd<bf16>(*d, (const bf16*)x, A, W, Wb, (const bf16*)dout, (bf16*)dx, dA, dW, dWb, ws, st);
+}
+
+int32_t stgcn_head_forward(int32_t dtype, int32_t n, int32_t t, int32_t v, int32_t c, int32_t classes, const void* feat,
+                           const float* fcw, const float* fcb, float* pooled, float* logits, void* stream) {
+  STGCN_TRY(check_ptrs(feat, fcw, fcb));
+  STGCN_TRY(check_ptrs(pooled, logits, logits));
+  return head_forward(dtype, n, t, v, c, classes, feat, fcw, fcb, pooled, logits, (cudaStream_t)stream);
+}
+int32_t stgcn_head_backward(int32_t dtype, int32_t n, int32_t t, int32_t v, int32_t c, int32_t classes, const float* pooled,
+                            const float* fcw, const float* dlogits, void* dfeat, float* dfcw, float* dfcb, void* stream) {
+  STGCN_TRY(check_ptrs(pooled, fcw, dlogits));
+  STGCN_TRY(check_ptrs(dfeat, dfcw, dfcb));
+  return head_backward(dtype, n, t, v, c, classes, pooled, fcw, dlogits, dfeat, dfcw, dfcb, (cudaStream_t)stream);
+}
+
+int32_t stgcn_cast(int32_t sd, int32_t dd, const void* src, void* dst, size_t count, void* stream) {
+  STGCN_TRY(check_ptrs(src, dst, dst));
+  cudaStream_t st = (cudaStream_t)stream;
+  if (sd == STGCN_F32 && dd == STGCN_BF16) return launch_cast<float, bf16>((const float*)src, (bf16*)dst, count, st);
+  if (sd == STGCN_BF16 && dd == STGCN_F32) return launch_cast<bf16, float>((const bf16*)src, (float*)dst, count, st);
+  if (sd == STGCN_F32 && dd == STGCN_F32) return launch_cast<float, float>((const float*)src, (float*)dst, count, st);
+  if (sd == STGCN_BF16 && dd == STGCN_BF16) return launch_cast<bf16, bf16>((const bf16*)src, (bf16*)dst, count, st);
+  set_error("cast: bad dtype"); return STGCN_ERR_INVALID;
+}
+
+int32_t stgcn_umma_conv_gemm(int32_t nb, int32_t t_in, int32_t t_out, int32_t v, int32_t c, int32_t n_out, int32_t taps,
+                             int32_t stride, int32_t pad, const void* in, const void* w, const float* bias, void* out, void* stream) {
+  STGCN_TRY(check_ptrs(in, w, out));
+  ConvGeom g = geom(nb, t_in, t_out, v, c, n_out, taps, stride, pad, 0);
+  if (!umma_conv_gemm_supported(g)) { set_error("umma_conv_gemm: shape unsupported (c%%64, n_out%%16, n_out<=256, V*frames<=128)"); return STGCN_ERR_UNSUPPORTED; }
+  GemmEpilogue ep; ep.bias = bias;
+  return launch_conv_gemm_umma(g, (const bf16*)in, (const bf16*)w, ep, (bf16*)out, (cudaStream_t)stream);
+}
+
+uint64_t stgcn_launch_count(void) { return g_launches.load(); }
+const char* stgcn_last_error(void) { return g_err; }
+const char* stgcn_version(void) { return "stgcn_b200 0.1 (sm_100a)"; }
+
+}  // extern "C"

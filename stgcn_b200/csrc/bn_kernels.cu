@@ -1,0 +1,376 @@
+// BatchNorm statistics / apply / backward, ReLU and dropout passes.
+// These are the HBM-bound passes of the block chain (reference:
+// nn.BatchNorm2d at st_graphconv.py:34,46 applied at :73,:77,:98,:100;
+// ReLU :74,:78,:105; Dropout :108).  One read (+ one write) of a
+// channels-last [rows, C] tensor each, 16-byte vector accesses, fp32 math,
+// grid sized to the 148 SMs; column sums go through per-CTA partials and a
+// double-precision finalize so the result is deterministic.
+#include "kernels.cuh"
+
+namespace stgcn {
+
+constexpr int kStatThreads = 256;
+constexpr int kMaxStatBlocks = 148 * 4;
+
+// ---------------------------------------------------------------------------
+// generic per-channel two-moment reduction.
+// Functor F(row, c, out g, out h) yields the two values whose column sums are
+// wanted (forward stats: x, x*x ; backward: g, g*zhat).
+// ---------------------------------------------------------------------------
+template <int VEC, class F>
+__global__ void __launch_bounds__(kStatThreads) colreduce_kernel(long long rows, int C, F f, float* __restrict__ partials) {
+  extern __shared__ float sm[];               // [2][rows_per_step][C] folded below
+  const int cv = C / VEC;                     // vectors per row
+  const int rps = kStatThreads / cv;          // rows per step (>=1, host guarantees cv <= 256)
+  const int tid = threadIdx.x;
+  const bool active = tid < rps * cv;
+  const int myc = (tid % cv) * VEC;
+  const int myr = tid / cv;
+  float s1[VEC], s2[VEC];
+#pragma unroll
+  for (int i = 0; i < VEC; ++i) { s1[i] = 0.f; s2[i] = 0.f; }
+  if (active) {
+    for (long long r = (long long)blockIdx.x * rps + myr; r < rows; r += (long long)gridDim.x * rps) {
+      float g[VEC], h[VEC];
+      f(r, myc, g, h);
+#pragma unroll
+      for (int i = 0; i < VEC; ++i) { s1[i] += g[i]; s2[i] += h[i]; }
+    }
+  }
+  // reduce over the rps row-lanes through shared memory
+  float* a1 = sm;                 // [rps][C]
+  float* a2 = sm + rps * C;
+  if (active) {
+#pragma unroll
+    for (int i = 0; i < VEC; ++i) { a1[myr * C + myc + i] = s1[i]; a2[myr * C + myc + i] = s2[i]; }
+  }
+  __syncthreads();
+  for (int c = tid; c < C; c += kStatThreads) {
+    float t1 = 0.f, t2 = 0.f;
+    for (int r = 0; r < rps; ++r) { t1 += a1[r * C + c]; t2 += a2[r * C + c]; }
+    partials[((size_t)blockIdx.x * 2 + 0) * C + c] = t1;
+    partials[((size_t)blockIdx.x * 2 + 1) * C + c] = t2;
+  }
+}
+
+template <class T, int VEC>
+struct FwdStatF {
+  const T* x; int C;
+  __device__ void operator()(long long r, int c, float (&g)[VEC], float (&h)[VEC]) const {
+    if constexpr (VEC == 4) { ld4(x + r * C + c, g); } else { g[0] = ldf(x + r * C + c); }
+#pragma unroll
+    for (int i = 0; i < VEC; ++i) h[i] = g[i] * g[i];
+  }
+};
+
+static int stat_blocks(long long rows, int C, int vec) {
+  int cv = C / vec, rps = kStatThreads / cv;
+  long long b = (rows + rps - 1) / rps;
+  // at least ~8 row-steps per block so the partial buffer stays small
+  b = (b + 7) / 8;
+  if (b < 1) b = 1;
+  if (b > kMaxStatBlocks) b = kMaxStatBlocks;
+  return (int)b;
+}
+
+size_t stat_partials_bytes(int C) { return (size_t)kMaxStatBlocks * 2 * C * sizeof(float); }
+
+template <class T>
+int32_t launch_colstats(const T* x, long long rows, int C, float* partials, int* nblk, cudaStream_t st) {
+  if (C > 1024) { set_error("colstats: C=%d > 1024 unsupported", C); return STGCN_ERR_UNSUPPORTED; }
+  if (C % 4 == 0) {
+    int nb = stat_blocks(rows, C, 4); *nblk = nb;
+    int rps = kStatThreads / (C / 4);
+    colreduce_kernel<4><<<nb, kStatThreads, 2 * rps * C * sizeof(float), st>>>(rows, C, FwdStatF<T, 4>{x, C}, partials);
+  } else {
+    if (C > 256) { set_error("colstats: C=%d not a multiple of 4 and > 256", C); return STGCN_ERR_UNSUPPORTED; }
+    int nb = stat_blocks(rows, C, 1); *nblk = nb;
+    int rps = kStatThreads / C;
+    colreduce_kernel<1><<<nb, kStatThreads, 2 * rps * C * sizeof(float), st>>>(rows, C, FwdStatF<T, 1>{x, C}, partials);
+  }
+  STGCN_CHECK_LAUNCH("colstats");
+  return STGCN_OK;
+}
+template int32_t launch_colstats<float>(const float*, long long, int, float*, int*, cudaStream_t);
+template int32_t launch_colstats<bf16>(const bf16*, long long, int, float*, int*, cudaStream_t);
+
+// ---------------------------------------------------------------------------
+// finalize forward statistics -> stats[4][C] = {mean, invstd, a, b}
+//   a = gamma*invstd, b = beta - a*mean ; running stats updated like torch
+// ---------------------------------------------------------------------------
+__global__ void bn_finalize_kernel(const float* __restrict__ partials, int nblk, int C, double count,
+                                   const float* __restrict__ gamma, const float* __restrict__ beta,
+                                   float* running_mean, float* running_var, long long* nbt,
+                                   float eps, float momentum, float* __restrict__ stats) {
+  int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c == 0 && nbt) *nbt += 1;
+  if (c >= C) return;
+  double s1 = 0, s2 = 0;
+  for (int b = 0; b < nblk; ++b) {
+    s1 += (double)partials[((size_t)b * 2 + 0) * C + c];
+    s2 += (double)partials[((size_t)b * 2 + 1) * C + c];
+  }
+  double mean = s1 / count;
+  double var = s2 / count - mean * mean;
+  if (var < 0) var = 0;
+  float invstd = (float)(1.0 / sqrt(var + (double)eps));
+  float a = gamma[c] * invstd;
+  stats[0 * C + c] = (float)mean;
+  stats[1 * C + c] = invstd;
+  stats[2 * C + c] = a;
+  stats[3 * C + c] = beta[c] - a * (float)mean;
+  if (running_mean) {
+    double unbiased = count > 1 ? var * count / (count - 1) : var;
+    running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * (float)mean;
+    running_var[c] = (1.f - momentum) * running_var[c] + momentum * (float)unbiased;
+  }
+}
+
+__global__ void bn_eval_coeffs_kernel(int C, const float* __restrict__ gamma, const float* __restrict__ beta,
+                                      const float* __restrict__ rm, const float* __restrict__ rv, float eps,
+                                      float* __restrict__ stats) {
+  int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  float invstd = rsqrtf(rv[c] + eps);
+  float a = gamma[c] * invstd;
+  stats[0 * C + c] = rm[c];
+  stats[1 * C + c] = invstd;
+  stats[2 * C + c] = a;
+  stats[3 * C + c] = beta[c] - a * rm[c];
+}
+
+int32_t launch_bn_finalize(const float* partials, int nblk, int C, double count, const float* gamma,
+                           const float* beta, float* rm, float* rv, long long* nbt, float eps, float momentum,
+                           float* stats, cudaStream_t st) {
+  bn_finalize_kernel<<<cdiv(C, 128), 128, 0, st>>>(partials, nblk, C, count, gamma, beta, rm, rv, nbt, eps, momentum, stats);
+  STGCN_CHECK_LAUNCH("bn_finalize");
+  return STGCN_OK;
+}
+int32_t launch_bn_eval_coeffs(int C, const float* gamma, const float* beta, const float* rm, const float* rv,
+                              float eps, float* stats, cudaStream_t st) {
+  bn_eval_coeffs_kernel<<<cdiv(C, 128), 128, 0, st>>>(C, gamma, beta, rm, rv, eps, stats);
+  STGCN_CHECK_LAUNCH("bn_eval_coeffs");
+  return STGCN_OK;
+}
+
+// ---------------------------------------------------------------------------
+// y = drop(act(a*x + b))   (a,b may be null -> identity affine)
+// ---------------------------------------------------------------------------
+template <class T, int VEC>
+__global__ void __launch_bounds__(256) affine_act_kernel(const T* __restrict__ x, long long total, int C,
+                                                         const float* __restrict__ a, const float* __restrict__ b,
+                                                         int relu, float p, float inv_keep, uint64_t seed,
+                                                         uint64_t offset, T* __restrict__ y) {
+  long long i = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * VEC;
+  const long long step = (long long)gridDim.x * blockDim.x * VEC;
+  for (; i < total; i += step) {
+    int c = (int)(i % C);
+    float v[VEC];
+    if constexpr (VEC == 4) ld4(x + i, v); else v[0] = ldf(x + i);
+#pragma unroll
+    for (int j = 0; j < VEC; ++j) {
+      float t = a ? fmaf(a[c + j], v[j], b[c + j]) : v[j];
+      if (relu) t = fmaxf(t, 0.f);
+      if (p > 0.f) t *= dropout_scale(seed, offset, (uint64_t)(i + j), p, inv_keep);
+      v[j] = t;
+    }
+    if constexpr (VEC == 4) st4(y + i, v); else stf(y + i, v[0]);
+  }
+}
+
+template <class T>
+int32_t launch_affine_act(const T* x, long long rows, int C, const float* a, const float* b, int relu, float p,
+                          uint64_t seed, uint64_t offset, T* y, cudaStream_t st) {
+  long long total = rows * C;
+  float inv_keep = p > 0.f ? 1.f / (1.f - p) : 1.f;
+  if (C % 4 == 0) {
+    int blocks = (int)std::min<long long>((total / 4 + 255) / 256, 148 * 16);
+    affine_act_kernel<T, 4><<<blocks, 256, 0, st>>>(x, total, C, a, b, relu, p, inv_keep, seed, offset, y);
+  } else {
+    int blocks = (int)std::min<long long>((total + 255) / 256, 148 * 16);
+    affine_act_kernel<T, 1><<<blocks, 256, 0, st>>>(x, total, C, a, b, relu, p, inv_keep, seed, offset, y);
+  }
+  STGCN_CHECK_LAUNCH("affine_act");
+  return STGCN_OK;
+}
+template int32_t launch_affine_act<float>(const float*, long long, int, const float*, const float*, int, float, uint64_t, uint64_t, float*, cudaStream_t);
+template int32_t launch_affine_act<bf16>(const bf16*, long long, int, const float*, const float*, int, float, uint64_t, uint64_t, bf16*, cudaStream_t);
+
+// ---------------------------------------------------------------------------
+// backward of  y = drop(relu?(a*z + b))  w.r.t. the BN:
+//   g    = dy * drop_scale * [a*z+b > 0]
+//   s1   = sum g ; s2 = sum g * zhat,  zhat = (z-mean)*invstd
+//   dz   = a * (g - s1/m - zhat*s2/m)      (training)   |   a * g   (eval)
+// ---------------------------------------------------------------------------
+template <class T, int VEC>
+struct BwdRedF {
+  const T* dy; const T* z; const float* stats; int C; int relu; float p; float inv_keep; uint64_t seed, offset;
+  __device__ void operator()(long long r, int c, float (&g)[VEC], float (&h)[VEC]) const {
+    float zz[VEC];
+    long long i = r * C + c;
+    if constexpr (VEC == 4) { ld4(dy + i, g); ld4(z + i, zz); } else { g[0] = ldf(dy + i); zz[0] = ldf(z + i); }
+#pragma unroll
+    for (int j = 0; j < VEC; ++j) {
+      float mean = stats[c + j], invstd = stats[C + c + j], a = stats[2 * C + c + j], b = stats[3 * C + c + j];
+      if (relu && !(fmaf(a, zz[j], b) > 0.f)) g[j] = 0.f;
+      if (p > 0.f) g[j] *= dropout_scale(seed, offset, (uint64_t)(i + j), p, inv_keep);
+      h[j] = g[j] * (zz[j] - mean) * invstd;
+    }
+  }
+};
+
+template <class T>
+int32_t launch_bn_bwd_reduce(const T* dy, const T* z, const float* stats, long long rows, int C, int relu, float p,
+                             uint64_t seed, uint64_t offset, float* partials, int* nblk, cudaStream_t st) {
+  float inv_keep = p > 0.f ? 1.f / (1.f - p) : 1.f;
+  if (C % 4 == 0) {
+    int nb = stat_blocks(rows, C, 4); *nblk = nb;
+    int rps = kStatThreads / (C / 4);
+    colreduce_kernel<4><<<nb, kStatThreads, 2 * rps * C * sizeof(float), st>>>(
+        rows, C, BwdRedF<T, 4>{dy, z, stats, C, relu, p, inv_keep, seed, offset}, partials);
+  } else {
+    int nb = stat_blocks(rows, C, 1); *nblk = nb;
+    int rps = kStatThreads / C;
+    colreduce_kernel<1><<<nb, kStatThreads, 2 * rps * C * sizeof(float), st>>>(
+        rows, C, BwdRedF<T, 1>{dy, z, stats, C, relu, p, inv_keep, seed, offset}, partials);
+  }
+  STGCN_CHECK_LAUNCH("bn_bwd_reduce");
+  return STGCN_OK;
+}
+template int32_t launch_bn_bwd_reduce<float>(const float*, const float*, const float*, long long, int, int, float, uint64_t, uint64_t, float*, int*, cudaStream_t);
+template int32_t launch_bn_bwd_reduce<bf16>(const bf16*, const bf16*, const float*, long long, int, int, float, uint64_t, uint64_t, float*, int*, cudaStream_t);
+
+// sums[2][C] = {s1, s2} reduced in double; also emits dgamma = s2, dbeta = s1
+__global__ void bn_bwd_finalize_kernel(const float* __restrict__ partials, int nblk, int C, float* __restrict__ sums,
+                                       float* __restrict__ dgamma, float* __restrict__ dbeta) {
+  int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  double s1 = 0, s2 = 0;
+  for (int b = 0; b < nblk; ++b) {
+    s1 += (double)partials[((size_t)b * 2 + 0) * C + c];
+    s2 += (double)partials[((size_t)b * 2 + 1) * C + c];
+  }
+  sums[c] = (float)s1; sums[C + c] = (float)s2;
+  if (dgamma) dgamma[c] = (float)s2;
+  if (dbeta) dbeta[c] = (float)s1;
+}
+int32_t launch_bn_bwd_finalize(const float* partials, int nblk, int C, float* sums, float* dgamma, float* dbeta, cudaStream_t st) {
+  bn_bwd_finalize_kernel<<<cdiv(C, 128), 128, 0, st>>>(partials, nblk, C, sums, dgamma, dbeta);
+  STGCN_CHECK_LAUNCH("bn_bwd_finalize");
+  return STGCN_OK;
+}
+
+template <class T, int VEC>
+__global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const T* __restrict__ dy, const T* __restrict__ z,
+                                                           const float* __restrict__ stats, const float* __restrict__ sums,
+                                                           long long total, int C, int relu, int training, float inv_m,
+                                                           float p, float inv_keep, uint64_t seed, uint64_t offset,
+                                                           T* __restrict__ dz) {
+  long long i = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * VEC;
+  const long long step = (long long)gridDim.x * blockDim.x * VEC;
+  for (; i < total; i += step) {
+    int c = (int)(i % C);
+    float g[VEC], zz[VEC];
+    if constexpr (VEC == 4) { ld4(dy + i, g); ld4(z + i, zz); } else { g[0] = ldf(dy + i); zz[0] = ldf(z + i); }
+#pragma unroll
+    for (int j = 0; j < VEC; ++j) {
+      float mean = stats[c + j], invstd = stats[C + c + j], a = stats[2 * C + c + j], b = stats[3 * C + c + j];
+      if (relu && !(fmaf(a, zz[j], b) > 0.f)) g[j] = 0.f;
+      if (p > 0.f) g[j] *= dropout_scale(seed, offset, (uint64_t)(i + j), p, inv_keep);
+      float r = g[j];
+      if (training) r = r - sums[c + j] * inv_m - (zz[j] - mean) * invstd * sums[C + c + j] * inv_m;
+      g[j] = a * r;
+    }
+    if constexpr (VEC == 4) st4(dz + i, g); else stf(dz + i, g[0]);
+  }
+}
+
+template <class T>
+int32_t launch_bn_bwd_apply(const T* dy, const T* z, const float* stats, const float* sums, long long rows, int C,
+                            int relu, int training, float p, uint64_t seed, uint64_t offset, T* dz, cudaStream_t st) {
+  long long total = rows * C;
+  float inv_keep = p > 0.f ? 1.f / (1.f - p) : 1.f;
+  float inv_m = 1.0f / (float)rows;
+  if (C % 4 == 0) {
+    int blocks = (int)std::min<long long>((total / 4 + 255) / 256, 148 * 16);
+    bn_bwd_apply_kernel<T, 4><<<blocks, 256, 0, st>>>(dy, z, stats, sums, total, C, relu, training, inv_m, p, inv_keep, seed, offset, dz);
+  } else {
+    int blocks = (int)std::min<long long>((total + 255) / 256, 148 * 16);
+    bn_bwd_apply_kernel<T, 1><<<blocks, 256, 0, st>>>(dy, z, stats, sums, total, C, relu, training, inv_m, p, inv_keep, seed, offset, dz);
+  }
+  STGCN_CHECK_LAUNCH("bn_bwd_apply");
+  return STGCN_OK;
+}
+template int32_t launch_bn_bwd_apply<float>(const float*, const float*, const float*, const float*, long long, int, int, int, float, uint64_t, uint64_t, float*, cudaStream_t);
+template int32_t launch_bn_bwd_apply<bf16>(const bf16*, const bf16*, const float*, const float*, long long, int, int, int, float, uint64_t, uint64_t, bf16*, cudaStream_t);
+
+// ---------------------------------------------------------------------------
+// dz = dy * [out > 0] * (1/(1-p) if dropout)    -- backward of the trailing
+// ReLU (+dropout) of the residual path (st_graphconv.py:105-108): out > 0
+// implies the element was kept.
+// ---------------------------------------------------------------------------
+template <class T, int VEC>
+__global__ void __launch_bounds__(256) relu_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ out, long long total,
+                                                       float inv_keep, T* __restrict__ dz) {
+  long long i = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * VEC;
+  const long long step = (long long)gridDim.x * blockDim.x * VEC;
+  for (; i < total; i += step) {
+    float g[VEC], o[VEC];
+    if constexpr (VEC == 4) { ld4(dy + i, g); ld4(out + i, o); } else { g[0] = ldf(dy + i); o[0] = ldf(out + i); }
+#pragma unroll
+    for (int j = 0; j < VEC; ++j) g[j] = o[j] > 0.f ? g[j] * inv_keep : 0.f;
+    if constexpr (VEC == 4) st4(dz + i, g); else stf(dz + i, g[0]);
+  }
+}
+template <class T>
+int32_t launch_relu_bwd(const T* dy, const T* out, long long total, float p, T* dz, cudaStream_t st) {
+  float inv_keep = p > 0.f ? 1.f / (1.f - p) : 1.f;
+  if (total % 4 == 0) {
+    int blocks = (int)std::min<long long>((total / 4 + 255) / 256, 148 * 16);
+    relu_bwd_kernel<T, 4><<<blocks, 256, 0, st>>>(dy, out, total, inv_keep, dz);
+  } else {
+    int blocks = (int)std::min<long long>((total + 255) / 256, 148 * 16);
+    relu_bwd_kernel<T, 1><<<blocks, 256, 0, st>>>(dy, out, total, inv_keep, dz);
+  }
+  STGCN_CHECK_LAUNCH("relu_bwd");
+  return STGCN_OK;
+}
+template int32_t launch_relu_bwd<float>(const float*, const float*, long long, float, float*, cudaStream_t);
+template int32_t launch_relu_bwd<bf16>(const bf16*, const bf16*, long long, float, bf16*, cudaStream_t);
+
+// dst = a + b (residual identity gradient merge), and cast
+template <class TS, class TD>
+__global__ void __launch_bounds__(256) cast_kernel(const TS* __restrict__ s, TD* __restrict__ d, size_t n) {
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  for (; i < n; i += (size_t)gridDim.x * blockDim.x) stf(d + i, ldf(s + i));
+}
+template <class TS, class TD>
+int32_t launch_cast(const TS* s, TD* d, size_t n, cudaStream_t st) {
+  int blocks = (int)std::min<size_t>((n + 255) / 256, 148 * 16);
+  if (blocks < 1) blocks = 1;
+  cast_kernel<TS, TD><<<blocks, 256, 0, st>>>(s, d, n);
+  STGCN_CHECK_LAUNCH("cast");
+  return STGCN_OK;
+}
+template int32_t launch_cast<float, bf16>(const float*, bf16*, size_t, cudaStream_t);
+template int32_t launch_cast<bf16, float>(const bf16*, float*, size_t, cudaStream_t);
+template int32_t launch_cast<float, float>(const float*, float*, size_t, cudaStream_t);
+template int32_t launch_cast<bf16, bf16>(const bf16*, bf16*, size_t, cudaStream_t);
+
+template <class T>
+__global__ void __launch_bounds__(256) add_inplace_kernel(T* __restrict__ d, const T* __restrict__ s, size_t n) {
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  for (; i < n; i += (size_t)gridDim.x * blockDim.x) stf(d + i, ldf(d + i) + ldf(s + i));
+}
+template <class T>
+int32_t launch_add_inplace(T* d, const T* s, size_t n, cudaStream_t st) {
+  int blocks = (int)std::min<size_t>((n + 255) / 256, 148 * 16);
+  if (blocks < 1) blocks = 1;
+  add_inplace_kernel<T><<<blocks, 256, 0, st>>>(d, s, n);
+  STGCN_CHECK_LAUNCH("add_inplace");
+  return STGCN_OK;
+}
+template int32_t launch_add_inplace<float>(float*, const float*, size_t, cudaStream_t);
+template int32_t launch_add_inplace<bf16>(bf16*, const bf16*, size_t, cudaStream_t);
+
+}  // namespace stgcn

@@ -1,0 +1,84 @@
+// Internal launch API shared by the .cu files of libstgcn_b200.
+#pragma once
+#include <algorithm>
+#include <type_traits>
+
+#include "common.cuh"
+
+namespace stgcn {
+
+// epilogue of the implicit-GEMM engines, applied in this order:
+//   t = acc (+bias[n]) (+bias2d[v][n]); t = scale[n]*t + shift[n]; t += residual[r][n];
+//   relu; dropout; (+= out[r][n])
+struct GemmEpilogue {
+  const float* bias = nullptr;
+  const float* bias2d = nullptr;     // [V][n_out]
+  const float* scale = nullptr;      // folded BatchNorm (eval) a,b
+  const float* shift = nullptr;
+  const void* residual = nullptr;    // same type / shape as out
+  int relu = 0;
+  int accumulate = 0;
+  float dropout_p = 0.f;
+  uint64_t seed = 0, offset = 0;
+  float* stat_partials = nullptr;    // tcgen05 engine only: per-CTA column sum / sumsq of the stored output
+};
+
+// element (tap, n, c) of a weight tensor kept in the reference's layout
+struct WIndex {
+  int ndiv = 1 << 30; long long snh = 0, snl = 0;
+  int cdiv = 1 << 30; long long sch = 0, scl = 0;
+  long long st = 0;
+  __host__ __device__ __forceinline__ long long at(int tap, int n, int c) const {
+    return (long long)(n / ndiv) * snh + (long long)(n % ndiv) * snl + (long long)(c / cdiv) * sch + (long long)(c % cdiv) * scl +
+           (long long)tap * st;
+  }
+};
+
+// bn_kernels.cu
+size_t stat_partials_bytes(int C);
+template <class T> int32_t launch_colstats(const T* x, long long rows, int C, float* partials, int* nblk, cudaStream_t st);
+int32_t launch_bn_finalize(const float* partials, int nblk, int C, double count, const float* gamma, const float* beta,
+                           float* rm, float* rv, long long* nbt, float eps, float momentum, float* stats, cudaStream_t st);
+int32_t launch_bn_eval_coeffs(int C, const float* gamma, const float* beta, const float* rm, const float* rv, float eps,
+                              float* stats, cudaStream_t st);
+template <class T> int32_t launch_affine_act(const T* x, long long rows, int C, const float* a, const float* b, int relu, float p,
+                                            uint64_t seed, uint64_t offset, T* y, cudaStream_t st);
+template <class T> int32_t launch_bn_bwd_reduce(const T* dy, const T* z, const float* stats, long long rows, int C, int relu, float p,
+                                               uint64_t seed, uint64_t offset, float* partials, int* nblk, cudaStream_t st);
+int32_t launch_bn_bwd_finalize(const float* partials, int nblk, int C, float* sums, float* dgamma, float* dbeta, cudaStream_t st);
+template <class T> int32_t launch_bn_bwd_apply(const T* dy, const T* z, const float* stats, const float* sums, long long rows, int C,
+                                              int relu, int training, float p, uint64_t seed, uint64_t offset, T* dz, cudaStream_t st);
+template <class T> int32_t launch_relu_bwd(const T* dy, const T* out, long long total, float p, T* dz, cudaStream_t st);
+template <class TS, class TD> int32_t launch_cast(const TS* s, TD* d, size_t n, cudaStream_t st);
+template <class T> int32_t launch_add_inplace(T* d, const T* s, size_t n, cudaStream_t st);
+
+// agg_kernels.cu
+template <class T> int32_t launch_agg_fwd(const T* x, long long frames, int V, int C, int K, const float* A, const float* a,
+                                         const float* b, int relu, T* xa, cudaStream_t st);
+template <class T> int32_t launch_agg_bwd(const T* dxa, long long frames, int V, int C, int K, const float* A, const T* x,
+                                         const float* a, const float* b, int relu, T* dh, cudaStream_t st);
+template <class T> int32_t launch_agg_dA(const T* dxa, const T* x, long long frames, int V, int C, int K, const float* a,
+                                        const float* b, int relu, float* dA, cudaStream_t st);
+template <class T> int32_t launch_vcolsum(const T* ds, long long frames, int V, int C, float* t1, cudaStream_t st);
+int32_t launch_bias2d(const float* A, const float* bias, int K, int V, int Co, float* out, cudaStream_t st);
+int32_t launch_spatial_bias_grads(const float* t1, const float* A, const float* bias, int K, int V, int Co, float* dbias, float* dA,
+                                  cudaStream_t st);
+
+// gemm_simt.cu
+template <class T> int32_t launch_conv_gemm_simt(const ConvGeom& g, const T* in, const float* w, const GemmEpilogue& ep, T* out,
+                                                cudaStream_t st);
+template <class T> int32_t launch_wgrad_simt(const ConvGeom& g, const T* dout, const T* in, const WIndex& wi, float* dw, cudaStream_t st);
+template <class TD> int32_t launch_pack_weights(const float* src, const WIndex& wi, int taps, int n_out, int c, TD* dst, cudaStream_t st);
+template <class T> int32_t launch_colsum(const T* x, long long rows, int C, float* partials, float* out, cudaStream_t st);
+
+// umma_gemm.cu  (tcgen05 / TMA engine, bf16)
+bool umma_conv_gemm_supported(const ConvGeom& g);
+int32_t launch_conv_gemm_umma(const ConvGeom& g, const bf16* in, const bf16* w, const GemmEpilogue& ep, bf16* out, cudaStream_t st);
+
+// head_kernels.cu
+int32_t head_forward(int dtype, int n, int t, int v, int c, int classes, const void* feat, const float* fcw, const float* fcb,
+                     float* pooled, float* logits, cudaStream_t st);
+int32_t head_backward(int dtype, int n, int t, int v, int c, int classes, const float* pooled, const float* fcw,
+                      const float* dlogits, void* dfeat, float* dfcw, float* dfcb, cudaStream_t st);
+
+}  // namespace stgcn

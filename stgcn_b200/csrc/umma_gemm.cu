@@ -1,0 +1,367 @@
+// tcgen05 implicit-GEMM engine (bf16 operands, fp32 accumulation in TMEM).
+//
+//   out[r][n] = sum_tap sum_c in[row(r,tap)][c] * w[tap][n][c]      (+ fused epilogue)
+//
+// Covers the two dense contractions of an ST-GCN block -- the 1x1 channel
+// mixing (taps = 1; nn.Conv2d at st_graphconv.py:136 and :28) and the 9x1
+// temporal convolution (nn.Conv2d(C,C,(9,1),stride=(s,1),padding=(4,0)) at
+// st_graphconv.py:41-43) -- and their data gradients (transposed conv).
+//
+// Tiling: one output tile = FT whole frames x V joints (<=128 rows = the MMA M)
+// by BN output channels.  The reduction runs over (tap, 64-channel block):
+// every step TMA-loads the frame-shifted activation tile through a 5-D tensor
+// map {C, V, stride-phase, T/stride, N} (zero fill outside [0,T) implements the
+// conv padding; the phase dimension implements stride 2 without gathers) and
+// the matching weight tile, both 128B-swizzled, and one elected thread issues
+// four tcgen05.mma (K=16 each).  Accumulators are double-buffered in TMEM so
+// the epilogue of tile i overlaps the MMAs of tile i+1.  Warp roles: 0 = TMA
+// producer, 1 = MMA issuer (+TMEM alloc), 2..5 = epilogue (TMEM -> registers
+// -> bias / folded BN / residual / ReLU / dropout -> bf16 -> swizzled smem ->
+// TMA store).  Persistent CTAs, one per SM.
+#include "kernels.cuh"
+#include "umma_common.cuh"
+
+namespace stgcn {
+
+using namespace umma;
+
+constexpr int kUmmaThreads = 192;
+constexpr int kMaxTaps = 16;
+constexpr int kATileBytes = 128 * 128;      // 128 rows x 64 bf16
+constexpr int kStagingBytes = 128 * 128;    // 128 rows x 64 bf16 (one TMA-store box)
+
+struct TapEntry { int w_tap; int parity; int h_off; };
+
+struct UmmaParams {
+  int nb, v, ft, phases;
+  int t_out_ph;          // output frames per phase
+  int t_out;             // total output frames (row index for residual / dropout)
+  int n_out, bn, n_tiles, kblocks_c, m_tiles_per_b, total_tiles;
+  int stages;
+  uint32_t tmem_cols;
+  uint32_t a_bytes, b_bytes;
+  int ntaps[2];
+  TapEntry taps[2][kMaxTaps];
+  // epilogue
+  const float* bias; const float* bias2d; const float* scale; const float* shift;
+  const bf16* residual;
+  int relu;
+  float dropout_p, inv_keep;
+  uint64_t seed, offset;
+};
+
+struct TileCoord { int n_t, ph, j0, b; };
+__device__ __forceinline__ TileCoord decode_tile(const UmmaParams& p, int tile) {
+  TileCoord t;
+  t.n_t = tile % p.n_tiles; tile /= p.n_tiles;
+  t.ph = tile % p.phases; tile /= p.phases;
+  t.j0 = (tile % p.m_tiles_per_b) * p.ft;
+  t.b = tile / p.m_tiles_per_b;
+  return t;
+}
+
+__global__ void __launch_bounds__(kUmmaThreads, 1)
+conv_gemm_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_constant__ CUtensorMap map_w,
+                      const __grid_constant__ CUtensorMap map_out, const __grid_constant__ UmmaParams p) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  // 1024-byte aligned carve-up (dynamic smem base is only guaranteed 16-byte aligned)
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint8_t* smem_a = smem;                                        // stages x 16 KB
+  uint8_t* smem_b = smem_a + (size_t)p.stages * kATileBytes;     // stages x bn*128 B (multiple of 1024)
+  uint8_t* staging = smem_b + (size_t)p.stages * p.b_bytes;      // 2 x 16 KB
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(staging + 2 * kStagingBytes);
+  uint64_t* empty_bar = full_bar + p.stages;
+  uint64_t* tfull_bar = empty_bar + p.stages;
+  uint64_t* tempty_bar = tfull_bar + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+
+  const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&map_in); prefetch_tmap(&map_w); prefetch_tmap(&map_out);
+    for (int s = 0; s < p.stages; ++s) { mbar_init(full_bar + s, 1); mbar_init(empty_bar + s, 1); }
+    for (int a = 0; a < 2; ++a) { mbar_init(tfull_bar + a, 1); mbar_init(tempty_bar + a, 128); }
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, p.tmem_cols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      int stage = 0; uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
+        const TileCoord tc = decode_tile(p, tile);
+        const int nt = p.ntaps[tc.ph];
+        for (int ti = 0; ti < nt; ++ti) {
+          const TapEntry te = p.taps[tc.ph][ti];
+          for (int kb = 0; kb < p.kblocks_c; ++kb) {
+            mbar_wait(empty_bar + stage, phase ^ 1);
+            mbar_expect_tx(full_bar + stage, p.a_bytes + p.b_bytes);
+            tma_load_5d(&map_in, smem_a + (size_t)stage * kATileBytes, full_bar + stage, kb * 64, 0, te.parity, tc.j0 + te.h_off, tc.b);
+            tma_load_3d(&map_w, smem_b + (size_t)stage * p.b_bytes, full_bar + stage, kb * 64, tc.n_t * p.bn, te.w_tap);
+            if (++stage == p.stages) { stage = 0; phase ^= 1; }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    if (lane == 0) {
+      const uint32_t idesc = make_idesc_bf16(128, p.bn, 0, 0);
+      int stage = 0; uint32_t phase = 0;
+      int as = 0; uint32_t aphase = 0;
+      for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
+        const TileCoord tc = decode_tile(p, tile);
+        const int nkb = p.ntaps[tc.ph] * p.kblocks_c;
+        mbar_wait(tempty_bar + as, aphase ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + (uint32_t)(as * p.bn);
+        for (int kb = 0; kb < nkb; ++kb) {
+          mbar_wait(full_bar + stage, phase);
+          tc_fence_after();
+          const uint64_t adesc = make_smem_desc_sw128(smem_u32(smem_a + (size_t)stage * kATileBytes), 16, 1024);
+          const uint64_t bdesc = make_smem_desc_sw128(smem_u32(smem_b + (size_t)stage * p.b_bytes), 16, 1024);
+#pragma unroll
+          for (int k = 0; k < 4; ++k)   // 4 x (K = 16 bf16 = 32 bytes) inside the 128-byte swizzle atom
+            umma_bf16_ss(d_tmem, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc, (kb | k) != 0 ? 1u : 0u);
+          umma_commit(empty_bar + stage);          // frees the smem stage when these MMAs retire
+          if (++stage == p.stages) { stage = 0; phase ^= 1; }
+        }
+        umma_commit(tfull_bar + as);               // accumulator ready for the epilogue
+        if (++as == 2) { as = 0; aphase ^= 1; }
+      }
+    }
+  } else {
+    // ===================== epilogue warps (2..5) =====================
+    const int q = warp % 4;                        // TMEM lane quarter this warp may access
+    const int row = q * 32 + lane;                 // tile row == TMEM lane
+    const int et = threadIdx.x - 64;               // 0..127
+    const int fl = row / p.v, vv = row % p.v;
+    int as = 0; uint32_t aphase = 0;
+    int chunk_ctr = 0;
+    for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
+      const TileCoord tc = decode_tile(p, tile);
+      mbar_wait(tfull_bar + as, aphase);
+      tc_fence_after();
+      const int jj = tc.j0 + fl;
+      const bool row_valid = row < p.ft * p.v && jj < p.t_out_ph;
+      const long long grow = ((long long)tc.b * p.t_out + (long long)jj * p.phases + tc.ph) * p.v + vv;   // global output row
+      for (int ch = 0; ch < p.bn / 64; ++ch, ++chunk_ctr) {
+        uint8_t* stg = staging + (chunk_ctr & 1) * kStagingBytes;
+        if (chunk_ctr >= 2) {
+          if (et == 0) tma_store_wait_read<1>();   // the store that last read this buffer has drained
+          asm volatile("bar.sync 1, 128;" ::: "memory");
+        }
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
+          uint32_t r[32];
+          const int col0 = ch * 64 + half * 32;    // column inside the bn-wide tile
+          tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * p.bn + col0), r);
+          tmem_ld_wait();
+          const int n0 = tc.n_t * p.bn + col0;     // global output channel of r[0]
+          float f[32];
+#pragma unroll
+          for (int i = 0; i < 32; ++i) f[i] = __uint_as_float(r[i]);
+          if (p.bias) {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) f[i] += __ldg(p.bias + n0 + i);
+          }
+          if (p.bias2d) {
+            const float* b2 = p.bias2d + (size_t)vv * p.n_out + n0;
+#pragma unroll
+            for (int i = 0; i < 32; ++i) f[i] += __ldg(b2 + i);
+          }
+          if (p.scale) {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) f[i] = fmaf(__ldg(p.scale + n0 + i), f[i], __ldg(p.shift + n0 + i));
+          }
+          if (p.residual && row_valid) {
+            const uint4* rp = reinterpret_cast<const uint4*>(p.residual + (size_t)grow * p.n_out + n0);
+#pragma unroll
+            for (int g = 0; g < 4; ++g) {
+              uint4 u = __ldg(rp + g);
+              const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+#pragma unroll
+              for (int e = 0; e < 4; ++e) { f[g * 8 + 2 * e] += __low2float(h[e]); f[g * 8 + 2 * e + 1] += __high2float(h[e]); }
+            }
+          }
+          if (p.relu) {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) f[i] = fmaxf(f[i], 0.f);
+          }
+          if (p.dropout_p > 0.f && row_valid) {
+            const uint64_t o = (uint64_t)grow * p.n_out + n0;
+#pragma unroll
+            for (int i = 0; i < 32; ++i) f[i] *= dropout_scale(p.seed, p.offset, o + i, p.dropout_p, p.inv_keep);
+          }
+          // bf16 pack and 128B-swizzled store: 16-byte chunk j of row lands at chunk (j ^ (row & 7))
+#pragma unroll
+          for (int g = 0; g < 4; ++g) {
+            uint4 u;
+            __nv_bfloat162 h0 = __floats2bfloat162_rn(f[g * 8 + 0], f[g * 8 + 1]);
+            __nv_bfloat162 h1 = __floats2bfloat162_rn(f[g * 8 + 2], f[g * 8 + 3]);
+            __nv_bfloat162 h2 = __floats2bfloat162_rn(f[g * 8 + 4], f[g * 8 + 5]);
+            __nv_bfloat162 h3 = __floats2bfloat162_rn(f[g * 8 + 6], f[g * 8 + 7]);
+            u.x = *reinterpret_cast<uint32_t*>(&h0); u.y = *reinterpret_cast<uint32_t*>(&h1);
+            u.z = *reinterpret_cast<uint32_t*>(&h2); u.w = *reinterpret_cast<uint32_t*>(&h3);
+            const int j = half * 4 + g;
+            *reinterpret_cast<uint4*>(stg + row * 128 + ((j ^ (row & 7)) << 4)) = u;
+          }
+        }
+        fence_proxy_async_smem();                  // generic-proxy smem writes -> visible to the TMA engine
+        asm volatile("bar.sync 2, 128;" ::: "memory");
+        if (et == 0) {
+          tma_store_5d(&map_out, stg, tc.n_t * p.bn + ch * 64, 0, tc.ph, tc.j0, tc.b);
+          tma_store_commit();
+        }
+      }
+      tc_fence_before();
+      mbar_arrive(tempty_bar + as);                // this thread is done reading accumulator `as`
+      if (++as == 2) { as = 0; aphase ^= 1; }
+    }
+    if (et == 0) tma_store_wait<0>();
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) { tc_fence_after(); tmem_dealloc(tmem_base, p.tmem_cols); }
+}
+
+// ---------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------
+PFN_encodeTiled get_encode_tiled() {
+  static PFN_encodeTiled fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) != cudaSuccess || !p) return nullptr;
+    fn = reinterpret_cast<PFN_encodeTiled>(p);
+  }
+  return fn;
+}
+
+int32_t make_tmap_bf16(CUtensorMap* m, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+                       const uint32_t* box) {
+  PFN_encodeTiled enc = get_encode_tiled();
+  if (!enc) { set_error("cuTensorMapEncodeTiled entry point unavailable (driver too old or no device)"); return STGCN_ERR_CUDA; }
+  cuuint64_t gd[5]; cuuint64_t gs[4]; cuuint32_t bx[5]; cuuint32_t es[5];
+  for (int i = 0; i < rank; ++i) { gd[i] = dims[i]; bx[i] = box[i]; es[i] = 1; }
+  for (int i = 0; i < rank - 1; ++i) gs[i] = strides_bytes[i];
+  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(base), gd, gs, bx, es,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled failed (%d): rank %d dims %llu,%llu,%llu box %u,%u,%u", (int)r, rank,
+              (unsigned long long)dims[0], (unsigned long long)dims[1], (unsigned long long)(rank > 2 ? dims[2] : 0), box[0], box[1],
+              rank > 2 ? box[2] : 0);
+    return STGCN_ERR_CUDA;
+  }
+  return STGCN_OK;
+}
+
+static int pick_bn(int n_out) {
+  if (n_out <= 256) return n_out;
+  if (n_out % 256 == 0) return 256;
+  if (n_out % 192 == 0) return 192;
+  if (n_out % 128 == 0) return 128;
+  return 64;
+}
+
+bool umma_conv_gemm_supported(const ConvGeom& g) {
+  if (g.c % 64 != 0 || g.n_out % 64 != 0) return false;
+  if (g.v < 1 || g.v > 32 || g.taps < 1 || g.taps > kMaxTaps - 1) return false;
+  if (g.stride < 1 || g.stride > 2 || g.taps < g.stride) return false;
+  if (!g.dgrad && g.t_in % g.stride != 0) return false;
+  if (g.dgrad && g.t_out % g.stride != 0) return false;
+  return true;
+}
+
+static int num_sms() {
+  static int n = 0;
+  if (!n) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev); if (n <= 0) n = 148; }
+  return n;
+}
+
+int32_t launch_conv_gemm_umma(const ConvGeom& g, const bf16* in, const bf16* w, const GemmEpilogue& ep, bf16* out, cudaStream_t st) {
+  if (!umma_conv_gemm_supported(g)) { set_error("umma conv-gemm: unsupported geometry"); return STGCN_ERR_UNSUPPORTED; }
+  if (ep.accumulate) { set_error("umma conv-gemm: accumulate epilogue unsupported"); return STGCN_ERR_UNSUPPORTED; }
+  UmmaParams p; memset(&p, 0, sizeof(p));
+  const int s = g.stride;
+  p.nb = g.nb; p.v = g.v; p.ft = 128 / g.v; p.t_out = g.t_out; p.n_out = g.n_out;
+  p.bn = pick_bn(g.n_out); p.n_tiles = g.n_out / p.bn; p.kblocks_c = g.c / 64;
+  p.phases = g.dgrad ? s : 1;
+  p.t_out_ph = g.t_out / p.phases;
+  p.m_tiles_per_b = cdiv(p.t_out_ph, p.ft);
+  p.total_tiles = p.n_tiles * p.phases * p.m_tiles_per_b * g.nb;
+  // tap tables
+  for (int ph = 0; ph < p.phases; ++ph) {
+    int n = 0;
+    for (int tap = 0; tap < g.taps; ++tap) {
+      if (!g.dgrad) {
+        int d = tap - g.pad;                              // input frame = j*s + d = s*(j + floor(d/s)) + (d mod s)
+        int r = ((d % s) + s) % s;
+        p.taps[ph][n].w_tap = tap; p.taps[ph][n].parity = r; p.taps[ph][n].h_off = (d - r) / s; ++n;
+      } else {
+        int d = ph + g.pad - tap;                         // output frame j = s*jj + ph ; input frame = (j + pad - tap)/s
+        if (((d % s) + s) % s != 0) continue;
+        p.taps[ph][n].w_tap = tap; p.taps[ph][n].parity = 0; p.taps[ph][n].h_off = d / s; ++n;
+      }
+    }
+    p.ntaps[ph] = n;
+    if (n == 0) { set_error("umma conv-gemm: empty tap phase"); return STGCN_ERR_UNSUPPORTED; }
+  }
+  p.a_bytes = (uint32_t)(p.ft * g.v * 128);
+  p.b_bytes = (uint32_t)(p.bn * 128);
+  const size_t stage_bytes = kATileBytes + p.b_bytes;
+  const size_t fixed = 2 * kStagingBytes + 1024 /*align slack*/ + 512 /*barriers*/;
+  int stages = (int)((220 * 1024 - fixed) / stage_bytes);
+  if (stages > 8) stages = 8;
+  if (stages < 2) { set_error("umma conv-gemm: not enough shared memory for 2 stages"); return STGCN_ERR_UNSUPPORTED; }
+  p.stages = stages;
+  uint32_t cols = 32; while (cols < (uint32_t)(2 * p.bn)) cols <<= 1;
+  p.tmem_cols = cols;
+  p.bias = ep.bias; p.bias2d = ep.bias2d; p.scale = ep.scale; p.shift = ep.shift;
+  p.residual = reinterpret_cast<const bf16*>(ep.residual); p.relu = ep.relu;
+  p.dropout_p = ep.dropout_p; p.inv_keep = ep.dropout_p > 0.f ? 1.f / (1.f - ep.dropout_p) : 1.f; p.seed = ep.seed; p.offset = ep.offset;
+
+  CUtensorMap map_in, map_w, map_out;
+  const uint64_t C = g.c, V = g.v, N = g.n_out;
+  {
+    // input viewed as {C, V, sp, T_in/sp, NB}; sp = conv stride in forward mode, 1 for dgrad
+    const uint64_t sp = g.dgrad ? 1 : s;
+    uint64_t dims[5] = {C, V, sp, (uint64_t)g.t_in / sp, (uint64_t)g.nb};
+    uint64_t str[4] = {C * 2, V * C * 2, sp * V * C * 2, (uint64_t)g.t_in * V * C * 2};
+    uint32_t box[5] = {64, (uint32_t)g.v, 1, (uint32_t)p.ft, 1};
+    STGCN_TRY(make_tmap_bf16(&map_in, in, 5, dims, str, box));
+  }
+  {
+    uint64_t dims[3] = {C, N, (uint64_t)g.taps};
+    uint64_t str[2] = {C * 2, N * C * 2};
+    uint32_t box[3] = {64, (uint32_t)p.bn, 1};
+    STGCN_TRY(make_tmap_bf16(&map_w, w, 3, dims, str, box));
+  }
+  {
+    const uint64_t ph = p.phases;
+    uint64_t dims[5] = {N, V, ph, (uint64_t)g.t_out / ph, (uint64_t)g.nb};
+    uint64_t str[4] = {N * 2, V * N * 2, ph * V * N * 2, (uint64_t)g.t_out * V * N * 2};
+    uint32_t box[5] = {64, (uint32_t)g.v, 1, (uint32_t)p.ft, 1};
+    STGCN_TRY(make_tmap_bf16(&map_out, out, 5, dims, str, box));
+  }
+  const size_t smem = (size_t)stages * stage_bytes + fixed;
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(conv_gemm_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    if (e != cudaSuccess) { set_error("cudaFuncSetAttribute(smem) failed: %s", cudaGetErrorString(e)); return STGCN_ERR_CUDA; }
+    attr_set = true;
+  }
+  const int grid = std::min(p.total_tiles, num_sms());
+  conv_gemm_umma_kernel<<<grid, kUmmaThreads, smem, st>>>(map_in, map_w, map_out, p);
+  STGCN_CHECK_LAUNCH("conv_gemm_umma");
+  return STGCN_OK;
+}
+
+}  // namespace stgcn

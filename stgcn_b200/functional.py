@@ -1,0 +1,192 @@
+"""torch.autograd bridges over the C ABI.
+
+Tensors cross the boundary as raw device pointers of channels-last buffers
+(N,T,V,C); logical shapes seen by callers stay (N,C,T,V) like the reference
+(st_graphconv.py:85-109).
+"""
+import ctypes as C
+
+import torch
+
+from . import _lib as L
+
+
+def _to_ntvc(x, dtype):
+    """logical (N,C,T,V) -> contiguous physical (N,T,V,C) of `dtype` (no copy when already so)."""
+    return x.permute(0, 2, 3, 1).to(dtype).contiguous()
+
+
+def _from_ntvc(y):
+    return y.permute(0, 3, 1, 2)
+
+
+def _f32(t):
+    if t is None:
+        return None
+    if t.dtype != torch.float32 or not t.is_contiguous():
+        raise RuntimeError('stgcn_b200: parameters must be contiguous float32 tensors')
+    return t
+
+
+class _BlockFn(torch.autograd.Function):
+    """SpatialTemporalConv.forward / its autograd (st_graphconv.py:85-109)."""
+
+    @staticmethod
+    def forward(ctx, x, cfg, buffers, bn1_w, bn1_b, A, W, Wb, Wt, bt, bn2_w, bn2_b, Wr, Wrb):
+        L.require_cuda(x, 'f_in')
+        lib = L.lib()
+        dt = cfg['dtype']
+        xp = _to_ntvc(x, dt)
+        n, t, v, ci = xp.shape
+        if ci != cfg['c_in'] or v != A.shape[1]:
+            raise RuntimeError('stgcn_b200: f_in has shape (N,%d,T,%d), block expects C_in=%d V=%d'
+                               % (ci, v, cfg['c_in'], A.shape[1]))
+        d = L.BlockDesc(n=n, c_in=ci, c_out=cfg['c_out'], t=t, v=v, k=A.shape[0], gamma=cfg['gamma'],
+                        stride=cfg['stride'], pad=cfg['pad'], dtype=L.dtype_code(dt), training=int(cfg['training']),
+                        residual=cfg['residual'], flags=cfg.get('flags', 0), dropout_p=cfg['dropout_p'],
+                        bn_eps=cfg['eps'], bn_momentum=cfg['momentum'], seed=cfg['seed'], offset=0)
+        t_out = lib.stgcn_block_t_out(C.byref(d))
+        if t_out < 1:
+            raise RuntimeError('stgcn_b200: sequence too short for the temporal kernel')
+        need_grad = cfg['need_grad']
+        rm1, rv1, nbt1, rm2, rv2, nbt2 = buffers
+        P = L.BlockParams(L.ptr(_f32(bn1_w)), L.ptr(_f32(bn1_b)), L.ptr(rm1), L.ptr(rv1), L.ptr(nbt1),
+                          L.ptr(_f32(A)), L.ptr(_f32(W)), L.ptr(_f32(Wb)), L.ptr(_f32(Wt)), L.ptr(_f32(bt)),
+                          L.ptr(_f32(bn2_w)), L.ptr(_f32(bn2_b)), L.ptr(rm2), L.ptr(rv2), L.ptr(nbt2),
+                          L.ptr(_f32(Wr)), L.ptr(_f32(Wrb)))
+        y = torch.empty((n, t_out, v, cfg['c_out']), dtype=dt, device=x.device)
+        saved = None
+        if need_grad:
+            sb = lib.stgcn_block_saved_bytes(C.byref(d))
+            saved = torch.empty(sb, dtype=torch.uint8, device=x.device)
+        wsb = lib.stgcn_block_workspace_bytes(C.byref(d), 0)
+        if wsb == 0:
+            raise RuntimeError('stgcn_b200: ' + lib.stgcn_last_error().decode())
+        ws = L.workspace(x.device, wsb)
+        L.check(lib.stgcn_block_forward(C.byref(d), L.ptr(xp), C.byref(P), L.ptr(y), L.ptr(saved), L.ptr(ws),
+                                        ws.numel(), L.stream_ptr(x.device)), 'block_forward')
+        if need_grad:
+            ctx.d = d
+            ctx.buffers = buffers
+            ctx.x_dtype = x.dtype
+            ctx.has_res_conv = Wr is not None
+            ctx.save_for_backward(xp, y, saved, bn1_w, bn1_b, A, W, Wb, Wt, bt, bn2_w, bn2_b, Wr, Wrb)
+        return _from_ntvc(y)
+
+    @staticmethod
+    def backward(ctx, gy):
+        lib = L.lib()
+        xp, y, saved, bn1_w, bn1_b, A, W, Wb, Wt, bt, bn2_w, bn2_b, Wr, Wrb = ctx.saved_tensors
+        d = ctx.d
+        rm1, rv1, nbt1, rm2, rv2, nbt2 = ctx.buffers
+        dyp = _to_ntvc(gy, y.dtype)
+        P = L.BlockParams(L.ptr(bn1_w), L.ptr(bn1_b), L.ptr(rm1), L.ptr(rv1), L.ptr(nbt1), L.ptr(A), L.ptr(W),
+                          L.ptr(Wb), L.ptr(Wt), L.ptr(bt), L.ptr(bn2_w), L.ptr(bn2_b), L.ptr(rm2), L.ptr(rv2),
+                          L.ptr(nbt2), L.ptr(Wr), L.ptr(Wrb))
+        g = {k: torch.empty_like(v) for k, v in (('bn1_w', bn1_w), ('bn1_b', bn1_b), ('A', A), ('W', W), ('Wb', Wb),
+                                                   ('Wt', Wt), ('bt', bt), ('bn2_w', bn2_w), ('bn2_b', bn2_b))}
+        gWr = torch.empty_like(Wr) if Wr is not None else None
+        gWrb = torch.empty_like(Wrb) if Wrb is not None else None
+        G = L.BlockGrads(L.ptr(g['bn1_w']), L.ptr(g['bn1_b']), L.ptr(g['A']), L.ptr(g['W']), L.ptr(g['Wb']),
+                         L.ptr(g['Wt']), L.ptr(g['bt']), L.ptr(g['bn2_w']), L.ptr(g['bn2_b']), L.ptr(gWr), L.ptr(gWrb))
+        dx = torch.empty_like(xp) if ctx.needs_input_grad[0] else None
+        wsb = lib.stgcn_block_workspace_bytes(C.byref(d), 1)
+        ws = L.workspace(xp.device, wsb)
+        L.check(lib.stgcn_block_backward(C.byref(d), L.ptr(xp), L.ptr(y), C.byref(P), L.ptr(saved), L.ptr(dyp),
+                                         L.ptr(dx), C.byref(G), L.ptr(ws), ws.numel(), L.stream_ptr(xp.device)),
+                'block_backward')
+        gx = _from_ntvc(dx).to(ctx.x_dtype) if dx is not None else None
+        return (gx, None, None, g['bn1_w'], g['bn1_b'], g['A'], g['W'], g['Wb'], g['Wt'], g['bt'], g['bn2_w'],
+                g['bn2_b'], gWr, gWrb)
+
+
+def block_forward(x, cfg, buffers, params):
+    return _BlockFn.apply(x, cfg, buffers, *params)
+
+
+class _SpatialFn(torch.autograd.Function):
+    """SpatialConv.forward / its autograd (st_graphconv.py:139-152)."""
+
+    @staticmethod
+    def forward(ctx, x, cfg, A, W, Wb):
+        L.require_cuda(x, 'f_in')
+        lib = L.lib()
+        dt = cfg['dtype']
+        xp = _to_ntvc(x, dt)
+        n, t, v, ci = xp.shape
+        co = W.shape[0] // A.shape[0]
+        d = L.BlockDesc(n=n, c_in=ci, c_out=co, t=t, v=v, k=A.shape[0], gamma=1, stride=1, pad=0,
+                        dtype=L.dtype_code(dt), training=0, residual=0, flags=cfg.get('flags', 0), dropout_p=0.0,
+                        bn_eps=1e-5, bn_momentum=0.1, seed=0, offset=0)
+        out = torch.empty((n, t, v, co), dtype=dt, device=x.device)
+        wsb = lib.stgcn_spatial_workspace_bytes(C.byref(d), 0)
+        if wsb == 0:
+            raise RuntimeError('stgcn_b200: ' + lib.stgcn_last_error().decode())
+        ws = L.workspace(x.device, wsb)
+        L.check(lib.stgcn_spatial_forward(C.byref(d), L.ptr(xp), L.ptr(_f32(A)), L.ptr(_f32(W)), L.ptr(_f32(Wb)),
+                                          L.ptr(out), L.ptr(ws), ws.numel(), L.stream_ptr(x.device)), 'spatial_forward')
+        ctx.d = d
+        ctx.x_dtype = x.dtype
+        ctx.save_for_backward(xp, A, W, Wb)
+        return _from_ntvc(out)
+
+    @staticmethod
+    def backward(ctx, gout):
+        lib = L.lib()
+        xp, A, W, Wb = ctx.saved_tensors
+        d = ctx.d
+        gp = _to_ntvc(gout, xp.dtype)
+        dx = torch.empty_like(xp) if ctx.needs_input_grad[0] else None
+        dA, dW, dWb = torch.empty_like(A), torch.empty_like(W), torch.empty_like(Wb)
+        wsb = lib.stgcn_spatial_workspace_bytes(C.byref(d), 1)
+        ws = L.workspace(xp.device, wsb)
+        L.check(lib.stgcn_spatial_backward(C.byref(d), L.ptr(xp), L.ptr(A), L.ptr(W), L.ptr(Wb), L.ptr(gp), L.ptr(dx),
+                                           L.ptr(dA), L.ptr(dW), L.ptr(dWb), L.ptr(ws), ws.numel(),
+                                           L.stream_ptr(xp.device)), 'spatial_backward')
+        gx = _from_ntvc(dx).to(ctx.x_dtype) if dx is not None else None
+        return gx, None, dA, dW, dWb
+
+
+def spatial_forward(x, cfg, A, W, Wb):
+    return _SpatialFn.apply(x, cfg, A, W, Wb)
+
+
+class _HeadFn(torch.autograd.Function):
+    """avg_pool2d over (T,V) + fc_layer (lightning_model.py:105-107). feat is logical (N,C,T,V)."""
+
+    @staticmethod
+    def forward(ctx, feat, fcw, fcb):
+        L.require_cuda(feat, 'features')
+        lib = L.lib()
+        fp = feat.permute(0, 2, 3, 1)
+        if not fp.is_contiguous():
+            fp = fp.contiguous()
+        n, t, v, c = fp.shape
+        classes = fcw.shape[0]
+        pooled = torch.empty((n, c), dtype=torch.float32, device=feat.device)
+        logits = torch.empty((n, classes), dtype=torch.float32, device=feat.device)
+        L.check(lib.stgcn_head_forward(L.dtype_code(fp.dtype), n, t, v, c, classes, L.ptr(fp), L.ptr(_f32(fcw)),
+                                       L.ptr(_f32(fcb)), L.ptr(pooled), L.ptr(logits), L.stream_ptr(feat.device)),
+                'head_forward')
+        ctx.shape = (n, t, v, c, classes)
+        ctx.dt = fp.dtype
+        ctx.save_for_backward(pooled, fcw)
+        return logits
+
+    @staticmethod
+    def backward(ctx, gl):
+        lib = L.lib()
+        pooled, fcw = ctx.saved_tensors
+        n, t, v, c, classes = ctx.shape
+        gl = gl.contiguous().float()
+        dfeat = torch.empty((n, t, v, c), dtype=ctx.dt, device=gl.device)
+        dW = torch.empty_like(fcw)
+        db = torch.empty((classes,), dtype=torch.float32, device=gl.device)
+        scratch = pooled.clone()      # head_backward reuses the pooled buffer as scratch
+        L.check(lib.stgcn_head_backward(L.dtype_code(ctx.dt), n, t, v, c, classes, L.ptr(scratch), L.ptr(fcw), L.ptr(gl),
+                                        L.ptr(dfeat), L.ptr(dW), L.ptr(db), L.stream_ptr(gl.device)), 'head_backward')
+        return _from_ntvc(dfeat), dW, db
+
+
+def head_forward(feat, fcw, fcb):
+    return _HeadFn.apply(feat, fcw, fcb)

@@ -1,0 +1,91 @@
+"""Drop-in modules for the reference's ST-GCN unit (src/network/st_graphconv.py).
+
+Same constructor signatures, attribute names and state_dict keys/shapes as the
+reference, so checkpoints load both ways and `optim.Adam(model.parameters())`
+works unchanged.  The stock nn.Conv2d / nn.BatchNorm2d sub-modules are kept only
+as PARAMETER CONTAINERS (and so that `torch.manual_seed` gives the reference's
+initial weights); their forward is never called -- all arithmetic runs in
+libstgcn_b200.so on the current CUDA stream.  No CPU fallback: a CPU tensor is an
+error.
+"""
+import torch
+import torch.nn as nn
+
+from . import _lib as L
+from . import functional as Fn
+
+
+class SpatialConv(nn.Module):
+    """Spatial graph convolution, reference st_graphconv.py:111-152.
+
+    out[n,c,t,v] = sum_k sum_w A[k,v,w] * (W f_in + b)[n, k*C_out + c, t, w]
+    """
+
+    def __init__(self, C_in, C_out, A, compute_dtype=torch.float32):
+        super().__init__()
+        self.C_in = C_in
+        self.C_out = C_out
+        self.A = nn.Parameter(A.float())       # detached trainable leaf, like st_graphconv.py:129
+        self.K = self.A.shape[0]
+        self.V = self.A.shape[1]
+        self.W = nn.Conv2d(C_in, self.K * C_out, (1, 1))
+        self.compute_dtype = compute_dtype
+        self.flags = 0
+
+    def forward(self, f_in):
+        cfg = {'dtype': self.compute_dtype, 'flags': self.flags}
+        w = self.W.weight.view(self.K * self.C_out, self.C_in)
+        out = Fn.spatial_forward(f_in, cfg, self.A, w, self.W.bias)
+        return out
+
+
+class SpatialTemporalConv(nn.Module):
+    """ST-GCN unit, reference st_graphconv.py:4-109 (default path :97-100, residual_block :60-82)."""
+
+    def __init__(self, C_in, C_out, A, gamma, temporal_stride, temporal_padding, dropout_rate=0.5, residual=False,
+                 compute_dtype=torch.float32):
+        super().__init__()
+        self._res_mode = L.RES_NONE
+        if residual:
+            if C_in == C_out and temporal_stride == 1:
+                self.apply_residual = lambda x: x
+                self._res_mode = L.RES_IDENTITY
+            else:
+                self.apply_residual = nn.Conv2d(C_in, C_out, kernel_size=1, stride=(temporal_stride, 1))
+                self._res_mode = L.RES_CONV
+        self.residual = residual
+        self.batch_n = nn.BatchNorm2d(C_in)
+        self.spatialConv = SpatialConv(C_in, C_out, A, compute_dtype)
+        self.temporalConv = nn.Conv2d(C_out, C_out, kernel_size=(gamma, 1), stride=(temporal_stride, 1),
+                                      padding=(temporal_padding, 0))
+        self.batch_n_2 = nn.BatchNorm2d(C_out)
+        self.relu = nn.ReLU(inplace=True)
+        self.dropout = nn.Dropout(dropout_rate, inplace=True) if dropout_rate != 0 else None
+        self.C_in, self.C_out = C_in, C_out
+        self.gamma, self.temporal_stride, self.temporal_padding = gamma, temporal_stride, temporal_padding
+        self.compute_dtype = compute_dtype
+        self.flags = 0
+        self._calls = 0
+
+    def forward(self, f_in):
+        sc, tc, b1, b2 = self.spatialConv, self.temporalConv, self.batch_n, self.batch_n_2
+        params = [b1.weight, b1.bias, sc.A, sc.W.weight.view(sc.K * sc.C_out, sc.C_in), sc.W.bias,
+                  tc.weight.view(self.C_out, self.C_out, self.gamma), tc.bias, b2.weight, b2.bias]
+        if self._res_mode == L.RES_CONV:
+            params += [self.apply_residual.weight.view(self.C_out, self.C_in), self.apply_residual.bias]
+        else:
+            params += [None, None]
+        need_grad = torch.is_grad_enabled() and (f_in.requires_grad or any(p is not None and p.requires_grad for p in params))
+        p_drop = float(self.dropout.p) if (self.dropout is not None and self.training) else 0.0
+        seed = 0
+        if p_drop > 0:
+            seed = int(torch.randint(0, 2 ** 62, (1,)).item())
+        self._calls += 1
+        cfg = {'dtype': self.compute_dtype, 'c_in': self.C_in, 'c_out': self.C_out, 'gamma': self.gamma,
+               'stride': self.temporal_stride, 'pad': self.temporal_padding, 'training': self.training,
+               'residual': self._res_mode, 'dropout_p': p_drop, 'eps': b1.eps,
+               'momentum': 0.1 if b1.momentum is None else b1.momentum, 'seed': seed, 'need_grad': need_grad,
+               'flags': self.flags}
+        buffers = (b1.running_mean, b1.running_var, b1.num_batches_tracked,
+                   b2.running_mean, b2.running_var, b2.num_batches_tracked)
+        return Fn.block_forward(f_in, cfg, buffers, params)
