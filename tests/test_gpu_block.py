@@ -1,0 +1,177 @@
+"""GPU parity tests (run with -m gpu on the B200 box).  Everything goes through the
+C-ABI via the drop-in modules; the checker is the CPU oracle (pinned to the reference by
+tests/test_oracle_golden.py) and the committed golden fixtures made from the reference.
+
+Tolerances (BASELINE.json north_star): fp32 path 1e-4, bf16 path 2e-2, both measured as
+max|got-ref| / max|ref| per tensor; structurally-zero gradients are
+checked absolutely.
+"""
+import contextlib
+import io
+
+import numpy as np
+import pytest
+import torch
+
+from _helpers import block_case_names, load_golden, params_from_golden, rel_err
+from oracle import stgcn_oracle as O
+
+pytestmark = pytest.mark.gpu
+TOL_F32 = 1e-4
+TOL_BF16 = 2e-2
+
+
+def build_block(ci, co, A, s, res, p=None, dtype=torch.float32, dropout=0.0):
+    from stgcn_b200 import SpatialTemporalConv
+    m = SpatialTemporalConv(ci, co, A, 9, s, 4, dropout_rate=dropout, residual=res, compute_dtype=dtype)
+    if p is not None:
+        m.load_state_dict({k: v for k, v in p.items()})
+    return m.cuda()
+
+
+def run_block(m, x, gy, training):
+    m.train(training)
+    xg = x.cuda().requires_grad_(True)
+    y = m(xg)
+    (y.float() * gy.cuda()).sum().backward()
+    grads = {k: v.grad.detach().cpu() for k, v in m.named_parameters() if v.grad is not None}
+    return y.detach().float().cpu(), xg.grad.detach().float().cpu(), grads
+
+
+@pytest.mark.parametrize('name', block_case_names())
+def test_fp32_block_matches_reference_golden(name):
+    g = load_golden(name)
+    ci, co, T, V, K, s, res, training = [int(v) for v in g['meta']]
+    p = params_from_golden(g)
+    m = build_block(ci, co, torch.tensor(g['A_init']), s, bool(res), p)
+    y, dx, grads = run_block(m, torch.tensor(g['x']), torch.tensor(g['gy']), bool(training))
+    big_a = float(np.abs(g['A_init']).max()) > 100
+    tol = 2e-3 if big_a else TOL_F32
+    assert rel_err(y, g['y']) < tol
+    assert rel_err(dx, g['dx']) < tol * 3
+    for k, v in grads.items():
+        ref = g['g.' + k]
+        if training and not res and k == 'temporalConv.bias':
+            assert float(v.abs().max()) < 1e-6 * float(np.abs(g['gy']).sum())
+            continue
+        assert rel_err(v.reshape(ref.shape), ref) < tol * 3, k
+    sd = m.state_dict()
+    for k in ('batch_n.running_mean', 'batch_n.running_var', 'batch_n_2.running_mean', 'batch_n_2.running_var'):
+        assert rel_err(sd[k], g['post.' + k]) < (1e-3 if big_a else TOL_F32), k
+    if training:
+        assert int(sd['batch_n.num_batches_tracked']) == int(g['post.batch_n.num_batches_tracked'])
+
+
+def oracle_block(x, gy, p, cfg, training):
+    leaves = {}
+    p = {k: v.clone() for k, v in p.items()}
+    for k, v in p.items():
+        if v.dtype.is_floating_point and 'running' not in k:
+            v.requires_grad_(True); leaves[k] = v
+    xr = x.clone().requires_grad_(True)
+    y = O.block_forward(xr, p, cfg, training)
+    (y * gy).sum().backward()
+    return y.detach(), xr.grad, {k: v.grad for k, v in leaves.items()}, p
+
+
+MID_CASES = [
+    # ci, co, T, V, K, stride, residual
+    (64, 64, 20, 25, 3, 1, False),
+    (64, 128, 20, 25, 3, 2, False),
+    (128, 256, 12, 18, 2, 2, False),
+    (3, 64, 16, 25, 3, 1, False),
+    (64, 64, 14, 18, 1, 1, True),
+    (64, 128, 20, 25, 3, 2, True),
+]
+
+
+@pytest.mark.parametrize('case', MID_CASES)
+@pytest.mark.parametrize('training', [True, False])
+@pytest.mark.parametrize('dtype', [torch.float32, torch.bfloat16])
+def test_block_matches_oracle(case, training, dtype):
+    ci, co, T, V, K, s, res = case
+    torch.manual_seed(1234 + ci + co + T)
+    A = torch.randn(K, V, V) * 0.2
+    with contextlib.redirect_stdout(io.StringIO()):
+        m = build_block(ci, co, A, s, res, dtype=dtype)
+    # non-trivial BN parameters / running stats
+    with torch.no_grad():
+        for bn in (m.batch_n, m.batch_n_2):
+            bn.weight.uniform_(0.5, 1.5); bn.bias.uniform_(-0.3, 0.3)
+            bn.running_mean.uniform_(-0.2, 0.2); bn.running_var.uniform_(0.6, 1.4)
+    p = {k: v.detach().cpu().clone() for k, v in m.state_dict().items()}
+    N = 3
+    x = torch.randn(N, ci, T, V)
+    T_out = (T + 8 - 9) // s + 1
+    gy = torch.randn(N, co, T_out, V)
+    cfg = O.BlockCfg(ci, co, 9, s, 4, 0.0, res)
+    y_ref, dx_ref, g_ref, p_after = oracle_block(x, gy, p, cfg, training)
+    y, dx, grads = run_block(m, x, gy, training)
+    tol = TOL_F32 if dtype == torch.float32 else TOL_BF16
+    assert rel_err(y, y_ref) < tol
+    assert rel_err(dx, dx_ref) < tol * 2
+    for k, v in grads.items():
+        ref = g_ref[k]
+        if training and not res and k == 'temporalConv.bias':
+            assert float(v.abs().max()) <= 1e-5 * float(gy.abs().sum())
+            continue
+        assert rel_err(v.reshape(ref.shape), ref) < tol * 2, k
+    if training:
+        sd = m.state_dict()
+        for k in ('batch_n.running_mean', 'batch_n.running_var', 'batch_n_2.running_mean', 'batch_n_2.running_var'):
+            assert rel_err(sd[k], p_after[k]) < (1e-4 if dtype == torch.float32 else 1e-2), k
+
+
+@pytest.mark.parametrize('dtype', [torch.float32, torch.bfloat16])
+def test_inference_path_without_grad(dtype):
+    """no-grad eval takes the fused-epilogue chain (BN2+ReLU inside the temporal GEMM)."""
+    torch.manual_seed(5)
+    ci, co, T, V, K = 64, 64, 20, 25, 3
+    A = torch.randn(K, V, V) * 0.2
+    m = build_block(ci, co, A, 1, False, dtype=dtype).eval()
+    with torch.no_grad():
+        m.batch_n_2.running_var.uniform_(0.5, 2.0); m.batch_n_2.running_mean.uniform_(-0.5, 0.5)
+    p = {k: v.detach().cpu().clone() for k, v in m.state_dict().items()}
+    x = torch.randn(2, ci, T, V)
+    with torch.no_grad():
+        y = m(x.cuda()).float().cpu()
+        y_ref = O.block_forward(x, p, O.BlockCfg(ci, co, 9, 1, 4, 0.0, False), False)
+    assert rel_err(y, y_ref) < (TOL_F32 if dtype == torch.float32 else TOL_BF16)
+
+
+@pytest.mark.parametrize('residual', [False, True])
+def test_dropout_mask_is_consistent(residual):
+    torch.manual_seed(3)
+    A = torch.randn(2, 25, 25) * 0.2
+    m = build_block(8, 8, A, 1, residual, dropout=0.5).train()
+    x = torch.randn(4, 8, 16, 25).cuda().requires_grad_(True)
+    y = m(x)
+    frac_zero = float((y == 0).float().mean())
+    assert 0.6 < frac_zero < 0.9          # ~0.5 from ReLU of a zero-mean signal, then half of the rest dropped
+    y.sum().backward()
+    assert torch.isfinite(x.grad).all()
+    m.eval()
+    with torch.no_grad():
+        y2 = m(x)
+    assert float((y2 == 0).float().mean()) < 0.7
+
+
+def test_spatial_conv_module_matches_oracle():
+    from stgcn_b200 import SpatialConv
+    torch.manual_seed(11)
+    A = torch.randn(3, 25, 25) * 0.3
+    m = SpatialConv(16, 24, A).cuda()
+    x = torch.randn(2, 16, 10, 25)
+    xg = x.cuda().requires_grad_(True)
+    out = m(xg)
+    go = torch.randn_like(out)
+    (out * go).sum().backward()
+    Ar = A.clone().requires_grad_(True); W = m.W.weight.detach().cpu().clone().requires_grad_(True)
+    b = m.W.bias.detach().cpu().clone().requires_grad_(True); xr = x.clone().requires_grad_(True)
+    ref = O.spatial_conv(xr, Ar, W, b)
+    (ref * go.cpu()).sum().backward()
+    assert rel_err(out, ref) < TOL_F32
+    assert rel_err(xg.grad, xr.grad) < TOL_F32 * 2
+    assert rel_err(m.A.grad, Ar.grad) < TOL_F32 * 2
+    assert rel_err(m.W.weight.grad, W.grad) < TOL_F32 * 2
+    assert rel_err(m.W.bias.grad, b.grad) < TOL_F32 * 2
