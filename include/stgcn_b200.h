@@ -151,6 +151,13 @@ int32_t stgcn_umma_conv_gemm(int32_t nb, int32_t t_in, int32_t t_out, int32_t v,
 int32_t stgcn_umma_probe(int32_t mode, int32_t row_off, int32_t base_off, int32_t a_rows, const void* a,
                          const void* b, float* d, void* stream);
 
+/* Optional device timing per kernel class (cudaEvent pairs on the launching stream; off by default). */
+void stgcn_timing_enable(int32_t on);
+void stgcn_timing_reset(void);
+int32_t stgcn_timing_classes(void);
+const char* stgcn_timing_class_name(int32_t cls);
+int32_t stgcn_timing_read(int32_t cls, double* ms, double* work, uint64_t* launches);
+
 /* Number of CUDA kernels this library has launched in this process (bench's gpu_launches). */
 uint64_t stgcn_launch_count(void);
 const char* stgcn_last_error(void);

@@ -66,6 +66,12 @@ def _declare(lib):
     lib.stgcn_umma_conv_gemm.argtypes = [i32] * 9 + [_P] * 4 + [_P]
     lib.stgcn_umma_probe.restype = i32
     lib.stgcn_umma_probe.argtypes = [i32] * 4 + [_P] * 3 + [_P]
+    lib.stgcn_timing_enable.restype = None; lib.stgcn_timing_enable.argtypes = [i32]
+    lib.stgcn_timing_reset.restype = None; lib.stgcn_timing_reset.argtypes = []
+    lib.stgcn_timing_classes.restype = i32; lib.stgcn_timing_classes.argtypes = []
+    lib.stgcn_timing_class_name.restype = C.c_char_p; lib.stgcn_timing_class_name.argtypes = [i32]
+    lib.stgcn_timing_read.restype = i32
+    lib.stgcn_timing_read.argtypes = [i32, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_uint64)]
     lib.stgcn_launch_count.restype = u64; lib.stgcn_launch_count.argtypes = []
     lib.stgcn_last_error.restype = C.c_char_p; lib.stgcn_last_error.argtypes = []
     lib.stgcn_version.restype = C.c_char_p; lib.stgcn_version.argtypes = []
@@ -128,3 +134,23 @@ def workspace(device, nbytes):
 
 def launch_count():
     return int(lib().stgcn_launch_count())
+
+
+def timing_enable(on=True):
+    lib().stgcn_timing_enable(int(on))
+
+
+def timing_reset():
+    lib().stgcn_timing_reset()
+
+
+def timing_read():
+    """{class name: (ms, work, launches)} accumulated since the last reset (synchronises the recorded events)."""
+    out = {}
+    l = lib()
+    for i in range(l.stgcn_timing_classes()):
+        ms, work, n = C.c_double(), C.c_double(), C.c_uint64()
+        l.stgcn_timing_read(i, C.byref(ms), C.byref(work), C.byref(n))
+        if n.value:
+            out[l.stgcn_timing_class_name(i).decode()] = (ms.value, work.value, int(n.value))
+    return out

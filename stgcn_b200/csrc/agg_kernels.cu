@@ -74,6 +74,7 @@ static int agg_fb(int V, int C, int K) {
 template <class T>
 int32_t launch_agg_fwd(const T* x, long long frames, int V, int C, int K, const float* A, const float* a, const float* b,
                        int relu, T* xa, cudaStream_t st) {
+  KernelTimer kt_(KC_AGG_FWD, 2.0 * frames * V * V * (double)K * C, st);
   if (V > kVP || K > 4) { set_error("agg: V=%d K=%d unsupported (V<=32, K<=4)", V, K); return STGCN_ERR_UNSUPPORTED; }
   int FB = agg_fb(V, C, K);
   size_t smem = ((size_t)K * V * kVP + (size_t)FB * V * C) * sizeof(float);
@@ -150,6 +151,7 @@ __global__ void __launch_bounds__(kAggThreads) agg_bwd_kernel(const T* __restric
 template <class T>
 int32_t launch_agg_bwd(const T* dxa, long long frames, int V, int C, int K, const float* A, const T* x, const float* a,
                        const float* b, int relu, T* dh, cudaStream_t st) {
+  KernelTimer kt_(KC_AGG_BWD, 2.0 * frames * V * V * (double)K * C, st);
   if (V > kVP || K > 4) { set_error("agg_bwd: V=%d K=%d unsupported", V, K); return STGCN_ERR_UNSUPPORTED; }
   size_t smem = (size_t)K * V * kVP * sizeof(float);
   int blocks = (int)std::min<long long>((frames * C + kAggThreads - 1) / kAggThreads, 148 * 8);
@@ -225,6 +227,7 @@ __global__ void __launch_bounds__(kAggThreads) agg_dA_kernel(const T* __restrict
 template <class T>
 int32_t launch_agg_dA(const T* dxa, const T* x, long long frames, int V, int C, int K, const float* a, const float* b,
                       int relu, float* dA, cudaStream_t st) {
+  KernelTimer kt_(KC_AGG_DA, 2.0 * frames * V * V * (double)K * C, st);
   if (K * V * V > kDaPer * kAggThreads) { set_error("agg_dA: K*V*V=%d too large", K * V * V); return STGCN_ERR_UNSUPPORTED; }
   int CC = std::min(C, 64);
   size_t smem = (size_t)(V + K * V) * (CC + 1) * sizeof(float);
@@ -250,6 +253,7 @@ __global__ void __launch_bounds__(256) vcolsum_kernel(const T* __restrict__ ds, 
 }
 template <class T>
 int32_t launch_vcolsum(const T* ds, long long frames, int V, int C, float* t1, cudaStream_t st) {
+  KernelTimer kt_(KC_BN_STATS, 0.0, st);
   int VC = V * C;
   dim3 grid((unsigned)std::min<long long>(frames, 64), (unsigned)cdiv(VC, 256));
   vcolsum_kernel<T><<<grid, 256, 0, st>>>(ds, frames, VC, t1);

@@ -77,6 +77,7 @@ size_t stat_partials_bytes(int C) { return (size_t)kMaxStatBlocks * 2 * C * size
 
 template <class T>
 int32_t launch_colstats(const T* x, long long rows, int C, float* partials, int* nblk, cudaStream_t st) {
+  KernelTimer kt_(KC_BN_STATS, (double)rows * C, st);
   if (C > 1024) { set_error("colstats: C=%d > 1024 unsupported", C); return STGCN_ERR_UNSUPPORTED; }
   if (C % 4 == 0) {
     int nb = stat_blocks(rows, C, 4); *nblk = nb;
@@ -181,6 +182,7 @@ __global__ void __launch_bounds__(256) affine_act_kernel(const T* __restrict__ x
 template <class T>
 int32_t launch_affine_act(const T* x, long long rows, int C, const float* a, const float* b, int relu, float p,
                           uint64_t seed, uint64_t offset, T* y, cudaStream_t st) {
+  KernelTimer kt_(KC_ELEMWISE, (double)rows * C, st);
   long long total = rows * C;
   float inv_keep = p > 0.f ? 1.f / (1.f - p) : 1.f;
   if (C % 4 == 0) {
@@ -222,6 +224,7 @@ struct BwdRedF {
 template <class T>
 int32_t launch_bn_bwd_reduce(const T* dy, const T* z, const float* stats, long long rows, int C, int relu, float p,
                              uint64_t seed, uint64_t offset, float* partials, int* nblk, cudaStream_t st) {
+  KernelTimer kt_(KC_BN_STATS, (double)rows * C, st);
   float inv_keep = p > 0.f ? 1.f / (1.f - p) : 1.f;
   if (C % 4 == 0) {
     int nb = stat_blocks(rows, C, 4); *nblk = nb;
@@ -288,6 +291,7 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const T* __restrict__
 template <class T>
 int32_t launch_bn_bwd_apply(const T* dy, const T* z, const float* stats, const float* sums, long long rows, int C,
                             int relu, int training, float p, uint64_t seed, uint64_t offset, T* dz, cudaStream_t st) {
+  KernelTimer kt_(KC_ELEMWISE, (double)rows * C, st);
   long long total = rows * C;
   float inv_keep = p > 0.f ? 1.f / (1.f - p) : 1.f;
   float inv_m = 1.0f / (float)rows;
@@ -324,6 +328,7 @@ __global__ void __launch_bounds__(256) relu_bwd_kernel(const T* __restrict__ dy,
 }
 template <class T>
 int32_t launch_relu_bwd(const T* dy, const T* out, long long total, float p, T* dz, cudaStream_t st) {
+  KernelTimer kt_(KC_ELEMWISE, (double)total, st);
   float inv_keep = p > 0.f ? 1.f / (1.f - p) : 1.f;
   if (total % 4 == 0) {
     int blocks = (int)std::min<long long>((total / 4 + 255) / 256, 148 * 16);
@@ -364,6 +369,7 @@ __global__ void __launch_bounds__(256) add_inplace_kernel(T* __restrict__ d, con
 }
 template <class T>
 int32_t launch_add_inplace(T* d, const T* s, size_t n, cudaStream_t st) {
+  KernelTimer kt_(KC_ELEMWISE, (double)n, st);
   int blocks = (int)std::min<size_t>((n + 255) / 256, 148 * 16);
   if (blocks < 1) blocks = 1;
   add_inplace_kernel<T><<<blocks, 256, 0, st>>>(d, s, n);

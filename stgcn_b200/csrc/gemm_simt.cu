@@ -97,6 +97,7 @@ __global__ void __launch_bounds__(256) conv_gemm_simt_kernel(ConvGeom g, const T
 
 template <class T>
 int32_t launch_conv_gemm_simt(const ConvGeom& g, const T* in, const float* w, const GemmEpilogue& ep, T* out, cudaStream_t st) {
+  KernelTimer kt_(KC_SIMT_GEMM, 2.0 * g.nb * g.t_out * g.v * (double)g.c * g.n_out * g.taps, st);
   long long rows = (long long)g.nb * g.t_out * g.v;
   dim3 grid((unsigned)cdiv(rows, BM), (unsigned)cdiv(g.n_out, BN));
   conv_gemm_simt_kernel<T><<<grid, 256, 0, st>>>(g, in, w, ep, out);
@@ -171,6 +172,7 @@ __global__ void __launch_bounds__(256) wgrad_simt_kernel(ConvGeom g, const T* __
 
 template <class T>
 int32_t launch_wgrad_simt(const ConvGeom& g, const T* dout, const T* in, const WIndex& wi, float* dw, cudaStream_t st) {
+  KernelTimer kt_(KC_WGRAD, 2.0 * g.nb * g.t_out * g.v * (double)g.c * g.n_out * g.taps, st);
   long long rows = (long long)g.nb * g.t_out * g.v;
   int n_tiles = cdiv(g.n_out, BN), c_tiles = cdiv(g.c, BN);
   int tiles = n_tiles * c_tiles * g.taps;
@@ -199,6 +201,7 @@ __global__ void __launch_bounds__(256) pack_weights_kernel(const float* __restri
 }
 template <class TD>
 int32_t launch_pack_weights(const float* src, const WIndex& wi, int taps, int n_out, int c, TD* dst, cudaStream_t st) {
+  KernelTimer kt_(KC_PACK, 0.0, st);
   size_t total = (size_t)taps * n_out * c;
   int blocks = (int)std::min<size_t>((total + 255) / 256, 148 * 4);
   pack_weights_kernel<TD><<<blocks, 256, 0, st>>>(src, wi, taps, n_out, c, dst);
@@ -218,6 +221,7 @@ __global__ void colsum_finalize_kernel(const float* __restrict__ partials, int n
 }
 template <class T>
 int32_t launch_colsum(const T* x, long long rows, int C, float* partials, float* out, cudaStream_t st) {
+  KernelTimer kt_(KC_BN_STATS, 0.0, st);
   int nblk = 0;
   STGCN_TRY(launch_colstats<T>(x, rows, C, partials, &nblk, st));
   colsum_finalize_kernel<<<cdiv(C, 128), 128, 0, st>>>(partials, nblk, C, out);

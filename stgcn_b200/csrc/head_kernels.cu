@@ -31,6 +31,7 @@ __global__ void __launch_bounds__(128) fc_kernel(const float* __restrict__ poole
 
 int32_t head_forward(int dtype, int n, int t, int v, int c, int classes, const void* feat, const float* fcw, const float* fcb,
                      float* pooled, float* logits, cudaStream_t st) {
+  KernelTimer kt_(KC_HEAD, 0.0, st);
   int rows = t * v;
   cudaMemsetAsync(pooled, 0, sizeof(float) * (size_t)n * c, st);
   dim3 grid((unsigned)n, (unsigned)std::min(rows, 16));
@@ -82,6 +83,7 @@ __global__ void __launch_bounds__(256) pool_bwd_kernel(const float* __restrict__
 // pooled doubles as scratch for dpooled after dw is formed (stream order)
 int32_t head_backward(int dtype, int n, int t, int v, int c, int classes, const float* pooled, const float* fcw,
                       const float* dlogits, void* dfeat, float* dfcw, float* dfcb, cudaStream_t st) {
+  KernelTimer kt_(KC_HEAD, 0.0, st);
   int rows = t * v;
   fc_bwd_weight_kernel<<<cdiv((long long)classes * c, 256), 256, 0, st>>>(dlogits, pooled, n, c, classes, dfcw, dfcb);
   STGCN_CHECK_LAUNCH("fc_bwd_weight");

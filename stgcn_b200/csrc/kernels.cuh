@@ -34,6 +34,15 @@ struct WIndex {
   }
 };
 
+// timing.cu: kernel classes for the optional device timing
+enum KernelClass { KC_UMMA_GEMM = 0, KC_SIMT_GEMM, KC_WGRAD, KC_AGG_FWD, KC_AGG_BWD, KC_AGG_DA, KC_BN_STATS, KC_ELEMWISE,
+                   KC_PACK, KC_HEAD, KC_UMMA_WGRAD, KC_UMMA_SPATIAL, KC_COUNT };
+struct KernelTimer {     // records an event pair around the launches issued in its scope (when timing is enabled)
+  KernelTimer(int cls, double work, cudaStream_t st);
+  ~KernelTimer();
+  int idx_; cudaStream_t st_;
+};
+
 // bn_kernels.cu
 size_t stat_partials_bytes(int C);
 template <class T> int32_t launch_colstats(const T* x, long long rows, int C, float* partials, int* nblk, cudaStream_t st);

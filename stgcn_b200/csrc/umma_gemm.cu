@@ -274,7 +274,8 @@ static int pick_bn(int n_out) {
 bool umma_conv_gemm_supported(const ConvGeom& g) {
   if (g.c % 64 != 0 || g.n_out % 64 != 0) return false;
   if (g.v < 1 || g.v > 32 || g.taps < 1 || g.taps > kMaxTaps - 1) return false;
-  if (g.stride < 1 || g.stride > 2 || g.taps < g.stride) return false;
+  if (g.stride < 1 || g.stride > 2) return false;
+  if (g.dgrad && g.taps < g.stride) return false;   // every output phase needs at least one tap
   if (!g.dgrad && g.t_in % g.stride != 0) return false;
   if (g.dgrad && g.t_out % g.stride != 0) return false;
   return true;
@@ -287,6 +288,7 @@ static int num_sms() {
 }
 
 int32_t launch_conv_gemm_umma(const ConvGeom& g, const bf16* in, const bf16* w, const GemmEpilogue& ep, bf16* out, cudaStream_t st) {
+  KernelTimer kt_(KC_UMMA_GEMM, 2.0 * g.nb * g.t_out * g.v * (double)g.c * g.n_out * g.taps, st);
   if (!umma_conv_gemm_supported(g)) { set_error("umma conv-gemm: unsupported geometry"); return STGCN_ERR_UNSUPPORTED; }
   if (ep.accumulate) { set_error("umma conv-gemm: accumulate epilogue unsupported"); return STGCN_ERR_UNSUPPORTED; }
   UmmaParams p; memset(&p, 0, sizeof(p));

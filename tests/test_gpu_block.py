@@ -87,7 +87,7 @@ MID_CASES = [
 
 @pytest.mark.parametrize('case', MID_CASES)
 @pytest.mark.parametrize('training', [True, False])
-@pytest.mark.parametrize('dtype', [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize('dtype', [torch.float32, torch.bfloat16], ids=['float32', 'bfloat16'])
 def test_block_matches_oracle(case, training, dtype):
     ci, co, T, V, K, s, res = case
     torch.manual_seed(1234 + ci + co + T)
@@ -122,7 +122,7 @@ def test_block_matches_oracle(case, training, dtype):
             assert rel_err(sd[k], p_after[k]) < (1e-4 if dtype == torch.float32 else 1e-2), k
 
 
-@pytest.mark.parametrize('dtype', [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize('dtype', [torch.float32, torch.bfloat16], ids=['float32', 'bfloat16'])
 def test_inference_path_without_grad(dtype):
     """no-grad eval takes the fused-epilogue chain (BN2+ReLU inside the temporal GEMM)."""
     torch.manual_seed(5)
