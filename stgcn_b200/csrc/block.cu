@@ -83,7 +83,7 @@ template <class T> struct Engine {
     float* wp = ws.template get<float>((size_t)g.taps * g.n_out * g.c);
     if (ws.dry) return STGCN_OK;
     if (!ws.ok()) { set_error("workspace too small"); return STGCN_ERR_WORKSPACE; }
-    STGCN_TRY(launch_pack_weights<float>(wsrc, wi, g.taps, g.n_out, g.c, wp, st));
+    STGCN_TRY(launch_pack_weights<float>(wsrc, wi, g.taps, g.n_out, g.c, wp, st, std::is_same<T, bf16>::value ? 1 : 0));
     return launch_conv_gemm_simt<T>(g, in, wp, ep, out, st);
   }
 };

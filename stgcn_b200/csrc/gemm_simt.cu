@@ -192,24 +192,26 @@ template int32_t launch_wgrad_simt<bf16>(const ConvGeom&, const bf16*, const bf1
 // ---------------------------------------------------------------------------
 template <class TD>
 __global__ void __launch_bounds__(256) pack_weights_kernel(const float* __restrict__ src, WIndex wi, int taps, int n_out, int c,
-                                                           TD* __restrict__ dst) {
+                                                           int round_bf16, TD* __restrict__ dst) {
   size_t total = (size_t)taps * n_out * c;
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
     int cc = (int)(i % c); size_t r = i / c; int n = (int)(r % n_out); int tap = (int)(r / n_out);
-    stf(dst + i, src[wi.at(tap, n, cc)]);
+    float wv = src[wi.at(tap, n, cc)];
+    if (round_bf16) wv = __bfloat162float(__float2bfloat16_rn(wv));   // bf16 mode: every GEMM operand is bf16-valued
+    stf(dst + i, wv);
   }
 }
 template <class TD>
-int32_t launch_pack_weights(const float* src, const WIndex& wi, int taps, int n_out, int c, TD* dst, cudaStream_t st) {
+int32_t launch_pack_weights(const float* src, const WIndex& wi, int taps, int n_out, int c, TD* dst, cudaStream_t st, int round_bf16) {
   KernelTimer kt_(KC_PACK, 0.0, st);
   size_t total = (size_t)taps * n_out * c;
   int blocks = (int)std::min<size_t>((total + 255) / 256, 148 * 4);
-  pack_weights_kernel<TD><<<blocks, 256, 0, st>>>(src, wi, taps, n_out, c, dst);
+  pack_weights_kernel<TD><<<blocks, 256, 0, st>>>(src, wi, taps, n_out, c, round_bf16, dst);
   STGCN_CHECK_LAUNCH("pack_weights");
   return STGCN_OK;
 }
-template int32_t launch_pack_weights<float>(const float*, const WIndex&, int, int, int, float*, cudaStream_t);
-template int32_t launch_pack_weights<bf16>(const float*, const WIndex&, int, int, int, bf16*, cudaStream_t);
+template int32_t launch_pack_weights<float>(const float*, const WIndex&, int, int, int, float*, cudaStream_t, int);
+template int32_t launch_pack_weights<bf16>(const float*, const WIndex&, int, int, int, bf16*, cudaStream_t, int);
 
 // column sums (bias gradients): out[c] = scale * sum_r x[r][c], via the stats partials
 __global__ void colsum_finalize_kernel(const float* __restrict__ partials, int nblk, int C, float* __restrict__ out) {

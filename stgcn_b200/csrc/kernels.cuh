@@ -77,7 +77,8 @@ int32_t launch_spatial_bias_grads(const float* t1, const float* A, const float* 
 template <class T> int32_t launch_conv_gemm_simt(const ConvGeom& g, const T* in, const float* w, const GemmEpilogue& ep, T* out,
                                                 cudaStream_t st);
 template <class T> int32_t launch_wgrad_simt(const ConvGeom& g, const T* dout, const T* in, const WIndex& wi, float* dw, cudaStream_t st);
-template <class TD> int32_t launch_pack_weights(const float* src, const WIndex& wi, int taps, int n_out, int c, TD* dst, cudaStream_t st);
+template <class TD> int32_t launch_pack_weights(const float* src, const WIndex& wi, int taps, int n_out, int c, TD* dst, cudaStream_t st,
+                                                int round_bf16 = 0);
 template <class T> int32_t launch_colsum(const T* x, long long rows, int C, float* partials, float* out, cudaStream_t st);
 
 // umma_gemm.cu  (tcgen05 / TMA engine, bf16)

