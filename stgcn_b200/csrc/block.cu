@@ -86,6 +86,18 @@ template <class T> struct Engine {
     STGCN_TRY(launch_pack_weights<float>(wsrc, wi, g.taps, g.n_out, g.c, wp, st, std::is_same<T, bf16>::value ? 1 : 0));
     return launch_conv_gemm_simt<T>(g, in, wp, ep, out, st);
   }
+  // dw (reference layout, overwritten) = sum over rows of dout (x) in
+  int32_t wgrad(const ConvGeom& g, const T* dout, const T* in, const WIndex& wi, float* dw, size_t dw_floats) {
+    if (want_umma() && umma_wgrad_supported(g) && (g.n_out == 64 || g.n_out % 128 == 0)) {
+      float* packed = ws.template get<float>(umma_wgrad_workspace_floats(g));
+      if (ws.dry) return STGCN_OK;
+      if (!ws.ok()) { set_error("workspace too small"); return STGCN_ERR_WORKSPACE; }
+      return launch_wgrad_umma(g, reinterpret_cast<const bf16*>(dout), reinterpret_cast<const bf16*>(in), wi, packed, dw, st);
+    }
+    if (ws.dry) return STGCN_OK;
+    cudaMemsetAsync(dw, 0, sizeof(float) * dw_floats, st);
+    return launch_wgrad_simt<T>(g, dout, in, wi, dw, st);
+  }
 };
 
 static ConvGeom geom(int nb, int t_in, int t_out, int v, int c, int n_out, int taps, int stride, int pad, int dgrad) {
@@ -129,13 +141,12 @@ static int32_t spatial_bwd(Engine<T>& e, const Dims& m, const T* x, const float*
   if (!ws.dry) {
     if (!ws.ok()) return STGCN_ERR_WORKSPACE;
     STGCN_TRY(launch_agg_fwd<T>(x, m.frames_in, m.v, m.ci, m.k, A, aff_a, aff_b, relu1, XA, e.st));
-    cudaMemsetAsync(dW, 0, sizeof(float) * (size_t)m.k * m.co * m.ci, e.st);
     cudaMemsetAsync(dA, 0, sizeof(float) * (size_t)m.k * m.v * m.v, e.st);
     cudaMemsetAsync(t1, 0, sizeof(float) * (size_t)m.v * m.co, e.st);
-    ConvGeom gw = geom(m.n, m.t, m.t, m.v, KCi, m.co, 1, 1, 0, 0);
-    STGCN_TRY(launch_wgrad_simt<T>(gw, dS, XA, widx(kNoDiv, 0, m.ci, m.ci, (long long)m.co * m.ci, 1, 0), dW, e.st));
     STGCN_TRY(launch_vcolsum<T>(dS, m.frames_in, m.v, m.co, t1, e.st));
   }
+  STGCN_TRY(e.wgrad(geom(m.n, m.t, m.t, m.v, KCi, m.co, 1, 1, 0, 0), dS, XA, widx(kNoDiv, 0, m.ci, m.ci, (long long)m.co * m.ci, 1, 0),
+                    dW, (size_t)m.k * m.co * m.ci));
   // dXA = dS . W2 : packed [n=k*Ci+ci][c=co] = W[(k*Co+co)*Ci+ci]
   GemmEpilogue ep;
   WIndex wiT = widx(m.ci, (long long)m.co * m.ci, 1, kNoDiv, 0, m.ci, 0);
@@ -262,10 +273,9 @@ static int32_t block_backward_t(const StgcnBlockDesc& d, const T* x, const T* y,
       STGCN_TRY(launch_affine_act<T>(S.S, m.rows_in, m.co, S.stats2 + 2 * m.co, S.stats2 + 3 * m.co, 1, 0.f, 0, 0, P2, st));
       tin = P2;
     }
-    cudaMemsetAsync(G.Wt, 0, sizeof(float) * (size_t)m.co * m.co * m.gamma, st);
-    STGCN_TRY(launch_wgrad_simt<T>(geom(m.n, m.t, m.to, m.v, m.co, m.co, m.gamma, m.stride, m.pad, 0), dU, tin,
-                                   widx(kNoDiv, 0, (long long)m.co * m.gamma, kNoDiv, 0, m.gamma, 1), G.Wt, st));
   }
+  STGCN_TRY(e.wgrad(geom(m.n, m.t, m.to, m.v, m.co, m.co, m.gamma, m.stride, m.pad, 0), dU, tin,
+                    widx(kNoDiv, 0, (long long)m.co * m.gamma, kNoDiv, 0, m.gamma, 1), G.Wt, (size_t)m.co * m.co * m.gamma));
   // temporal dgrad: packed [tap][n=ci][c=co] = Wt[(co*Co+ci)*gamma + tap]
   {
     GemmEpilogue ep;
@@ -286,12 +296,9 @@ static int32_t block_backward_t(const StgcnBlockDesc& d, const T* x, const T* y,
   if (d.residual == STGCN_RES_IDENTITY) {
     if (!ws.dry && dx) STGCN_TRY(launch_add_inplace<T>(dx, dU, (size_t)m.rows_in * m.ci, st));
   } else if (d.residual == STGCN_RES_CONV) {
-    if (!ws.dry) {
-      cudaMemsetAsync(G.Wr, 0, sizeof(float) * (size_t)m.co * m.ci, st);
-      STGCN_TRY(launch_wgrad_simt<T>(geom(m.n, m.t, m.to, m.v, m.ci, m.co, 1, m.stride, 0, 0), dU, x,
-                                     widx(kNoDiv, 0, m.ci, kNoDiv, 0, 1, 0), G.Wr, st));
-      cudaMemcpyAsync(G.Wr_bias, G.Wt_bias, sizeof(float) * m.co, cudaMemcpyDeviceToDevice, st);
-    }
+    STGCN_TRY(e.wgrad(geom(m.n, m.t, m.to, m.v, m.ci, m.co, 1, m.stride, 0, 0), dU, x, widx(kNoDiv, 0, m.ci, kNoDiv, 0, 1, 0), G.Wr,
+                      (size_t)m.co * m.ci));
+    if (!ws.dry) cudaMemcpyAsync(G.Wr_bias, G.Wt_bias, sizeof(float) * m.co, cudaMemcpyDeviceToDevice, st);
     if (dx) {
       GemmEpilogue ep; ep.accumulate = 1;
       STGCN_TRY(e.gemm(geom(m.n, m.to, m.t, m.v, m.co, m.ci, 1, m.stride, 0, 1), dU, P.Wr, widx(kNoDiv, 0, 1, kNoDiv, 0, m.ci, 0), ep, dx));

@@ -85,6 +85,12 @@ template <class T> int32_t launch_colsum(const T* x, long long rows, int C, floa
 bool umma_conv_gemm_supported(const ConvGeom& g);
 int32_t launch_conv_gemm_umma(const ConvGeom& g, const bf16* in, const bf16* w, const GemmEpilogue& ep, bf16* out, cudaStream_t st);
 
+// umma_wgrad.cu  (tcgen05 weight gradient, bf16, MN-major operands)
+bool umma_wgrad_supported(const ConvGeom& g);
+size_t umma_wgrad_workspace_floats(const ConvGeom& g);
+int32_t launch_wgrad_umma(const ConvGeom& g, const bf16* dout, const bf16* in, const WIndex& wi, float* packed_ws, float* dw,
+                          cudaStream_t st);
+
 // head_kernels.cu
 int32_t head_forward(int dtype, int n, int t, int v, int c, int classes, const void* feat, const float* fcw, const float* fcb,
                      float* pooled, float* logits, cudaStream_t st);

@@ -1,0 +1,278 @@
+// tcgen05 weight-gradient kernel (bf16 operands, fp32 accumulation in TMEM):
+//
+//     dw[tap][n][c] = sum_r dout[r][n] * in[row(r,tap)][c]
+//
+// for the temporal convolution (9 taps, stride 1|2; autograd of nn.Conv2d at
+// st_graphconv.py:41-43), the 1x1 channel mixing (:136) and the residual 1x1 conv (:28).
+// The reduction runs over rows = (sample, frame, joint), so BOTH operands are MN-major:
+// their shared-memory tiles are [rows][64 channels] exactly as TMA delivers them.
+//
+// One work item = (n-tile of 128 output channels, c-tile, tap group, split of the row range).
+// Per reduction step the CTA TMA-loads FJ whole frames of dout (FJ*V <= 128 rows, the
+// unused rows stay zero from a one-time shared-memory clear) and ONE slab of
+// FJ + span frames of the input; every tap of the group reads that slab through a
+// descriptor whose start address is shifted by (tap offset)*V rows (validated on hardware
+// by tests/test_gpu_umma.py: the 128B swizzle is a function of the absolute address).
+// Each tap owns its own accumulator columns in TMEM; at the end of the item the epilogue
+// warps add the tile into a packed fp32 buffer with red.global.add.
+#include "kernels.cuh"
+#include "umma_common.cuh"
+
+namespace stgcn {
+using namespace umma;
+
+constexpr int kWgThreads = 192;
+constexpr int kWgMaxGroups = 8;
+constexpr int kWgMaxTapsPerGroup = 8;
+constexpr int kMaxSlabRows = 232;              // 4*25 + 128 = 228 -> multiple of 8
+constexpr int kATile = 128 * 128;              // 128 rows x 64 ch bf16
+
+struct WgGroup { int ntaps; int parity; int h_min; int w_tap[kWgMaxTapsPerGroup]; int row_off[kWgMaxTapsPerGroup]; };
+
+struct WgParams {
+  int nb, v, fj, jblocks;            // frames per reduction step, steps per sample
+  int n_out, c, n_tiles, c_tiles, c_tile, n_slabs;   // n_slabs: 64-wide slabs of dout per tile (1 or 2)
+  int ngroups, splits, kblocks_total, total_items;
+  int stages;
+  uint32_t tmem_cols, a_bytes, b_bytes;
+  int b_slab;                        // bytes of one 64-channel input slab (rows * 128, rows % 8 == 0)
+  WgGroup groups[kWgMaxGroups];
+  float* packed;                     // [taps][n_out][c] fp32, zeroed by the host
+};
+
+__global__ void __launch_bounds__(kWgThreads, 1)
+wgrad_umma_kernel(const __grid_constant__ CUtensorMap map_dout, const __grid_constant__ CUtensorMap map_in,
+                  const __grid_constant__ WgParams p) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  const int a_stage = p.n_slabs * kATile;
+  const int b_stage = (p.c_tile / 64) * p.b_slab;
+  uint8_t* smem_a = smem;
+  uint8_t* smem_b = smem_a + (size_t)p.stages * a_stage;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem_b + (size_t)p.stages * b_stage);
+  uint64_t* empty_bar = full_bar + p.stages;
+  uint64_t* tfull_bar = empty_bar + p.stages;
+  uint64_t* tempty_bar = tfull_bar + 1;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 1);
+  const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
+
+  // one-time clear: rows TMA never writes (tile padding) must read as zero, never as NaN bit patterns
+  {
+    uint4* z = reinterpret_cast<uint4*>(smem);
+    const int n16 = (int)(((size_t)p.stages * (a_stage + b_stage)) / 16);
+    for (int i = threadIdx.x; i < n16; i += kWgThreads) z[i] = make_uint4(0, 0, 0, 0);
+  }
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&map_dout); prefetch_tmap(&map_in);
+    for (int s = 0; s < p.stages; ++s) { mbar_init(full_bar + s, 1); mbar_init(empty_bar + s, 1); }
+    mbar_init(tfull_bar, 1); mbar_init(tempty_bar, 128);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, p.tmem_cols);
+  fence_proxy_async_smem();          // the generic-proxy zero fill must be ordered before TMA writes
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  // item -> (n_t, c_t, group, split)
+  auto decode = [&](int item, int& n_t, int& c_t, int& g, int& kb0, int& kb1) {
+    n_t = item % p.n_tiles; item /= p.n_tiles;
+    c_t = item % p.c_tiles; item /= p.c_tiles;
+    g = item % p.ngroups; item /= p.ngroups;
+    const int per = (p.kblocks_total + p.splits - 1) / p.splits;
+    kb0 = item * per; kb1 = min(p.kblocks_total, kb0 + per);
+  };
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int stage = 0; uint32_t phase = 0;
+      for (int item = blockIdx.x; item < p.total_items; item += gridDim.x) {
+        int n_t, c_t, g, kb0, kb1; decode(item, n_t, c_t, g, kb0, kb1);
+        const WgGroup& G = p.groups[g];
+        for (int kb = kb0; kb < kb1; ++kb) {
+          const int b = kb / p.jblocks, j0 = (kb % p.jblocks) * p.fj;
+          mbar_wait(empty_bar + stage, phase ^ 1);
+          mbar_expect_tx(full_bar + stage, p.a_bytes + p.b_bytes);
+          for (int s = 0; s < p.n_slabs; ++s)
+            tma_load_5d(&map_dout, smem_a + (size_t)stage * a_stage + s * kATile, full_bar + stage, n_t * 128 + s * 64, 0, 0, j0, b);
+          for (int s = 0; s < p.c_tile / 64; ++s)
+            tma_load_5d(&map_in, smem_b + (size_t)stage * b_stage + s * p.b_slab, full_bar + stage, c_t * p.c_tile + s * 64, 0,
+                        G.parity, j0 + G.h_min, b);
+          if (++stage == p.stages) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      const uint32_t idesc = make_idesc_bf16(128, p.c_tile, 1, 1);
+      const uint32_t a_lbo = p.n_slabs == 2 ? (uint32_t)kATile : 0u;   // one slab: rows 64..127 alias rows 0..63 (ignored)
+      int stage = 0; uint32_t phase = 0; uint32_t tphase = 0;
+      for (int item = blockIdx.x; item < p.total_items; item += gridDim.x) {
+        int n_t, c_t, g, kb0, kb1; decode(item, n_t, c_t, g, kb0, kb1);
+        const WgGroup& G = p.groups[g];
+        mbar_wait(tempty_bar, tphase ^ 1);
+        tc_fence_after();
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(full_bar + stage, phase);
+          tc_fence_after();
+          const uint32_t a_addr = smem_u32(smem_a + (size_t)stage * a_stage);
+          const uint32_t b_addr = smem_u32(smem_b + (size_t)stage * b_stage);
+          for (int t = 0; t < G.ntaps; ++t) {
+            const uint64_t ad = make_smem_desc_sw128(a_addr, a_lbo, 1024);
+            const uint64_t bd = make_smem_desc_sw128(b_addr + (uint32_t)G.row_off[t] * 128u, (uint32_t)p.b_slab, 1024);
+#pragma unroll
+            for (int k = 0; k < 8; ++k)          // 8 x 16 rows of the 128-row reduction step (2048 B each)
+              umma_bf16_ss(tmem_base + (uint32_t)(t * p.c_tile), ad + (uint64_t)(k * 128), bd + (uint64_t)(k * 128), idesc,
+                           (kb > kb0 || k > 0) ? 1u : 0u);
+          }
+          umma_commit(empty_bar + stage);
+          if (++stage == p.stages) { stage = 0; phase ^= 1; }
+        }
+        umma_commit(tfull_bar);
+        tphase ^= 1;
+      }
+    }
+  } else {
+    const int q = warp % 4;
+    const int row = q * 32 + lane;               // accumulator row = output channel inside the n-tile
+    uint32_t tphase = 0;
+    for (int item = blockIdx.x; item < p.total_items; item += gridDim.x) {
+      int n_t, c_t, g, kb0, kb1; decode(item, n_t, c_t, g, kb0, kb1);
+      const WgGroup& G = p.groups[g];
+      mbar_wait(tfull_bar, tphase);
+      tc_fence_after();
+      const int n = n_t * 128 + row;
+      const bool n_ok = row < p.n_slabs * 64 && n < p.n_out && kb1 > kb0;
+      for (int t = 0; t < G.ntaps; ++t) {
+        float* dst = p.packed + ((size_t)G.w_tap[t] * p.n_out + n) * p.c + (size_t)c_t * p.c_tile;
+        for (int cc = 0; cc < p.c_tile; cc += 32) {
+          uint32_t r[32];
+          tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(t * p.c_tile + cc), r);
+          tmem_ld_wait();
+          if (n_ok) {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) atomicAdd(dst + cc + i, __uint_as_float(r[i]));
+          }
+        }
+      }
+      tc_fence_before();
+      mbar_arrive(tempty_bar);
+      tphase ^= 1;
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) { tc_fence_after(); tmem_dealloc(tmem_base, p.tmem_cols); }
+}
+
+// packed [taps][n][c] -> the reference's parameter layout
+__global__ void __launch_bounds__(256) wgrad_unpack_kernel(const float* __restrict__ packed, WIndex wi, int taps, int n_out, int c,
+                                                           float* __restrict__ dw) {
+  size_t total = (size_t)taps * n_out * c;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    int cc = (int)(i % c); size_t r = i / c; int n = (int)(r % n_out); int tap = (int)(r / n_out);
+    dw[wi.at(tap, n, cc)] = packed[i];
+  }
+}
+
+bool umma_wgrad_supported(const ConvGeom& g) {
+  if (g.dgrad) return false;
+  if (g.c % 64 != 0 || g.n_out % 64 != 0) return false;
+  if (g.v < 1 || g.v > 32 || g.taps < 1 || g.taps > 15) return false;
+  if (g.stride < 1 || g.stride > 2 || g.t_in % g.stride != 0) return false;
+  return true;
+}
+
+size_t umma_wgrad_workspace_floats(const ConvGeom& g) { return (size_t)g.taps * g.n_out * g.c; }
+
+static int num_sms_wg() {
+  static int n = 0;
+  if (!n) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev); if (n <= 0) n = 148; }
+  return n;
+}
+
+int32_t launch_wgrad_umma(const ConvGeom& g, const bf16* dout, const bf16* in, const WIndex& wi, float* packed_ws, float* dw,
+                          cudaStream_t st) {
+  KernelTimer kt_(KC_UMMA_WGRAD, 2.0 * g.nb * g.t_out * g.v * (double)g.c * g.n_out * g.taps, st);
+  if (!umma_wgrad_supported(g)) { set_error("umma wgrad: unsupported geometry"); return STGCN_ERR_UNSUPPORTED; }
+  WgParams p; memset(&p, 0, sizeof(p));
+  const int s = g.stride;
+  p.nb = g.nb; p.v = g.v; p.fj = 128 / g.v; p.jblocks = cdiv(g.t_out, p.fj);
+  p.n_out = g.n_out; p.c = g.c;
+  p.n_tiles = cdiv(g.n_out, 128); p.n_slabs = g.n_out >= 128 ? 2 : 1;
+  if (g.n_out % 128 != 0 && g.n_out > 64) { set_error("umma wgrad: n_out must be 64 or a multiple of 128"); return STGCN_ERR_UNSUPPORTED; }
+  // tap groups: same input parity, consecutive frame offsets, at most `tg_max` taps (TMEM: taps*c_tile <= 512 columns)
+  if (g.taps == 1) p.c_tile = g.c % 256 == 0 ? 256 : (g.c % 192 == 0 ? 192 : (g.c % 128 == 0 ? 128 : 64));
+  else p.c_tile = g.c == 64 ? 64 : 128;
+  p.c_tiles = g.c / p.c_tile;
+  const int tg_max = std::min(kWgMaxTapsPerGroup, 512 / p.c_tile);
+  int span_max = 0;
+  p.ngroups = 0;
+  for (int par = 0; par < s; ++par) {
+    int taps_p[16], hoff_p[16], np = 0;
+    for (int tap = 0; tap < g.taps; ++tap) {
+      int d = tap - g.pad; int r = ((d % s) + s) % s;
+      if (r == par) { taps_p[np] = tap; hoff_p[np] = (d - r) / s; ++np; }
+    }
+    if (!np) continue;
+    int ng = cdiv(np, tg_max), per = cdiv(np, ng);
+    for (int i0 = 0; i0 < np; i0 += per) {
+      if (p.ngroups >= kWgMaxGroups) { set_error("umma wgrad: too many tap groups"); return STGCN_ERR_UNSUPPORTED; }
+      WgGroup& G = p.groups[p.ngroups++];
+      G.ntaps = std::min(per, np - i0); G.parity = par; G.h_min = hoff_p[i0];
+      for (int i = 0; i < G.ntaps; ++i) { G.w_tap[i] = taps_p[i0 + i]; G.row_off[i] = (hoff_p[i0 + i] - G.h_min) * g.v; }
+      span_max = std::max(span_max, hoff_p[i0 + G.ntaps - 1] - G.h_min);
+    }
+  }
+  const int slab_rows = (span_max * g.v + 128 + 7) / 8 * 8;      // every tap reads 128 rows starting at its row offset
+  if (slab_rows > kMaxSlabRows) { set_error("umma wgrad: slab too large"); return STGCN_ERR_UNSUPPORTED; }
+  p.b_slab = slab_rows * 128;
+  p.kblocks_total = g.nb * p.jblocks;
+  const int base_items = p.n_tiles * p.c_tiles * p.ngroups;
+  p.splits = std::max(1, std::min(p.kblocks_total, (2 * num_sms_wg() + base_items - 1) / base_items));
+  p.total_items = base_items * p.splits;
+  p.a_bytes = (uint32_t)(p.n_slabs * p.fj * g.v * 128);
+  p.b_bytes = (uint32_t)((p.c_tile / 64) * (p.fj + span_max) * g.v * 128);
+  const size_t stage_bytes = (size_t)p.n_slabs * kATile + (size_t)(p.c_tile / 64) * p.b_slab;
+  int stages = (int)((220 * 1024 - 2048) / stage_bytes);
+  if (stages > 4) stages = 4;
+  if (stages < 2) { set_error("umma wgrad: not enough shared memory"); return STGCN_ERR_UNSUPPORTED; }
+  p.stages = stages;
+  int maxt = 0; for (int i = 0; i < p.ngroups; ++i) maxt = std::max(maxt, p.groups[i].ntaps);
+  uint32_t cols = 32; while (cols < (uint32_t)(maxt * p.c_tile)) cols <<= 1;
+  p.tmem_cols = cols;
+  p.packed = packed_ws;
+  cudaMemsetAsync(packed_ws, 0, sizeof(float) * umma_wgrad_workspace_floats(g), st);
+
+  CUtensorMap map_dout, map_in;
+  const uint64_t C = g.c, V = g.v, N = g.n_out;
+  {
+    uint64_t dims[5] = {N, V, 1, (uint64_t)g.t_out, (uint64_t)g.nb};
+    uint64_t str[4] = {N * 2, V * N * 2, V * N * 2, (uint64_t)g.t_out * V * N * 2};
+    uint32_t box[5] = {64, (uint32_t)g.v, 1, (uint32_t)p.fj, 1};
+    STGCN_TRY(make_tmap_bf16(&map_dout, dout, 5, dims, str, box));
+  }
+  {
+    uint64_t dims[5] = {C, V, (uint64_t)s, (uint64_t)g.t_in / s, (uint64_t)g.nb};
+    uint64_t str[4] = {C * 2, V * C * 2, (uint64_t)s * V * C * 2, (uint64_t)g.t_in * V * C * 2};
+    uint32_t box[5] = {64, (uint32_t)g.v, 1, (uint32_t)(p.fj + span_max), 1};
+    STGCN_TRY(make_tmap_bf16(&map_in, in, 5, dims, str, box));
+  }
+  const size_t smem = (size_t)stages * stage_bytes + 2048;
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(wgrad_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    if (e != cudaSuccess) { set_error("cudaFuncSetAttribute(smem) failed: %s", cudaGetErrorString(e)); return STGCN_ERR_CUDA; }
+    attr_set = true;
+  }
+  const int grid = std::min(p.total_items, num_sms_wg());
+  wgrad_umma_kernel<<<grid, kWgThreads, smem, st>>>(map_dout, map_in, p);
+  STGCN_CHECK_LAUNCH("wgrad_umma");
+  size_t total = umma_wgrad_workspace_floats(g);
+  wgrad_unpack_kernel<<<(int)std::min<size_t>((total + 255) / 256, 148 * 4), 256, 0, st>>>(packed_ws, wi, g.taps, g.n_out, g.c, dw);
+  STGCN_CHECK_LAUNCH("wgrad_unpack");
+  return STGCN_OK;
+}
+
+}  // namespace stgcn
