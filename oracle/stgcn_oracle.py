@@ -404,7 +404,7 @@ def _bn_coeffs(x, gamma, beta, rm, rv, training, update_running, eps=BN_EPS, mom
     return a, beta - a * mean
 
 
-def block_forward_bf16(x, p, cfg: BlockCfg, training: bool, update_running=True, keep_u=True):
+def block_forward_bf16(x, p, cfg: BlockCfg, training: bool, update_running=True, keep_u=True, round_A=None):
     """`block_forward` with bf16 storage emulation at the CUDA chain's tensor boundaries
     (x, XA, S, [P2], U, R, y and their gradients; GEMM weights rounded to bf16).
     keep_u=False models the fused inference epilogue where U is never stored."""
@@ -417,7 +417,18 @@ def block_forward_bf16(x, p, cfg: BlockCfg, training: bool, update_running=True,
     h = x * a1[None, :, None, None] + b1[None, :, None, None]
     if cfg.residual:
         h = torch.relu(h)
-    xa = _q(torch.einsum('kvw,nctw->nkctv', A, h))                      # aggregate on the C_in side
+    if round_A is None:
+        round_A = cfg.c_in % 64 == 0             # the tensor-core aggregation (C_in % 64 == 0) takes A as a bf16 operand
+    if round_A:
+        Aq = A + (_rb(A) - A).detach()           # forward rounding only: dA stays an fp32 accumulation
+        if cfg.residual:
+            h = _q(h)                            # a ReLU between BN-1 and the aggregation: h is stored in bf16
+            xa = _q(torch.einsum('kvw,nctw->nkctv', Aq, h))
+        else:                                    # BN-1 affine applied in the epilogue to the aggregated raw input
+            xa = _q(torch.einsum('kvw,nctw->nkctv', Aq, x) * a1[None, None, :, None, None]
+                    + (b1[None, :, None] * Aq.sum(dim=2)[:, None, :])[None, :, :, None, :])
+    else:
+        xa = _q(torch.einsum('kvw,nctw->nkctv', A, h))                  # aggregate on the C_in side
     Wk = _q(p['spatialConv.W.weight'].reshape(K, Co, Ci))
     bias2d = torch.einsum('ko,kv->ov', p['spatialConv.W.bias'].reshape(K, Co), A.sum(dim=2))
     s = _q(torch.einsum('koc,nkctv->notv', Wk, xa) + bias2d[None, :, None, :])

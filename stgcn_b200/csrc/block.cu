@@ -118,7 +118,26 @@ static int32_t spatial_fwd(Engine<T>& e, const Dims& m, const T* x, const float*
   Arena& ws = e.ws;
   T* XA = ws.template get<T>(m.rows_in * m.k * m.ci);
   float* b2d = ws.template get<float>((size_t)m.v * m.co);
-  if (!ws.dry) {
+  bool tc_agg = false;
+  if constexpr (std::is_same<T, bf16>::value) tc_agg = e.want_umma() && umma_agg_supported(m.v, m.ci, m.k);
+  if (tc_agg) {
+    // tensor-core aggregation: BN-1 affine rides in the epilogue; a ReLU in between (residual block) needs h stored
+    void* prep = ws.template get<uint8_t>(umma_agg_prep_bytes(m.k));
+    T* P1 = relu1 ? ws.template get<T>(m.rows_in * m.ci) : nullptr;
+    if (!ws.dry) {
+      if (!ws.ok()) return STGCN_ERR_WORKSPACE;
+      if constexpr (std::is_same<T, bf16>::value) {
+        STGCN_TRY(launch_build_big_adjacency(A, m.k, m.v, prep, e.st));
+        if (relu1) {
+          STGCN_TRY(launch_affine_act<T>(x, m.rows_in, m.ci, aff_a, aff_b, 1, 0.f, 0, 0, P1, e.st));
+          STGCN_TRY(launch_agg_fwd_umma(P1, m.n, m.t, m.v, m.ci, m.k, prep, nullptr, nullptr, XA, e.st));
+        } else {
+          STGCN_TRY(launch_agg_fwd_umma(x, m.n, m.t, m.v, m.ci, m.k, prep, aff_a, aff_b, XA, e.st));
+        }
+      }
+      STGCN_TRY(launch_bias2d(A, Wb, m.k, m.v, m.co, b2d, e.st));
+    }
+  } else if (!ws.dry) {
     if (!ws.ok()) return STGCN_ERR_WORKSPACE;
     STGCN_TRY(launch_agg_fwd<T>(x, m.frames_in, m.v, m.ci, m.k, A, aff_a, aff_b, relu1, XA, e.st));
     STGCN_TRY(launch_bias2d(A, Wb, m.k, m.v, m.co, b2d, e.st));
@@ -138,9 +157,24 @@ static int32_t spatial_bwd(Engine<T>& e, const Dims& m, const T* x, const float*
   T* XA = ws.template get<T>(m.rows_in * KCi);
   T* dXA = ws.template get<T>(m.rows_in * KCi);
   float* t1 = ws.template get<float>((size_t)m.v * m.co);
+  bool tc_agg = false;
+  if constexpr (std::is_same<T, bf16>::value) tc_agg = e.want_umma() && umma_agg_supported(m.v, m.ci, m.k);
+  void* prep = tc_agg ? ws.template get<uint8_t>(umma_agg_prep_bytes(m.k)) : nullptr;
+  // tensor-core path: h = act(a*x+b) is an MMA operand of the dA contraction, so it is materialised once
+  const bool need_h = tc_agg && (aff_a != nullptr || relu1);
+  T* hbuf = need_h ? ws.template get<T>(m.rows_in * m.ci) : nullptr;
+  const T* h = need_h ? hbuf : x;
   if (!ws.dry) {
     if (!ws.ok()) return STGCN_ERR_WORKSPACE;
-    STGCN_TRY(launch_agg_fwd<T>(x, m.frames_in, m.v, m.ci, m.k, A, aff_a, aff_b, relu1, XA, e.st));
+    if (tc_agg) {
+      if constexpr (std::is_same<T, bf16>::value) {
+        STGCN_TRY(launch_build_big_adjacency(A, m.k, m.v, prep, e.st));
+        if (need_h) STGCN_TRY(launch_affine_act<T>(x, m.rows_in, m.ci, aff_a, aff_b, relu1, 0.f, 0, 0, hbuf, e.st));
+        STGCN_TRY(launch_agg_fwd_umma(h, m.n, m.t, m.v, m.ci, m.k, prep, nullptr, nullptr, XA, e.st));
+      }
+    } else {
+      STGCN_TRY(launch_agg_fwd<T>(x, m.frames_in, m.v, m.ci, m.k, A, aff_a, aff_b, relu1, XA, e.st));
+    }
     cudaMemsetAsync(dA, 0, sizeof(float) * (size_t)m.k * m.v * m.v, e.st);
     cudaMemsetAsync(t1, 0, sizeof(float) * (size_t)m.v * m.co, e.st);
     STGCN_TRY(launch_vcolsum<T>(dS, m.frames_in, m.v, m.co, t1, e.st));
@@ -152,6 +186,14 @@ static int32_t spatial_bwd(Engine<T>& e, const Dims& m, const T* x, const float*
   WIndex wiT = widx(m.ci, (long long)m.co * m.ci, 1, kNoDiv, 0, m.ci, 0);
   STGCN_TRY(e.gemm(geom(m.n, m.t, m.t, m.v, m.co, KCi, 1, 1, 0, 0), dS, W, wiT, ep, dXA));
   if (ws.dry) return STGCN_OK;
+  if (tc_agg) {
+    if constexpr (std::is_same<T, bf16>::value) {
+      STGCN_TRY(launch_agg_dA_umma(dXA, h, m.n, m.t, m.v, m.ci, m.k, dA, e.st));
+      STGCN_TRY(launch_spatial_bias_grads(t1, A, Wb, m.k, m.v, m.co, dWb, dA, e.st));
+      if (dh) STGCN_TRY(launch_agg_bwd_umma(dXA, m.n, m.t, m.v, m.ci, m.k, prep, relu1 ? h : nullptr, dh, e.st));
+    }
+    return STGCN_OK;
+  }
   STGCN_TRY(launch_agg_dA<T>(dXA, x, m.frames_in, m.v, m.ci, m.k, aff_a, aff_b, relu1, dA, e.st));
   STGCN_TRY(launch_spatial_bias_grads(t1, A, Wb, m.k, m.v, m.co, dWb, dA, e.st));
   if (dh) STGCN_TRY(launch_agg_bwd<T>(dXA, m.frames_in, m.v, m.ci, m.k, A, x, aff_a, aff_b, relu1, dh, e.st));

@@ -91,6 +91,16 @@ size_t umma_wgrad_workspace_floats(const ConvGeom& g);
 int32_t launch_wgrad_umma(const ConvGeom& g, const bf16* dout, const bf16* in, const WIndex& wi, float* packed_ws, float* dw,
                           cudaStream_t st);
 
+// umma_agg.cu  (tensor-core adjacency aggregation, bf16)
+bool umma_agg_supported(int V, int C, int K);
+size_t umma_agg_prep_bytes(int K);
+int32_t launch_build_big_adjacency(const float* A, int K, int V, void* prep_mem, cudaStream_t st);
+int32_t launch_agg_fwd_umma(const bf16* x, int nb, int t, int v, int c, int k, const void* prep, const float* aff_a,
+                            const float* aff_b, bf16* xa, cudaStream_t st);
+int32_t launch_agg_bwd_umma(const bf16* dxa, int nb, int t, int v, int c, int k, const void* prep, const bf16* mask_h, bf16* dh,
+                            cudaStream_t st);
+int32_t launch_agg_dA_umma(const bf16* dxa, const bf16* h, int nb, int t, int v, int c, int k, float* dA, cudaStream_t st);
+
 // head_kernels.cu
 int32_t head_forward(int dtype, int n, int t, int v, int c, int classes, const void* feat, const float* fcw, const float* fcb,
                      float* pooled, float* logits, cudaStream_t st);

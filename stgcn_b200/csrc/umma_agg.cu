@@ -1,0 +1,445 @@
+// K-partition adjacency aggregation on tcgen05 tensor cores.
+//
+// Reference: torch.einsum('kvw,nkctw->nctv', A, Z) at st_graphconv.py:150, applied on the
+// C_in side (aggregation and 1x1 channel mixing commute):
+//     XA[f, v, k*C + c] = sum_w A[k,v,w] * h[f, w, c]
+// A tile of FT whole frames (FT*V <= 128 rows) is aggregated with ONE dense MMA against a
+// block-diagonal 128x128 expansion of A_k that lives in shared memory for the whole kernel:
+//     XA_k tile [128 x C] = BigA_k [128 x 128] . h tile [128 x C]
+// so the V x V products of all frames of the tile run on the tensor pipe (the 5.1x zero
+// padding of the block-diagonal costs far less than CUDA-core FMAs: measured 9.6 ms -> see
+// profiles/).  The activation tile is the MMA's B operand in MN-major form, i.e. exactly the
+// [rows][64 channels] image TMA delivers; BigA_k is the K-major A operand.
+//
+//   agg_fwd : XA_k = a (.) (BigA_k . x) + b * rowsum_k      (BatchNorm-1 affine in the epilogue)
+//   agg_bwd : dh   = sum_k BigA_k^T . dXA_k                 (optionally masked by ReLU(h) > 0)
+//   agg_dA  : G_k += dXA_k tile . h tile^T  accumulated in TMEM over all tiles of the CTA;
+//             dA[k] = sum of the FT diagonal V x V blocks of G_k
+#include "kernels.cuh"
+#include "umma_common.cuh"
+
+namespace stgcn {
+using namespace umma;
+
+constexpr int kAggUThreads = 192;
+constexpr int kTile16K = 128 * 128;     // one [128 rows][64 bf16] tile image
+
+// ---------------------------------------------------------------------------
+// block-diagonal expansions of A (bf16), their transposes, and row sums of the rounded A
+//   big [k][r][c]  : r = f*V+v, c = f*V+w  -> A[k][v][w]      (zero elsewhere)
+//   bigT[k][r][c]  : r = f*V+w, c = f*V+v  -> A[k][v][w]
+// ---------------------------------------------------------------------------
+__global__ void build_big_adjacency_kernel(const float* __restrict__ A, int K, int V, int FT, bf16* __restrict__ big,
+                                           bf16* __restrict__ bigT, float* __restrict__ rowsum) {
+  const int total = K * 128 * 128;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int c = i % 128, r = (i / 128) % 128, k = i / (128 * 128);
+    const int fr = r / V, fc = c / V;
+    float a = 0.f, at = 0.f;
+    if (fr == fc && fr < FT) {
+      a = A[(k * V + r % V) * V + c % V];
+      at = A[(k * V + c % V) * V + r % V];
+    }
+    big[i] = __float2bfloat16_rn(a);
+    bigT[i] = __float2bfloat16_rn(at);
+  }
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < K * V) {
+    float s = 0.f;
+    for (int w = 0; w < V; ++w) s += __bfloat162float(__float2bfloat16_rn(A[i * V + w]));
+    rowsum[i] = s;
+  }
+}
+
+size_t umma_agg_prep_bytes(int K) { return (size_t)K * 128 * 128 * 2 * 2 + 4096; }
+
+struct AggPrep { bf16* big; bf16* bigT; float* rowsum; };
+AggPrep carve_agg_prep(void* mem, int K) {
+  AggPrep a;
+  a.big = reinterpret_cast<bf16*>(mem);
+  a.bigT = a.big + (size_t)K * 128 * 128;
+  a.rowsum = reinterpret_cast<float*>(a.bigT + (size_t)K * 128 * 128);
+  return a;
+}
+
+int32_t launch_build_big_adjacency(const float* A, int K, int V, void* prep_mem, cudaStream_t st) {
+  KernelTimer kt_(KC_PACK, 0.0, st);
+  AggPrep a = carve_agg_prep(prep_mem, K);
+  build_big_adjacency_kernel<<<cdiv(K * 128 * 128, 256), 256, 0, st>>>(A, K, V, 128 / V, a.big, a.bigT, a.rowsum);
+  STGCN_CHECK_LAUNCH("build_big_adjacency");
+  return STGCN_OK;
+}
+
+bool umma_agg_supported(int V, int C, int K) { return C % 64 == 0 && C <= 1024 && V >= 4 && V <= 32 && K >= 1 && K <= 3; }
+
+static int num_sms_agg() {
+  static int n = 0;
+  if (!n) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev); if (n <= 0) n = 148; }
+  return n;
+}
+
+struct AggParams {
+  int nb, t, v, ft, c, k, nch;            // nch = channels per work item (64 or 128)
+  int c_chunks, m_tiles_per_b, total_items, stages;
+  uint32_t tmem_cols, tile_bytes;
+  int transpose;                           // 0: fwd (K outputs), 1: bwd (sum over k)
+  const float* aff_a; const float* aff_b;  // fwd epilogue affine (may be null)
+  const float* rowsum;                     // [K][V]
+  const bf16* mask_h;                      // bwd: zero where h <= 0 (may be null), layout [rows][c]
+};
+
+// smem: bigA (K x 32 KB) | stages x (nch/64 x 16 KB) | staging 2 x 16 KB | barriers
+__global__ void __launch_bounds__(kAggUThreads, 1)
+agg_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_constant__ CUtensorMap map_big,
+                const __grid_constant__ CUtensorMap map_out, const __grid_constant__ AggParams p) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  const int slabs = p.nch / 64;
+  const int stage_bytes = slabs * kTile16K;
+  uint8_t* smem_big = smem;                                          // [k][2 halves of 64 cols][128 rows x 128 B]
+  uint8_t* smem_x = smem_big + (size_t)p.k * 2 * kTile16K;
+  uint8_t* staging = smem_x + (size_t)p.stages * stage_bytes;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(staging + 2 * kTile16K);
+  uint64_t* empty_bar = full_bar + p.stages;
+  uint64_t* tfull_bar = empty_bar + p.stages;
+  uint64_t* tempty_bar = tfull_bar + 2;
+  uint64_t* big_bar = tempty_bar + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(big_bar + 1);
+  const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
+
+  {  // padding rows of the activation tiles must be finite (they meet BigA's zero columns)
+    uint4* z = reinterpret_cast<uint4*>(smem_x);
+    const int n16 = p.stages * stage_bytes / 16;
+    for (int i = threadIdx.x; i < n16; i += kAggUThreads) z[i] = make_uint4(0, 0, 0, 0);
+  }
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&map_in); prefetch_tmap(&map_big); prefetch_tmap(&map_out);
+    for (int s = 0; s < p.stages; ++s) { mbar_init(full_bar + s, 1); mbar_init(empty_bar + s, 1); }
+    for (int a = 0; a < 2; ++a) { mbar_init(tfull_bar + a, 1); mbar_init(tempty_bar + a, 128); }
+    mbar_init(big_bar, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, p.tmem_cols);
+  fence_proxy_async_smem();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  auto decode = [&](int item, int& cch, int& j0, int& b) {
+    cch = item % p.c_chunks; item /= p.c_chunks;
+    j0 = (item % p.m_tiles_per_b) * p.ft; b = item / p.m_tiles_per_b;
+  };
+  // forward: 1 load, K accumulations (K outputs).  transpose: K loads, 1 output.
+  const int loads_per_item = p.transpose ? p.k : 1;
+  const int outs_per_item = p.transpose ? 1 : p.k;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      mbar_expect_tx(big_bar, (uint32_t)(p.k * 2 * kTile16K));
+      for (int k = 0; k < p.k; ++k)
+        for (int h = 0; h < 2; ++h) tma_load_2d(&map_big, smem_big + (size_t)(k * 2 + h) * kTile16K, big_bar, h * 64, k * 128);
+      int stage = 0; uint32_t phase = 0;
+      for (int item = blockIdx.x; item < p.total_items; item += gridDim.x) {
+        int cch, j0, b; decode(item, cch, j0, b);
+        for (int l = 0; l < loads_per_item; ++l) {
+          mbar_wait(empty_bar + stage, phase ^ 1);
+          mbar_expect_tx(full_bar + stage, (uint32_t)slabs * p.tile_bytes);
+          const int col0 = (p.transpose ? l * p.c : 0) + cch * p.nch;
+          for (int s = 0; s < slabs; ++s)
+            tma_load_5d(&map_in, smem_x + (size_t)stage * stage_bytes + s * kTile16K, full_bar + stage, col0 + s * 64, 0, 0, j0, b);
+          if (++stage == p.stages) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      const uint32_t idesc = make_idesc_bf16(128, p.nch, 0, 1);     // A K-major (BigA), B MN-major (activation tile)
+      mbar_wait(big_bar, 0);
+      int stage = 0; uint32_t phase = 0; int as = 0; uint32_t aphase = 0;
+      for (int item = blockIdx.x; item < p.total_items; item += gridDim.x) {
+        if (p.transpose) { mbar_wait(tempty_bar + as, aphase ^ 1); tc_fence_after(); }
+        for (int k = 0; k < p.k; ++k) {
+          if (!p.transpose) { mbar_wait(tempty_bar + as, aphase ^ 1); tc_fence_after(); }
+          if (p.transpose || k == 0) { mbar_wait(full_bar + stage, phase); tc_fence_after(); }
+          const uint32_t x_addr = smem_u32(smem_x + (size_t)stage * stage_bytes);
+          const uint32_t d_tmem = tmem_base + (uint32_t)(as * p.nch);
+#pragma unroll
+          for (int kk = 0; kk < 8; ++kk) {         // reduction over the 128 tile rows, 16 per instruction
+            const uint64_t ad = make_smem_desc_sw128(smem_u32(smem_big + (size_t)(k * 2 + kk / 4) * kTile16K), 16, 1024) + (uint64_t)((kk % 4) * 2);
+            const uint64_t bd = make_smem_desc_sw128(x_addr, (uint32_t)kTile16K, 1024) + (uint64_t)(kk * 128);
+            umma_bf16_ss(d_tmem, ad, bd, idesc, (p.transpose ? (k | kk) : kk) != 0 ? 1u : 0u);
+          }
+          if (p.transpose || k == p.k - 1) { umma_commit(empty_bar + stage); if (++stage == p.stages) { stage = 0; phase ^= 1; } }
+          if (!p.transpose) { umma_commit(tfull_bar + as); if (++as == 2) { as = 0; aphase ^= 1; } }
+        }
+        if (p.transpose) { umma_commit(tfull_bar + as); if (++as == 2) { as = 0; aphase ^= 1; } }
+      }
+    }
+  } else {
+    const int q = warp % 4, row = q * 32 + lane, et = threadIdx.x - 64;
+    const int fl = row / p.v, vv = row % p.v;
+    const int c_out_total = p.transpose ? p.c : p.k * p.c;
+    int as = 0; uint32_t aphase = 0; int chunk_ctr = 0;
+    for (int item = blockIdx.x; item < p.total_items; item += gridDim.x) {
+      int cch, j0, b; decode(item, cch, j0, b);
+      const bool row_valid = row < p.ft * p.v && (j0 + fl) < p.t;
+      const long long grow = ((long long)b * p.t + j0 + fl) * p.v + vv;
+      for (int o = 0; o < outs_per_item; ++o) {
+        mbar_wait(tfull_bar + as, aphase);
+        tc_fence_after();
+        const float rs = (!p.transpose && p.aff_b && row_valid) ? p.rowsum[o * p.v + vv] : 0.f;
+        for (int ch = 0; ch < slabs; ++ch, ++chunk_ctr) {
+          uint8_t* stg = staging + (chunk_ctr & 1) * kTile16K;
+          if (chunk_ctr >= 2) {
+            if (et == 0) tma_store_wait_read<1>();
+            asm volatile("bar.sync 1, 128;" ::: "memory");
+          }
+#pragma unroll
+          for (int half = 0; half < 2; ++half) {
+            uint32_t r[32];
+            const int col0 = ch * 64 + half * 32;
+            tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * p.nch + col0), r);
+            tmem_ld_wait();
+            const int c0 = cch * p.nch + col0;          // channel of r[0]
+            float f[32];
+#pragma unroll
+            for (int i = 0; i < 32; ++i) f[i] = __uint_as_float(r[i]);
+            if (!p.transpose && p.aff_a) {
+#pragma unroll
+              for (int i = 0; i < 32; ++i) f[i] = fmaf(__ldg(p.aff_a + c0 + i), f[i], __ldg(p.aff_b + c0 + i) * rs);
+            }
+            if (p.transpose && p.mask_h && row_valid) {
+              const uint4* hp = reinterpret_cast<const uint4*>(p.mask_h + (size_t)grow * p.c + c0);
+#pragma unroll
+              for (int g = 0; g < 4; ++g) {
+                uint4 u = __ldg(hp + g);
+                const __nv_bfloat162* h2 = reinterpret_cast<const __nv_bfloat162*>(&u);
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                  if (!(__low2float(h2[e]) > 0.f)) f[g * 8 + 2 * e] = 0.f;
+                  if (!(__high2float(h2[e]) > 0.f)) f[g * 8 + 2 * e + 1] = 0.f;
+                }
+              }
+            }
+#pragma unroll
+            for (int g = 0; g < 4; ++g) {
+              uint4 u;
+              __nv_bfloat162 h0 = __floats2bfloat162_rn(f[g * 8 + 0], f[g * 8 + 1]);
+              __nv_bfloat162 h1 = __floats2bfloat162_rn(f[g * 8 + 2], f[g * 8 + 3]);
+              __nv_bfloat162 h2 = __floats2bfloat162_rn(f[g * 8 + 4], f[g * 8 + 5]);
+              __nv_bfloat162 h3 = __floats2bfloat162_rn(f[g * 8 + 6], f[g * 8 + 7]);
+              u.x = *reinterpret_cast<uint32_t*>(&h0); u.y = *reinterpret_cast<uint32_t*>(&h1);
+              u.z = *reinterpret_cast<uint32_t*>(&h2); u.w = *reinterpret_cast<uint32_t*>(&h3);
+              const int j = half * 4 + g;
+              *reinterpret_cast<uint4*>(stg + row * 128 + ((j ^ (row & 7)) << 4)) = u;
+            }
+          }
+          fence_proxy_async_smem();
+          asm volatile("bar.sync 2, 128;" ::: "memory");
+          if (et == 0) {
+            const int oc = (p.transpose ? 0 : o * p.c) + cch * p.nch + ch * 64;
+            tma_store_5d(&map_out, stg, oc, 0, 0, j0, b);
+            tma_store_commit();
+          }
+        }
+        tc_fence_before();
+        mbar_arrive(tempty_bar + as);
+        if (++as == 2) { as = 0; aphase ^= 1; }
+      }
+      (void)c_out_total;
+    }
+    if (et == 0) tma_store_wait<0>();
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) { tc_fence_after(); tmem_dealloc(tmem_base, p.tmem_cols); }
+}
+
+// ---------------------------------------------------------------------------
+// adjacency gradient: G_k[v'][w'] += sum_c dXA_k[v'][c] * h[w'][c] over all tiles of the CTA
+// (both operands K-major: channels are contiguous), accumulators stay in TMEM for the
+// whole kernel; the FT diagonal V x V blocks are folded into dA with atomics at the end.
+// ---------------------------------------------------------------------------
+struct DaParams {
+  int nb, t, v, ft, c, k, m_tiles_per_b, total_tiles, stages;
+  uint32_t tmem_cols, tile_bytes;
+  float* dA;
+};
+
+__global__ void __launch_bounds__(kAggUThreads, 1)
+agg_dA_umma_kernel(const __grid_constant__ CUtensorMap map_dxa, const __grid_constant__ CUtensorMap map_h,
+                   const __grid_constant__ DaParams p) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  const int stage_bytes = (p.k + 1) * kTile16K;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + (size_t)p.stages * stage_bytes);
+  uint64_t* empty_bar = full_bar + p.stages;
+  uint64_t* done_bar = empty_bar + p.stages;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(done_bar + 1);
+  const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&map_dxa); prefetch_tmap(&map_h);
+    for (int s = 0; s < p.stages; ++s) { mbar_init(full_bar + s, 1); mbar_init(empty_bar + s, 1); }
+    mbar_init(done_bar, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, p.tmem_cols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const int cbs = p.c / 64;
+  const bool have_work = (int)blockIdx.x < p.total_tiles;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int stage = 0; uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
+        const int j0 = (tile % p.m_tiles_per_b) * p.ft, b = tile / p.m_tiles_per_b;
+        for (int cb = 0; cb < cbs; ++cb) {
+          mbar_wait(empty_bar + stage, phase ^ 1);
+          mbar_expect_tx(full_bar + stage, (uint32_t)(p.k + 1) * p.tile_bytes);
+          uint8_t* sb = smem + (size_t)stage * stage_bytes;
+          for (int k = 0; k < p.k; ++k) tma_load_5d(&map_dxa, sb + k * kTile16K, full_bar + stage, k * p.c + cb * 64, 0, 0, j0, b);
+          tma_load_5d(&map_h, sb + p.k * kTile16K, full_bar + stage, cb * 64, 0, 0, j0, b);
+          if (++stage == p.stages) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      const uint32_t idesc = make_idesc_bf16(128, 128, 0, 0);
+      int stage = 0; uint32_t phase = 0; bool first = true;
+      for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
+        for (int cb = 0; cb < cbs; ++cb) {
+          mbar_wait(full_bar + stage, phase);
+          tc_fence_after();
+          const uint32_t sb = smem_u32(smem + (size_t)stage * stage_bytes);
+          const uint64_t hd = make_smem_desc_sw128(sb + (uint32_t)(p.k * kTile16K), 16, 1024);
+          for (int k = 0; k < p.k; ++k) {
+            const uint64_t ad = make_smem_desc_sw128(sb + (uint32_t)(k * kTile16K), 16, 1024);
+#pragma unroll
+            for (int kk = 0; kk < 4; ++kk)
+              umma_bf16_ss(tmem_base + (uint32_t)(k * 128), ad + (uint64_t)(kk * 2), hd + (uint64_t)(kk * 2), idesc, (!first || kk) ? 1u : 0u);
+          }
+          first = false;
+          umma_commit(empty_bar + stage);
+          if (++stage == p.stages) { stage = 0; phase ^= 1; }
+        }
+      }
+      umma_commit(done_bar);
+    }
+  } else {
+    const int q = warp % 4, row = q * 32 + lane;
+    const int fl = row / p.v, vv = row % p.v;
+    mbar_wait(done_bar, 0);
+    tc_fence_after();
+    for (int k = 0; k < p.k; ++k) {
+#pragma unroll
+      for (int chunk = 0; chunk < 4; ++chunk) {
+        uint32_t r[32];
+        tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(k * 128 + chunk * 32), r);
+        tmem_ld_wait();
+        if (have_work && row < p.ft * p.v) {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) {
+            const int w = chunk * 32 + i - fl * p.v;          // column inside this row's own frame block
+            if (w >= 0 && w < p.v) atomicAdd(p.dA + (k * p.v + vv) * p.v + w, __uint_as_float(r[i]));
+          }
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) { tc_fence_after(); tmem_dealloc(tmem_base, p.tmem_cols); }
+}
+
+// ---------------------------------------------------------------------------
+// host
+// ---------------------------------------------------------------------------
+static int32_t make_act_map(CUtensorMap* m, const bf16* base, int cols, int v, int t, int nb, int ft) {
+  uint64_t dims[5] = {(uint64_t)cols, (uint64_t)v, 1, (uint64_t)t, (uint64_t)nb};
+  uint64_t str[4] = {(uint64_t)cols * 2, (uint64_t)v * cols * 2, (uint64_t)v * cols * 2, (uint64_t)t * v * cols * 2};
+  uint32_t box[5] = {64, (uint32_t)v, 1, (uint32_t)ft, 1};
+  return make_tmap_bf16(m, base, 5, dims, str, box);
+}
+
+static int32_t launch_agg_common(int transpose, const bf16* in, int nb, int t, int v, int c, int k, const void* prep_mem,
+                                 const float* aff_a, const float* aff_b, const bf16* mask_h, bf16* out, cudaStream_t st) {
+  if (!umma_agg_supported(v, c, k)) { set_error("umma agg: unsupported shape V=%d C=%d K=%d", v, c, k); return STGCN_ERR_UNSUPPORTED; }
+  AggPrep prep = carve_agg_prep(const_cast<void*>(prep_mem), k);
+  AggParams p; memset(&p, 0, sizeof(p));
+  p.nb = nb; p.t = t; p.v = v; p.ft = 128 / v; p.c = c; p.k = k; p.transpose = transpose;
+  p.nch = c % 128 == 0 ? 128 : 64;
+  p.c_chunks = c / p.nch; p.m_tiles_per_b = cdiv(t, p.ft); p.total_items = p.c_chunks * p.m_tiles_per_b * nb;
+  p.tile_bytes = (uint32_t)(p.ft * v * 128);
+  p.aff_a = aff_a; p.aff_b = aff_b; p.rowsum = prep.rowsum; p.mask_h = mask_h;
+  const size_t stage_bytes = (size_t)(p.nch / 64) * kTile16K;
+  const size_t fixed = (size_t)k * 2 * kTile16K + 2 * kTile16K + 1024 + 512;
+  int stages = (int)((220 * 1024 - fixed) / stage_bytes);
+  if (stages > 4) stages = 4;
+  if (stages < 2) { set_error("umma agg: not enough shared memory"); return STGCN_ERR_UNSUPPORTED; }
+  p.stages = stages;
+  uint32_t cols = 32; while (cols < (uint32_t)(2 * p.nch)) cols <<= 1;
+  p.tmem_cols = cols;
+  CUtensorMap map_in, map_big, map_out;
+  STGCN_TRY(make_act_map(&map_in, in, transpose ? k * c : c, v, t, nb, p.ft));
+  STGCN_TRY(make_act_map(&map_out, out, transpose ? c : k * c, v, t, nb, p.ft));
+  {
+    uint64_t dims[2] = {128, (uint64_t)k * 128}; uint64_t str[1] = {256}; uint32_t box[2] = {64, 128};
+    STGCN_TRY(make_tmap_bf16(&map_big, transpose ? prep.bigT : prep.big, 2, dims, str, box));
+  }
+  const size_t smem = fixed + (size_t)stages * stage_bytes;
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(agg_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    if (e != cudaSuccess) { set_error("cudaFuncSetAttribute failed: %s", cudaGetErrorString(e)); return STGCN_ERR_CUDA; }
+    attr_set = true;
+  }
+  agg_umma_kernel<<<std::min(p.total_items, num_sms_agg()), kAggUThreads, smem, st>>>(map_in, map_big, map_out, p);
+  STGCN_CHECK_LAUNCH("agg_umma");
+  return STGCN_OK;
+}
+
+int32_t launch_agg_fwd_umma(const bf16* x, int nb, int t, int v, int c, int k, const void* prep, const float* aff_a,
+                            const float* aff_b, bf16* xa, cudaStream_t st) {
+  KernelTimer kt_(KC_AGG_FWD, 2.0 * nb * t * v * v * (double)k * c, st);
+  return launch_agg_common(0, x, nb, t, v, c, k, prep, aff_a, aff_b, nullptr, xa, st);
+}
+int32_t launch_agg_bwd_umma(const bf16* dxa, int nb, int t, int v, int c, int k, const void* prep, const bf16* mask_h, bf16* dh,
+                            cudaStream_t st) {
+  KernelTimer kt_(KC_AGG_BWD, 2.0 * nb * t * v * v * (double)k * c, st);
+  return launch_agg_common(1, dxa, nb, t, v, c, k, prep, nullptr, nullptr, mask_h, dh, st);
+}
+
+int32_t launch_agg_dA_umma(const bf16* dxa, const bf16* h, int nb, int t, int v, int c, int k, float* dA, cudaStream_t st) {
+  KernelTimer kt_(KC_AGG_DA, 2.0 * nb * t * v * v * (double)k * c, st);
+  if (!umma_agg_supported(v, c, k)) { set_error("umma dA: unsupported shape"); return STGCN_ERR_UNSUPPORTED; }
+  DaParams p; memset(&p, 0, sizeof(p));
+  p.nb = nb; p.t = t; p.v = v; p.ft = 128 / v; p.c = c; p.k = k;
+  p.m_tiles_per_b = cdiv(t, p.ft); p.total_tiles = p.m_tiles_per_b * nb;
+  p.tile_bytes = (uint32_t)(p.ft * v * 128);
+  const size_t stage_bytes = (size_t)(k + 1) * kTile16K;
+  int stages = (int)((220 * 1024 - 2048) / stage_bytes);
+  if (stages > 4) stages = 4;
+  p.stages = stages;
+  uint32_t cols = 32; while (cols < (uint32_t)(k * 128)) cols <<= 1;
+  p.tmem_cols = cols; p.dA = dA;
+  CUtensorMap map_dxa, map_h;
+  STGCN_TRY(make_act_map(&map_dxa, dxa, k * c, v, t, nb, p.ft));
+  STGCN_TRY(make_act_map(&map_h, h, c, v, t, nb, p.ft));
+  const size_t smem = (size_t)stages * stage_bytes + 2048;
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(agg_dA_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    if (e != cudaSuccess) { set_error("cudaFuncSetAttribute failed: %s", cudaGetErrorString(e)); return STGCN_ERR_CUDA; }
+    attr_set = true;
+  }
+  agg_dA_umma_kernel<<<std::min(p.total_tiles, num_sms_agg()), kAggUThreads, smem, st>>>(map_dxa, map_h, p);
+  STGCN_CHECK_LAUNCH("agg_dA_umma");
+  return STGCN_OK;
+}
+
+}  // namespace stgcn
