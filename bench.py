@@ -147,6 +147,7 @@ def main():
     ap.add_argument('--seqs-per-gpu', type=int, default=32)
     ap.add_argument('--dtype', default='bf16', choices=['bf16', 'f32'])
     ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--only-train', action='store_true', help='profiling aid: skip the e2e and inference legs')
     args = ap.parse_args()
     if args.impl == 'reference':
         return run_reference(args)
@@ -225,6 +226,13 @@ def main():
         hx, hy = host_batches[i % n_batches]
         xin.copy_(hx, non_blocking=True); yin.copy_(hy, non_blocking=True)
         return train_step(xin, yin).item()
+    if args.only_train:
+        if rank == 0:
+            print(json.dumps({'value': value, 'ms_per_step': ms_step, 'gpu_launches': launches,
+                              'kernel_ms_per_step': {k: round(v[0] / args.steps, 4) for k, v in prof.items()}}))
+        if world > 1:
+            dist.destroy_process_group()
+        return
     for i in range(2):
         e2e_step(i)
     ms_e2e = timed(e2e_step, args.steps) / args.steps
