@@ -251,63 +251,109 @@ __global__ void __launch_bounds__(256) vcolsum_kernel(const T* __restrict__ ds, 
   for (long long f = blockIdx.x; f < frames; f += gridDim.x) s += ldf(ds + f * VC + e);
   atomicAdd(t1 + e, s);
 }
+// vector form: one thread owns 4 consecutive (v,c) elements and strides over frames with 4 independent loads in flight
+template <class T>
+__global__ void __launch_bounds__(256) vcolsum4_kernel(const T* __restrict__ ds, long long frames, int VC, float* __restrict__ t1) {
+  const int e = (blockIdx.y * 256 + threadIdx.x) * 4;
+  if (e >= VC) return;
+  float s[4] = {0.f, 0.f, 0.f, 0.f};
+  const long long step = gridDim.x;
+  long long f = blockIdx.x;
+  for (; f + 3 * step < frames; f += 4 * step) {
+    float a[4], b[4], c[4], d[4];
+    ld4(ds + f * VC + e, a); ld4(ds + (f + step) * VC + e, b); ld4(ds + (f + 2 * step) * VC + e, c); ld4(ds + (f + 3 * step) * VC + e, d);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) s[i] += (a[i] + b[i]) + (c[i] + d[i]);
+  }
+  for (; f < frames; f += step) {
+    float a[4]; ld4(ds + f * VC + e, a);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) s[i] += a[i];
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) atomicAdd(t1 + e + i, s[i]);
+}
 template <class T>
 int32_t launch_vcolsum(const T* ds, long long frames, int V, int C, float* t1, cudaStream_t st) {
   KernelTimer kt_(KC_BN_STATS, 0.0, st);
   int VC = V * C;
-  dim3 grid((unsigned)std::min<long long>(frames, 64), (unsigned)cdiv(VC, 256));
-  vcolsum_kernel<T><<<grid, 256, 0, st>>>(ds, frames, VC, t1);
+  if (VC % 4 == 0) {
+    const int by = cdiv(VC / 4, 256);
+    const int bx = (int)std::max<long long>(1, std::min<long long>(frames / 8, (148 * 8 + by - 1) / by));
+    vcolsum4_kernel<T><<<dim3((unsigned)bx, (unsigned)by), 256, 0, st>>>(ds, frames, VC, t1);
+  } else {
+    dim3 grid((unsigned)std::min<long long>(frames, 64), (unsigned)cdiv(VC, 256));
+    vcolsum_kernel<T><<<grid, 256, 0, st>>>(ds, frames, VC, t1);
+  }
   STGCN_CHECK_LAUNCH("vcolsum");
   return STGCN_OK;
 }
 template int32_t launch_vcolsum<float>(const float*, long long, int, int, float*, cudaStream_t);
 template int32_t launch_vcolsum<bf16>(const bf16*, long long, int, int, float*, cudaStream_t);
 
+// row sums of A into shared memory: rs[k*V+v] = sum_w A[k,v,w]   (K*V <= 128 entries, one warp-sliced pass)
+__device__ __forceinline__ void adjacency_rowsums(const float* __restrict__ A, int K, int V, float* rs) {
+  for (int i = threadIdx.x; i < K * V; i += blockDim.x) {
+    float s = 0.f;
+    for (int w = 0; w < V; ++w) s += A[i * V + w];
+    rs[i] = s;
+  }
+  __syncthreads();
+}
+
 // bias2d[v][co] = sum_k rowsum_k[v] * bias[k*Co+co]   (bias of W passes through A, st_graphconv.py:148-150)
-__global__ void bias2d_kernel(const float* __restrict__ A, const float* __restrict__ bias, int K, int V, int Co,
-                              float* __restrict__ out) {
+__global__ void __launch_bounds__(256) bias2d_kernel(const float* __restrict__ A, const float* __restrict__ bias, int K, int V, int Co,
+                                                     float* __restrict__ out) {
+  __shared__ float rs[128];
+  adjacency_rowsums(A, K, V, rs);
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= V * Co) return;
   int co = i % Co, v = i / Co;
   float s = 0.f;
-  for (int k = 0; k < K; ++k) {
-    float rs = 0.f;
-    for (int w = 0; w < V; ++w) rs += A[(k * V + v) * V + w];
-    s = fmaf(rs, bias[k * Co + co], s);
-  }
+  for (int k = 0; k < K; ++k) s = fmaf(rs[k * V + v], bias[k * Co + co], s);
   out[i] = s;
 }
 int32_t launch_bias2d(const float* A, const float* bias, int K, int V, int Co, float* out, cudaStream_t st) {
-  bias2d_kernel<<<cdiv(V * Co, 128), 128, 0, st>>>(A, bias, K, V, Co, out);
+  bias2d_kernel<<<cdiv(V * Co, 256), 256, 0, st>>>(A, bias, K, V, Co, out);
   STGCN_CHECK_LAUNCH("bias2d");
   return STGCN_OK;
 }
 
 // dbias[k*Co+co] = sum_v t1[v][co]*rowsum_k[v] ;  dA[k,v,w] += sum_co t1[v][co]*bias[k*Co+co]
-__global__ void spatial_bias_grads_kernel(const float* __restrict__ t1, const float* __restrict__ A, const float* __restrict__ bias,
-                                          int K, int V, int Co, float* __restrict__ dbias, float* __restrict__ dA) {
-  int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < K * Co) {
-    int co = i % Co, k = i / Co;
-    float s = 0.f;
-    for (int v = 0; v < V; ++v) {
-      float rs = 0.f;
-      for (int w = 0; w < V; ++w) rs += A[(k * V + v) * V + w];
-      s = fmaf(t1[v * Co + co], rs, s);
+// blocks [0, nb_bias): dbias, 256 outputs each;  blocks [nb_bias, nb_bias + K*V): one (k,v) row of dA each
+__global__ void __launch_bounds__(256) spatial_bias_grads_kernel(const float* __restrict__ t1, const float* __restrict__ A,
+                                                                 const float* __restrict__ bias, int K, int V, int Co, int nb_bias,
+                                                                 float* __restrict__ dbias, float* __restrict__ dA) {
+  __shared__ float rs[128];
+  __shared__ float wsum[8];
+  if ((int)blockIdx.x < nb_bias) {
+    adjacency_rowsums(A, K, V, rs);
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < K * Co && dbias) {
+      int co = i % Co, k = i / Co;
+      float s = 0.f;
+      for (int v = 0; v < V; ++v) s = fmaf(t1[v * Co + co], rs[k * V + v], s);
+      dbias[i] = s;
     }
-    if (dbias) dbias[i] = s;
+    return;
   }
-  if (dA && i < K * V) {
-    int v = i % V, k = i / V;
-    float s = 0.f;
-    for (int co = 0; co < Co; ++co) s = fmaf(t1[v * Co + co], bias[k * Co + co], s);
-    for (int w = 0; w < V; ++w) dA[(k * V + v) * V + w] += s;
+  if (!dA) return;
+  const int kv = blockIdx.x - nb_bias, v = kv % V, k = kv / V;
+  float s = 0.f;
+  for (int co = threadIdx.x; co < Co; co += blockDim.x) s = fmaf(t1[v * Co + co], bias[k * Co + co], s);
+  s = warp_sum(s);
+  if ((threadIdx.x & 31) == 0) wsum[threadIdx.x >> 5] = s;
+  __syncthreads();
+  if (threadIdx.x < V) {
+    float tot = 0.f;
+    for (int i = 0; i < 8; ++i) tot += wsum[i];
+    dA[(k * V + v) * V + threadIdx.x] += tot;
   }
 }
 int32_t launch_spatial_bias_grads(const float* t1, const float* A, const float* bias, int K, int V, int Co, float* dbias,
                                   float* dA, cudaStream_t st) {
-  int n = std::max(K * Co, K * V);
-  spatial_bias_grads_kernel<<<cdiv(n, 128), 128, 0, st>>>(t1, A, bias, K, V, Co, dbias, dA);
+  const int nb_bias = cdiv(K * Co, 256);
+  spatial_bias_grads_kernel<<<nb_bias + K * V, 256, 0, st>>>(t1, A, bias, K, V, Co, nb_bias, dbias, dA);
   STGCN_CHECK_LAUNCH("spatial_bias_grads");
   return STGCN_OK;
 }

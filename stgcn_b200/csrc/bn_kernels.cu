@@ -99,18 +99,38 @@ template int32_t launch_colstats<bf16>(const bf16*, long long, int, float*, int*
 // finalize forward statistics -> stats[4][C] = {mean, invstd, a, b}
 //   a = gamma*invstd, b = beta - a*mean ; running stats updated like torch
 // ---------------------------------------------------------------------------
-__global__ void bn_finalize_kernel(const float* __restrict__ partials, int nblk, int C, double count,
-                                   const float* __restrict__ gamma, const float* __restrict__ beta,
-                                   float* running_mean, float* running_var, long long* nbt,
-                                   float eps, float momentum, float* __restrict__ stats) {
-  int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c == 0 && nbt) *nbt += 1;
-  if (c >= C) return;
-  double s1 = 0, s2 = 0;
-  for (int b = 0; b < nblk; ++b) {
-    s1 += (double)partials[((size_t)b * 2 + 0) * C + c];
-    s2 += (double)partials[((size_t)b * 2 + 1) * C + c];
+// 32 channels per CTA; 32 partial-slices per channel reduced in double through shared memory, so the ~600
+// per-CTA partials are read with 32-way memory parallelism instead of one dependent chain per channel.
+constexpr int kFinThreads = 1024;
+__device__ __forceinline__ bool reduce_partials_32x32(const float* __restrict__ partials, int nblk, int C, double& s1, double& s2) {
+  __shared__ double red[2][32][33];
+  const int cl = threadIdx.x & 31, bs = threadIdx.x >> 5;
+  const int c = blockIdx.x * 32 + cl;
+  double a1 = 0, a2 = 0;
+  if (c < C) {
+    for (int b = bs; b < nblk; b += 32) {
+      a1 += (double)partials[((size_t)b * 2 + 0) * C + c];
+      a2 += (double)partials[((size_t)b * 2 + 1) * C + c];
+    }
   }
+  red[0][bs][cl] = a1; red[1][bs][cl] = a2;
+  __syncthreads();
+  if (bs != 0 || c >= C) return false;
+  s1 = 0; s2 = 0;
+#pragma unroll 8
+  for (int i = 0; i < 32; ++i) { s1 += red[0][i][cl]; s2 += red[1][i][cl]; }
+  return true;
+}
+
+__global__ void __launch_bounds__(kFinThreads)
+bn_finalize_kernel(const float* __restrict__ partials, int nblk, int C, double count,
+                   const float* __restrict__ gamma, const float* __restrict__ beta,
+                   float* running_mean, float* running_var, long long* nbt,
+                   float eps, float momentum, float* __restrict__ stats) {
+  if (blockIdx.x == 0 && threadIdx.x == 0 && nbt) *nbt += 1;
+  double s1, s2;
+  if (!reduce_partials_32x32(partials, nblk, C, s1, s2)) return;
+  const int c = blockIdx.x * 32 + (threadIdx.x & 31);
   double mean = s1 / count;
   double var = s2 / count - mean * mean;
   if (var < 0) var = 0;
@@ -143,7 +163,7 @@ __global__ void bn_eval_coeffs_kernel(int C, const float* __restrict__ gamma, co
 int32_t launch_bn_finalize(const float* partials, int nblk, int C, double count, const float* gamma,
                            const float* beta, float* rm, float* rv, long long* nbt, float eps, float momentum,
                            float* stats, cudaStream_t st) {
-  bn_finalize_kernel<<<cdiv(C, 128), 128, 0, st>>>(partials, nblk, C, count, gamma, beta, rm, rv, nbt, eps, momentum, stats);
+  bn_finalize_kernel<<<cdiv(C, 32), kFinThreads, 0, st>>>(partials, nblk, C, count, gamma, beta, rm, rv, nbt, eps, momentum, stats);
   STGCN_CHECK_LAUNCH("bn_finalize");
   return STGCN_OK;
 }
@@ -244,21 +264,18 @@ template int32_t launch_bn_bwd_reduce<float>(const float*, const float*, const f
 template int32_t launch_bn_bwd_reduce<bf16>(const bf16*, const bf16*, const float*, long long, int, int, float, uint64_t, uint64_t, float*, int*, cudaStream_t);
 
 // sums[2][C] = {s1, s2} reduced in double; also emits dgamma = s2, dbeta = s1
-__global__ void bn_bwd_finalize_kernel(const float* __restrict__ partials, int nblk, int C, float* __restrict__ sums,
-                                       float* __restrict__ dgamma, float* __restrict__ dbeta) {
-  int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= C) return;
-  double s1 = 0, s2 = 0;
-  for (int b = 0; b < nblk; ++b) {
-    s1 += (double)partials[((size_t)b * 2 + 0) * C + c];
-    s2 += (double)partials[((size_t)b * 2 + 1) * C + c];
-  }
+__global__ void __launch_bounds__(kFinThreads)
+bn_bwd_finalize_kernel(const float* __restrict__ partials, int nblk, int C, float* __restrict__ sums,
+                       float* __restrict__ dgamma, float* __restrict__ dbeta) {
+  double s1, s2;
+  if (!reduce_partials_32x32(partials, nblk, C, s1, s2)) return;
+  const int c = blockIdx.x * 32 + (threadIdx.x & 31);
   sums[c] = (float)s1; sums[C + c] = (float)s2;
   if (dgamma) dgamma[c] = (float)s2;
   if (dbeta) dbeta[c] = (float)s1;
 }
 int32_t launch_bn_bwd_finalize(const float* partials, int nblk, int C, float* sums, float* dgamma, float* dbeta, cudaStream_t st) {
-  bn_bwd_finalize_kernel<<<cdiv(C, 128), 128, 0, st>>>(partials, nblk, C, sums, dgamma, dbeta);
+  bn_bwd_finalize_kernel<<<cdiv(C, 32), kFinThreads, 0, st>>>(partials, nblk, C, sums, dgamma, dbeta);
   STGCN_CHECK_LAUNCH("bn_bwd_finalize");
   return STGCN_OK;
 }

@@ -277,7 +277,9 @@ agg_dA_umma_kernel(const __grid_constant__ CUtensorMap map_dxa, const __grid_con
   uint64_t* empty_bar = full_bar + p.stages;
   uint64_t* done_bar = empty_bar + p.stages;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(done_bar + 1);
+  float* da_tab = reinterpret_cast<float*>(smem + (size_t)p.stages * stage_bytes + 256);   // [K][V][V] CTA-local sums
   const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
+  for (int i = threadIdx.x; i < p.k * p.v * p.v; i += kAggUThreads) da_tab[i] = 0.f;
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&map_dxa); prefetch_tmap(&map_h);
     for (int s = 0; s < p.stages; ++s) { mbar_init(full_bar + s, 1); mbar_init(empty_bar + s, 1); }
@@ -345,11 +347,14 @@ agg_dA_umma_kernel(const __grid_constant__ CUtensorMap map_dxa, const __grid_con
 #pragma unroll
           for (int i = 0; i < 32; ++i) {
             const int w = chunk * 32 + i - fl * p.v;          // column inside this row's own frame block
-            if (w >= 0 && w < p.v) atomicAdd(p.dA + (k * p.v + vv) * p.v + w, __uint_as_float(r[i]));
+            if (w >= 0 && w < p.v) atomicAdd(da_tab + (k * p.v + vv) * p.v + w, __uint_as_float(r[i]));   // FT-way smem contention only
           }
         }
       }
     }
+    asm volatile("bar.sync 1, 128;" ::: "memory");
+    if (have_work)
+      for (int i = threadIdx.x - 64; i < p.k * p.v * p.v; i += 128) atomicAdd(p.dA + i, da_tab[i]);   // one global atomic per entry per CTA
   }
   tc_fence_before();
   __syncthreads();
@@ -422,15 +427,17 @@ int32_t launch_agg_dA_umma(const bf16* dxa, const bf16* h, int nb, int t, int v,
   p.m_tiles_per_b = cdiv(t, p.ft); p.total_tiles = p.m_tiles_per_b * nb;
   p.tile_bytes = (uint32_t)(p.ft * v * 128);
   const size_t stage_bytes = (size_t)(k + 1) * kTile16K;
-  int stages = (int)((220 * 1024 - 2048) / stage_bytes);
+  const size_t tail_bytes = 2048 + (size_t)k * v * v * sizeof(float);      // align slack + barriers + CTA-local dA table
+  int stages = (int)((220 * 1024 - tail_bytes) / stage_bytes);
   if (stages > 4) stages = 4;
+  if (stages < 2) { set_error("umma dA: not enough shared memory"); return STGCN_ERR_UNSUPPORTED; }
   p.stages = stages;
   uint32_t cols = 32; while (cols < (uint32_t)(k * 128)) cols <<= 1;
   p.tmem_cols = cols; p.dA = dA;
   CUtensorMap map_dxa, map_h;
   STGCN_TRY(make_act_map(&map_dxa, dxa, k * c, v, t, nb, p.ft));
   STGCN_TRY(make_act_map(&map_h, h, c, v, t, nb, p.ft));
-  const size_t smem = (size_t)stages * stage_bytes + 2048;
+  const size_t smem = (size_t)stages * stage_bytes + tail_bytes;
   static bool attr_set = false;
   if (!attr_set) {
     cudaError_t e = cudaFuncSetAttribute(agg_dA_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);

@@ -44,6 +44,7 @@ struct UmmaParams {
   TapEntry taps[2][kMaxTaps];
   // epilogue
   const float* bias; const float* bias2d; const float* scale; const float* shift;
+  int b2_smem;           // bias2d staged in shared memory as [V][bn+4] floats (only when n_tiles == 1)
   const bf16* residual;
   int relu;
   float dropout_p, inv_keep;
@@ -74,6 +75,7 @@ conv_gemm_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_c
   uint64_t* tfull_bar = empty_bar + p.stages;
   uint64_t* tempty_bar = tfull_bar + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+  float* b2_tab = reinterpret_cast<float*>(tmem_slot + 4);       // 16-byte aligned: barriers start on a 1024-byte boundary
 
   const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
 
@@ -143,6 +145,11 @@ conv_gemm_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_c
     const int fl = row / p.v, vv = row % p.v;
     int as = 0; uint32_t aphase = 0;
     int chunk_ctr = 0;
+    const int b2_ld = p.bn + 4;                    // row pitch (floats): 16-byte rows, conflict-free across joints
+    if (p.b2_smem) {
+      for (int i = et; i < p.v * p.bn; i += 128) b2_tab[(i / p.bn) * b2_ld + (i % p.bn)] = __ldg(p.bias2d + i);
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+    }
     for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
       const TileCoord tc = decode_tile(p, tile);
       mbar_wait(tfull_bar + as, aphase);
@@ -170,7 +177,14 @@ conv_gemm_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_c
 #pragma unroll
             for (int i = 0; i < 32; ++i) f[i] += __ldg(p.bias + n0 + i);
           }
-          if (p.bias2d) {
+          if (p.b2_smem) {
+            const float4* b2 = reinterpret_cast<const float4*>(b2_tab + vv * b2_ld + col0);
+#pragma unroll
+            for (int g = 0; g < 8; ++g) {
+              const float4 t = b2[g];
+              f[g * 4 + 0] += t.x; f[g * 4 + 1] += t.y; f[g * 4 + 2] += t.z; f[g * 4 + 3] += t.w;
+            }
+          } else if (p.bias2d) {
             const float* b2 = p.bias2d + (size_t)vv * p.n_out + n0;
 #pragma unroll
             for (int i = 0; i < 32; ++i) f[i] += __ldg(b2 + i);
@@ -319,7 +333,9 @@ int32_t launch_conv_gemm_umma(const ConvGeom& g, const bf16* in, const bf16* w, 
   p.a_bytes = (uint32_t)(p.ft * g.v * 128);
   p.b_bytes = (uint32_t)(p.bn * 128);
   const size_t stage_bytes = kATileBytes + p.b_bytes;
-  const size_t fixed = 2 * kStagingBytes + 1024 /*align slack*/ + 512 /*barriers*/;
+  p.b2_smem = (ep.bias2d && p.n_tiles == 1) ? 1 : 0;
+  const size_t b2_bytes = p.b2_smem ? (size_t)g.v * (p.bn + 4) * sizeof(float) : 0;
+  const size_t fixed = 2 * kStagingBytes + 1024 /*align slack*/ + 512 /*barriers*/ + b2_bytes;
   int stages = (int)((220 * 1024 - fixed) / stage_bytes);
   if (stages > 8) stages = 8;
   if (stages < 2) { set_error("umma conv-gemm: not enough shared memory for 2 stages"); return STGCN_ERR_UNSUPPORTED; }
