@@ -73,13 +73,92 @@ static int stat_blocks(long long rows, int C, int vec) {
   return (int)b;
 }
 
+// ---------------------------------------------------------------------------
+// fast path of the two-moment reduction: 16-byte loads, a thread keeps ONE column group for the whole
+// kernel (so per-column constants live in registers), four independent rows in flight per thread.
+//   MODE 0: g = x, h = x*x                                (forward statistics)
+//   MODE 1: g = dy*[a*z+b > 0 if relu], h = g*(z-mean)*invstd   (BatchNorm backward sums; no dropout)
+// ---------------------------------------------------------------------------
+template <class T, int MODE>
+__global__ void __launch_bounds__(kStatThreads) colreduce_fast_kernel(const T* __restrict__ x, const T* __restrict__ z,
+                                                                      const float* __restrict__ stats, int relu, long long rows,
+                                                                      int C, float* __restrict__ partials) {
+  constexpr int VEC = VecN<T>::N;
+  extern __shared__ float sm[];
+  const int cv = C / VEC, rps = kStatThreads / cv, tid = threadIdx.x;
+  const bool active = tid < rps * cv;
+  const int myc = (tid % cv) * VEC, myr = tid / cv;
+  float s1[VEC], s2[VEC], mean[VEC], invstd[VEC], ca[VEC], cb[VEC];
+#pragma unroll
+  for (int i = 0; i < VEC; ++i) { s1[i] = 0.f; s2[i] = 0.f; mean[i] = 0.f; invstd[i] = 0.f; ca[i] = 0.f; cb[i] = 0.f; }
+  if (MODE == 1 && active) {
+#pragma unroll
+    for (int i = 0; i < VEC; ++i) { mean[i] = stats[myc + i]; invstd[i] = stats[C + myc + i]; ca[i] = stats[2 * C + myc + i]; cb[i] = stats[3 * C + myc + i]; }
+  }
+  auto accum = [&](const float (&g0)[VEC], const float (&z0)[VEC]) {
+#pragma unroll
+    for (int i = 0; i < VEC; ++i) {
+      if (MODE == 0) { s1[i] += g0[i]; s2[i] = fmaf(g0[i], g0[i], s2[i]); }
+      else {
+        float g = g0[i];
+        if (relu && !(fmaf(ca[i], z0[i], cb[i]) > 0.f)) g = 0.f;
+        s1[i] += g; s2[i] = fmaf(g, (z0[i] - mean[i]) * invstd[i], s2[i]);
+      }
+    }
+  };
+  if (active) {
+    const long long step = (long long)gridDim.x * rps;
+    long long r = (long long)blockIdx.x * rps + myr;
+    for (; r + 3 * step < rows; r += 4 * step) {
+      float g[4][VEC], zz[4][VEC];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        ldv(x + (r + u * step) * C + myc, g[u]);
+        if (MODE == 1) ldv(z + (r + u * step) * C + myc, zz[u]);
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) accum(g[u], MODE == 1 ? zz[u] : g[u]);
+    }
+    for (; r < rows; r += step) {
+      float g[VEC], zz[VEC];
+      ldv(x + r * C + myc, g);
+      if (MODE == 1) ldv(z + r * C + myc, zz);
+      accum(g, MODE == 1 ? zz : g);
+    }
+  }
+  float* a1 = sm; float* a2 = sm + rps * C;
+  if (active) {
+#pragma unroll
+    for (int i = 0; i < VEC; ++i) { a1[myr * C + myc + i] = s1[i]; a2[myr * C + myc + i] = s2[i]; }
+  }
+  __syncthreads();
+  for (int c = tid; c < C; c += kStatThreads) {
+    float t1 = 0.f, t2 = 0.f;
+    for (int rr = 0; rr < rps; ++rr) { t1 += a1[rr * C + c]; t2 += a2[rr * C + c]; }
+    partials[((size_t)blockIdx.x * 2 + 0) * C + c] = t1;
+    partials[((size_t)blockIdx.x * 2 + 1) * C + c] = t2;
+  }
+}
+template <class T> static bool colreduce_fast_ok(int C) { return C % VecN<T>::N == 0 && C / VecN<T>::N <= kStatThreads; }
+template <class T, int MODE>
+static void launch_colreduce_fast(const T* x, const T* z, const float* stats, int relu, long long rows, int C, float* partials,
+                                  int* nblk, cudaStream_t st) {
+  const int cv = C / VecN<T>::N, rps = kStatThreads / cv;
+  long long b = (rows + rps - 1) / rps; b = (b + 7) / 8;
+  if (b < 1) b = 1; if (b > kMaxStatBlocks) b = kMaxStatBlocks;
+  *nblk = (int)b;
+  colreduce_fast_kernel<T, MODE><<<(int)b, kStatThreads, 2 * rps * C * sizeof(float), st>>>(x, z, stats, relu, rows, C, partials);
+}
+
 size_t stat_partials_bytes(int C) { return (size_t)kMaxStatBlocks * 2 * C * sizeof(float); }
 
 template <class T>
 int32_t launch_colstats(const T* x, long long rows, int C, float* partials, int* nblk, cudaStream_t st) {
   KernelTimer kt_(KC_BN_STATS, (double)rows * C, st);
   if (C > 1024) { set_error("colstats: C=%d > 1024 unsupported", C); return STGCN_ERR_UNSUPPORTED; }
-  if (C % 4 == 0) {
+  if (colreduce_fast_ok<T>(C)) {
+    launch_colreduce_fast<T, 0>(x, nullptr, nullptr, 0, rows, C, partials, nblk, st);
+  } else if (C % 4 == 0) {
     int nb = stat_blocks(rows, C, 4); *nblk = nb;
     int rps = kStatThreads / (C / 4);
     colreduce_kernel<4><<<nb, kStatThreads, 2 * rps * C * sizeof(float), st>>>(rows, C, FwdStatF<T, 4>{x, C}, partials);
@@ -199,13 +278,47 @@ __global__ void __launch_bounds__(256) affine_act_kernel(const T* __restrict__ x
   }
 }
 
+// fast path: 16-byte accesses; the grid stride is a multiple of C, so a thread keeps one column group and its
+// affine coefficients in registers; two independent vectors in flight per thread.  No dropout on this path.
+template <class T>
+__global__ void __launch_bounds__(256) affine_act_fast_kernel(const T* __restrict__ x, long long total, int C,
+                                                              const float* __restrict__ a, const float* __restrict__ b,
+                                                              int relu, T* __restrict__ y) {
+  constexpr int VEC = VecN<T>::N;
+  long long i = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * VEC;
+  const long long step = (long long)gridDim.x * blockDim.x * VEC;
+  const int c = (int)(i % C);
+  float ca[VEC], cb[VEC];
+#pragma unroll
+  for (int j = 0; j < VEC; ++j) { ca[j] = a ? a[c + j] : 1.f; cb[j] = a ? b[c + j] : 0.f; }
+  auto apply = [&](float (&v)[VEC]) {
+#pragma unroll
+    for (int j = 0; j < VEC; ++j) { float t = fmaf(ca[j], v[j], cb[j]); v[j] = relu ? fmaxf(t, 0.f) : t; }
+  };
+  for (; i + step < total; i += 2 * step) {
+    float v0[VEC], v1[VEC];
+    ldv(x + i, v0); ldv(x + i + step, v1);
+    apply(v0); apply(v1);
+    stv(y + i, v0); stv(y + i + step, v1);
+  }
+  if (i < total) { float v0[VEC]; ldv(x + i, v0); apply(v0); stv(y + i, v0); }
+}
+template <class T> static bool elementwise_fast_ok(long long total, int C) {
+  return (256 * VecN<T>::N) % C == 0 && C % VecN<T>::N == 0 && total % VecN<T>::N == 0;
+}
+static int elementwise_blocks(long long total, int vec) {
+  return (int)std::max<long long>(1, std::min<long long>((total / vec + 255) / 256, 148 * 8));
+}
+
 template <class T>
 int32_t launch_affine_act(const T* x, long long rows, int C, const float* a, const float* b, int relu, float p,
                           uint64_t seed, uint64_t offset, T* y, cudaStream_t st) {
   KernelTimer kt_(KC_ELEMWISE, (double)rows * C, st);
   long long total = rows * C;
   float inv_keep = p > 0.f ? 1.f / (1.f - p) : 1.f;
-  if (C % 4 == 0) {
+  if (p == 0.f && elementwise_fast_ok<T>(total, C)) {
+    affine_act_fast_kernel<T><<<elementwise_blocks(total, VecN<T>::N), 256, 0, st>>>(x, total, C, a, b, relu, y);
+  } else if (C % 4 == 0) {
     int blocks = (int)std::min<long long>((total / 4 + 255) / 256, 148 * 16);
     affine_act_kernel<T, 4><<<blocks, 256, 0, st>>>(x, total, C, a, b, relu, p, inv_keep, seed, offset, y);
   } else {
@@ -246,7 +359,9 @@ int32_t launch_bn_bwd_reduce(const T* dy, const T* z, const float* stats, long l
                              uint64_t seed, uint64_t offset, float* partials, int* nblk, cudaStream_t st) {
   KernelTimer kt_(KC_BN_STATS, (double)rows * C, st);
   float inv_keep = p > 0.f ? 1.f / (1.f - p) : 1.f;
-  if (C % 4 == 0) {
+  if (p == 0.f && colreduce_fast_ok<T>(C)) {
+    launch_colreduce_fast<T, 1>(dy, z, stats, relu, rows, C, partials, nblk, st);
+  } else if (C % 4 == 0) {
     int nb = stat_blocks(rows, C, 4); *nblk = nb;
     int rps = kStatThreads / (C / 4);
     colreduce_kernel<4><<<nb, kStatThreads, 2 * rps * C * sizeof(float), st>>>(
@@ -306,13 +421,50 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const T* __restrict__
 }
 
 template <class T>
+__global__ void __launch_bounds__(256) bn_bwd_apply_fast_kernel(const T* __restrict__ dy, const T* __restrict__ z,
+                                                                const float* __restrict__ stats, const float* __restrict__ sums,
+                                                                long long total, int C, int relu, int training, float inv_m,
+                                                                T* __restrict__ dz) {
+  constexpr int VEC = VecN<T>::N;
+  long long i = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * VEC;
+  const long long step = (long long)gridDim.x * blockDim.x * VEC;
+  const int c = (int)(i % C);
+  float mean[VEC], ca[VEC], cb[VEC], k1[VEC], k2[VEC];
+#pragma unroll
+  for (int j = 0; j < VEC; ++j) {
+    mean[j] = stats[c + j]; ca[j] = stats[2 * C + c + j]; cb[j] = stats[3 * C + c + j];
+    k1[j] = training ? sums[c + j] * inv_m : 0.f;
+    k2[j] = training ? stats[C + c + j] * sums[C + c + j] * inv_m : 0.f;
+  }
+  auto apply = [&](float (&g)[VEC], const float (&zz)[VEC]) {
+#pragma unroll
+    for (int j = 0; j < VEC; ++j) {
+      float r = g[j];
+      if (relu && !(fmaf(ca[j], zz[j], cb[j]) > 0.f)) r = 0.f;
+      r = r - k1[j] - (zz[j] - mean[j]) * k2[j];
+      g[j] = ca[j] * r;
+    }
+  };
+  for (; i + step < total; i += 2 * step) {
+    float g0[VEC], z0[VEC], g1[VEC], z1[VEC];
+    ldv(dy + i, g0); ldv(z + i, z0); ldv(dy + i + step, g1); ldv(z + i + step, z1);
+    apply(g0, z0); apply(g1, z1);
+    stv(dz + i, g0); stv(dz + i + step, g1);
+  }
+  if (i < total) { float g0[VEC], z0[VEC]; ldv(dy + i, g0); ldv(z + i, z0); apply(g0, z0); stv(dz + i, g0); }
+}
+
+template <class T>
 int32_t launch_bn_bwd_apply(const T* dy, const T* z, const float* stats, const float* sums, long long rows, int C,
                             int relu, int training, float p, uint64_t seed, uint64_t offset, T* dz, cudaStream_t st) {
   KernelTimer kt_(KC_ELEMWISE, (double)rows * C, st);
   long long total = rows * C;
   float inv_keep = p > 0.f ? 1.f / (1.f - p) : 1.f;
   float inv_m = 1.0f / (float)rows;
-  if (C % 4 == 0) {
+  if (p == 0.f && elementwise_fast_ok<T>(total, C)) {
+    bn_bwd_apply_fast_kernel<T><<<elementwise_blocks(total, VecN<T>::N), 256, 0, st>>>(dy, z, stats, sums, total, C, relu, training,
+                                                                                         inv_m, dz);
+  } else if (C % 4 == 0) {
     int blocks = (int)std::min<long long>((total / 4 + 255) / 256, 148 * 16);
     bn_bwd_apply_kernel<T, 4><<<blocks, 256, 0, st>>>(dy, z, stats, sums, total, C, relu, training, inv_m, p, inv_keep, seed, offset, dz);
   } else {

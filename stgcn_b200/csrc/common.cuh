@@ -66,6 +66,26 @@ __device__ __forceinline__ void st4(bf16* p, const float (&v)[4]) {
   *reinterpret_cast<uint2*>(p) = t;
 }
 
+// 16-byte vector access: VecN<T>::N elements per access (4 floats / 8 bf16)
+template <class T> struct VecN;
+template <> struct VecN<float> { static constexpr int N = 4; };
+template <> struct VecN<bf16> { static constexpr int N = 8; };
+__device__ __forceinline__ void ldv(const float* p, float (&v)[4]) { ld4(p, v); }
+__device__ __forceinline__ void stv(float* p, const float (&v)[4]) { st4(p, v); }
+__device__ __forceinline__ void ldv(const bf16* p, float (&v)[8]) {
+  const uint4 t = *reinterpret_cast<const uint4*>(p);
+  const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&t);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) { v[2 * i] = __low2float(h[i]); v[2 * i + 1] = __high2float(h[i]); }
+}
+__device__ __forceinline__ void stv(bf16* p, const float (&v)[8]) {
+  uint4 t;
+  __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&t);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) h[i] = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
+  *reinterpret_cast<uint4*>(p) = t;
+}
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
