@@ -419,19 +419,28 @@ def block_forward_bf16(x, p, cfg: BlockCfg, training: bool, update_running=True,
         h = torch.relu(h)
     if round_A is None:
         round_A = cfg.c_in % 64 == 0             # the tensor-core aggregation (C_in % 64 == 0) takes A as a bf16 operand
-    if round_A:
+    W3 = p['spatialConv.W.weight'].reshape(K, Co, Ci)
+    Wb = p['spatialConv.W.bias'].reshape(K, Co)
+    if round_A and not cfg.residual:
+        # tensor-core default block: BatchNorm-1 is folded into the 1x1 weights.  The RAW input is aggregated
+        # (bf16 A operand, XA stored in bf16), GEMM-1 runs against bf16(W.diag(a1)), and the BN shift travels
+        # through the weights into the per-joint bias:  sum_k rowsum(Aq)_k[v] * (W_k b1)[co].
         Aq = A + (_rb(A) - A).detach()           # forward rounding only: dA stays an fp32 accumulation
-        if cfg.residual:
+        xa = _q(torch.einsum('kvw,nctw->nkctv', Aq, x))
+        Wk = _q(W3 * a1[None, None, :])
+        wb = torch.einsum('koc,c->ko', W3, b1)
+        bias2d = torch.einsum('ko,kv->ov', Wb, A.sum(dim=2)) + torch.einsum('ko,kv->ov', wb, Aq.sum(dim=2))
+        s = _q(torch.einsum('koc,nkctv->notv', Wk, xa) + bias2d[None, :, None, :])
+    else:
+        if round_A:
+            Aq = A + (_rb(A) - A).detach()
             h = _q(h)                            # a ReLU between BN-1 and the aggregation: h is stored in bf16
             xa = _q(torch.einsum('kvw,nctw->nkctv', Aq, h))
-        else:                                    # BN-1 affine applied in the epilogue to the aggregated raw input
-            xa = _q(torch.einsum('kvw,nctw->nkctv', Aq, x) * a1[None, None, :, None, None]
-                    + (b1[None, :, None] * Aq.sum(dim=2)[:, None, :])[None, :, :, None, :])
-    else:
-        xa = _q(torch.einsum('kvw,nctw->nkctv', A, h))                  # aggregate on the C_in side
-    Wk = _q(p['spatialConv.W.weight'].reshape(K, Co, Ci))
-    bias2d = torch.einsum('ko,kv->ov', p['spatialConv.W.bias'].reshape(K, Co), A.sum(dim=2))
-    s = _q(torch.einsum('koc,nkctv->notv', Wk, xa) + bias2d[None, :, None, :])
+        else:
+            xa = _q(torch.einsum('kvw,nctw->nkctv', A, h))                  # aggregate on the C_in side
+        Wk = _q(W3)
+        bias2d = torch.einsum('ko,kv->ov', Wb, A.sum(dim=2))
+        s = _q(torch.einsum('koc,nkctv->notv', Wk, xa) + bias2d[None, :, None, :])
     Wt = _q(p['temporalConv.weight'])
     if not cfg.residual:
         u = temporal_conv(s, Wt, p['temporalConv.bias'], cfg.stride, cfg.pad)

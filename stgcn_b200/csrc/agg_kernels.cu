@@ -322,7 +322,8 @@ int32_t launch_bias2d(const float* A, const float* bias, int K, int V, int Co, f
 // dbias[k*Co+co] = sum_v t1[v][co]*rowsum_k[v] ;  dA[k,v,w] += sum_co t1[v][co]*bias[k*Co+co]
 // blocks [0, nb_bias): dbias, 256 outputs each;  blocks [nb_bias, nb_bias + K*V): one (k,v) row of dA each
 __global__ void __launch_bounds__(256) spatial_bias_grads_kernel(const float* __restrict__ t1, const float* __restrict__ A,
-                                                                 const float* __restrict__ bias, int K, int V, int Co, int nb_bias,
+                                                                 const float* __restrict__ bias, const float* __restrict__ bias_dA,
+                                                                 int K, int V, int Co, int nb_bias,
                                                                  float* __restrict__ dbias, float* __restrict__ dA) {
   __shared__ float rs[128];
   __shared__ float wsum[8];
@@ -337,6 +338,7 @@ __global__ void __launch_bounds__(256) spatial_bias_grads_kernel(const float* __
     }
     return;
   }
+  bias = bias_dA ? bias_dA : bias;
   if (!dA) return;
   const int kv = blockIdx.x - nb_bias, v = kv % V, k = kv / V;
   float s = 0.f;
@@ -351,10 +353,120 @@ __global__ void __launch_bounds__(256) spatial_bias_grads_kernel(const float* __
   }
 }
 int32_t launch_spatial_bias_grads(const float* t1, const float* A, const float* bias, int K, int V, int Co, float* dbias,
-                                  float* dA, cudaStream_t st) {
+                                  float* dA, cudaStream_t st, const float* bias_dA) {
   const int nb_bias = cdiv(K * Co, 256);
-  spatial_bias_grads_kernel<<<nb_bias + K * V, 256, 0, st>>>(t1, A, bias, K, V, Co, nb_bias, dbias, dA);
+  spatial_bias_grads_kernel<<<nb_bias + K * V, 256, 0, st>>>(t1, A, bias, bias_dA, K, V, Co, nb_bias, dbias, dA);
   STGCN_CHECK_LAUNCH("spatial_bias_grads");
+  return STGCN_OK;
+}
+
+// ---------------------------------------------------------------------------
+// BatchNorm-1 folded into the 1x1 weights (tensor-core path, default block):
+//   S = sum_k (A_k (a.x + b)) W_k^T + ...  =  sum_k (A_k x) (W_k diag(a))^T + bias2d'
+// so the aggregation runs on the RAW input and BN-1 costs two tiny kernels:
+//   w2p [co][k*Ci+ci] = bf16(W[(k*Co+co)*Ci+ci] * a[ci])        GEMM-1 operand
+//   w2pT[k*Ci+ci][co] = same value                                 operand of dXA' = dS . W2'
+//   wb  [k*Co+co]     = sum_ci W[(k*Co+co)*Ci+ci] * b[ci]          BN shift through the weights
+//   bias2d'[v][co]    = sum_k rowsum(A)_k[v]*Wb[k,co] + rowsum(bf16 A)_k[v]*wb[k,co]
+// (reference: batch_n -> spatialConv at st_graphconv.py:98-99,148-150)
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) bn1_fold_weights_kernel(const float* __restrict__ W, const float* __restrict__ a,
+                                                               const float* __restrict__ b, int K, int Co, int Ci,
+                                                               bf16* __restrict__ w2p, bf16* __restrict__ w2pT, float* __restrict__ wb) {
+  __shared__ float red[4];
+  const int r = blockIdx.x, k = r / Co, co = r % Co;
+  float part = 0.f;
+  for (int ci = threadIdx.x; ci < Ci; ci += blockDim.x) {
+    const float w = W[(size_t)r * Ci + ci];
+    const bf16 q = __float2bfloat16_rn(w * a[ci]);
+    w2p[(size_t)co * (K * Ci) + k * Ci + ci] = q;
+    w2pT[(size_t)(k * Ci + ci) * Co + co] = q;
+    part = fmaf(w, b[ci], part);
+  }
+  part = warp_sum(part);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = part;
+  __syncthreads();
+  if (threadIdx.x == 0) wb[r] = red[0] + red[1] + red[2] + red[3];
+}
+__global__ void __launch_bounds__(256) bias2d_fold_kernel(const float* __restrict__ A, const float* __restrict__ rowsum_q,
+                                                          const float* __restrict__ Wb, const float* __restrict__ wb, int K, int V, int Co,
+                                                          float* __restrict__ out, float* __restrict__ wbb) {
+  __shared__ float rs[128];
+  adjacency_rowsums(A, K, V, rs);
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < K * Co) wbb[i] = Wb[i] + wb[i];
+  if (i >= V * Co) return;
+  const int co = i % Co, v = i / Co;
+  float s = 0.f;
+  for (int k = 0; k < K; ++k) s += rs[k * V + v] * Wb[k * Co + co] + rowsum_q[k * V + v] * wb[k * Co + co];
+  out[i] = s;
+}
+int32_t launch_bn1_fold(const float* W, const float* Wb, const float* A, const float* rowsum_q, const float* a, const float* b, int K,
+                        int V, int Co, int Ci, bf16* w2p, bf16* w2pT, float* wb, float* wbb, float* bias2d, cudaStream_t st) {
+  KernelTimer kt_(KC_PACK, 0.0, st);
+  bn1_fold_weights_kernel<<<K * Co, 128, 0, st>>>(W, a, b, K, Co, Ci, w2p, w2pT, wb);
+  STGCN_CHECK_LAUNCH("bn1_fold_weights");
+  bias2d_fold_kernel<<<cdiv(std::max(V, K) * Co, 256), 256, 0, st>>>(A, rowsum_q, Wb, wb, K, V, Co, bias2d, wbb);
+  STGCN_CHECK_LAUNCH("bias2d_fold");
+  return STGCN_OK;
+}
+
+// gradients of the folded BatchNorm-1 (no pass over activations):
+//   q[k,co]  = sum_v rowsum_q_k[v] * t1[v,co]
+//   dbeta_c  = sum_{k,co} q[k,co] * W[(k,co),c]
+//   dgamma_c = invstd_c * ( sum_{k,co} W[(k,co),c] * dWraw[(k,co),c]  -  mean_c * dbeta_c )
+//   dW       = dWraw (.) a  +  q (x) b        (in place; the second term is the BN shift travelling through bias2d')
+//   coef     = { mean, a*dbeta/m, a*invstd*dgamma/m }  for the fused  dx = dh' - c1 - (x-mean)*c2   epilogue
+// 32 channels per CTA, 32 row-slices reduced through shared memory.
+__global__ void __launch_bounds__(1024) bn1_fold_grads_kernel(const float* __restrict__ W, float* __restrict__ dW,
+                                                              const float* __restrict__ stats, const float* __restrict__ t1,
+                                                              const float* __restrict__ rowsum_q, int K, int V, int Co, int Ci,
+                                                              int training, float inv_m, float* __restrict__ dgamma,
+                                                              float* __restrict__ dbeta, float* __restrict__ coef) {
+  __shared__ float q[1024];
+  __shared__ float red[2][32][33];
+  const int KCo = K * Co;
+  for (int i = threadIdx.x; i < KCo; i += blockDim.x) {
+    const int k = i / Co, co = i % Co;
+    float s = 0.f;
+    for (int v = 0; v < V; ++v) s = fmaf(rowsum_q[k * V + v], t1[v * Co + co], s);
+    q[i] = s;
+  }
+  __syncthreads();
+  const int cl = threadIdx.x & 31, sl = threadIdx.x >> 5, c = blockIdx.x * 32 + cl;
+  float s1 = 0.f, s2 = 0.f;
+  if (c < Ci) {
+    for (int r = sl; r < KCo; r += 32) {
+      const float w = W[(size_t)r * Ci + c];
+      s1 = fmaf(q[r], w, s1);
+      s2 = fmaf(w, dW[(size_t)r * Ci + c], s2);
+    }
+  }
+  red[0][sl][cl] = s1; red[1][sl][cl] = s2;
+  __syncthreads();
+  if (c < Ci) {
+    const float a = stats[2 * Ci + c];
+    const float b = stats[3 * Ci + c];
+    for (int r = sl; r < KCo; r += 32) dW[(size_t)r * Ci + c] = fmaf(dW[(size_t)r * Ci + c], a, q[r] * b);   // + shift term through bias2d'
+    if (sl == 0) {
+      float db = 0.f, sw = 0.f;
+      for (int i = 0; i < 32; ++i) { db += red[0][i][cl]; sw += red[1][i][cl]; }
+      const float mean = stats[c], invstd = stats[Ci + c];
+      const float dg = invstd * (sw - mean * db);
+      dgamma[c] = dg; dbeta[c] = db;
+      coef[c] = mean;
+      coef[Ci + c] = training ? a * db * inv_m : 0.f;
+      coef[2 * Ci + c] = training ? a * invstd * dg * inv_m : 0.f;
+    }
+  }
+}
+int32_t launch_bn1_fold_grads(const float* W, float* dW, const float* stats, const float* t1, const float* rowsum_q, int K, int V,
+                              int Co, int Ci, int training, double rows, float* dgamma, float* dbeta, float* coef, cudaStream_t st) {
+  KernelTimer kt_(KC_PACK, 0.0, st);
+  if (K * Co > 1024) { set_error("bn1_fold_grads: K*C_out=%d > 1024", K * Co); return STGCN_ERR_UNSUPPORTED; }
+  bn1_fold_grads_kernel<<<cdiv(Ci, 32), 1024, 0, st>>>(W, dW, stats, t1, rowsum_q, K, V, Co, Ci, training, (float)(1.0 / rows), dgamma,
+                                                       dbeta, coef);
+  STGCN_CHECK_LAUNCH("bn1_fold_grads");
   return STGCN_OK;
 }
 

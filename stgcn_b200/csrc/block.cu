@@ -86,6 +86,14 @@ template <class T> struct Engine {
     STGCN_TRY(launch_pack_weights<float>(wsrc, wi, g.taps, g.n_out, g.c, wp, st, std::is_same<T, bf16>::value ? 1 : 0));
     return launch_conv_gemm_simt<T>(g, in, wp, ep, out, st);
   }
+  // same, with the weights already packed as bf16 [taps][n_out][c] by the caller (folded BatchNorm path)
+  int32_t gemm_packed(const ConvGeom& g, const T* in, const bf16* wp, const GemmEpilogue& ep, T* out) {
+    if (ws.dry) return STGCN_OK;
+    if constexpr (std::is_same<T, bf16>::value) {
+      if (umma_conv_gemm_supported(g)) return launch_conv_gemm_umma(g, in, wp, ep, out, st);
+    }
+    set_error("gemm_packed: geometry not supported by the tcgen05 engine"); return STGCN_ERR_UNSUPPORTED;
+  }
   // dw (reference layout, overwritten) = sum over rows of dout (x) in
   int32_t wgrad(const ConvGeom& g, const T* dout, const T* in, const WIndex& wi, float* dw, size_t dw_floats) {
     if (want_umma() && umma_wgrad_supported(g) && (g.n_out == 64 || g.n_out % 128 == 0)) {
@@ -112,6 +120,18 @@ constexpr int kNoDiv = 1 << 30;
 // ---------------------------------------------------------------------------
 // spatial graph convolution:  S = sum_k (A_k h) W_k^T + bias through A
 // ---------------------------------------------------------------------------
+// BatchNorm-1 can be folded into the 1x1 weights when nothing non-linear sits between it and the aggregation
+// (default block, st_graphconv.py:98-99) and every contraction of the spatial stage runs on the tcgen05 engine.
+template <class T> static bool fold_ok(const Engine<T>& e, const Dims& m, const float* aff_a, int relu1) {
+  if (!std::is_same<T, bf16>::value || !aff_a || relu1 || !e.want_umma()) return false;
+  if (!umma_agg_supported(m.v, m.ci, m.k) || m.k * m.co > 1024) return false;
+  const int KCi = m.k * m.ci;
+  return umma_conv_gemm_supported(geom(m.n, m.t, m.t, m.v, KCi, m.co, 1, 1, 0, 0)) &&
+         umma_conv_gemm_supported(geom(m.n, m.t, m.t, m.v, m.co, KCi, 1, 1, 0, 0));
+}
+template <class T> struct Bn1Fold {      // backward of the folded BatchNorm-1 (spatial_bwd fills dgamma / dbeta / dx itself)
+  const float* stats; int training; float* dgamma; float* dbeta; T* dx; bool done;
+};
 template <class T>
 static int32_t spatial_fwd(Engine<T>& e, const Dims& m, const T* x, const float* aff_a, const float* aff_b, int relu1,
                            const float* A, const float* W, const float* Wb, T* S) {
@@ -120,6 +140,24 @@ static int32_t spatial_fwd(Engine<T>& e, const Dims& m, const T* x, const float*
   float* b2d = ws.template get<float>((size_t)m.v * m.co);
   bool tc_agg = false;
   if constexpr (std::is_same<T, bf16>::value) tc_agg = e.want_umma() && umma_agg_supported(m.v, m.ci, m.k);
+  if constexpr (std::is_same<T, bf16>::value) {
+    if (fold_ok<T>(e, m, aff_a, relu1)) {
+      // BatchNorm-1 folded into the 1x1 weights: aggregate the RAW input, GEMM-1 against W.diag(a), shift through bias2d
+      const int KCi = m.k * m.ci;
+      void* prep = ws.template get<uint8_t>(umma_agg_prep_bytes(m.k));
+      bf16* w2p = ws.template get<bf16>((size_t)m.co * KCi);
+      bf16* w2pT = ws.template get<bf16>((size_t)m.co * KCi);
+      float* wb = ws.template get<float>((size_t)m.k * m.co);
+      float* wbb = ws.template get<float>((size_t)m.k * m.co);
+      if (ws.dry) return STGCN_OK;
+      if (!ws.ok()) return STGCN_ERR_WORKSPACE;
+      STGCN_TRY(launch_build_big_adjacency(A, m.k, m.v, prep, e.st));
+      STGCN_TRY(launch_bn1_fold(W, Wb, A, umma_agg_rowsum_q(prep, m.k), aff_a, aff_b, m.k, m.v, m.co, m.ci, w2p, w2pT, wb, wbb, b2d, e.st));
+      STGCN_TRY(launch_agg_fwd_umma(x, m.n, m.t, m.v, m.ci, m.k, prep, nullptr, nullptr, XA, e.st));
+      GemmEpilogue ep; ep.bias2d = b2d;
+      return e.gemm_packed(geom(m.n, m.t, m.t, m.v, KCi, m.co, 1, 1, 0, 0), XA, w2p, ep, S);
+    }
+  }
   if (tc_agg) {
     // tensor-core aggregation: BN-1 affine rides in the epilogue; a ReLU in between (residual block) needs h stored
     void* prep = ws.template get<uint8_t>(umma_agg_prep_bytes(m.k));
@@ -151,12 +189,45 @@ static int32_t spatial_fwd(Engine<T>& e, const Dims& m, const T* x, const float*
 // gradients of the above given dS; dx_pre = d/d(h) masked by relu1 (NOT yet through the BN)
 template <class T>
 static int32_t spatial_bwd(Engine<T>& e, const Dims& m, const T* x, const float* aff_a, const float* aff_b, int relu1,
-                           const float* A, const float* W, const float* Wb, const T* dS, T* dh, float* dA, float* dW, float* dWb) {
+                           const float* A, const float* W, const float* Wb, const T* dS, T* dh, float* dA, float* dW, float* dWb,
+                           Bn1Fold<T>* bf = nullptr) {
   Arena& ws = e.ws;
   const int KCi = m.k * m.ci;
   T* XA = ws.template get<T>(m.rows_in * KCi);
   T* dXA = ws.template get<T>(m.rows_in * KCi);
   float* t1 = ws.template get<float>((size_t)m.v * m.co);
+  if constexpr (std::is_same<T, bf16>::value) {
+    if (bf && fold_ok<T>(e, m, aff_a, relu1)) {
+      bf->done = true;
+      void* prep = ws.template get<uint8_t>(umma_agg_prep_bytes(m.k));
+      bf16* w2p = ws.template get<bf16>((size_t)m.co * KCi);
+      bf16* w2pT = ws.template get<bf16>((size_t)m.co * KCi);
+      float* wb = ws.template get<float>((size_t)m.k * m.co);
+      float* wbb = ws.template get<float>((size_t)m.k * m.co);
+      float* b2d = ws.template get<float>((size_t)m.v * m.co);
+      float* coef = ws.template get<float>((size_t)3 * m.ci);
+      if (!ws.dry) {
+        if (!ws.ok()) return STGCN_ERR_WORKSPACE;
+        STGCN_TRY(launch_build_big_adjacency(A, m.k, m.v, prep, e.st));
+        STGCN_TRY(launch_bn1_fold(W, Wb, A, umma_agg_rowsum_q(prep, m.k), aff_a, aff_b, m.k, m.v, m.co, m.ci, w2p, w2pT, wb, wbb, b2d, e.st));
+        STGCN_TRY(launch_agg_fwd_umma(x, m.n, m.t, m.v, m.ci, m.k, prep, nullptr, nullptr, XA, e.st));     // raw-input XA, recomputed
+        cudaMemsetAsync(dA, 0, sizeof(float) * (size_t)m.k * m.v * m.v, e.st);
+        cudaMemsetAsync(t1, 0, sizeof(float) * (size_t)m.v * m.co, e.st);
+        STGCN_TRY(launch_vcolsum<T>(dS, m.frames_in, m.v, m.co, t1, e.st));
+      }
+      STGCN_TRY(e.wgrad(geom(m.n, m.t, m.t, m.v, KCi, m.co, 1, 1, 0, 0), dS, XA, widx(kNoDiv, 0, m.ci, m.ci, (long long)m.co * m.ci, 1, 0),
+                        dW, (size_t)m.k * m.co * m.ci));                                                    // raw: w.r.t. W.diag(a)
+      GemmEpilogue ep;
+      STGCN_TRY(e.gemm_packed(geom(m.n, m.t, m.t, m.v, m.co, KCi, 1, 1, 0, 0), dS, w2pT, ep, dXA));         // dXA' = dXA (.) a
+      if (ws.dry) return STGCN_OK;
+      STGCN_TRY(launch_agg_dA_umma(dXA, x, m.n, m.t, m.v, m.ci, m.k, dA, e.st));
+      STGCN_TRY(launch_spatial_bias_grads(t1, A, Wb, m.k, m.v, m.co, dWb, dA, e.st, wbb));
+      STGCN_TRY(launch_bn1_fold_grads(W, dW, bf->stats, t1, umma_agg_rowsum_q(prep, m.k), m.k, m.v, m.co, m.ci, bf->training,
+                                      (double)m.rows_in, bf->dgamma, bf->dbeta, coef, e.st));
+      if (bf->dx) STGCN_TRY(launch_agg_bwd_umma(dXA, m.n, m.t, m.v, m.ci, m.k, prep, nullptr, bf->dx, e.st, x, coef));
+      return STGCN_OK;
+    }
+  }
   bool tc_agg = false;
   if constexpr (std::is_same<T, bf16>::value) tc_agg = e.want_umma() && umma_agg_supported(m.v, m.ci, m.k);
   void* prep = tc_agg ? ws.template get<uint8_t>(umma_agg_prep_bytes(m.k)) : nullptr;
@@ -329,8 +400,9 @@ static int32_t block_backward_t(const StgcnBlockDesc& d, const T* x, const T* y,
     STGCN_TRY(launch_bn_bwd_finalize(partials, nblk, m.co, sums2, G.bn2_weight, G.bn2_bias, st));
     STGCN_TRY(launch_bn_bwd_apply<T>(dTin, S.S, S.stats2, sums2, m.rows_in, m.co, 1, d.training, 0.f, 0, 0, dS, st));
   }
-  STGCN_TRY(spatial_bwd<T>(e, m, x, S.stats1 + 2 * m.ci, S.stats1 + 3 * m.ci, relu1, P.A, P.W, P.W_bias, dS, dh, G.A, G.W, G.W_bias));
-  if (!ws.dry) {
+  Bn1Fold<T> bf{S.stats1, d.training, G.bn1_weight, G.bn1_bias, dx, false};
+  STGCN_TRY(spatial_bwd<T>(e, m, x, S.stats1 + 2 * m.ci, S.stats1 + 3 * m.ci, relu1, P.A, P.W, P.W_bias, dS, dh, G.A, G.W, G.W_bias, &bf));
+  if (!ws.dry && !bf.done) {
     STGCN_TRY(launch_bn_bwd_reduce<T>(dh, x, S.stats1, m.rows_in, m.ci, 0, 0.f, 0, 0, partials, &nblk, st));
     STGCN_TRY(launch_bn_bwd_finalize(partials, nblk, m.ci, sums1, G.bn1_weight, G.bn1_bias, st));
     if (dx) STGCN_TRY(launch_bn_bwd_apply<T>(dh, x, S.stats1, sums1, m.rows_in, m.ci, 0, d.training, 0.f, 0, 0, dx, st));

@@ -71,7 +71,11 @@ template <class T> int32_t launch_agg_dA(const T* dxa, const T* x, long long fra
 template <class T> int32_t launch_vcolsum(const T* ds, long long frames, int V, int C, float* t1, cudaStream_t st);
 int32_t launch_bias2d(const float* A, const float* bias, int K, int V, int Co, float* out, cudaStream_t st);
 int32_t launch_spatial_bias_grads(const float* t1, const float* A, const float* bias, int K, int V, int Co, float* dbias, float* dA,
-                                  cudaStream_t st);
+                                  cudaStream_t st, const float* bias_dA = nullptr);
+int32_t launch_bn1_fold(const float* W, const float* Wb, const float* A, const float* rowsum_q, const float* a, const float* b, int K,
+                        int V, int Co, int Ci, bf16* w2p, bf16* w2pT, float* wb, float* wbb, float* bias2d, cudaStream_t st);
+int32_t launch_bn1_fold_grads(const float* W, float* dW, const float* stats, const float* t1, const float* rowsum_q, int K, int V,
+                              int Co, int Ci, int training, double rows, float* dgamma, float* dbeta, float* coef, cudaStream_t st);
 
 // gemm_simt.cu
 template <class T> int32_t launch_conv_gemm_simt(const ConvGeom& g, const T* in, const float* w, const GemmEpilogue& ep, T* out,
@@ -98,7 +102,8 @@ int32_t launch_build_big_adjacency(const float* A, int K, int V, void* prep_mem,
 int32_t launch_agg_fwd_umma(const bf16* x, int nb, int t, int v, int c, int k, const void* prep, const float* aff_a,
                             const float* aff_b, bf16* xa, cudaStream_t st);
 int32_t launch_agg_bwd_umma(const bf16* dxa, int nb, int t, int v, int c, int k, const void* prep, const bf16* mask_h, bf16* dh,
-                            cudaStream_t st);
+                            cudaStream_t st, const bf16* bn_x = nullptr, const float* bn_coef = nullptr);
+const float* umma_agg_rowsum_q(const void* prep, int k);
 int32_t launch_agg_dA_umma(const bf16* dxa, const bf16* h, int nb, int t, int v, int c, int k, float* dA, cudaStream_t st);
 
 // head_kernels.cu

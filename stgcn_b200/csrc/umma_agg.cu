@@ -86,6 +86,7 @@ struct AggParams {
   const float* aff_a; const float* aff_b;  // fwd epilogue affine (may be null)
   const float* rowsum;                     // [K][V]
   const bf16* mask_h;                      // bwd: zero where h <= 0 (may be null), layout [rows][c]
+  const bf16* bn_x; const float* bn_coef;  // bwd: fused BatchNorm-1 backward  dx = dh' - c1 - (x - mean)*c2 ; coef = [3][C] {mean, c1, c2}
 };
 
 // smem: bigA (K x 32 KB) | stages x (nch/64 x 16 KB) | staging 2 x 16 KB | barriers
@@ -105,6 +106,7 @@ agg_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_constan
   uint64_t* tempty_bar = tfull_bar + 2;
   uint64_t* big_bar = tempty_bar + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(big_bar + 1);
+  float* aff_tab = reinterpret_cast<float*>(full_bar + 32);          // [3][C] per-channel epilogue coefficients
   const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
 
   {  // padding rows of the activation tiles must be finite (they meet BigA's zero columns)
@@ -181,6 +183,15 @@ agg_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_constan
     const int fl = row / p.v, vv = row % p.v;
     const int c_out_total = p.transpose ? p.c : p.k * p.c;
     int as = 0; uint32_t aphase = 0; int chunk_ctr = 0;
+    const bool affine = !p.transpose && p.aff_a;
+    const bool bnb = p.transpose && p.bn_coef;
+    if (affine) {
+      for (int i = et; i < p.c; i += 128) { aff_tab[i] = __ldg(p.aff_a + i); aff_tab[p.c + i] = __ldg(p.aff_b + i); }
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+    } else if (bnb) {
+      for (int i = et; i < 3 * p.c; i += 128) aff_tab[i] = __ldg(p.bn_coef + i);
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+    }
     for (int item = blockIdx.x; item < p.total_items; item += gridDim.x) {
       int cch, j0, b; decode(item, cch, j0, b);
       const bool row_valid = row < p.ft * p.v && (j0 + fl) < p.t;
@@ -205,9 +216,15 @@ agg_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_constan
             float f[32];
 #pragma unroll
             for (int i = 0; i < 32; ++i) f[i] = __uint_as_float(r[i]);
-            if (!p.transpose && p.aff_a) {
+            if (affine) {
+              const float4* ta = reinterpret_cast<const float4*>(aff_tab + c0);
+              const float4* tb = reinterpret_cast<const float4*>(aff_tab + p.c + c0);
 #pragma unroll
-              for (int i = 0; i < 32; ++i) f[i] = fmaf(__ldg(p.aff_a + c0 + i), f[i], __ldg(p.aff_b + c0 + i) * rs);
+              for (int g = 0; g < 8; ++g) {
+                const float4 a4 = ta[g], b4 = tb[g];
+                f[g * 4 + 0] = fmaf(a4.x, f[g * 4 + 0], b4.x * rs); f[g * 4 + 1] = fmaf(a4.y, f[g * 4 + 1], b4.y * rs);
+                f[g * 4 + 2] = fmaf(a4.z, f[g * 4 + 2], b4.z * rs); f[g * 4 + 3] = fmaf(a4.w, f[g * 4 + 3], b4.w * rs);
+              }
             }
             if (p.transpose && p.mask_h && row_valid) {
               const uint4* hp = reinterpret_cast<const uint4*>(p.mask_h + (size_t)grow * p.c + c0);
@@ -219,6 +236,27 @@ agg_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_constan
                 for (int e = 0; e < 4; ++e) {
                   if (!(__low2float(h2[e]) > 0.f)) f[g * 8 + 2 * e] = 0.f;
                   if (!(__high2float(h2[e]) > 0.f)) f[g * 8 + 2 * e + 1] = 0.f;
+                }
+              }
+            }
+            if (bnb && row_valid) {
+              const uint4* xp = reinterpret_cast<const uint4*>(p.bn_x + (size_t)grow * p.c + c0);
+              const float4* mu4 = reinterpret_cast<const float4*>(aff_tab + c0);
+              const float4* c14 = reinterpret_cast<const float4*>(aff_tab + p.c + c0);
+              const float4* c24 = reinterpret_cast<const float4*>(aff_tab + 2 * p.c + c0);
+#pragma unroll
+              for (int g = 0; g < 4; ++g) {
+                const uint4 u = __ldg(xp + g);
+                const __nv_bfloat162* x2 = reinterpret_cast<const __nv_bfloat162*>(&u);
+                float xv[8];
+#pragma unroll
+                for (int e = 0; e < 4; ++e) { xv[2 * e] = __low2float(x2[e]); xv[2 * e + 1] = __high2float(x2[e]); }
+#pragma unroll
+                for (int hh = 0; hh < 2; ++hh) {
+                  const float4 m = mu4[g * 2 + hh], a1 = c14[g * 2 + hh], a2 = c24[g * 2 + hh];
+                  float* ff = f + g * 8 + hh * 4; const float* xx = xv + hh * 4;
+                  ff[0] = ff[0] - a1.x - (xx[0] - m.x) * a2.x; ff[1] = ff[1] - a1.y - (xx[1] - m.y) * a2.y;
+                  ff[2] = ff[2] - a1.z - (xx[2] - m.z) * a2.z; ff[3] = ff[3] - a1.w - (xx[3] - m.w) * a2.w;
                 }
               }
             }
@@ -371,8 +409,11 @@ static int32_t make_act_map(CUtensorMap* m, const bf16* base, int cols, int v, i
   return make_tmap_bf16(m, base, 5, dims, str, box);
 }
 
+const float* umma_agg_rowsum_q(const void* prep, int k) { return carve_agg_prep(const_cast<void*>(prep), k).rowsum; }
+
 static int32_t launch_agg_common(int transpose, const bf16* in, int nb, int t, int v, int c, int k, const void* prep_mem,
-                                 const float* aff_a, const float* aff_b, const bf16* mask_h, bf16* out, cudaStream_t st) {
+                                 const float* aff_a, const float* aff_b, const bf16* mask_h, bf16* out, cudaStream_t st,
+                                 const bf16* bn_x = nullptr, const float* bn_coef = nullptr) {
   if (!umma_agg_supported(v, c, k)) { set_error("umma agg: unsupported shape V=%d C=%d K=%d", v, c, k); return STGCN_ERR_UNSUPPORTED; }
   AggPrep prep = carve_agg_prep(const_cast<void*>(prep_mem), k);
   AggParams p; memset(&p, 0, sizeof(p));
@@ -380,9 +421,9 @@ static int32_t launch_agg_common(int transpose, const bf16* in, int nb, int t, i
   p.nch = c % 128 == 0 ? 128 : 64;
   p.c_chunks = c / p.nch; p.m_tiles_per_b = cdiv(t, p.ft); p.total_items = p.c_chunks * p.m_tiles_per_b * nb;
   p.tile_bytes = (uint32_t)(p.ft * v * 128);
-  p.aff_a = aff_a; p.aff_b = aff_b; p.rowsum = prep.rowsum; p.mask_h = mask_h;
+  p.aff_a = aff_a; p.aff_b = aff_b; p.rowsum = prep.rowsum; p.mask_h = mask_h; p.bn_x = bn_x; p.bn_coef = bn_coef;
   const size_t stage_bytes = (size_t)(p.nch / 64) * kTile16K;
-  const size_t fixed = (size_t)k * 2 * kTile16K + 2 * kTile16K + 1024 + 512;
+  const size_t fixed = (size_t)k * 2 * kTile16K + 2 * kTile16K + 1024 + 512 + 3 * (size_t)c * sizeof(float);
   int stages = (int)((220 * 1024 - fixed) / stage_bytes);
   if (stages > 4) stages = 4;
   if (stages < 2) { set_error("umma agg: not enough shared memory"); return STGCN_ERR_UNSUPPORTED; }
@@ -414,9 +455,9 @@ int32_t launch_agg_fwd_umma(const bf16* x, int nb, int t, int v, int c, int k, c
   return launch_agg_common(0, x, nb, t, v, c, k, prep, aff_a, aff_b, nullptr, xa, st);
 }
 int32_t launch_agg_bwd_umma(const bf16* dxa, int nb, int t, int v, int c, int k, const void* prep, const bf16* mask_h, bf16* dh,
-                            cudaStream_t st) {
+                            cudaStream_t st, const bf16* bn_x, const float* bn_coef) {
   KernelTimer kt_(KC_AGG_BWD, 2.0 * nb * t * v * v * (double)k * c, st);
-  return launch_agg_common(1, dxa, nb, t, v, c, k, prep, nullptr, nullptr, mask_h, dh, st);
+  return launch_agg_common(1, dxa, nb, t, v, c, k, prep, nullptr, nullptr, mask_h, dh, st, bn_x, bn_coef);
 }
 
 int32_t launch_agg_dA_umma(const bf16* dxa, const bf16* h, int nb, int t, int v, int c, int k, float* dA, cudaStream_t st) {

@@ -174,8 +174,12 @@ conv_gemm_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_c
 #pragma unroll
           for (int i = 0; i < 32; ++i) f[i] = __uint_as_float(r[i]);
           if (p.bias) {
+            const float4* bp = reinterpret_cast<const float4*>(p.bias + n0);
 #pragma unroll
-            for (int i = 0; i < 32; ++i) f[i] += __ldg(p.bias + n0 + i);
+            for (int g = 0; g < 8; ++g) {
+              const float4 t = __ldg(bp + g);
+              f[g * 4 + 0] += t.x; f[g * 4 + 1] += t.y; f[g * 4 + 2] += t.z; f[g * 4 + 3] += t.w;
+            }
           }
           if (p.b2_smem) {
             const float4* b2 = reinterpret_cast<const float4*>(b2_tab + vv * b2_ld + col0);
@@ -190,8 +194,14 @@ conv_gemm_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_c
             for (int i = 0; i < 32; ++i) f[i] += __ldg(b2 + i);
           }
           if (p.scale) {
+            const float4* sp = reinterpret_cast<const float4*>(p.scale + n0);
+            const float4* hp = reinterpret_cast<const float4*>(p.shift + n0);
 #pragma unroll
-            for (int i = 0; i < 32; ++i) f[i] = fmaf(__ldg(p.scale + n0 + i), f[i], __ldg(p.shift + n0 + i));
+            for (int g = 0; g < 8; ++g) {
+              const float4 a4 = __ldg(sp + g), b4 = __ldg(hp + g);
+              f[g * 4 + 0] = fmaf(a4.x, f[g * 4 + 0], b4.x); f[g * 4 + 1] = fmaf(a4.y, f[g * 4 + 1], b4.y);
+              f[g * 4 + 2] = fmaf(a4.z, f[g * 4 + 2], b4.z); f[g * 4 + 3] = fmaf(a4.w, f[g * 4 + 3], b4.w);
+            }
           }
           if (p.residual && row_valid) {
             const uint4* rp = reinterpret_cast<const uint4*>(p.residual + (size_t)grow * p.n_out + n0);
@@ -305,6 +315,9 @@ int32_t launch_conv_gemm_umma(const ConvGeom& g, const bf16* in, const bf16* w, 
   KernelTimer kt_(KC_UMMA_GEMM, 2.0 * g.nb * g.t_out * g.v * (double)g.c * g.n_out * g.taps, st);
   if (!umma_conv_gemm_supported(g)) { set_error("umma conv-gemm: unsupported geometry"); return STGCN_ERR_UNSUPPORTED; }
   if (ep.accumulate) { set_error("umma conv-gemm: accumulate epilogue unsupported"); return STGCN_ERR_UNSUPPORTED; }
+  if (((uintptr_t)ep.bias | (uintptr_t)ep.scale | (uintptr_t)ep.shift) & 15) {
+    set_error("umma conv-gemm: bias / scale / shift must be 16-byte aligned"); return STGCN_ERR_INVALID;
+  }
   UmmaParams p; memset(&p, 0, sizeof(p));
   const int s = g.stride;
   p.nb = g.nb; p.v = g.v; p.ft = 128 / g.v; p.t_out = g.t_out; p.n_out = g.n_out;

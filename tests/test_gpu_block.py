@@ -114,7 +114,13 @@ def test_block_matches_oracle(case, training, dtype):
         y_ref, dx_ref, g_ref, p_after = oracle_block(x, gy, p, cfg, training, bf16=True)
         assert rel_err(y, y_ref) < tol
     kinks = check_dx_kink_tolerant(dx, dx_ref, tol * 2)
-    ptol = tol * 2 if kinks == 0 else 5e-2       # a flipped ReLU element moves each parameter gradient by one term
+    # ReLU-kink flips seen directly on the output mask: a pre-activation within one bf16 ulp of zero may take the
+    # other branch (fp32 accumulation order differs).  They must be rare (<= 1e-4 of the elements); each one moves a
+    # whole (c_out, :, :) slice of the temporal weight gradient by |gy * S| / rows, which on these tiny test
+    # tensors (a few hundred rows) is several percent of max|grad| -- measured 7e-2 with 2 flips of 82944.
+    flips = int(((y > 0) != (y_ref > 0)).sum())
+    assert flips <= max(2, int(1e-4 * y.numel())), flips
+    ptol = tol * 2 if (kinks == 0 and flips == 0) else (5e-2 if flips == 0 else 1e-1)
     for k, v in grads.items():
         ref = g_ref[k]
         if training and not res and k == 'temporalConv.bias':
