@@ -58,13 +58,16 @@ static int32_t validate(const StgcnBlockDesc* d) {
 }
 
 // saved-for-backward layout
-template <class T> struct Saved { float* stats1; float* stats2; T* S; T* U; };
+static bool fold_ok_desc(const StgcnBlockDesc& d, const Dims& m);
+template <class T> struct Saved { float* stats1; float* stats2; T* S; T* U; T* XA; };
 template <class T> static Saved<T> carve_saved(Arena& a, const StgcnBlockDesc& d, const Dims& m) {
   Saved<T> s;
   s.stats1 = a.get<float>(4 * m.ci);
   s.stats2 = a.get<float>(4 * m.co);
   s.S = a.get<T>(m.rows_in * m.co);
   s.U = d.residual == STGCN_RES_NONE ? a.get<T>(m.rows_out * m.co) : nullptr;
+  // folded-BatchNorm path: the aggregated raw input (rows x K*C_in) is kept so backward does not re-aggregate
+  s.XA = fold_ok_desc(d, m) ? a.get<T>(m.rows_in * m.k * m.ci) : nullptr;
   return s;
 }
 
@@ -122,21 +125,27 @@ constexpr int kNoDiv = 1 << 30;
 // ---------------------------------------------------------------------------
 // BatchNorm-1 can be folded into the 1x1 weights when nothing non-linear sits between it and the aggregation
 // (default block, st_graphconv.py:98-99) and every contraction of the spatial stage runs on the tcgen05 engine.
-template <class T> static bool fold_ok(const Engine<T>& e, const Dims& m, const float* aff_a, int relu1) {
-  if (!std::is_same<T, bf16>::value || !aff_a || relu1 || !e.want_umma()) return false;
+static bool fold_shapes_ok(const Dims& m) {
   if (!umma_agg_supported(m.v, m.ci, m.k) || m.k * m.co > 1024) return false;
   const int KCi = m.k * m.ci;
   return umma_conv_gemm_supported(geom(m.n, m.t, m.t, m.v, KCi, m.co, 1, 1, 0, 0)) &&
          umma_conv_gemm_supported(geom(m.n, m.t, m.t, m.v, m.co, KCi, 1, 1, 0, 0));
 }
+static bool fold_ok_desc(const StgcnBlockDesc& d, const Dims& m) {       // same decision from the descriptor alone (block chains)
+  return d.dtype == STGCN_BF16 && !(d.flags & STGCN_FLAG_FORCE_SIMT) && d.residual == STGCN_RES_NONE && fold_shapes_ok(m);
+}
+template <class T> static bool fold_ok(const Engine<T>& e, const Dims& m, const float* aff_a, int relu1) {
+  if (!std::is_same<T, bf16>::value || !aff_a || relu1 || !e.want_umma()) return false;
+  return fold_shapes_ok(m);
+}
 template <class T> struct Bn1Fold {      // backward of the folded BatchNorm-1 (spatial_bwd fills dgamma / dbeta / dx itself)
-  const float* stats; int training; float* dgamma; float* dbeta; T* dx; bool done;
+  const float* stats; int training; float* dgamma; float* dbeta; T* dx; bool done; const T* xa_saved;
 };
 template <class T>
 static int32_t spatial_fwd(Engine<T>& e, const Dims& m, const T* x, const float* aff_a, const float* aff_b, int relu1,
-                           const float* A, const float* W, const float* Wb, T* S) {
+                           const float* A, const float* W, const float* Wb, T* S, T* xa_keep = nullptr) {
   Arena& ws = e.ws;
-  T* XA = ws.template get<T>(m.rows_in * m.k * m.ci);
+  T* XA = xa_keep ? xa_keep : ws.template get<T>(m.rows_in * m.k * m.ci);
   float* b2d = ws.template get<float>((size_t)m.v * m.co);
   bool tc_agg = false;
   if constexpr (std::is_same<T, bf16>::value) tc_agg = e.want_umma() && umma_agg_supported(m.v, m.ci, m.k);
@@ -210,13 +219,13 @@ static int32_t spatial_bwd(Engine<T>& e, const Dims& m, const T* x, const float*
         if (!ws.ok()) return STGCN_ERR_WORKSPACE;
         STGCN_TRY(launch_build_big_adjacency(A, m.k, m.v, prep, e.st));
         STGCN_TRY(launch_bn1_fold(W, Wb, A, umma_agg_rowsum_q(prep, m.k), aff_a, aff_b, m.k, m.v, m.co, m.ci, w2p, w2pT, wb, wbb, b2d, e.st));
-        STGCN_TRY(launch_agg_fwd_umma(x, m.n, m.t, m.v, m.ci, m.k, prep, nullptr, nullptr, XA, e.st));     // raw-input XA, recomputed
+        if (!bf->xa_saved) STGCN_TRY(launch_agg_fwd_umma(x, m.n, m.t, m.v, m.ci, m.k, prep, nullptr, nullptr, XA, e.st));   // else kept by forward
         cudaMemsetAsync(dA, 0, sizeof(float) * (size_t)m.k * m.v * m.v, e.st);
         cudaMemsetAsync(t1, 0, sizeof(float) * (size_t)m.v * m.co, e.st);
         STGCN_TRY(launch_vcolsum<T>(dS, m.frames_in, m.v, m.co, t1, e.st));
       }
-      STGCN_TRY(e.wgrad(geom(m.n, m.t, m.t, m.v, KCi, m.co, 1, 1, 0, 0), dS, XA, widx(kNoDiv, 0, m.ci, m.ci, (long long)m.co * m.ci, 1, 0),
-                        dW, (size_t)m.k * m.co * m.ci));                                                    // raw: w.r.t. W.diag(a)
+      STGCN_TRY(e.wgrad(geom(m.n, m.t, m.t, m.v, KCi, m.co, 1, 1, 0, 0), dS, bf->xa_saved ? bf->xa_saved : XA,
+                        widx(kNoDiv, 0, m.ci, m.ci, (long long)m.co * m.ci, 1, 0), dW, (size_t)m.k * m.co * m.ci));   // raw: w.r.t. W.diag(a)
       GemmEpilogue ep;
       STGCN_TRY(e.gemm_packed(geom(m.n, m.t, m.t, m.v, m.co, KCi, 1, 1, 0, 0), dS, w2pT, ep, dXA));         // dXA' = dXA (.) a
       if (ws.dry) return STGCN_OK;
@@ -282,7 +291,7 @@ static int32_t block_forward_t(const StgcnBlockDesc& d, const T* x, const StgcnB
   Saved<T> S;
   const bool keep = saved_mem != nullptr || ws.dry;
   if (saved_mem) S = carve_saved<T>(sv, d, m);
-  else { S.stats1 = ws.get<float>(4 * m.ci); S.stats2 = ws.get<float>(4 * m.co); S.S = ws.get<T>(m.rows_in * m.co); S.U = nullptr; }
+  else { S.stats1 = ws.get<float>(4 * m.ci); S.stats2 = ws.get<float>(4 * m.co); S.S = ws.get<T>(m.rows_in * m.co); S.U = nullptr; S.XA = nullptr; }
   float* partials = ws.get<float>(stat_partials_bytes(std::max(m.ci, m.co)) / sizeof(float));
   Engine<T> e{d, ws, st};
   const bool res = d.residual != STGCN_RES_NONE;
@@ -298,7 +307,7 @@ static int32_t block_forward_t(const StgcnBlockDesc& d, const T* x, const StgcnB
       STGCN_TRY(launch_bn_eval_coeffs(m.ci, P.bn1_weight, P.bn1_bias, P.bn1_running_mean, P.bn1_running_var, d.bn_eps, S.stats1, st));
     }
   }
-  STGCN_TRY(spatial_fwd<T>(e, m, x, S.stats1 + 2 * m.ci, S.stats1 + 3 * m.ci, relu1, P.A, P.W, P.W_bias, S.S));
+  STGCN_TRY(spatial_fwd<T>(e, m, x, S.stats1 + 2 * m.ci, S.stats1 + 3 * m.ci, relu1, P.A, P.W, P.W_bias, S.S, saved_mem ? S.XA : nullptr));
 
   // temporal weights: packed [tap][n=co][c=ci] = Wt[(co*Co+ci)*gamma + tap]
   const WIndex wiT = widx(kNoDiv, 0, (long long)m.co * m.gamma, kNoDiv, 0, m.gamma, 1);
@@ -400,7 +409,7 @@ static int32_t block_backward_t(const StgcnBlockDesc& d, const T* x, const T* y,
     STGCN_TRY(launch_bn_bwd_finalize(partials, nblk, m.co, sums2, G.bn2_weight, G.bn2_bias, st));
     STGCN_TRY(launch_bn_bwd_apply<T>(dTin, S.S, S.stats2, sums2, m.rows_in, m.co, 1, d.training, 0.f, 0, 0, dS, st));
   }
-  Bn1Fold<T> bf{S.stats1, d.training, G.bn1_weight, G.bn1_bias, dx, false};
+  Bn1Fold<T> bf{S.stats1, d.training, G.bn1_weight, G.bn1_bias, dx, false, S.XA};
   STGCN_TRY(spatial_bwd<T>(e, m, x, S.stats1 + 2 * m.ci, S.stats1 + 3 * m.ci, relu1, P.A, P.W, P.W_bias, dS, dh, G.A, G.W, G.W_bias, &bf));
   if (!ws.dry && !bf.done) {
     STGCN_TRY(launch_bn_bwd_reduce<T>(dh, x, S.stats1, m.rows_in, m.ci, 0, 0.f, 0, 0, partials, &nblk, st));

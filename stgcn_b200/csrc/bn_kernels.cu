@@ -187,10 +187,13 @@ __device__ __forceinline__ bool reduce_partials_32x32(const float* __restrict__ 
   const int c = blockIdx.x * 32 + cl;
   double a1 = 0, a2 = 0;
   if (c < C) {
+    float f1 = 0.f, f2 = 0.f;        // <= 19 fp32 terms per slice (nblk <= 592); the cross-slice sum below is in double
+#pragma unroll 8
     for (int b = bs; b < nblk; b += 32) {
-      a1 += (double)partials[((size_t)b * 2 + 0) * C + c];
-      a2 += (double)partials[((size_t)b * 2 + 1) * C + c];
+      f1 += partials[((size_t)b * 2 + 0) * C + c];
+      f2 += partials[((size_t)b * 2 + 1) * C + c];
     }
+    a1 = f1; a2 = f2;
   }
   red[0][bs][cl] = a1; red[1][bs][cl] = a2;
   __syncthreads();

@@ -54,6 +54,7 @@ wgrad_umma_kernel(const __grid_constant__ CUtensorMap map_dout, const __grid_con
   uint64_t* tfull_bar = empty_bar + p.stages;
   uint64_t* tempty_bar = tfull_bar + 1;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 1);
+  float* tr_base = reinterpret_cast<float*>(full_bar + 32);      // 4 x [32][33] floats, after the barrier block
   const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
 
   // one-time clear: rows TMA never writes (tile padding) must read as zero, never as NaN bit patterns
@@ -134,25 +135,30 @@ wgrad_umma_kernel(const __grid_constant__ CUtensorMap map_dout, const __grid_con
       }
     }
   } else {
-    const int q = warp % 4;
-    const int row = q * 32 + lane;               // accumulator row = output channel inside the n-tile
+    const int q = warp % 4;                      // TMEM lane quarter = accumulator rows q*32 .. q*32+31 (output channels)
+    float* tr = tr_base + q * (32 * 33);         // this warp's 32x32 transpose tile (+1 padding: conflict-free both ways)
     uint32_t tphase = 0;
     for (int item = blockIdx.x; item < p.total_items; item += gridDim.x) {
       int n_t, c_t, g, kb0, kb1; decode(item, n_t, c_t, g, kb0, kb1);
       const WgGroup& G = p.groups[g];
       mbar_wait(tfull_bar, tphase);
       tc_fence_after();
-      const int n = n_t * 128 + row;
-      const bool n_ok = row < p.n_slabs * 64 && n < p.n_out && kb1 > kb0;
-      for (int t = 0; t < G.ntaps; ++t) {
-        float* dst = p.packed + ((size_t)G.w_tap[t] * p.n_out + n) * p.c + (size_t)c_t * p.c_tile;
-        for (int cc = 0; cc < p.c_tile; cc += 32) {
-          uint32_t r[32];
-          tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(t * p.c_tile + cc), r);
-          tmem_ld_wait();
-          if (n_ok) {
+      const int n0 = n_t * 128 + q * 32;          // first output channel of this warp's rows
+      const int rows_ok = (kb1 > kb0) ? max(0, min(32, min(p.n_slabs * 64 - q * 32, p.n_out - n0))) : 0;
+      if (rows_ok > 0) {
+        for (int t = 0; t < G.ntaps; ++t) {
+          float* dst = p.packed + ((size_t)G.w_tap[t] * p.n_out + n0) * p.c + (size_t)c_t * p.c_tile + lane;
+          for (int cc = 0; cc < p.c_tile; cc += 32) {
+            uint32_t r[32];
+            tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(t * p.c_tile + cc), r);
+            tmem_ld_wait();
+            // transpose through shared memory so that one red instruction covers 32 CONSECUTIVE columns of one
+            // output channel (a single 128-byte L2 atomic) instead of 32 scattered 4-byte atomics
 #pragma unroll
-            for (int i = 0; i < 32; ++i) atomicAdd(dst + cc + i, __uint_as_float(r[i]));
+            for (int i = 0; i < 32; ++i) tr[i * 33 + lane] = __uint_as_float(r[i]);
+            __syncwarp();
+            for (int rr = 0; rr < rows_ok; ++rr) atomicAdd(dst + (size_t)rr * p.c + cc, tr[lane * 33 + rr]);
+            __syncwarp();
           }
         }
       }
@@ -230,12 +236,13 @@ int32_t launch_wgrad_umma(const ConvGeom& g, const bf16* dout, const bf16* in, c
   p.b_slab = slab_rows * 128;
   p.kblocks_total = g.nb * p.jblocks;
   const int base_items = p.n_tiles * p.c_tiles * p.ngroups;
-  p.splits = std::max(1, std::min(p.kblocks_total, (2 * num_sms_wg() + base_items - 1) / base_items));
+  p.splits = std::max(1, std::min(p.kblocks_total, num_sms_wg() / base_items));   // one item per CTA: a single epilogue each
   p.total_items = base_items * p.splits;
   p.a_bytes = (uint32_t)(p.n_slabs * p.fj * g.v * 128);
   p.b_bytes = (uint32_t)((p.c_tile / 64) * (p.fj + span_max) * g.v * 128);
   const size_t stage_bytes = (size_t)p.n_slabs * kATile + (size_t)(p.c_tile / 64) * p.b_slab;
-  int stages = (int)((220 * 1024 - 2048) / stage_bytes);
+  const size_t tail_bytes = 2048 + 4 * 32 * 33 * sizeof(float);     // align slack + barriers + transpose tiles
+  int stages = (int)((220 * 1024 - tail_bytes) / stage_bytes);
   if (stages > 4) stages = 4;
   if (stages < 2) { set_error("umma wgrad: not enough shared memory"); return STGCN_ERR_UNSUPPORTED; }
   p.stages = stages;
@@ -259,7 +266,7 @@ int32_t launch_wgrad_umma(const ConvGeom& g, const bf16* dout, const bf16* in, c
     uint32_t box[5] = {64, (uint32_t)g.v, 1, (uint32_t)(p.fj + span_max), 1};
     STGCN_TRY(make_tmap_bf16(&map_in, in, 5, dims, str, box));
   }
-  const size_t smem = (size_t)stages * stage_bytes + 2048;
+  const size_t smem = (size_t)stages * stage_bytes + tail_bytes;
   static bool attr_set = false;
   if (!attr_set) {
     cudaError_t e = cudaFuncSetAttribute(wgrad_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
