@@ -3,6 +3,7 @@
 // residual_block (:60-82), SpatialConv.forward (:139-152); backward = what
 // torch autograd derives for those.
 #include <stdarg.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include "kernels.cuh"
@@ -89,6 +90,8 @@ template <class T> struct Engine {
     STGCN_TRY(launch_pack_weights<float>(wsrc, wi, g.taps, g.n_out, g.c, wp, st, std::is_same<T, bf16>::value ? 1 : 0));
     return launch_conv_gemm_simt<T>(g, in, wp, ep, out, st);
   }
+  // true when gemm() runs on the tcgen05 engine, whose epilogue can also produce BatchNorm statistics / per-joint sums
+  bool gemm_on_umma(const ConvGeom& g) const { return want_umma() && umma_conv_gemm_supported(g); }
   // same, with the weights already packed as bf16 [taps][n_out][c] by the caller (folded BatchNorm path)
   int32_t gemm_packed(const ConvGeom& g, const T* in, const bf16* wp, const GemmEpilogue& ep, T* out) {
     if (ws.dry) return STGCN_OK;
@@ -140,6 +143,7 @@ template <class T> static bool fold_ok(const Engine<T>& e, const Dims& m, const 
 }
 template <class T> struct Bn1Fold {      // backward of the folded BatchNorm-1 (spatial_bwd fills dgamma / dbeta / dx itself)
   const float* stats; int training; float* dgamma; float* dbeta; T* dx; bool done; const T* xa_saved;
+  float* t1_ready;      // per-joint column sums of dS already produced by the temporal dgrad epilogue (or null)
 };
 template <class T>
 static int32_t spatial_fwd(Engine<T>& e, const Dims& m, const T* x, const float* aff_a, const float* aff_b, int relu1,
@@ -204,7 +208,8 @@ static int32_t spatial_bwd(Engine<T>& e, const Dims& m, const T* x, const float*
   const int KCi = m.k * m.ci;
   T* XA = ws.template get<T>(m.rows_in * KCi);
   T* dXA = ws.template get<T>(m.rows_in * KCi);
-  float* t1 = ws.template get<float>((size_t)m.v * m.co);
+  float* t1 = (bf && bf->t1_ready) ? bf->t1_ready : ws.template get<float>((size_t)m.v * m.co);
+  const bool have_t1 = bf && bf->t1_ready;
   if constexpr (std::is_same<T, bf16>::value) {
     if (bf && fold_ok<T>(e, m, aff_a, relu1)) {
       bf->done = true;
@@ -221,8 +226,10 @@ static int32_t spatial_bwd(Engine<T>& e, const Dims& m, const T* x, const float*
         STGCN_TRY(launch_bn1_fold(W, Wb, A, umma_agg_rowsum_q(prep, m.k), aff_a, aff_b, m.k, m.v, m.co, m.ci, w2p, w2pT, wb, wbb, b2d, e.st));
         if (!bf->xa_saved) STGCN_TRY(launch_agg_fwd_umma(x, m.n, m.t, m.v, m.ci, m.k, prep, nullptr, nullptr, XA, e.st));   // else kept by forward
         cudaMemsetAsync(dA, 0, sizeof(float) * (size_t)m.k * m.v * m.v, e.st);
-        cudaMemsetAsync(t1, 0, sizeof(float) * (size_t)m.v * m.co, e.st);
-        STGCN_TRY(launch_vcolsum<T>(dS, m.frames_in, m.v, m.co, t1, e.st));
+        if (!have_t1) {
+          cudaMemsetAsync(t1, 0, sizeof(float) * (size_t)m.v * m.co, e.st);
+          STGCN_TRY(launch_vcolsum<T>(dS, m.frames_in, m.v, m.co, t1, e.st));
+        }
       }
       STGCN_TRY(e.wgrad(geom(m.n, m.t, m.t, m.v, KCi, m.co, 1, 1, 0, 0), dS, bf->xa_saved ? bf->xa_saved : XA,
                         widx(kNoDiv, 0, m.ci, m.ci, (long long)m.co * m.ci, 1, 0), dW, (size_t)m.k * m.co * m.ci));   // raw: w.r.t. W.diag(a)
@@ -256,8 +263,10 @@ static int32_t spatial_bwd(Engine<T>& e, const Dims& m, const T* x, const float*
       STGCN_TRY(launch_agg_fwd<T>(x, m.frames_in, m.v, m.ci, m.k, A, aff_a, aff_b, relu1, XA, e.st));
     }
     cudaMemsetAsync(dA, 0, sizeof(float) * (size_t)m.k * m.v * m.v, e.st);
-    cudaMemsetAsync(t1, 0, sizeof(float) * (size_t)m.v * m.co, e.st);
-    STGCN_TRY(launch_vcolsum<T>(dS, m.frames_in, m.v, m.co, t1, e.st));
+    if (!have_t1) {
+      cudaMemsetAsync(t1, 0, sizeof(float) * (size_t)m.v * m.co, e.st);
+      STGCN_TRY(launch_vcolsum<T>(dS, m.frames_in, m.v, m.co, t1, e.st));
+    }
   }
   STGCN_TRY(e.wgrad(geom(m.n, m.t, m.t, m.v, KCi, m.co, 1, 1, 0, 0), dS, XA, widx(kNoDiv, 0, m.ci, m.ci, (long long)m.co * m.ci, 1, 0),
                     dW, (size_t)m.k * m.co * m.ci));
@@ -316,11 +325,15 @@ static int32_t block_forward_t(const StgcnBlockDesc& d, const T* x, const StgcnB
     if (d.training || keep) {
       T* U = S.U ? S.U : ws.get<T>(m.rows_out * m.co);
       GemmEpilogue ep; ep.bias = P.Wt_bias;
+      static const bool no_fs = getenv("STGCN_NO_FUSED_STATS") != nullptr;
+      const bool fused_stats = !no_fs && d.training && e.gemm_on_umma(gt);     // BN-2 statistics ride in the GEMM epilogue
+      if (fused_stats) ep.stat_partials = partials;
       STGCN_TRY(e.gemm(gt, S.S, P.Wt, wiT, ep, U));
       if (ws.dry) return STGCN_OK;
       if (!ws.ok()) { set_error("workspace too small"); return STGCN_ERR_WORKSPACE; }
       if (d.training) {
-        STGCN_TRY(launch_colstats<T>(U, m.rows_out, m.co, partials, &nblk, st));
+        if (fused_stats) nblk = umma_conv_gemm_grid(gt);
+        else STGCN_TRY(launch_colstats<T>(U, m.rows_out, m.co, partials, &nblk, st));
         STGCN_TRY(launch_bn_finalize(partials, nblk, m.co, (double)m.rows_out, P.bn2_weight, P.bn2_bias, P.bn2_running_mean,
                                      P.bn2_running_var, (long long*)P.bn2_num_batches_tracked, d.bn_eps, d.bn_momentum, S.stats2, st));
       } else {
@@ -399,17 +412,26 @@ static int32_t block_backward_t(const StgcnBlockDesc& d, const T* x, const T* y,
   STGCN_TRY(e.wgrad(geom(m.n, m.t, m.to, m.v, m.co, m.co, m.gamma, m.stride, m.pad, 0), dU, tin,
                     widx(kNoDiv, 0, (long long)m.co * m.gamma, kNoDiv, 0, m.gamma, 1), G.Wt, (size_t)m.co * m.co * m.gamma));
   // temporal dgrad: packed [tap][n=ci][c=co] = Wt[(co*Co+ci)*gamma + tap]
+  float* t1 = ws.get<float>((size_t)m.v * m.co);     // per-joint column sums of dS (bias / BN-fold gradients)
+  bool t1_ready = false;
   {
     GemmEpilogue ep;
-    STGCN_TRY(e.gemm(geom(m.n, m.to, m.t, m.v, m.co, m.co, m.gamma, m.stride, m.pad, 1), dU, P.Wt,
-                     widx(kNoDiv, 0, m.gamma, kNoDiv, 0, (long long)m.co * m.gamma, 1), ep, dTin));
+    const ConvGeom gd = geom(m.n, m.to, m.t, m.v, m.co, m.co, m.gamma, m.stride, m.pad, 1);
+    // measured on B200: summing dS in the dgrad epilogue costs more (+60 us per launch) than the separate 30 us pass,
+    // so it is off unless STGCN_FUSED_VSUM is set (kept for re-evaluation with a wider epilogue)
+    static const bool fv = getenv("STGCN_FUSED_VSUM") != nullptr;
+    if (fv && !res && e.gemm_on_umma(gd)) {
+      if (!ws.dry) cudaMemsetAsync(t1, 0, sizeof(float) * (size_t)m.v * m.co, st);
+      ep.vsum = t1; t1_ready = true;
+    }
+    STGCN_TRY(e.gemm(gd, dU, P.Wt, widx(kNoDiv, 0, m.gamma, kNoDiv, 0, (long long)m.co * m.gamma, 1), ep, dTin));
   }
   if (res && !ws.dry) {
     STGCN_TRY(launch_bn_bwd_reduce<T>(dTin, S.S, S.stats2, m.rows_in, m.co, 1, 0.f, 0, 0, partials, &nblk, st));
     STGCN_TRY(launch_bn_bwd_finalize(partials, nblk, m.co, sums2, G.bn2_weight, G.bn2_bias, st));
     STGCN_TRY(launch_bn_bwd_apply<T>(dTin, S.S, S.stats2, sums2, m.rows_in, m.co, 1, d.training, 0.f, 0, 0, dS, st));
   }
-  Bn1Fold<T> bf{S.stats1, d.training, G.bn1_weight, G.bn1_bias, dx, false, S.XA};
+  Bn1Fold<T> bf{S.stats1, d.training, G.bn1_weight, G.bn1_bias, dx, false, S.XA, t1_ready ? t1 : nullptr};
   STGCN_TRY(spatial_bwd<T>(e, m, x, S.stats1 + 2 * m.ci, S.stats1 + 3 * m.ci, relu1, P.A, P.W, P.W_bias, dS, dh, G.A, G.W, G.W_bias, &bf));
   if (!ws.dry && !bf.done) {
     STGCN_TRY(launch_bn_bwd_reduce<T>(dh, x, S.stats1, m.rows_in, m.ci, 0, 0.f, 0, 0, partials, &nblk, st));

@@ -20,7 +20,8 @@ struct GemmEpilogue {
   int accumulate = 0;
   float dropout_p = 0.f;
   uint64_t seed = 0, offset = 0;
-  float* stat_partials = nullptr;    // tcgen05 engine only: per-CTA column sum / sumsq of the stored output
+  float* stat_partials = nullptr;    // tcgen05 engine only: per-CTA column sum / sumsq of the stored output, [grid][2][n_out]
+  float* vsum = nullptr;             // tcgen05 engine only: [V][n_out] += per-joint column sums of the stored output
 };
 
 // element (tap, n, c) of a weight tensor kept in the reference's layout
@@ -87,6 +88,7 @@ template <class T> int32_t launch_colsum(const T* x, long long rows, int C, floa
 
 // umma_gemm.cu  (tcgen05 / TMA engine, bf16)
 bool umma_conv_gemm_supported(const ConvGeom& g);
+int umma_conv_gemm_grid(const ConvGeom& g);
 int32_t launch_conv_gemm_umma(const ConvGeom& g, const bf16* in, const bf16* w, const GemmEpilogue& ep, bf16* out, cudaStream_t st);
 
 // umma_wgrad.cu  (tcgen05 weight gradient, bf16, MN-major operands)

@@ -45,6 +45,8 @@ struct UmmaParams {
   // epilogue
   const float* bias; const float* bias2d; const float* scale; const float* shift;
   int b2_smem;           // bias2d staged in shared memory as [V][bn+4] floats (only when n_tiles == 1)
+  float* stat_partials;  // [gridDim][2][n_out] per-CTA column sum / sum of squares of the STORED output (BatchNorm statistics)
+  float* vsum;           // [V][n_out] += sum over frames of the stored output (per-joint column sums)
   const bf16* residual;
   int relu;
   float dropout_p, inv_keep;
@@ -76,6 +78,8 @@ conv_gemm_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_c
   uint64_t* tempty_bar = tfull_bar + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
   float* b2_tab = reinterpret_cast<float*>(tmem_slot + 4);       // 16-byte aligned: barriers start on a 1024-byte boundary
+  float* stat_acc = b2_tab + (p.b2_smem ? p.v * (p.bn + 4) : 0);  // [2][n_out]
+  float* vsum_acc = stat_acc + (p.stat_partials ? 2 * p.n_out : 0);   // [V][n_out]
 
   const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
 
@@ -146,10 +150,11 @@ conv_gemm_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_c
     int as = 0; uint32_t aphase = 0;
     int chunk_ctr = 0;
     const int b2_ld = p.bn + 4;                    // row pitch (floats): 16-byte rows, conflict-free across joints
-    if (p.b2_smem) {
+    if (p.b2_smem)
       for (int i = et; i < p.v * p.bn; i += 128) b2_tab[(i / p.bn) * b2_ld + (i % p.bn)] = __ldg(p.bias2d + i);
-      asm volatile("bar.sync 1, 128;" ::: "memory");
-    }
+    if (p.stat_partials) for (int i = et; i < 2 * p.n_out; i += 128) stat_acc[i] = 0.f;
+    if (p.vsum) for (int i = et; i < p.v * p.n_out; i += 128) vsum_acc[i] = 0.f;
+    asm volatile("bar.sync 1, 128;" ::: "memory");
     for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
       const TileCoord tc = decode_tile(p, tile);
       mbar_wait(tfull_bar + as, aphase);
@@ -242,12 +247,47 @@ conv_gemm_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_c
           tma_store_5d(&map_out, stg, tc.n_t * p.bn + ch * 64, 0, tc.ph, tc.j0, tc.b);
           tma_store_commit();
         }
+        if (p.stat_partials || p.vsum) {
+          // column reductions of the tile as stored (bf16), read back from the swizzled staging image
+          const int vframes = min(p.ft, p.t_out_ph - tc.j0);
+          const int nbase = tc.n_t * p.bn + ch * 64;
+          if (p.stat_partials) {
+            const int col = et & 63, r0 = (et >> 6) * 64, r1 = min(r0 + 64, vframes * p.v);
+            const uint8_t* cp = stg + ((col & 7) << 1);
+            const int cj = col >> 3;
+            float s1 = 0.f, s2 = 0.f;
+            for (int r = r0; r < r1; ++r) {
+              const float vv2 = __bfloat162float(*reinterpret_cast<const bf16*>(cp + r * 128 + ((cj ^ (r & 7)) << 4)));
+              s1 += vv2; s2 = fmaf(vv2, vv2, s2);
+            }
+            atomicAdd(stat_acc + nbase + col, s1);                 // two row-halves share a column
+            atomicAdd(stat_acc + p.n_out + nbase + col, s2);
+          }
+          if (p.vsum) {
+            for (int o = et; o < p.v * 64; o += 128) {
+              const int v2 = o >> 6, col = o & 63, cj = col >> 3;
+              float sacc = 0.f;
+              for (int f2 = 0; f2 < vframes; ++f2) {
+                const int r = f2 * p.v + v2;
+                sacc += __bfloat162float(*reinterpret_cast<const bf16*>(stg + r * 128 + ((cj ^ (r & 7)) << 4) + ((col & 7) << 1)));
+              }
+              vsum_acc[v2 * p.n_out + nbase + col] += sacc;        // (v, col) of a chunk always belongs to this thread
+            }
+          }
+        }
       }
       tc_fence_before();
       mbar_arrive(tempty_bar + as);                // this thread is done reading accumulator `as`
       if (++as == 2) { as = 0; aphase ^= 1; }
     }
     if (et == 0) tma_store_wait<0>();
+    if (p.stat_partials || p.vsum) {
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      if (p.stat_partials)
+        for (int i = et; i < 2 * p.n_out; i += 128) p.stat_partials[(size_t)blockIdx.x * 2 * p.n_out + i] = stat_acc[i];
+      if (p.vsum)
+        for (int i = et; i < p.v * p.n_out; i += 128) atomicAdd(p.vsum + i, vsum_acc[i]);
+    }
   }
   tc_fence_before();
   __syncthreads();
@@ -295,6 +335,19 @@ static int pick_bn(int n_out) {
   return 64;
 }
 
+static int num_sms() {
+  static int n = 0;
+  if (!n) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev); if (n <= 0) n = 148; }
+  return n;
+}
+
+int umma_conv_gemm_grid(const ConvGeom& g) {       // CTAs the engine launches for this geometry (= number of stat partials)
+  const int phases = g.dgrad ? g.stride : 1;
+  const int ft = 128 / g.v, bn = pick_bn(g.n_out);
+  const long long tiles = (long long)(g.n_out / bn) * phases * cdiv(g.t_out / phases, ft) * g.nb;
+  return (int)std::min<long long>(tiles, num_sms());
+}
+
 bool umma_conv_gemm_supported(const ConvGeom& g) {
   if (g.c % 64 != 0 || g.n_out % 64 != 0) return false;
   if (g.v < 1 || g.v > 32 || g.taps < 1 || g.taps > kMaxTaps - 1) return false;
@@ -303,12 +356,6 @@ bool umma_conv_gemm_supported(const ConvGeom& g) {
   if (!g.dgrad && g.t_in % g.stride != 0) return false;
   if (g.dgrad && g.t_out % g.stride != 0) return false;
   return true;
-}
-
-static int num_sms() {
-  static int n = 0;
-  if (!n) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev); if (n <= 0) n = 148; }
-  return n;
 }
 
 int32_t launch_conv_gemm_umma(const ConvGeom& g, const bf16* in, const bf16* w, const GemmEpilogue& ep, bf16* out, cudaStream_t st) {
@@ -347,7 +394,10 @@ int32_t launch_conv_gemm_umma(const ConvGeom& g, const bf16* in, const bf16* w, 
   p.b_bytes = (uint32_t)(p.bn * 128);
   const size_t stage_bytes = kATileBytes + p.b_bytes;
   p.b2_smem = (ep.bias2d && p.n_tiles == 1) ? 1 : 0;
-  const size_t b2_bytes = p.b2_smem ? (size_t)g.v * (p.bn + 4) * sizeof(float) : 0;
+  p.stat_partials = ep.stat_partials; p.vsum = ep.vsum;
+  const size_t b2_bytes = (p.b2_smem ? (size_t)g.v * (p.bn + 4) * sizeof(float) : 0) +
+                          (ep.stat_partials ? 2 * (size_t)g.n_out * sizeof(float) : 0) +
+                          (ep.vsum ? (size_t)g.v * g.n_out * sizeof(float) : 0);
   const size_t fixed = 2 * kStagingBytes + 1024 /*align slack*/ + 512 /*barriers*/ + b2_bytes;
   int stages = (int)((220 * 1024 - fixed) / stage_bytes);
   if (stages > 8) stages = 8;
