@@ -236,11 +236,13 @@ static int32_t spatial_bwd(Engine<T>& e, const Dims& m, const T* x, const float*
       GemmEpilogue ep;
       STGCN_TRY(e.gemm_packed(geom(m.n, m.t, m.t, m.v, m.co, KCi, 1, 1, 0, 0), dS, w2pT, ep, dXA));         // dXA' = dXA (.) a
       if (ws.dry) return STGCN_OK;
-      STGCN_TRY(launch_agg_dA_umma(dXA, x, m.n, m.t, m.v, m.ci, m.k, dA, e.st));
-      STGCN_TRY(launch_spatial_bias_grads(t1, A, Wb, m.k, m.v, m.co, dWb, dA, e.st, wbb));
+      static const bool split_dA = getenv("STGCN_SPLIT_DA") != nullptr;       // A/B switch: separate dA kernel
+      const bool merged = bf->dx && !split_dA;                                 // dA rides in the transposed aggregation
+      if (!merged) STGCN_TRY(launch_agg_dA_umma(dXA, x, m.n, m.t, m.v, m.ci, m.k, dA, e.st));
       STGCN_TRY(launch_bn1_fold_grads(W, dW, bf->stats, t1, umma_agg_rowsum_q(prep, m.k), m.k, m.v, m.co, m.ci, bf->training,
                                       (double)m.rows_in, bf->dgamma, bf->dbeta, coef, e.st));
-      if (bf->dx) STGCN_TRY(launch_agg_bwd_umma(dXA, m.n, m.t, m.v, m.ci, m.k, prep, nullptr, bf->dx, e.st, x, coef));
+      if (bf->dx) STGCN_TRY(launch_agg_bwd_umma(dXA, m.n, m.t, m.v, m.ci, m.k, prep, nullptr, bf->dx, e.st, x, coef, merged ? dA : nullptr));
+      STGCN_TRY(launch_spatial_bias_grads(t1, A, Wb, m.k, m.v, m.co, dWb, dA, e.st, wbb));
       return STGCN_OK;
     }
   }

@@ -104,7 +104,7 @@ int32_t launch_build_big_adjacency(const float* A, int K, int V, void* prep_mem,
 int32_t launch_agg_fwd_umma(const bf16* x, int nb, int t, int v, int c, int k, const void* prep, const float* aff_a,
                             const float* aff_b, bf16* xa, cudaStream_t st);
 int32_t launch_agg_bwd_umma(const bf16* dxa, int nb, int t, int v, int c, int k, const void* prep, const bf16* mask_h, bf16* dh,
-                            cudaStream_t st, const bf16* bn_x = nullptr, const float* bn_coef = nullptr);
+                            cudaStream_t st, const bf16* bn_x = nullptr, const float* bn_coef = nullptr, float* dA = nullptr);
 const float* umma_agg_rowsum_q(const void* prep, int k);
 int32_t launch_agg_dA_umma(const bf16* dxa, const bf16* h, int nb, int t, int v, int c, int k, float* dA, cudaStream_t st);
 

@@ -87,38 +87,44 @@ struct AggParams {
   const float* rowsum;                     // [K][V]
   const bf16* mask_h;                      // bwd: zero where h <= 0 (may be null), layout [rows][c]
   const bf16* bn_x; const float* bn_coef;  // bwd: fused BatchNorm-1 backward  dx = dh' - c1 - (x - mean)*c2 ; coef = [3][C] {mean, c1, c2}
+  float* dA;                               // bwd: also accumulate dA[k][v][w] += sum dXA_k[(f,v),c] * x[(f,w),c]  (null = off)
 };
 
 // smem: bigA (K x 32 KB) | stages x (nch/64 x 16 KB) | staging 2 x 16 KB | barriers
 __global__ void __launch_bounds__(kAggUThreads, 1)
 agg_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_constant__ CUtensorMap map_big,
-                const __grid_constant__ CUtensorMap map_out, const __grid_constant__ AggParams p) {
+                const __grid_constant__ CUtensorMap map_out, const __grid_constant__ CUtensorMap map_x,
+                const __grid_constant__ AggParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   const int slabs = p.nch / 64;
   const int stage_bytes = slabs * kTile16K;
   uint8_t* smem_big = smem;                                          // [k][2 halves of 64 cols][128 rows x 128 B]
   uint8_t* smem_x = smem_big + (size_t)p.k * 2 * kTile16K;
-  uint8_t* staging = smem_x + (size_t)p.stages * stage_bytes;
+  uint8_t* smem_xb = smem_x + (size_t)p.stages * stage_bytes;        // dA mode: 2 x stage_bytes ring of raw-input tiles
+  uint8_t* staging = smem_xb + (p.dA ? 2 * (size_t)stage_bytes : 0);
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(staging + 2 * kTile16K);
   uint64_t* empty_bar = full_bar + p.stages;
   uint64_t* tfull_bar = empty_bar + p.stages;
   uint64_t* tempty_bar = tfull_bar + 2;
   uint64_t* big_bar = tempty_bar + 2;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(big_bar + 1);
+  uint64_t* xfull_bar = big_bar + 1;       // [2]
+  uint64_t* xempty_bar = xfull_bar + 2;    // [2]
+  uint64_t* done_bar = xempty_bar + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(done_bar + 1);
   float* aff_tab = reinterpret_cast<float*>(full_bar + 32);          // [3][C] per-channel epilogue coefficients
   const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
 
   {  // padding rows of the activation tiles must be finite (they meet BigA's zero columns)
     uint4* z = reinterpret_cast<uint4*>(smem_x);
-    const int n16 = p.stages * stage_bytes / 16;
+    const int n16 = (p.stages + (p.dA ? 2 : 0)) * stage_bytes / 16;
     for (int i = threadIdx.x; i < n16; i += kAggUThreads) z[i] = make_uint4(0, 0, 0, 0);
   }
   if (warp == 0 && lane == 0) {
-    prefetch_tmap(&map_in); prefetch_tmap(&map_big); prefetch_tmap(&map_out);
+    prefetch_tmap(&map_in); prefetch_tmap(&map_big); prefetch_tmap(&map_out); prefetch_tmap(&map_x);
     for (int s = 0; s < p.stages; ++s) { mbar_init(full_bar + s, 1); mbar_init(empty_bar + s, 1); }
-    for (int a = 0; a < 2; ++a) { mbar_init(tfull_bar + a, 1); mbar_init(tempty_bar + a, 128); }
-    mbar_init(big_bar, 1);
+    for (int a = 0; a < 2; ++a) { mbar_init(tfull_bar + a, 1); mbar_init(tempty_bar + a, 128); mbar_init(xfull_bar + a, 1); mbar_init(xempty_bar + a, 1); }
+    mbar_init(big_bar, 1); mbar_init(done_bar, 1);
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc(tmem_slot, p.tmem_cols);
@@ -141,9 +147,16 @@ agg_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_constan
       mbar_expect_tx(big_bar, (uint32_t)(p.k * 2 * kTile16K));
       for (int k = 0; k < p.k; ++k)
         for (int h = 0; h < 2; ++h) tma_load_2d(&map_big, smem_big + (size_t)(k * 2 + h) * kTile16K, big_bar, h * 64, k * 128);
-      int stage = 0; uint32_t phase = 0;
+      int stage = 0; uint32_t phase = 0; int xs = 0; uint32_t xphase = 0;
       for (int item = blockIdx.x; item < p.total_items; item += gridDim.x) {
         int cch, j0, b; decode(item, cch, j0, b);
+        if (p.dA) {                                  // raw-input tile of the same rows / channels: B operand of the dA products
+          mbar_wait(xempty_bar + xs, xphase ^ 1);
+          mbar_expect_tx(xfull_bar + xs, (uint32_t)slabs * p.tile_bytes);
+          for (int s = 0; s < slabs; ++s)
+            tma_load_5d(&map_x, smem_xb + (size_t)xs * stage_bytes + s * kTile16K, xfull_bar + xs, cch * p.nch + s * 64, 0, 0, j0, b);
+          if (++xs == 2) { xs = 0; xphase ^= 1; }
+        }
         for (int l = 0; l < loads_per_item; ++l) {
           mbar_wait(empty_bar + stage, phase ^ 1);
           mbar_expect_tx(full_bar + stage, (uint32_t)slabs * p.tile_bytes);
@@ -158,9 +171,12 @@ agg_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_constan
     if (lane == 0) {
       const uint32_t idesc = make_idesc_bf16(128, p.nch, 0, 1);     // A K-major (BigA), B MN-major (activation tile)
       mbar_wait(big_bar, 0);
-      int stage = 0; uint32_t phase = 0; int as = 0; uint32_t aphase = 0;
+      const uint32_t idesc_da = make_idesc_bf16(128, 32, 0, 0);      // dA: both operands K-major (channels contiguous), N = 32 >= V
+      const uint32_t g_tmem = tmem_base + (uint32_t)(2 * p.nch);     // K accumulators of 32 columns, live for the whole kernel
+      int stage = 0; uint32_t phase = 0; int as = 0; uint32_t aphase = 0; int xs = 0; uint32_t xphase = 0; bool g_first = true;
       for (int item = blockIdx.x; item < p.total_items; item += gridDim.x) {
         if (p.transpose) { mbar_wait(tempty_bar + as, aphase ^ 1); tc_fence_after(); }
+        if (p.dA) { mbar_wait(xfull_bar + xs, xphase); tc_fence_after(); }
         for (int k = 0; k < p.k; ++k) {
           if (!p.transpose) { mbar_wait(tempty_bar + as, aphase ^ 1); tc_fence_after(); }
           if (p.transpose || k == 0) { mbar_wait(full_bar + stage, phase); tc_fence_after(); }
@@ -172,11 +188,28 @@ agg_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_constan
             const uint64_t bd = make_smem_desc_sw128(x_addr, (uint32_t)kTile16K, 1024) + (uint64_t)(kk * 128);
             umma_bf16_ss(d_tmem, ad, bd, idesc, (p.transpose ? (k | kk) : kk) != 0 ? 1u : 0u);
           }
+          if (p.dA) {
+            // G_k[m][n] += sum_f sum_c dXA_k[(f, m), c] * x[(f, n), c]: per frame one M=128 x N=32 product whose operands are
+            // the SAME tile images read K-major from a start address shifted by f*V rows; only rows/cols < V are meaningful
+            const uint32_t xb_addr = smem_u32(smem_xb + (size_t)xs * stage_bytes);
+            for (int s2 = 0; s2 < slabs; ++s2)
+              for (int f = 0; f < p.ft; ++f) {
+                const uint32_t off = (uint32_t)(s2 * kTile16K + f * p.v * 128);
+                const uint64_t ad = make_smem_desc_sw128(x_addr + off, 16, 1024);
+                const uint64_t bd = make_smem_desc_sw128(xb_addr + off, 16, 1024);
+#pragma unroll
+                for (int kk = 0; kk < 4; ++kk)
+                  umma_bf16_ss(g_tmem + (uint32_t)(k * 32), ad + (uint64_t)(kk * 2), bd + (uint64_t)(kk * 2), idesc_da,
+                               (g_first && s2 == 0 && f == 0 && kk == 0) ? 0u : 1u);
+              }
+          }
           if (p.transpose || k == p.k - 1) { umma_commit(empty_bar + stage); if (++stage == p.stages) { stage = 0; phase ^= 1; } }
           if (!p.transpose) { umma_commit(tfull_bar + as); if (++as == 2) { as = 0; aphase ^= 1; } }
         }
         if (p.transpose) { umma_commit(tfull_bar + as); if (++as == 2) { as = 0; aphase ^= 1; } }
+        if (p.dA) { umma_commit(xempty_bar + xs); if (++xs == 2) { xs = 0; xphase ^= 1; } g_first = false; }
       }
+      if (p.dA) umma_commit(done_bar);
     }
   } else {
     const int q = warp % 4, row = q * 32 + lane, et = threadIdx.x - 64;
@@ -288,6 +321,20 @@ agg_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_constan
       (void)c_out_total;
     }
     if (et == 0) tma_store_wait<0>();
+    if (p.dA && q == 0) {                          // TMEM lanes 0..31 hold the rows v < V of every G_k
+      mbar_wait(done_bar, 0);
+      tc_fence_after();
+      for (int k = 0; k < p.k; ++k) {
+        uint32_t r[32];
+        tmem_ld_32x32(tmem_base + (uint32_t)(2 * p.nch + k * 32), r);
+        tmem_ld_wait();
+        if (lane < p.v) {
+#pragma unroll
+          for (int i = 0; i < 32; ++i)
+            if (i < p.v) atomicAdd(p.dA + (k * p.v + lane) * p.v + i, __uint_as_float(r[i]));
+        }
+      }
+    }
   }
   tc_fence_before();
   __syncthreads();
@@ -413,26 +460,29 @@ const float* umma_agg_rowsum_q(const void* prep, int k) { return carve_agg_prep(
 
 static int32_t launch_agg_common(int transpose, const bf16* in, int nb, int t, int v, int c, int k, const void* prep_mem,
                                  const float* aff_a, const float* aff_b, const bf16* mask_h, bf16* out, cudaStream_t st,
-                                 const bf16* bn_x = nullptr, const float* bn_coef = nullptr) {
+                                 const bf16* bn_x = nullptr, const float* bn_coef = nullptr, float* dA = nullptr) {
   if (!umma_agg_supported(v, c, k)) { set_error("umma agg: unsupported shape V=%d C=%d K=%d", v, c, k); return STGCN_ERR_UNSUPPORTED; }
   AggPrep prep = carve_agg_prep(const_cast<void*>(prep_mem), k);
   AggParams p; memset(&p, 0, sizeof(p));
   p.nb = nb; p.t = t; p.v = v; p.ft = 128 / v; p.c = c; p.k = k; p.transpose = transpose;
-  p.nch = c % 128 == 0 ? 128 : 64;
+  p.nch = (c % 128 == 0 && !dA) ? 128 : 64;          // dA mode keeps a second tile ring in shared memory: 64-channel items
+  p.dA = dA;
   p.c_chunks = c / p.nch; p.m_tiles_per_b = cdiv(t, p.ft); p.total_items = p.c_chunks * p.m_tiles_per_b * nb;
   p.tile_bytes = (uint32_t)(p.ft * v * 128);
   p.aff_a = aff_a; p.aff_b = aff_b; p.rowsum = prep.rowsum; p.mask_h = mask_h; p.bn_x = bn_x; p.bn_coef = bn_coef;
   const size_t stage_bytes = (size_t)(p.nch / 64) * kTile16K;
-  const size_t fixed = (size_t)k * 2 * kTile16K + 2 * kTile16K + 1024 + 512 + 3 * (size_t)c * sizeof(float);
+  const size_t fixed = (size_t)k * 2 * kTile16K + 2 * kTile16K + 1024 + 512 + 3 * (size_t)c * sizeof(float) +
+                       (dA ? 2 * (size_t)(p.nch / 64) * kTile16K : 0);
   int stages = (int)((220 * 1024 - fixed) / stage_bytes);
   if (stages > 4) stages = 4;
   if (stages < 2) { set_error("umma agg: not enough shared memory"); return STGCN_ERR_UNSUPPORTED; }
   p.stages = stages;
-  uint32_t cols = 32; while (cols < (uint32_t)(2 * p.nch)) cols <<= 1;
+  uint32_t cols = 32; while (cols < (uint32_t)(2 * p.nch + (dA ? k * 32 : 0))) cols <<= 1;
   p.tmem_cols = cols;
-  CUtensorMap map_in, map_big, map_out;
+  CUtensorMap map_in, map_big, map_out, map_x;
   STGCN_TRY(make_act_map(&map_in, in, transpose ? k * c : c, v, t, nb, p.ft));
   STGCN_TRY(make_act_map(&map_out, out, transpose ? c : k * c, v, t, nb, p.ft));
+  if (dA) { STGCN_TRY(make_act_map(&map_x, bn_x, c, v, t, nb, p.ft)); } else map_x = map_in;
   {
     uint64_t dims[2] = {128, (uint64_t)k * 128}; uint64_t str[1] = {256}; uint32_t box[2] = {64, 128};
     STGCN_TRY(make_tmap_bf16(&map_big, transpose ? prep.bigT : prep.big, 2, dims, str, box));
@@ -444,7 +494,7 @@ static int32_t launch_agg_common(int transpose, const bf16* in, int nb, int t, i
     if (e != cudaSuccess) { set_error("cudaFuncSetAttribute failed: %s", cudaGetErrorString(e)); return STGCN_ERR_CUDA; }
     attr_set = true;
   }
-  agg_umma_kernel<<<std::min(p.total_items, num_sms_agg()), kAggUThreads, smem, st>>>(map_in, map_big, map_out, p);
+  agg_umma_kernel<<<std::min(p.total_items, num_sms_agg()), kAggUThreads, smem, st>>>(map_in, map_big, map_out, map_x, p);
   STGCN_CHECK_LAUNCH("agg_umma");
   return STGCN_OK;
 }
@@ -455,9 +505,10 @@ int32_t launch_agg_fwd_umma(const bf16* x, int nb, int t, int v, int c, int k, c
   return launch_agg_common(0, x, nb, t, v, c, k, prep, aff_a, aff_b, nullptr, xa, st);
 }
 int32_t launch_agg_bwd_umma(const bf16* dxa, int nb, int t, int v, int c, int k, const void* prep, const bf16* mask_h, bf16* dh,
-                            cudaStream_t st, const bf16* bn_x, const float* bn_coef) {
-  KernelTimer kt_(KC_AGG_BWD, 2.0 * nb * t * v * v * (double)k * c, st);
-  return launch_agg_common(1, dxa, nb, t, v, c, k, prep, nullptr, nullptr, mask_h, dh, st, bn_x, bn_coef);
+                            cudaStream_t st, const bf16* bn_x, const float* bn_coef, float* dA) {
+  KernelTimer kt_(KC_AGG_BWD, 2.0 * nb * t * v * v * (double)k * c * (dA ? 2 : 1), st);
+  if (dA && !bn_x) { set_error("umma agg bwd: dA accumulation needs the raw input"); return STGCN_ERR_INVALID; }
+  return launch_agg_common(1, dxa, nb, t, v, c, k, prep, nullptr, nullptr, mask_h, dh, st, bn_x, bn_coef, dA);
 }
 
 int32_t launch_agg_dA_umma(const bf16* dxa, const bf16* h, int nb, int t, int v, int c, int k, float* dA, cudaStream_t st) {
