@@ -421,11 +421,13 @@ def block_forward_bf16(x, p, cfg: BlockCfg, training: bool, update_running=True,
         round_A = cfg.c_in % 64 == 0             # the tensor-core aggregation (C_in % 64 == 0) takes A as a bf16 operand
     W3 = p['spatialConv.W.weight'].reshape(K, Co, Ci)
     Wb = p['spatialConv.W.bias'].reshape(K, Co)
-    if round_A and not cfg.residual:
+    small_c = (Ci % 64 != 0) and (K * Ci <= 64) and (Co % 64 == 0) and not round_A
+    if (round_A or small_c) and not cfg.residual:
         # tensor-core default block: BatchNorm-1 is folded into the 1x1 weights.  The RAW input is aggregated
         # (bf16 A operand, XA stored in bf16), GEMM-1 runs against bf16(W.diag(a1)), and the BN shift travels
         # through the weights into the per-joint bias:  sum_k rowsum(Aq)_k[v] * (W_k b1)[co].
-        Aq = A + (_rb(A) - A).detach()           # forward rounding only: dA stays an fp32 accumulation
+        # small C_in (block 0): same algebra, but the aggregation runs on CUDA cores with the fp32 A.
+        Aq = A + (_rb(A) - A).detach() if round_A else A   # forward rounding only: dA stays an fp32 accumulation
         xa = _q(torch.einsum('kvw,nctw->nkctv', Aq, x))
         Wk = _q(W3 * a1[None, None, :])
         wb = torch.einsum('koc,c->ko', W3, b1)

@@ -174,7 +174,7 @@ constexpr int kDaPer = 8;   // accumulators per thread: 256*8 = 2048 >= 4*... se
 template <class T>
 __global__ void __launch_bounds__(kAggThreads) agg_dA_kernel(const T* __restrict__ dxa, const T* __restrict__ x, long long frames,
                                                              int V, int C, int K, const float* __restrict__ aff_a,
-                                                             const float* __restrict__ aff_b, int relu, int CC,
+                                                             const float* __restrict__ aff_b, int relu, int CC, int KC,
                                                              float* __restrict__ dA) {
   extern __shared__ float sm[];
   const int KV = K * V;
@@ -190,7 +190,6 @@ __global__ void __launch_bounds__(kAggThreads) agg_dA_kernel(const T* __restrict
     okv[j] = o < nout ? o / V : -1;
     ow[j] = o < nout ? o % V : 0;
   }
-  const int KC = K * C;
   for (long long f = blockIdx.x; f < frames; f += gridDim.x) {
     for (int c0 = 0; c0 < C; c0 += CC) {
       int cc = min(CC, C - c0);
@@ -226,18 +225,18 @@ __global__ void __launch_bounds__(kAggThreads) agg_dA_kernel(const T* __restrict
 
 template <class T>
 int32_t launch_agg_dA(const T* dxa, const T* x, long long frames, int V, int C, int K, const float* a, const float* b,
-                      int relu, float* dA, cudaStream_t st) {
+                      int relu, float* dA, cudaStream_t st, int ld) {
   KernelTimer kt_(KC_AGG_DA, 2.0 * frames * V * V * (double)K * C, st);
   if (K * V * V > kDaPer * kAggThreads) { set_error("agg_dA: K*V*V=%d too large", K * V * V); return STGCN_ERR_UNSUPPORTED; }
   int CC = std::min(C, 64);
   size_t smem = (size_t)(V + K * V) * (CC + 1) * sizeof(float);
   int blocks = (int)std::min<long long>(frames, 148 * 4);
-  agg_dA_kernel<T><<<blocks, kAggThreads, smem, st>>>(dxa, x, frames, V, C, K, a, b, relu, CC, dA);
+  agg_dA_kernel<T><<<blocks, kAggThreads, smem, st>>>(dxa, x, frames, V, C, K, a, b, relu, CC, ld > 0 ? ld : K * C, dA);
   STGCN_CHECK_LAUNCH("agg_dA");
   return STGCN_OK;
 }
-template int32_t launch_agg_dA<float>(const float*, const float*, long long, int, int, int, const float*, const float*, int, float*, cudaStream_t);
-template int32_t launch_agg_dA<bf16>(const bf16*, const bf16*, long long, int, int, int, const float*, const float*, int, float*, cudaStream_t);
+template int32_t launch_agg_dA<float>(const float*, const float*, long long, int, int, int, const float*, const float*, int, float*, cudaStream_t, int);
+template int32_t launch_agg_dA<bf16>(const bf16*, const bf16*, long long, int, int, int, const float*, const float*, int, float*, cudaStream_t, int);
 
 // ---------------------------------------------------------------------------
 // per-joint column sums  t1[v][c] = sum_f ds[f,v,c]   (feeds dW_bias and the
@@ -371,7 +370,7 @@ int32_t launch_spatial_bias_grads(const float* t1, const float* A, const float* 
 // (reference: batch_n -> spatialConv at st_graphconv.py:98-99,148-150)
 // ---------------------------------------------------------------------------
 __global__ void __launch_bounds__(128) bn1_fold_weights_kernel(const float* __restrict__ W, const float* __restrict__ a,
-                                                               const float* __restrict__ b, int K, int Co, int Ci,
+                                                               const float* __restrict__ b, int K, int Co, int Ci, int ld,
                                                                bf16* __restrict__ w2p, bf16* __restrict__ w2pT, float* __restrict__ wb) {
   __shared__ float red[4];
   const int r = blockIdx.x, k = r / Co, co = r % Co;
@@ -379,7 +378,7 @@ __global__ void __launch_bounds__(128) bn1_fold_weights_kernel(const float* __re
   for (int ci = threadIdx.x; ci < Ci; ci += blockDim.x) {
     const float w = W[(size_t)r * Ci + ci];
     const bf16 q = __float2bfloat16_rn(w * a[ci]);
-    w2p[(size_t)co * (K * Ci) + k * Ci + ci] = q;
+    w2p[(size_t)co * ld + k * Ci + ci] = q;
     w2pT[(size_t)(k * Ci + ci) * Co + co] = q;
     part = fmaf(w, b[ci], part);
   }
@@ -402,12 +401,85 @@ __global__ void __launch_bounds__(256) bias2d_fold_kernel(const float* __restric
   out[i] = s;
 }
 int32_t launch_bn1_fold(const float* W, const float* Wb, const float* A, const float* rowsum_q, const float* a, const float* b, int K,
-                        int V, int Co, int Ci, bf16* w2p, bf16* w2pT, float* wb, float* wbb, float* bias2d, cudaStream_t st) {
+                        int V, int Co, int Ci, bf16* w2p, bf16* w2pT, float* wb, float* wbb, float* bias2d, cudaStream_t st, int ld) {
   KernelTimer kt_(KC_PACK, 0.0, st);
-  bn1_fold_weights_kernel<<<K * Co, 128, 0, st>>>(W, a, b, K, Co, Ci, w2p, w2pT, wb);
+  if (ld <= 0) ld = K * Ci;
+  if (ld > K * Ci) {      // zero-padded reduction dimension (small C_in): rows / columns K*Ci..ld-1 stay zero
+    cudaMemsetAsync(w2p, 0, sizeof(bf16) * (size_t)Co * ld, st);
+    cudaMemsetAsync(w2pT, 0, sizeof(bf16) * (size_t)Co * ld, st);
+  }
+  bn1_fold_weights_kernel<<<K * Co, 128, 0, st>>>(W, a, b, K, Co, Ci, ld, w2p, w2pT, wb);
   STGCN_CHECK_LAUNCH("bn1_fold_weights");
   bias2d_fold_kernel<<<cdiv(std::max(V, K) * Co, 256), 256, 0, st>>>(A, rowsum_q, Wb, wb, K, V, Co, bias2d, wbb);
   STGCN_CHECK_LAUNCH("bias2d_fold");
+  return STGCN_OK;
+}
+
+// ---------------------------------------------------------------------------
+// small C_in (block 0: 3 coordinates): XA[r][k*C+c] = sum_w A[k,v,w] * x[f,w,c] written as zero-padded rows of
+// `ld` channels (ld = 64) so that GEMM-1 / its gradients run on the tcgen05 engine.  One thread per (frame, joint)
+// row; the frames of a CTA and A are staged in shared memory; every row is one 16-byte-vector burst.
+// ---------------------------------------------------------------------------
+template <class T>
+__global__ void __launch_bounds__(256) agg_small_fwd_kernel(const T* __restrict__ x, long long frames, int V, int C, int K, int ld,
+                                                            const float* __restrict__ A, int FB, T* __restrict__ xa) {
+  extern __shared__ float sm[];
+  float* As = sm;                   // [K][V][V]
+  float* xs = sm + K * V * V;       // [FB][V][C]
+  for (int i = threadIdx.x; i < K * V * V; i += blockDim.x) As[i] = A[i];
+  constexpr int VEC = VecN<T>::N;
+  const int KC = K * C;
+  for (long long f0 = (long long)blockIdx.x * FB; f0 < frames; f0 += (long long)gridDim.x * FB) {
+    const int nf = (int)min((long long)FB, frames - f0);
+    __syncthreads();
+    for (int i = threadIdx.x; i < nf * V * C; i += blockDim.x) xs[i] = ldf(x + f0 * V * C + i);
+    __syncthreads();
+    for (int r = threadIdx.x; r < nf * V; r += blockDim.x) {
+      const int fl = r / V, v = r % V;
+      T* op = xa + ((f0 + fl) * V + v) * (long long)ld;
+      for (int j0 = 0; j0 < ld; j0 += VEC) {
+        float o[VEC];
+#pragma unroll
+        for (int u = 0; u < VEC; ++u) {
+          const int j = j0 + u;
+          float acc = 0.f;
+          if (j < KC) {
+            const int k = j / C, c = j % C;
+            const float* ar = As + (k * V + v) * V;
+            const float* xr = xs + fl * V * C + c;
+            for (int w = 0; w < V; ++w) acc = fmaf(ar[w], xr[w * C], acc);
+          }
+          o[u] = acc;
+        }
+        stv(op + j0, o);
+      }
+    }
+  }
+}
+template <class T>
+int32_t launch_agg_small_fwd(const T* x, long long frames, int V, int C, int K, int ld, const float* A, T* xa, cudaStream_t st) {
+  KernelTimer kt_(KC_AGG_FWD, 2.0 * frames * V * V * (double)K * C, st);
+  if (K * C > ld || ld % VecN<T>::N != 0) { set_error("agg_small: K*C=%d does not fit ld=%d", K * C, ld); return STGCN_ERR_UNSUPPORTED; }
+  const int FB = std::max(1, 256 / V);
+  const size_t smem = ((size_t)K * V * V + (size_t)FB * V * C) * sizeof(float);
+  const int blocks = (int)std::min<long long>((frames + FB - 1) / FB, 148 * 8);
+  agg_small_fwd_kernel<T><<<blocks, 256, smem, st>>>(x, frames, V, C, K, ld, A, FB, xa);
+  STGCN_CHECK_LAUNCH("agg_small_fwd");
+  return STGCN_OK;
+}
+template int32_t launch_agg_small_fwd<float>(const float*, long long, int, int, int, int, const float*, float*, cudaStream_t);
+template int32_t launch_agg_small_fwd<bf16>(const bf16*, long long, int, int, int, int, const float*, bf16*, cudaStream_t);
+
+__global__ void adjacency_rowsum_kernel(const float* __restrict__ A, int KV, int V, float* __restrict__ rs) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= KV) return;
+  float s = 0.f;
+  for (int w = 0; w < V; ++w) s += A[i * V + w];
+  rs[i] = s;
+}
+int32_t launch_adjacency_rowsum(const float* A, int K, int V, float* rs, cudaStream_t st) {
+  adjacency_rowsum_kernel<<<cdiv(K * V, 128), 128, 0, st>>>(A, K * V, V, rs);
+  STGCN_CHECK_LAUNCH("adjacency_rowsum");
   return STGCN_OK;
 }
 

@@ -60,6 +60,8 @@ static int32_t validate(const StgcnBlockDesc* d) {
 
 // saved-for-backward layout
 static bool fold_ok_desc(const StgcnBlockDesc& d, const Dims& m);
+static bool smallc_ok_desc(const StgcnBlockDesc& d, const Dims& m);
+constexpr int kSmallLd = 64;      // padded K*C_in of the small-C_in path
 template <class T> struct Saved { float* stats1; float* stats2; T* S; T* U; T* XA; };
 template <class T> static Saved<T> carve_saved(Arena& a, const StgcnBlockDesc& d, const Dims& m) {
   Saved<T> s;
@@ -68,7 +70,7 @@ template <class T> static Saved<T> carve_saved(Arena& a, const StgcnBlockDesc& d
   s.S = a.get<T>(m.rows_in * m.co);
   s.U = d.residual == STGCN_RES_NONE ? a.get<T>(m.rows_out * m.co) : nullptr;
   // folded-BatchNorm path: the aggregated raw input (rows x K*C_in) is kept so backward does not re-aggregate
-  s.XA = fold_ok_desc(d, m) ? a.get<T>(m.rows_in * m.k * m.ci) : nullptr;
+  s.XA = fold_ok_desc(d, m) ? a.get<T>(m.rows_in * m.k * m.ci) : (smallc_ok_desc(d, m) ? a.get<T>(m.rows_in * kSmallLd) : nullptr);
   return s;
 }
 
@@ -101,13 +103,14 @@ template <class T> struct Engine {
     set_error("gemm_packed: geometry not supported by the tcgen05 engine"); return STGCN_ERR_UNSUPPORTED;
   }
   // dw (reference layout, overwritten) = sum over rows of dout (x) in
-  int32_t wgrad(const ConvGeom& g, const T* dout, const T* in, const WIndex& wi, float* dw, size_t dw_floats) {
+  int32_t wgrad(const ConvGeom& g, const T* dout, const T* in, const WIndex& wi, float* dw, size_t dw_floats, int c_valid = -1) {
     if (want_umma() && umma_wgrad_supported(g) && (g.n_out == 64 || g.n_out % 128 == 0)) {
       float* packed = ws.template get<float>(umma_wgrad_workspace_floats(g));
       if (ws.dry) return STGCN_OK;
       if (!ws.ok()) { set_error("workspace too small"); return STGCN_ERR_WORKSPACE; }
-      return launch_wgrad_umma(g, reinterpret_cast<const bf16*>(dout), reinterpret_cast<const bf16*>(in), wi, packed, dw, st);
+      return launch_wgrad_umma(g, reinterpret_cast<const bf16*>(dout), reinterpret_cast<const bf16*>(in), wi, packed, dw, st, c_valid);
     }
+    if (c_valid >= 0) { set_error("wgrad: padded reduction operand needs the tcgen05 engine"); return STGCN_ERR_UNSUPPORTED; }
     if (ws.dry) return STGCN_OK;
     cudaMemsetAsync(dw, 0, sizeof(float) * dw_floats, st);
     return launch_wgrad_simt<T>(g, dout, in, wi, dw, st);
@@ -137,6 +140,21 @@ static bool fold_shapes_ok(const Dims& m) {
 static bool fold_ok_desc(const StgcnBlockDesc& d, const Dims& m) {       // same decision from the descriptor alone (block chains)
   return d.dtype == STGCN_BF16 && !(d.flags & STGCN_FLAG_FORCE_SIMT) && d.residual == STGCN_RES_NONE && fold_shapes_ok(m);
 }
+// small C_in (block 0): K*C_in <= 64 is zero-padded to one 64-channel reduction block so GEMM-1, its weight gradient and
+// dXA run on the tcgen05 engine; the tiny aggregation itself stays on CUDA cores.
+static bool smallc_shapes_ok(const Dims& m) {
+  if (m.ci % 64 == 0 || m.k * m.ci > kSmallLd || m.co % 64 != 0 || m.k * m.co > 1024) return false;
+  const ConvGeom g1 = geom(m.n, m.t, m.t, m.v, kSmallLd, m.co, 1, 1, 0, 0);
+  return umma_conv_gemm_supported(g1) && umma_conv_gemm_supported(geom(m.n, m.t, m.t, m.v, m.co, kSmallLd, 1, 1, 0, 0)) &&
+         umma_wgrad_supported(g1) && (m.co == 64 || m.co % 128 == 0);
+}
+static bool smallc_ok_desc(const StgcnBlockDesc& d, const Dims& m) {
+  return d.dtype == STGCN_BF16 && !(d.flags & STGCN_FLAG_FORCE_SIMT) && d.residual == STGCN_RES_NONE && smallc_shapes_ok(m);
+}
+template <class T> static bool smallc_ok(const Engine<T>& e, const Dims& m, const float* aff_a, int relu1) {
+  if (!std::is_same<T, bf16>::value || !aff_a || relu1 || !e.want_umma()) return false;
+  return smallc_shapes_ok(m);
+}
 template <class T> static bool fold_ok(const Engine<T>& e, const Dims& m, const float* aff_a, int relu1) {
   if (!std::is_same<T, bf16>::value || !aff_a || relu1 || !e.want_umma()) return false;
   return fold_shapes_ok(m);
@@ -154,6 +172,22 @@ static int32_t spatial_fwd(Engine<T>& e, const Dims& m, const T* x, const float*
   bool tc_agg = false;
   if constexpr (std::is_same<T, bf16>::value) tc_agg = e.want_umma() && umma_agg_supported(m.v, m.ci, m.k);
   if constexpr (std::is_same<T, bf16>::value) {
+    if (smallc_ok<T>(e, m, aff_a, relu1)) {
+      // small C_in: CUDA-core aggregation of the raw input into zero-padded 64-channel rows, then the folded-BN GEMM-1
+      T* XAp = xa_keep ? xa_keep : ws.template get<T>(m.rows_in * kSmallLd);
+      bf16* w2p = ws.template get<bf16>((size_t)m.co * kSmallLd);
+      bf16* w2pT = ws.template get<bf16>((size_t)m.co * kSmallLd);
+      float* wb = ws.template get<float>((size_t)m.k * m.co);
+      float* wbb = ws.template get<float>((size_t)m.k * m.co);
+      float* rs = ws.template get<float>((size_t)m.k * m.v);
+      if (ws.dry) return STGCN_OK;
+      if (!ws.ok()) return STGCN_ERR_WORKSPACE;
+      STGCN_TRY(launch_adjacency_rowsum(A, m.k, m.v, rs, e.st));
+      STGCN_TRY(launch_bn1_fold(W, Wb, A, rs, aff_a, aff_b, m.k, m.v, m.co, m.ci, w2p, w2pT, wb, wbb, b2d, e.st, kSmallLd));
+      STGCN_TRY(launch_agg_small_fwd<T>(x, m.frames_in, m.v, m.ci, m.k, kSmallLd, A, XAp, e.st));
+      GemmEpilogue ep; ep.bias2d = b2d;
+      return e.gemm_packed(geom(m.n, m.t, m.t, m.v, kSmallLd, m.co, 1, 1, 0, 0), XAp, w2p, ep, S);
+    }
     if (fold_ok<T>(e, m, aff_a, relu1)) {
       // BatchNorm-1 folded into the 1x1 weights: aggregate the RAW input, GEMM-1 against W.diag(a), shift through bias2d
       const int KCi = m.k * m.ci;
@@ -211,6 +245,37 @@ static int32_t spatial_bwd(Engine<T>& e, const Dims& m, const T* x, const float*
   float* t1 = (bf && bf->t1_ready) ? bf->t1_ready : ws.template get<float>((size_t)m.v * m.co);
   const bool have_t1 = bf && bf->t1_ready;
   if constexpr (std::is_same<T, bf16>::value) {
+    if (bf && !bf->dx && bf->xa_saved && smallc_ok<T>(e, m, aff_a, relu1)) {
+      // small C_in, no input gradient wanted (first block): everything through the padded 64-channel operand kept by forward
+      bf->done = true;
+      T* dXAp = ws.template get<T>(m.rows_in * kSmallLd);
+      bf16* w2p = ws.template get<bf16>((size_t)m.co * kSmallLd);
+      bf16* w2pT = ws.template get<bf16>((size_t)m.co * kSmallLd);
+      float* wb = ws.template get<float>((size_t)m.k * m.co);
+      float* wbb = ws.template get<float>((size_t)m.k * m.co);
+      float* b2d = ws.template get<float>((size_t)m.v * m.co);
+      float* rs = ws.template get<float>((size_t)m.k * m.v);
+      float* coef = ws.template get<float>((size_t)3 * m.ci);
+      if (!ws.dry) {
+        if (!ws.ok()) return STGCN_ERR_WORKSPACE;
+        STGCN_TRY(launch_adjacency_rowsum(A, m.k, m.v, rs, e.st));
+        STGCN_TRY(launch_bn1_fold(W, Wb, A, rs, aff_a, aff_b, m.k, m.v, m.co, m.ci, w2p, w2pT, wb, wbb, b2d, e.st, kSmallLd));
+        cudaMemsetAsync(dA, 0, sizeof(float) * (size_t)m.k * m.v * m.v, e.st);
+        if (!have_t1) {
+          cudaMemsetAsync(t1, 0, sizeof(float) * (size_t)m.v * m.co, e.st);
+          STGCN_TRY(launch_vcolsum<T>(dS, m.frames_in, m.v, m.co, t1, e.st));
+        }
+      }
+      STGCN_TRY(e.wgrad(geom(m.n, m.t, m.t, m.v, kSmallLd, m.co, 1, 1, 0, 0), dS, bf->xa_saved,
+                        widx(kNoDiv, 0, m.ci, m.ci, (long long)m.co * m.ci, 1, 0), dW, (size_t)m.k * m.co * m.ci, KCi));
+      GemmEpilogue ep;
+      STGCN_TRY(e.gemm_packed(geom(m.n, m.t, m.t, m.v, m.co, kSmallLd, 1, 1, 0, 0), dS, w2pT, ep, dXAp));
+      if (ws.dry) return STGCN_OK;
+      STGCN_TRY(launch_agg_dA<T>(dXAp, x, m.frames_in, m.v, m.ci, m.k, nullptr, nullptr, 0, dA, e.st, kSmallLd));
+      STGCN_TRY(launch_bn1_fold_grads(W, dW, bf->stats, t1, rs, m.k, m.v, m.co, m.ci, bf->training, (double)m.rows_in, bf->dgamma,
+                                      bf->dbeta, coef, e.st));
+      return launch_spatial_bias_grads(t1, A, Wb, m.k, m.v, m.co, dWb, dA, e.st, wbb);
+    }
     if (bf && fold_ok<T>(e, m, aff_a, relu1)) {
       bf->done = true;
       void* prep = ws.template get<uint8_t>(umma_agg_prep_bytes(m.k));
@@ -500,16 +565,22 @@ size_t stgcn_block_workspace_bytes(const StgcnBlockDesc* d, int32_t backward) {
   if (validate(d) != STGCN_OK) return 0;
   StgcnBlockParams P; memset(&P, 0, sizeof(P));
   StgcnBlockGrads G; memset(&G, 0, sizeof(G));
-  Arena dry(nullptr, 0);   // dry arena: the chain only records its allocation plan, nothing is launched
-  int32_t rc;
-  if (d->dtype == STGCN_F32)
-    rc = backward ? block_backward_t<float>(*d, nullptr, nullptr, P, nullptr, nullptr, (float*)256, G, dry, 0)
-                  : block_forward_t<float>(*d, nullptr, P, nullptr, nullptr, dry, 0);
-  else
-    rc = backward ? block_backward_t<bf16>(*d, nullptr, nullptr, P, nullptr, nullptr, (bf16*)256, G, dry, 0)
-                  : block_forward_t<bf16>(*d, nullptr, P, nullptr, nullptr, dry, 0);
-  if (rc != STGCN_OK) return 0;
-  return dry.off + 256;
+  // dry arena: the chain only records its allocation plan, nothing is launched.  Backward is planned both with and
+  // without an input gradient (the first block takes a different spatial path when dx is not wanted).
+  size_t need = 0;
+  for (int pass = 0; pass < (backward ? 2 : 1); ++pass) {
+    Arena dry(nullptr, 0);
+    int32_t rc;
+    if (d->dtype == STGCN_F32)
+      rc = backward ? block_backward_t<float>(*d, nullptr, nullptr, P, nullptr, nullptr, pass ? nullptr : (float*)256, G, dry, 0)
+                    : block_forward_t<float>(*d, nullptr, P, nullptr, nullptr, dry, 0);
+    else
+      rc = backward ? block_backward_t<bf16>(*d, nullptr, nullptr, P, nullptr, nullptr, pass ? nullptr : (bf16*)256, G, dry, 0)
+                    : block_forward_t<bf16>(*d, nullptr, P, nullptr, nullptr, dry, 0);
+    if (rc != STGCN_OK) return 0;
+    need = std::max(need, dry.off);
+  }
+  return need + 256;
 }
 
 static int32_t check_ptrs(const void* a, const void* b, const void* c) {

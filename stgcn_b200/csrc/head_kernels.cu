@@ -18,6 +18,47 @@ __global__ void __launch_bounds__(256) pool_kernel(const T* __restrict__ feat, i
   }
 }
 
+// vector form: a thread owns one 16-byte channel group of one sample and strides over rows, 4 loads in flight
+template <class T>
+__global__ void __launch_bounds__(256) pool_vec_kernel(const T* __restrict__ feat, int rows, int C, float inv_rows, float* __restrict__ pooled) {
+  constexpr int VEC = VecN<T>::N;
+  const int n = blockIdx.x, cv = C / VEC, lanes = 256 / cv;        // host guarantees cv <= 256
+  const int myc = (threadIdx.x % cv) * VEC, myr = threadIdx.x / cv;
+  if (myr >= lanes) return;
+  const T* f = feat + (size_t)n * rows * C + myc;
+  float s[VEC];
+#pragma unroll
+  for (int i = 0; i < VEC; ++i) s[i] = 0.f;
+  const int step = gridDim.y * lanes;
+  int r = blockIdx.y * lanes + myr;
+  for (; r + 3 * step < rows; r += 4 * step) {
+    float a[4][VEC];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) ldv(f + (size_t)(r + u * step) * C, a[u]);
+#pragma unroll
+    for (int i = 0; i < VEC; ++i) s[i] += (a[0][i] + a[1][i]) + (a[2][i] + a[3][i]);
+  }
+  for (; r < rows; r += step) {
+    float a[VEC]; ldv(f + (size_t)r * C, a);
+#pragma unroll
+    for (int i = 0; i < VEC; ++i) s[i] += a[i];
+  }
+#pragma unroll
+  for (int i = 0; i < VEC; ++i) atomicAdd(pooled + (size_t)n * C + myc + i, s[i] * inv_rows);
+}
+template <class T>
+__global__ void __launch_bounds__(256) pool_bwd_vec_kernel(const float* __restrict__ dpooled, int rows, int C, float inv_rows, T* __restrict__ dfeat) {
+  constexpr int VEC = VecN<T>::N;
+  const int n = blockIdx.x, cv = C / VEC, lanes = 256 / cv;
+  const int myc = (threadIdx.x % cv) * VEC, myr = threadIdx.x / cv;
+  if (myr >= lanes) return;
+  float v[VEC];
+#pragma unroll
+  for (int i = 0; i < VEC; ++i) v[i] = dpooled[(size_t)n * C + myc + i] * inv_rows;
+  T* d = dfeat + (size_t)n * rows * C + myc;
+  for (int r = blockIdx.y * lanes + myr; r < rows; r += gridDim.y * lanes) stv(d + (size_t)r * C, v);
+}
+
 __global__ void __launch_bounds__(128) fc_kernel(const float* __restrict__ pooled, const float* __restrict__ w, const float* __restrict__ b,
                                                  int N, int C, int classes, float* __restrict__ logits) {
   int warp = (blockIdx.x * blockDim.x + threadIdx.x) / 32, lane = threadIdx.x % 32;
@@ -35,7 +76,12 @@ int32_t head_forward(int dtype, int n, int t, int v, int c, int classes, const v
   int rows = t * v;
   cudaMemsetAsync(pooled, 0, sizeof(float) * (size_t)n * c, st);
   dim3 grid((unsigned)n, (unsigned)std::min(rows, 16));
-  if (dtype == STGCN_F32) pool_kernel<float><<<grid, 256, 0, st>>>((const float*)feat, rows, c, 1.f / rows, pooled);
+  const int vec = dtype == STGCN_F32 ? 4 : 8;
+  if (c % vec == 0 && c / vec <= 256) {
+    dim3 gv((unsigned)n, (unsigned)std::max(1, std::min(rows / 16, cdiv(148 * 8, n))));
+    if (dtype == STGCN_F32) pool_vec_kernel<float><<<gv, 256, 0, st>>>((const float*)feat, rows, c, 1.f / rows, pooled);
+    else pool_vec_kernel<bf16><<<gv, 256, 0, st>>>((const bf16*)feat, rows, c, 1.f / rows, pooled);
+  } else if (dtype == STGCN_F32) pool_kernel<float><<<grid, 256, 0, st>>>((const float*)feat, rows, c, 1.f / rows, pooled);
   else pool_kernel<bf16><<<grid, 256, 0, st>>>((const bf16*)feat, rows, c, 1.f / rows, pooled);
   STGCN_CHECK_LAUNCH("pool");
   fc_kernel<<<cdiv((long long)n * classes * 32, 128), 128, 0, st>>>(pooled, fcw, fcb, n, c, classes, logits);
@@ -92,7 +138,12 @@ int32_t head_backward(int dtype, int n, int t, int v, int c, int classes, const 
   STGCN_CHECK_LAUNCH("fc_bwd_data");
   size_t total = (size_t)n * rows * c;
   int blocks = (int)std::min<size_t>((total + 255) / 256, 148 * 16);
-  if (dtype == STGCN_F32) pool_bwd_kernel<float><<<blocks, 256, 0, st>>>(dpooled, rows, c, 1.f / rows, total, (float*)dfeat);
+  const int vec = dtype == STGCN_F32 ? 4 : 8;
+  if (c % vec == 0 && c / vec <= 256) {
+    dim3 gv((unsigned)n, (unsigned)std::max(1, std::min(rows / 16, cdiv(148 * 8, n))));
+    if (dtype == STGCN_F32) pool_bwd_vec_kernel<float><<<gv, 256, 0, st>>>(dpooled, rows, c, 1.f / rows, (float*)dfeat);
+    else pool_bwd_vec_kernel<bf16><<<gv, 256, 0, st>>>(dpooled, rows, c, 1.f / rows, (bf16*)dfeat);
+  } else if (dtype == STGCN_F32) pool_bwd_kernel<float><<<blocks, 256, 0, st>>>(dpooled, rows, c, 1.f / rows, total, (float*)dfeat);
   else pool_bwd_kernel<bf16><<<blocks, 256, 0, st>>>(dpooled, rows, c, 1.f / rows, total, (bf16*)dfeat);
   STGCN_CHECK_LAUNCH("pool_bwd");
   return STGCN_OK;

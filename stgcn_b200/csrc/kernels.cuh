@@ -68,13 +68,17 @@ template <class T> int32_t launch_agg_fwd(const T* x, long long frames, int V, i
 template <class T> int32_t launch_agg_bwd(const T* dxa, long long frames, int V, int C, int K, const float* A, const T* x,
                                          const float* a, const float* b, int relu, T* dh, cudaStream_t st);
 template <class T> int32_t launch_agg_dA(const T* dxa, const T* x, long long frames, int V, int C, int K, const float* a,
-                                        const float* b, int relu, float* dA, cudaStream_t st);
+                                        const float* b, int relu, float* dA, cudaStream_t st, int ld = 0);
+template <class T> int32_t launch_agg_small_fwd(const T* x, long long frames, int V, int C, int K, int ld, const float* A, T* xa,
+                                               cudaStream_t st);
+int32_t launch_adjacency_rowsum(const float* A, int K, int V, float* rs, cudaStream_t st);
 template <class T> int32_t launch_vcolsum(const T* ds, long long frames, int V, int C, float* t1, cudaStream_t st);
 int32_t launch_bias2d(const float* A, const float* bias, int K, int V, int Co, float* out, cudaStream_t st);
 int32_t launch_spatial_bias_grads(const float* t1, const float* A, const float* bias, int K, int V, int Co, float* dbias, float* dA,
                                   cudaStream_t st, const float* bias_dA = nullptr);
 int32_t launch_bn1_fold(const float* W, const float* Wb, const float* A, const float* rowsum_q, const float* a, const float* b, int K,
-                        int V, int Co, int Ci, bf16* w2p, bf16* w2pT, float* wb, float* wbb, float* bias2d, cudaStream_t st);
+                        int V, int Co, int Ci, bf16* w2p, bf16* w2pT, float* wb, float* wbb, float* bias2d, cudaStream_t st,
+                        int ld = 0);
 int32_t launch_bn1_fold_grads(const float* W, float* dW, const float* stats, const float* t1, const float* rowsum_q, int K, int V,
                               int Co, int Ci, int training, double rows, float* dgamma, float* dbeta, float* coef, cudaStream_t st);
 
@@ -95,7 +99,7 @@ int32_t launch_conv_gemm_umma(const ConvGeom& g, const bf16* in, const bf16* w, 
 bool umma_wgrad_supported(const ConvGeom& g);
 size_t umma_wgrad_workspace_floats(const ConvGeom& g);
 int32_t launch_wgrad_umma(const ConvGeom& g, const bf16* dout, const bf16* in, const WIndex& wi, float* packed_ws, float* dw,
-                          cudaStream_t st);
+                          cudaStream_t st, int c_valid = -1);
 
 // umma_agg.cu  (tensor-core adjacency aggregation, bf16)
 bool umma_agg_supported(int V, int C, int K);

@@ -174,11 +174,11 @@ wgrad_umma_kernel(const __grid_constant__ CUtensorMap map_dout, const __grid_con
 
 // packed [taps][n][c] -> the reference's parameter layout
 __global__ void __launch_bounds__(256) wgrad_unpack_kernel(const float* __restrict__ packed, WIndex wi, int taps, int n_out, int c,
-                                                           float* __restrict__ dw) {
+                                                           int c_valid, float* __restrict__ dw) {
   size_t total = (size_t)taps * n_out * c;
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
     int cc = (int)(i % c); size_t r = i / c; int n = (int)(r % n_out); int tap = (int)(r / n_out);
-    dw[wi.at(tap, n, cc)] = packed[i];
+    if (cc < c_valid) dw[wi.at(tap, n, cc)] = packed[i];       // columns beyond c_valid are zero padding of the reduction operand
   }
 }
 
@@ -199,7 +199,7 @@ static int num_sms_wg() {
 }
 
 int32_t launch_wgrad_umma(const ConvGeom& g, const bf16* dout, const bf16* in, const WIndex& wi, float* packed_ws, float* dw,
-                          cudaStream_t st) {
+                          cudaStream_t st, int c_valid) {
   KernelTimer kt_(KC_UMMA_WGRAD, 2.0 * g.nb * g.t_out * g.v * (double)g.c * g.n_out * g.taps, st);
   if (!umma_wgrad_supported(g)) { set_error("umma wgrad: unsupported geometry"); return STGCN_ERR_UNSUPPORTED; }
   WgParams p; memset(&p, 0, sizeof(p));
@@ -277,7 +277,7 @@ int32_t launch_wgrad_umma(const ConvGeom& g, const bf16* dout, const bf16* in, c
   wgrad_umma_kernel<<<grid, kWgThreads, smem, st>>>(map_dout, map_in, p);
   STGCN_CHECK_LAUNCH("wgrad_umma");
   size_t total = umma_wgrad_workspace_floats(g);
-  wgrad_unpack_kernel<<<(int)std::min<size_t>((total + 255) / 256, 148 * 4), 256, 0, st>>>(packed_ws, wi, g.taps, g.n_out, g.c, dw);
+  wgrad_unpack_kernel<<<(int)std::min<size_t>((total + 255) / 256, 148 * 4), 256, 0, st>>>(packed_ws, wi, g.taps, g.n_out, g.c, c_valid < 0 ? g.c : c_valid, dw);
   STGCN_CHECK_LAUNCH("wgrad_unpack");
   return STGCN_OK;
 }

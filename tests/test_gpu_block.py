@@ -186,3 +186,37 @@ def test_spatial_conv_module_matches_oracle():
     assert rel_err(m.A.grad, Ar.grad) < TOL_F32 * 2
     assert rel_err(m.W.weight.grad, W.grad) < TOL_F32 * 2
     assert rel_err(m.W.bias.grad, b.grad) < TOL_F32 * 2
+
+
+@pytest.mark.parametrize('training', [True, False])
+def test_first_block_without_input_gradient(training):
+    """Block 0 of the stack (C_in = 3, input needs no gradient) takes the padded tensor-core path in backward."""
+    ci, co, T, V, K, s = 3, 64, 16, 25, 3, 1
+    torch.manual_seed(77)
+    A = torch.randn(K, V, V) * 0.2
+    with contextlib.redirect_stdout(io.StringIO()):
+        m = build_block(ci, co, A, s, False, dtype=torch.bfloat16)
+    with torch.no_grad():
+        for bn in (m.batch_n, m.batch_n_2):
+            bn.weight.uniform_(0.5, 1.5); bn.bias.uniform_(-0.3, 0.3)
+            bn.running_mean.uniform_(-0.2, 0.2); bn.running_var.uniform_(0.6, 1.4)
+    p = {k: v.detach().cpu().clone() for k, v in m.state_dict().items()}
+    x = torch.randn(3, ci, T, V) * 2.0 + 0.5
+    gy = torch.randn(3, co, T, V)
+    m.train(training)
+    y = m(x.cuda())                                   # x does not require grad -> dx is not computed
+    (y.float() * gy.cuda()).sum().backward()
+    grads = {k: v.grad.detach().cpu() for k, v in m.named_parameters() if v.grad is not None}
+    cfg = O.BlockCfg(ci, co, 9, s, 4, 0.0, False)
+    y_ref, _, g_ref, _ = oracle_block(x, gy, p, cfg, training, bf16=True)
+    y = y.detach().float().cpu()
+    assert rel_err(y, y_ref) < TOL_BF16
+    flips = int(((y > 0) != (y_ref > 0)).sum())
+    assert flips <= max(2, int(1e-4 * y.numel())), flips
+    ptol = TOL_BF16 * 2 if flips == 0 else 1e-1
+    for k, v in grads.items():
+        ref = g_ref[k]
+        if training and k == 'temporalConv.bias':
+            assert float(v.abs().max()) <= 1e-5 * float(gy.abs().sum())
+            continue
+        assert rel_err(v.reshape(ref.shape), ref) < ptol, k
