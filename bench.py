@@ -148,6 +148,7 @@ def main():
     ap.add_argument('--dtype', default='bf16', choices=['bf16', 'f32'])
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--only-train', action='store_true', help='profiling aid: skip the e2e and inference legs')
+    ap.add_argument('--only-infer', action='store_true', help='profiling aid: time the eval-mode forward only')
     args = ap.parse_args()
     if args.impl == 'reference':
         return run_reference(args)
@@ -202,6 +203,29 @@ def main():
         if world > 1:
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         return float(ms)
+
+    if args.only_infer:
+        for i in range(2):
+            train_step(*dev_batches[i % n_batches])          # calibrate the BatchNorm running statistics
+        model.eval()
+        with torch.no_grad():
+            for i in range(W):
+                model(dev_batches[i % n_batches][0])
+            l0 = _lib.launch_count()
+            ms_t = timed(lambda i: (flush.zero_(), model(dev_batches[i % n_batches][0])), args.steps)
+            launches = _lib.launch_count() - l0
+            ms_f = timed(lambda i: flush.zero_(), args.steps)
+            ms_inf = (ms_t - ms_f) / args.steps
+            _lib.timing_reset(); _lib.timing_enable(True)
+            timed(lambda i: (flush.zero_(), model(dev_batches[i % n_batches][0])), args.steps)
+            _lib.timing_enable(False)
+        prof = _lib.timing_read()
+        if rank == 0:
+            print(json.dumps({'infer_seq_s': S * world / (ms_inf * 1e-3), 'ms_per_step': ms_inf, 'gpu_launches': launches,
+                              'kernel_ms_per_step': {k: round(v[0] / args.steps, 4) for k, v in prof.items()}}))
+        if world > 1:
+            dist.destroy_process_group()
+        return
 
     # ---- device-resident training -------------------------------------------------------
     for i in range(W):

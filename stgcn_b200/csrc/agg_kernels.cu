@@ -250,36 +250,46 @@ __global__ void __launch_bounds__(256) vcolsum_kernel(const T* __restrict__ ds, 
   for (long long f = blockIdx.x; f < frames; f += gridDim.x) s += ldf(ds + f * VC + e);
   atomicAdd(t1 + e, s);
 }
-// vector form: one thread owns 4 consecutive (v,c) elements and strides over frames with 4 independent loads in flight
+// vector form: one thread owns one 16-byte group of consecutive (v,c) elements and strides over frames with 4 independent loads
+// in flight
 template <class T>
-__global__ void __launch_bounds__(256) vcolsum4_kernel(const T* __restrict__ ds, long long frames, int VC, float* __restrict__ t1) {
-  const int e = (blockIdx.y * 256 + threadIdx.x) * 4;
+__global__ void __launch_bounds__(256) vcolsum_vec_kernel(const T* __restrict__ ds, long long frames, int VC, float* __restrict__ t1) {
+  constexpr int VEC = VecN<T>::N;
+  const int e = (blockIdx.y * 256 + threadIdx.x) * VEC;
   if (e >= VC) return;
-  float s[4] = {0.f, 0.f, 0.f, 0.f};
+  float s[VEC];
+#pragma unroll
+  for (int i = 0; i < VEC; ++i) s[i] = 0.f;
   const long long step = gridDim.x;
   long long f = blockIdx.x;
-  for (; f + 3 * step < frames; f += 4 * step) {
-    float a[4], b[4], c[4], d[4];
-    ld4(ds + f * VC + e, a); ld4(ds + (f + step) * VC + e, b); ld4(ds + (f + 2 * step) * VC + e, c); ld4(ds + (f + 3 * step) * VC + e, d);
+  for (; f + 7 * step < frames; f += 8 * step) {
+    float a[8][VEC];
 #pragma unroll
-    for (int i = 0; i < 4; ++i) s[i] += (a[i] + b[i]) + (c[i] + d[i]);
+    for (int u = 0; u < 8; ++u) ldv(ds + (f + u * step) * VC + e, a[u]);
+#pragma unroll
+    for (int i = 0; i < VEC; ++i) s[i] += ((a[0][i] + a[1][i]) + (a[2][i] + a[3][i])) + ((a[4][i] + a[5][i]) + (a[6][i] + a[7][i]));
   }
   for (; f < frames; f += step) {
-    float a[4]; ld4(ds + f * VC + e, a);
+    float a[VEC]; ldv(ds + f * VC + e, a);
 #pragma unroll
-    for (int i = 0; i < 4; ++i) s[i] += a[i];
+    for (int i = 0; i < VEC; ++i) s[i] += a[i];
   }
+  // 16-byte vector reductions: a quarter of the L2 atomic operations of scalar atomicAdd
 #pragma unroll
-  for (int i = 0; i < 4; ++i) atomicAdd(t1 + e + i, s[i]);
+  for (int i = 0; i < VEC; i += 4)
+    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(t1 + e + i), "f"(s[i]), "f"(s[i + 1]), "f"(s[i + 2]), "f"(s[i + 3])
+                 : "memory");
 }
 template <class T>
 int32_t launch_vcolsum(const T* ds, long long frames, int V, int C, float* t1, cudaStream_t st) {
   KernelTimer kt_(KC_BN_STATS, 0.0, st);
   int VC = V * C;
-  if (VC % 4 == 0) {
-    const int by = cdiv(VC / 4, 256);
-    const int bx = (int)std::max<long long>(1, std::min<long long>(frames / 8, (148 * 8 + by - 1) / by));
-    vcolsum4_kernel<T><<<dim3((unsigned)bx, (unsigned)by), 256, 0, st>>>(ds, frames, VC, t1);
+  constexpr int VEC = VecN<T>::N;
+  if (VC % VEC == 0) {
+    const int by = cdiv(VC / VEC, 256);
+    // few, long-running CTAs: the final atomics contend bx-way per address
+    const int bx = (int)std::max<long long>(1, std::min<long long>(frames / 16, (148 * 2 + by - 1) / by));
+    vcolsum_vec_kernel<T><<<dim3((unsigned)bx, (unsigned)by), 256, 0, st>>>(ds, frames, VC, t1);
   } else {
     dim3 grid((unsigned)std::min<long long>(frames, 64), (unsigned)cdiv(VC, 256));
     vcolsum_kernel<T><<<grid, 256, 0, st>>>(ds, frames, VC, t1);

@@ -113,6 +113,8 @@ agg_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_constan
   uint64_t* done_bar = xempty_bar + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(done_bar + 1);
   float* aff_tab = reinterpret_cast<float*>(full_bar + 32);          // [3][C] per-channel epilogue coefficients
+  float* da_tab = aff_tab + 3 * p.c;                                 // dA mode: [K][V][V] CTA-local sums
+  if (p.dA) for (int i = threadIdx.x; i < p.k * p.v * p.v; i += kAggUThreads) da_tab[i] = 0.f;
   const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
 
   {  // padding rows of the activation tiles must be finite (they meet BigA's zero columns)
@@ -123,7 +125,7 @@ agg_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_constan
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&map_in); prefetch_tmap(&map_big); prefetch_tmap(&map_out); prefetch_tmap(&map_x);
     for (int s = 0; s < p.stages; ++s) { mbar_init(full_bar + s, 1); mbar_init(empty_bar + s, 1); }
-    for (int a = 0; a < 2; ++a) { mbar_init(tfull_bar + a, 1); mbar_init(tempty_bar + a, 128); mbar_init(xfull_bar + a, 1); mbar_init(xempty_bar + a, 1); }
+    for (int a = 0; a < 2; ++a) { mbar_init(tfull_bar + a, 1); mbar_init(tempty_bar + a, 128); mbar_init(xfull_bar + a, 1); mbar_init(xempty_bar + a, 129); }
     mbar_init(big_bar, 1); mbar_init(done_bar, 1);
     fence_barrier_init();
   }
@@ -171,8 +173,8 @@ agg_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_constan
     if (lane == 0) {
       const uint32_t idesc = make_idesc_bf16(128, p.nch, 0, 1);     // A K-major (BigA), B MN-major (activation tile)
       mbar_wait(big_bar, 0);
-      const uint32_t idesc_da = make_idesc_bf16(128, 32, 0, 0);      // dA: both operands K-major (channels contiguous), N = 32 >= V
-      const uint32_t g_tmem = tmem_base + (uint32_t)(2 * p.nch);     // K accumulators of 32 columns, live for the whole kernel
+      const uint32_t idesc_da = make_idesc_bf16(128, 128, 0, 0);     // dA: both operands K-major (channels contiguous)
+      const uint32_t g_tmem = tmem_base + (uint32_t)(2 * p.nch);     // K accumulators of 128 columns, live for the whole kernel
       int stage = 0; uint32_t phase = 0; int as = 0; uint32_t aphase = 0; int xs = 0; uint32_t xphase = 0; bool g_first = true;
       for (int item = blockIdx.x; item < p.total_items; item += gridDim.x) {
         if (p.transpose) { mbar_wait(tempty_bar + as, aphase ^ 1); tc_fence_after(); }
@@ -189,19 +191,17 @@ agg_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_constan
             umma_bf16_ss(d_tmem, ad, bd, idesc, (p.transpose ? (k | kk) : kk) != 0 ? 1u : 0u);
           }
           if (p.dA) {
-            // G_k[m][n] += sum_f sum_c dXA_k[(f, m), c] * x[(f, n), c]: per frame one M=128 x N=32 product whose operands are
-            // the SAME tile images read K-major from a start address shifted by f*V rows; only rows/cols < V are meaningful
+            // G_k[(f,v)][(f',w)] += sum_c dXA_k[(f,v),c] * x[(f',w),c]: the SAME tile images read K-major; the FT diagonal
+            // V x V blocks (f == f') are folded into dA at the end of the kernel
             const uint32_t xb_addr = smem_u32(smem_xb + (size_t)xs * stage_bytes);
-            for (int s2 = 0; s2 < slabs; ++s2)
-              for (int f = 0; f < p.ft; ++f) {
-                const uint32_t off = (uint32_t)(s2 * kTile16K + f * p.v * 128);
-                const uint64_t ad = make_smem_desc_sw128(x_addr + off, 16, 1024);
-                const uint64_t bd = make_smem_desc_sw128(xb_addr + off, 16, 1024);
+            for (int s2 = 0; s2 < slabs; ++s2) {
+              const uint64_t ad = make_smem_desc_sw128(x_addr + (uint32_t)(s2 * kTile16K), 16, 1024);
+              const uint64_t bd = make_smem_desc_sw128(xb_addr + (uint32_t)(s2 * kTile16K), 16, 1024);
 #pragma unroll
-                for (int kk = 0; kk < 4; ++kk)
-                  umma_bf16_ss(g_tmem + (uint32_t)(k * 32), ad + (uint64_t)(kk * 2), bd + (uint64_t)(kk * 2), idesc_da,
-                               (g_first && s2 == 0 && f == 0 && kk == 0) ? 0u : 1u);
-              }
+              for (int kk = 0; kk < 4; ++kk)
+                umma_bf16_ss(g_tmem + (uint32_t)(k * 128), ad + (uint64_t)(kk * 2), bd + (uint64_t)(kk * 2), idesc_da,
+                             (g_first && s2 == 0 && kk == 0) ? 0u : 1u);
+            }
           }
           if (p.transpose || k == p.k - 1) { umma_commit(empty_bar + stage); if (++stage == p.stages) { stage = 0; phase ^= 1; } }
           if (!p.transpose) { umma_commit(tfull_bar + as); if (++as == 2) { as = 0; aphase ^= 1; } }
@@ -215,7 +215,7 @@ agg_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_constan
     const int q = warp % 4, row = q * 32 + lane, et = threadIdx.x - 64;
     const int fl = row / p.v, vv = row % p.v;
     const int c_out_total = p.transpose ? p.c : p.k * p.c;
-    int as = 0; uint32_t aphase = 0; int chunk_ctr = 0;
+    int as = 0; uint32_t aphase = 0; int chunk_ctr = 0; int xslot = 0; uint32_t xph = 0;
     const bool affine = !p.transpose && p.aff_a;
     const bool bnb = p.transpose && p.bn_coef;
     if (affine) {
@@ -229,6 +229,7 @@ agg_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_constan
       int cch, j0, b; decode(item, cch, j0, b);
       const bool row_valid = row < p.ft * p.v && (j0 + fl) < p.t;
       const long long grow = ((long long)b * p.t + j0 + fl) * p.v + vv;
+      if (p.dA) mbar_wait(xfull_bar + xslot, xph);      // acquire the TMA-written raw-input tile for generic reads (already complete)
       for (int o = 0; o < outs_per_item; ++o) {
         mbar_wait(tfull_bar + as, aphase);
         tc_fence_after();
@@ -273,13 +274,15 @@ agg_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_constan
               }
             }
             if (bnb && row_valid) {
+              // raw input of this row: from the shared-memory tile ring in dA mode (the swizzled image TMA delivered), else global
               const uint4* xp = reinterpret_cast<const uint4*>(p.bn_x + (size_t)grow * p.c + c0);
+              const uint8_t* xsm = smem_xb + (size_t)xslot * stage_bytes + (size_t)ch * kTile16K + row * 128;
               const float4* mu4 = reinterpret_cast<const float4*>(aff_tab + c0);
               const float4* c14 = reinterpret_cast<const float4*>(aff_tab + p.c + c0);
               const float4* c24 = reinterpret_cast<const float4*>(aff_tab + 2 * p.c + c0);
 #pragma unroll
               for (int g = 0; g < 4; ++g) {
-                const uint4 u = __ldg(xp + g);
+                const uint4 u = p.dA ? *reinterpret_cast<const uint4*>(xsm + (((half * 4 + g) ^ (row & 7)) << 4)) : __ldg(xp + g);
                 const __nv_bfloat162* x2 = reinterpret_cast<const __nv_bfloat162*>(&u);
                 float xv[8];
 #pragma unroll
@@ -318,22 +321,30 @@ agg_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_constan
         mbar_arrive(tempty_bar + as);
         if (++as == 2) { as = 0; aphase ^= 1; }
       }
+      if (p.dA) { mbar_arrive(xempty_bar + xslot); if ((xslot ^= 1) == 0) xph ^= 1; }     // done reading the raw-input tile
       (void)c_out_total;
     }
     if (et == 0) tma_store_wait<0>();
-    if (p.dA && q == 0) {                          // TMEM lanes 0..31 hold the rows v < V of every G_k
+    if (p.dA) {                                    // fold the FT diagonal V x V blocks of every G_k into dA
       mbar_wait(done_bar, 0);
       tc_fence_after();
       for (int k = 0; k < p.k; ++k) {
-        uint32_t r[32];
-        tmem_ld_32x32(tmem_base + (uint32_t)(2 * p.nch + k * 32), r);
-        tmem_ld_wait();
-        if (lane < p.v) {
 #pragma unroll
-          for (int i = 0; i < 32; ++i)
-            if (i < p.v) atomicAdd(p.dA + (k * p.v + lane) * p.v + i, __uint_as_float(r[i]));
+        for (int chunk = 0; chunk < 4; ++chunk) {
+          uint32_t r[32];
+          tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(2 * p.nch + k * 128 + chunk * 32), r);
+          tmem_ld_wait();
+          if (row < p.ft * p.v) {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+              const int w = chunk * 32 + i - fl * p.v;          // column inside this row's own frame block
+              if (w >= 0 && w < p.v) atomicAdd(da_tab + (k * p.v + vv) * p.v + w, __uint_as_float(r[i]));
+            }
+          }
         }
       }
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      for (int i = et; i < p.k * p.v * p.v; i += 128) atomicAdd(p.dA + i, da_tab[i]);   // one global atomic per entry per CTA
     }
   }
   tc_fence_before();
@@ -472,12 +483,12 @@ static int32_t launch_agg_common(int transpose, const bf16* in, int nb, int t, i
   p.aff_a = aff_a; p.aff_b = aff_b; p.rowsum = prep.rowsum; p.mask_h = mask_h; p.bn_x = bn_x; p.bn_coef = bn_coef;
   const size_t stage_bytes = (size_t)(p.nch / 64) * kTile16K;
   const size_t fixed = (size_t)k * 2 * kTile16K + 2 * kTile16K + 1024 + 512 + 3 * (size_t)c * sizeof(float) +
-                       (dA ? 2 * (size_t)(p.nch / 64) * kTile16K : 0);
+                       (dA ? 2 * (size_t)(p.nch / 64) * kTile16K + (size_t)k * v * v * sizeof(float) : 0);
   int stages = (int)((220 * 1024 - fixed) / stage_bytes);
   if (stages > 4) stages = 4;
   if (stages < 2) { set_error("umma agg: not enough shared memory"); return STGCN_ERR_UNSUPPORTED; }
   p.stages = stages;
-  uint32_t cols = 32; while (cols < (uint32_t)(2 * p.nch + (dA ? k * 32 : 0))) cols <<= 1;
+  uint32_t cols = 32; while (cols < (uint32_t)(2 * p.nch + (dA ? k * 128 : 0))) cols <<= 1;
   p.tmem_cols = cols;
   CUtensorMap map_in, map_big, map_out, map_x;
   STGCN_TRY(make_act_map(&map_in, in, transpose ? k * c : c, v, t, nb, p.ft));
