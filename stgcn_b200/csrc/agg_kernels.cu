@@ -399,11 +399,16 @@ __global__ void __launch_bounds__(128) bn1_fold_weights_kernel(const float* __re
 }
 __global__ void __launch_bounds__(256) bias2d_fold_kernel(const float* __restrict__ A, const float* __restrict__ rowsum_q,
                                                           const float* __restrict__ Wb, const float* __restrict__ wb, int K, int V, int Co,
-                                                          float* __restrict__ out, float* __restrict__ wbb) {
+                                                          float* __restrict__ out, float* __restrict__ wbb,
+                                                          float* __restrict__ rsum2, float* __restrict__ bvec2) {
   __shared__ float rs[128];
   adjacency_rowsums(A, K, V, rs);
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < K * Co) wbb[i] = Wb[i] + wb[i];
+  if (rsum2) {          // rank-2K factors of bias2d' for the fused spatial kernel: [2K][V] row sums, [2K][Co] bias vectors
+    if (i < K * V) { rsum2[i] = rs[i]; rsum2[K * V + i] = rowsum_q[i]; }
+    if (i < K * Co) { bvec2[i] = Wb[i]; bvec2[K * Co + i] = wb[i]; }
+  }
   if (i >= V * Co) return;
   const int co = i % Co, v = i / Co;
   float s = 0.f;
@@ -411,7 +416,8 @@ __global__ void __launch_bounds__(256) bias2d_fold_kernel(const float* __restric
   out[i] = s;
 }
 int32_t launch_bn1_fold(const float* W, const float* Wb, const float* A, const float* rowsum_q, const float* a, const float* b, int K,
-                        int V, int Co, int Ci, bf16* w2p, bf16* w2pT, float* wb, float* wbb, float* bias2d, cudaStream_t st, int ld) {
+                        int V, int Co, int Ci, bf16* w2p, bf16* w2pT, float* wb, float* wbb, float* bias2d, cudaStream_t st, int ld,
+                        float* rsum2, float* bvec2) {
   KernelTimer kt_(KC_PACK, 0.0, st);
   if (ld <= 0) ld = K * Ci;
   if (ld > K * Ci) {      // zero-padded reduction dimension (small C_in): rows / columns K*Ci..ld-1 stay zero
@@ -420,7 +426,7 @@ int32_t launch_bn1_fold(const float* W, const float* Wb, const float* A, const f
   }
   bn1_fold_weights_kernel<<<K * Co, 128, 0, st>>>(W, a, b, K, Co, Ci, ld, w2p, w2pT, wb);
   STGCN_CHECK_LAUNCH("bn1_fold_weights");
-  bias2d_fold_kernel<<<cdiv(std::max(V, K) * Co, 256), 256, 0, st>>>(A, rowsum_q, Wb, wb, K, V, Co, bias2d, wbb);
+  bias2d_fold_kernel<<<cdiv(std::max(V, K) * Co, 256), 256, 0, st>>>(A, rowsum_q, Wb, wb, K, V, Co, bias2d, wbb, rsum2, bvec2);
   STGCN_CHECK_LAUNCH("bias2d_fold");
   return STGCN_OK;
 }

@@ -196,10 +196,17 @@ static int32_t spatial_fwd(Engine<T>& e, const Dims& m, const T* x, const float*
       bf16* w2pT = ws.template get<bf16>((size_t)m.co * KCi);
       float* wb = ws.template get<float>((size_t)m.k * m.co);
       float* wbb = ws.template get<float>((size_t)m.k * m.co);
+      float* rsum2 = ws.template get<float>((size_t)2 * m.k * m.v);
+      float* bvec2 = ws.template get<float>((size_t)2 * m.k * m.co);
       if (ws.dry) return STGCN_OK;
       if (!ws.ok()) return STGCN_ERR_WORKSPACE;
+      static const bool unfused = getenv("STGCN_UNFUSED_SPATIAL") != nullptr;    // A/B switch: separate aggregation + GEMM-1
+      const bool fused = !unfused && umma_spatial_supported(m.v, m.ci, m.co, m.k);
       STGCN_TRY(launch_build_big_adjacency(A, m.k, m.v, prep, e.st));
-      STGCN_TRY(launch_bn1_fold(W, Wb, A, umma_agg_rowsum_q(prep, m.k), aff_a, aff_b, m.k, m.v, m.co, m.ci, w2p, w2pT, wb, wbb, b2d, e.st));
+      STGCN_TRY(launch_bn1_fold(W, Wb, A, umma_agg_rowsum_q(prep, m.k), aff_a, aff_b, m.k, m.v, m.co, m.ci, w2p, w2pT, wb, wbb, b2d, e.st, 0,
+                                rsum2, bvec2));
+      if (fused)     // one kernel: aggregation -> (TMEM -> bf16 smem) -> channel mixing; XA goes to HBM only when backward wants it
+        return launch_spatial_fused(x, m.n, m.t, m.v, m.ci, m.co, m.k, umma_agg_big(prep, m.k), w2p, rsum2, bvec2, xa_keep, S, e.st);
       STGCN_TRY(launch_agg_fwd_umma(x, m.n, m.t, m.v, m.ci, m.k, prep, nullptr, nullptr, XA, e.st));
       GemmEpilogue ep; ep.bias2d = b2d;
       return e.gemm_packed(geom(m.n, m.t, m.t, m.v, KCi, m.co, 1, 1, 0, 0), XA, w2p, ep, S);

@@ -78,7 +78,7 @@ int32_t launch_spatial_bias_grads(const float* t1, const float* A, const float* 
                                   cudaStream_t st, const float* bias_dA = nullptr);
 int32_t launch_bn1_fold(const float* W, const float* Wb, const float* A, const float* rowsum_q, const float* a, const float* b, int K,
                         int V, int Co, int Ci, bf16* w2p, bf16* w2pT, float* wb, float* wbb, float* bias2d, cudaStream_t st,
-                        int ld = 0);
+                        int ld = 0, float* rsum2 = nullptr, float* bvec2 = nullptr);
 int32_t launch_bn1_fold_grads(const float* W, float* dW, const float* stats, const float* t1, const float* rowsum_q, int K, int V,
                               int Co, int Ci, int training, double rows, float* dgamma, float* dbeta, float* coef, cudaStream_t st);
 
@@ -111,6 +111,12 @@ int32_t launch_agg_bwd_umma(const bf16* dxa, int nb, int t, int v, int c, int k,
                             cudaStream_t st, const bf16* bn_x = nullptr, const float* bn_coef = nullptr, float* dA = nullptr);
 const float* umma_agg_rowsum_q(const void* prep, int k);
 int32_t launch_agg_dA_umma(const bf16* dxa, const bf16* h, int nb, int t, int v, int c, int k, float* dA, cudaStream_t st);
+
+// umma_spatial.cu  (fused aggregation + 1x1 channel mixing, forward)
+bool umma_spatial_supported(int v, int ci, int co, int k);
+int32_t launch_spatial_fused(const bf16* x, int nb, int t, int v, int ci, int co, int k, const bf16* big, const bf16* w2p,
+                             const float* rsum, const float* bvec, bf16* xa, bf16* s_out, cudaStream_t st);
+const bf16* umma_agg_big(const void* prep, int k);
 
 // head_kernels.cu
 int32_t head_forward(int dtype, int n, int t, int v, int c, int classes, const void* feat, const float* fcw, const float* fcb,

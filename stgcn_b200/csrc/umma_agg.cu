@@ -467,6 +467,7 @@ static int32_t make_act_map(CUtensorMap* m, const bf16* base, int cols, int v, i
   return make_tmap_bf16(m, base, 5, dims, str, box);
 }
 
+const bf16* umma_agg_big(const void* prep, int k) { return carve_agg_prep(const_cast<void*>(prep), k).big; }
 const float* umma_agg_rowsum_q(const void* prep, int k) { return carve_agg_prep(const_cast<void*>(prep), k).rowsum; }
 
 static int32_t launch_agg_common(int transpose, const bf16* in, int nb, int t, int v, int c, int k, const void* prep_mem,
