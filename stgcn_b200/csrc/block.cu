@@ -200,8 +200,10 @@ static int32_t spatial_fwd(Engine<T>& e, const Dims& m, const T* x, const float*
       float* bvec2 = ws.template get<float>((size_t)2 * m.k * m.co);
       if (ws.dry) return STGCN_OK;
       if (!ws.ok()) return STGCN_ERR_WORKSPACE;
-      static const bool unfused = getenv("STGCN_UNFUSED_SPATIAL") != nullptr;    // A/B switch: separate aggregation + GEMM-1
-      const bool fused = !unfused && umma_spatial_supported(m.v, m.ci, m.co, m.k);
+      // The single-kernel aggregation + mixing path is opt-in: measured on B200 it is still behind the two-kernel pair
+      // (per-chunk MMA -> epilogue -> MMA latency chain), see DESIGN.md section 8.
+      static const bool want_fused = getenv("STGCN_FUSED_SPATIAL") != nullptr;
+      const bool fused = want_fused && umma_spatial_supported(m.v, m.ci, m.co, m.k);
       STGCN_TRY(launch_build_big_adjacency(A, m.k, m.v, prep, e.st));
       STGCN_TRY(launch_bn1_fold(W, Wb, A, umma_agg_rowsum_q(prep, m.k), aff_a, aff_b, m.k, m.v, m.co, m.ci, w2p, w2pT, wb, wbb, b2d, e.st, 0,
                                 rsum2, bvec2));

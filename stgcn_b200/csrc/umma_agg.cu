@@ -175,6 +175,10 @@ agg_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_constan
       mbar_wait(big_bar, 0);
       const uint32_t idesc_da = make_idesc_bf16(128, 128, 0, 0);     // dA: both operands K-major (channels contiguous)
       const uint32_t g_tmem = tmem_base + (uint32_t)(2 * p.nch);     // K accumulators of 128 columns, live for the whole kernel
+      const uint64_t big_d0 = make_smem_desc_sw128(smem_u32(smem_big), 16, 1024);
+      const uint64_t x_d0 = make_smem_desc_sw128(smem_u32(smem_x), (uint32_t)kTile16K, 1024);      // MN-major view (aggregation)
+      const uint64_t xk_d0 = make_smem_desc_sw128(smem_u32(smem_x), 16, 1024);                      // K-major view (dA products)
+      const uint64_t xb_d0 = make_smem_desc_sw128(smem_u32(smem_xb), 16, 1024);
       int stage = 0; uint32_t phase = 0; int as = 0; uint32_t aphase = 0; int xs = 0; uint32_t xphase = 0; bool g_first = true;
       for (int item = blockIdx.x; item < p.total_items; item += gridDim.x) {
         if (p.transpose) { mbar_wait(tempty_bar + as, aphase ^ 1); tc_fence_after(); }
@@ -182,25 +186,26 @@ agg_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_constan
         for (int k = 0; k < p.k; ++k) {
           if (!p.transpose) { mbar_wait(tempty_bar + as, aphase ^ 1); tc_fence_after(); }
           if (p.transpose || k == 0) { mbar_wait(full_bar + stage, phase); tc_fence_after(); }
-          const uint32_t x_addr = smem_u32(smem_x + (size_t)stage * stage_bytes);
+          // shared-memory descriptors are affine in the address (field = addr >> 4): one base each, then constant offsets
+          const uint32_t st16 = (uint32_t)(stage * (stage_bytes >> 4));
+          const uint64_t ad0 = big_d0 + (uint64_t)(k * (2 * kTile16K >> 4));
+          const uint64_t bd0 = x_d0 + (uint64_t)st16;
           const uint32_t d_tmem = tmem_base + (uint32_t)(as * p.nch);
+          const uint32_t acc0 = (p.transpose && k != 0) ? 1u : 0u;
 #pragma unroll
-          for (int kk = 0; kk < 8; ++kk) {         // reduction over the 128 tile rows, 16 per instruction
-            const uint64_t ad = make_smem_desc_sw128(smem_u32(smem_big + (size_t)(k * 2 + kk / 4) * kTile16K), 16, 1024) + (uint64_t)((kk % 4) * 2);
-            const uint64_t bd = make_smem_desc_sw128(x_addr, (uint32_t)kTile16K, 1024) + (uint64_t)(kk * 128);
-            umma_bf16_ss(d_tmem, ad, bd, idesc, (p.transpose ? (k | kk) : kk) != 0 ? 1u : 0u);
-          }
+          for (int kk = 0; kk < 8; ++kk)           // reduction over the 128 tile rows, 16 per instruction
+            umma_bf16_ss(d_tmem, ad0 + (uint64_t)((kk / 4) * (kTile16K >> 4) + (kk % 4) * 2), bd0 + (uint64_t)(kk * 128), idesc,
+                         kk != 0 ? 1u : acc0);
           if (p.dA) {
             // G_k[(f,v)][(f',w)] += sum_c dXA_k[(f,v),c] * x[(f',w),c]: the SAME tile images read K-major; the FT diagonal
             // V x V blocks (f == f') are folded into dA at the end of the kernel
-            const uint32_t xb_addr = smem_u32(smem_xb + (size_t)xs * stage_bytes);
+            const uint64_t ga0 = xk_d0 + (uint64_t)st16;
+            const uint64_t gb0 = xb_d0 + (uint64_t)(xs * (stage_bytes >> 4));
             for (int s2 = 0; s2 < slabs; ++s2) {
-              const uint64_t ad = make_smem_desc_sw128(x_addr + (uint32_t)(s2 * kTile16K), 16, 1024);
-              const uint64_t bd = make_smem_desc_sw128(xb_addr + (uint32_t)(s2 * kTile16K), 16, 1024);
 #pragma unroll
               for (int kk = 0; kk < 4; ++kk)
-                umma_bf16_ss(g_tmem + (uint32_t)(k * 128), ad + (uint64_t)(kk * 2), bd + (uint64_t)(kk * 2), idesc_da,
-                             (g_first && s2 == 0 && kk == 0) ? 0u : 1u);
+                umma_bf16_ss(g_tmem + (uint32_t)(k * 128), ga0 + (uint64_t)(s2 * (kTile16K >> 4) + kk * 2),
+                             gb0 + (uint64_t)(s2 * (kTile16K >> 4) + kk * 2), idesc_da, (g_first && s2 == 0 && kk == 0) ? 0u : 1u);
             }
           }
           if (p.transpose || k == p.k - 1) { umma_commit(empty_bar + stage); if (++stage == p.stages) { stage = 0; phase ^= 1; } }
@@ -222,7 +227,11 @@ agg_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_constan
       for (int i = et; i < p.c; i += 128) { aff_tab[i] = __ldg(p.aff_a + i); aff_tab[p.c + i] = __ldg(p.aff_b + i); }
       asm volatile("bar.sync 1, 128;" ::: "memory");
     } else if (bnb) {
-      for (int i = et; i < 3 * p.c; i += 128) aff_tab[i] = __ldg(p.bn_coef + i);
+      // dx = dh' - c1 - (x - mean) * c2 = (dh' + d0) - c2 * x  with d0 = mean * c2 - c1: two coefficients per channel
+      for (int i = et; i < p.c; i += 128) {
+        const float mu = __ldg(p.bn_coef + i), c1 = __ldg(p.bn_coef + p.c + i), c2 = __ldg(p.bn_coef + 2 * p.c + i);
+        aff_tab[i] = mu * c2 - c1; aff_tab[p.c + i] = -c2;
+      }
       asm volatile("bar.sync 1, 128;" ::: "memory");
     }
     for (int item = blockIdx.x; item < p.total_items; item += gridDim.x) {
@@ -277,9 +286,8 @@ agg_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_constan
               // raw input of this row: from the shared-memory tile ring in dA mode (the swizzled image TMA delivered), else global
               const uint4* xp = reinterpret_cast<const uint4*>(p.bn_x + (size_t)grow * p.c + c0);
               const uint8_t* xsm = smem_xb + (size_t)xslot * stage_bytes + (size_t)ch * kTile16K + row * 128;
-              const float4* mu4 = reinterpret_cast<const float4*>(aff_tab + c0);
-              const float4* c14 = reinterpret_cast<const float4*>(aff_tab + p.c + c0);
-              const float4* c24 = reinterpret_cast<const float4*>(aff_tab + 2 * p.c + c0);
+              const float4* d04 = reinterpret_cast<const float4*>(aff_tab + c0);
+              const float4* n24 = reinterpret_cast<const float4*>(aff_tab + p.c + c0);
 #pragma unroll
               for (int g = 0; g < 4; ++g) {
                 const uint4 u = p.dA ? *reinterpret_cast<const uint4*>(xsm + (((half * 4 + g) ^ (row & 7)) << 4)) : __ldg(xp + g);
@@ -289,10 +297,10 @@ agg_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_constan
                 for (int e = 0; e < 4; ++e) { xv[2 * e] = __low2float(x2[e]); xv[2 * e + 1] = __high2float(x2[e]); }
 #pragma unroll
                 for (int hh = 0; hh < 2; ++hh) {
-                  const float4 m = mu4[g * 2 + hh], a1 = c14[g * 2 + hh], a2 = c24[g * 2 + hh];
+                  const float4 d0 = d04[g * 2 + hh], n2 = n24[g * 2 + hh];
                   float* ff = f + g * 8 + hh * 4; const float* xx = xv + hh * 4;
-                  ff[0] = ff[0] - a1.x - (xx[0] - m.x) * a2.x; ff[1] = ff[1] - a1.y - (xx[1] - m.y) * a2.y;
-                  ff[2] = ff[2] - a1.z - (xx[2] - m.z) * a2.z; ff[3] = ff[3] - a1.w - (xx[3] - m.w) * a2.w;
+                  ff[0] = fmaf(n2.x, xx[0], ff[0] + d0.x); ff[1] = fmaf(n2.y, xx[1], ff[1] + d0.y);
+                  ff[2] = fmaf(n2.z, xx[2], ff[2] + d0.z); ff[3] = fmaf(n2.w, xx[3], ff[3] + d0.w);
                 }
               }
             }
@@ -328,23 +336,33 @@ agg_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_constan
     if (p.dA) {                                    // fold the FT diagonal V x V blocks of every G_k into dA
       mbar_wait(done_bar, 0);
       tc_fence_after();
+      // every load has landed and every product has completed: the activation ring is free and holds the unfolded blocks,
+      // fold_tab[k][f][v][w] = G_k[(f,v)][(f,w)] written with plain stores (each thread owns its row), then summed over f
+      float* fold_tab = reinterpret_cast<float*>(smem_x);
+      asm volatile("bar.sync 1, 128;" ::: "memory");                 // every epilogue thread is done with the raw-input ring
+      const int vv2 = p.v * p.v;
       for (int k = 0; k < p.k; ++k) {
+        float* mine = fold_tab + ((size_t)(k * p.ft + fl) * p.v + vv) * p.v - fl * p.v;   // indexed by the tile column
 #pragma unroll
         for (int chunk = 0; chunk < 4; ++chunk) {
           uint32_t r[32];
           tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(2 * p.nch + k * 128 + chunk * 32), r);
           tmem_ld_wait();
           if (row < p.ft * p.v) {
+            const int lo = fl * p.v - chunk * 32, hi = lo + p.v;     // this row's own frame block, in chunk-local columns
 #pragma unroll
-            for (int i = 0; i < 32; ++i) {
-              const int w = chunk * 32 + i - fl * p.v;          // column inside this row's own frame block
-              if (w >= 0 && w < p.v) atomicAdd(da_tab + (k * p.v + vv) * p.v + w, __uint_as_float(r[i]));
-            }
+            for (int i = 0; i < 32; ++i)
+              if (i >= lo && i < hi) mine[chunk * 32 + i] = __uint_as_float(r[i]);
           }
         }
       }
       asm volatile("bar.sync 1, 128;" ::: "memory");
-      for (int i = et; i < p.k * p.v * p.v; i += 128) atomicAdd(p.dA + i, da_tab[i]);   // one global atomic per entry per CTA
+      for (int i = et; i < p.k * vv2; i += 128) {                     // one global atomic per entry per CTA
+        const int k = i / vv2, rem = i - k * vv2;
+        float acc = 0.f;
+        for (int f = 0; f < p.ft; ++f) acc += fold_tab[(size_t)(k * p.ft + f) * vv2 + rem];
+        atomicAdd(p.dA + i, acc);
+      }
     }
   }
   tc_fence_before();
