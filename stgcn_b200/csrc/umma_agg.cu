@@ -115,7 +115,7 @@ agg_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_constan
   float* aff_tab = reinterpret_cast<float*>(full_bar + 32);          // [3][C] per-channel epilogue coefficients
   float* da_tab = aff_tab + 3 * p.c;                                 // dA mode: [K][V][V] CTA-local sums
   if (p.dA) for (int i = threadIdx.x; i < p.k * p.v * p.v; i += kAggUThreads) da_tab[i] = 0.f;
-  const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
+  const int warp = uniform_warp_idx(), lane = threadIdx.x % 32;
 
   {  // padding rows of the activation tiles must be finite (they meet BigA's zero columns)
     uint4* z = reinterpret_cast<uint4*>(smem_x);
@@ -170,7 +170,7 @@ agg_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_constan
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
+    {   // whole warp runs the issue loop, one elected lane issues (umma_common.cuh)
       const uint32_t idesc = make_idesc_bf16(128, p.nch, 0, 1);     // A K-major (BigA), B MN-major (activation tile)
       mbar_wait(big_bar, 0);
       const uint32_t idesc_da = make_idesc_bf16(128, 128, 0, 0);     // dA: both operands K-major (channels contiguous)
@@ -194,7 +194,7 @@ agg_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_constan
           const uint32_t acc0 = (p.transpose && k != 0) ? 1u : 0u;
 #pragma unroll
           for (int kk = 0; kk < 8; ++kk)           // reduction over the 128 tile rows, 16 per instruction
-            umma_bf16_ss(d_tmem, ad0 + (uint64_t)((kk / 4) * (kTile16K >> 4) + (kk % 4) * 2), bd0 + (uint64_t)(kk * 128), idesc,
+            umma_bf16_ss_elect(d_tmem, ad0 + (uint64_t)((kk / 4) * (kTile16K >> 4) + (kk % 4) * 2), bd0 + (uint64_t)(kk * 128), idesc,
                          kk != 0 ? 1u : acc0);
           if (p.dA) {
             // G_k[(f,v)][(f',w)] += sum_c dXA_k[(f,v),c] * x[(f',w),c]: the SAME tile images read K-major; the FT diagonal
@@ -204,17 +204,17 @@ agg_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_constan
             for (int s2 = 0; s2 < slabs; ++s2) {
 #pragma unroll
               for (int kk = 0; kk < 4; ++kk)
-                umma_bf16_ss(g_tmem + (uint32_t)(k * 128), ga0 + (uint64_t)(s2 * (kTile16K >> 4) + kk * 2),
+                umma_bf16_ss_elect(g_tmem + (uint32_t)(k * 128), ga0 + (uint64_t)(s2 * (kTile16K >> 4) + kk * 2),
                              gb0 + (uint64_t)(s2 * (kTile16K >> 4) + kk * 2), idesc_da, (g_first && s2 == 0 && kk == 0) ? 0u : 1u);
             }
           }
-          if (p.transpose || k == p.k - 1) { umma_commit(empty_bar + stage); if (++stage == p.stages) { stage = 0; phase ^= 1; } }
-          if (!p.transpose) { umma_commit(tfull_bar + as); if (++as == 2) { as = 0; aphase ^= 1; } }
+          if (p.transpose || k == p.k - 1) { umma_commit_elect(empty_bar + stage); if (++stage == p.stages) { stage = 0; phase ^= 1; } }
+          if (!p.transpose) { umma_commit_elect(tfull_bar + as); if (++as == 2) { as = 0; aphase ^= 1; } }
         }
-        if (p.transpose) { umma_commit(tfull_bar + as); if (++as == 2) { as = 0; aphase ^= 1; } }
-        if (p.dA) { umma_commit(xempty_bar + xs); if (++xs == 2) { xs = 0; xphase ^= 1; } g_first = false; }
+        if (p.transpose) { umma_commit_elect(tfull_bar + as); if (++as == 2) { as = 0; aphase ^= 1; } }
+        if (p.dA) { umma_commit_elect(xempty_bar + xs); if (++xs == 2) { xs = 0; xphase ^= 1; } g_first = false; }
       }
-      if (p.dA) umma_commit(done_bar);
+      if (p.dA) umma_commit_elect(done_bar);
     }
   } else {
     const int q = warp % 4, row = q * 32 + lane, et = threadIdx.x - 64;
@@ -392,7 +392,7 @@ agg_dA_umma_kernel(const __grid_constant__ CUtensorMap map_dxa, const __grid_con
   uint64_t* done_bar = empty_bar + p.stages;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(done_bar + 1);
   float* da_tab = reinterpret_cast<float*>(smem + (size_t)p.stages * stage_bytes + 256);   // [K][V][V] CTA-local sums
-  const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
+  const int warp = uniform_warp_idx(), lane = threadIdx.x % 32;
   for (int i = threadIdx.x; i < p.k * p.v * p.v; i += kAggUThreads) da_tab[i] = 0.f;
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&map_dxa); prefetch_tmap(&map_h);
@@ -424,7 +424,7 @@ agg_dA_umma_kernel(const __grid_constant__ CUtensorMap map_dxa, const __grid_con
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
+    {   // whole warp runs the issue loop, one elected lane issues (umma_common.cuh)
       const uint32_t idesc = make_idesc_bf16(128, 128, 0, 0);
       int stage = 0; uint32_t phase = 0; bool first = true;
       for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
@@ -437,14 +437,14 @@ agg_dA_umma_kernel(const __grid_constant__ CUtensorMap map_dxa, const __grid_con
             const uint64_t ad = make_smem_desc_sw128(sb + (uint32_t)(k * kTile16K), 16, 1024);
 #pragma unroll
             for (int kk = 0; kk < 4; ++kk)
-              umma_bf16_ss(tmem_base + (uint32_t)(k * 128), ad + (uint64_t)(kk * 2), hd + (uint64_t)(kk * 2), idesc, (!first || kk) ? 1u : 0u);
+              umma_bf16_ss_elect(tmem_base + (uint32_t)(k * 128), ad + (uint64_t)(kk * 2), hd + (uint64_t)(kk * 2), idesc, (!first || kk) ? 1u : 0u);
           }
           first = false;
-          umma_commit(empty_bar + stage);
+          umma_commit_elect(empty_bar + stage);
           if (++stage == p.stages) { stage = 0; phase ^= 1; }
         }
       }
-      umma_commit(done_bar);
+      umma_commit_elect(done_bar);
     }
   } else {
     const int q = warp % 4, row = q * 32 + lane;

@@ -94,6 +94,24 @@ __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
+// Warp-converged variants: the WHOLE warp runs the issue loop and one elected lane issues.  With every operand derived from
+// warp-uniform values in converged code, ptxas keeps descriptors and addresses in uniform registers; issuing from inside an
+// `if (lane == 0)` region instead costs a register->uniform "waterfall" loop (ELECT / R2UR.BROADCAST / BRA.U.ANY) per instruction,
+// ~70 cycles per tcgen05.mma -- longer than a 128x64x16 or 128x128x16 MMA takes to execute.
+__device__ __forceinline__ void umma_commit_elect(uint64_t* bar) {
+  asm volatile(
+      "{\n\t.reg .pred P;\n\telect.sync _|P, 0xffffffff;\n\t"
+      "@P tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t}\n" ::"r"(smem_u32(bar))
+      : "memory");
+}
+__device__ __forceinline__ void umma_bf16_ss_elect(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p, P;\n\tsetp.ne.b32 p, %4, 0;\n\telect.sync _|P, 0xffffffff;\n\t"
+      "@P tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}\n" ::"r"(d_tmem),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ int uniform_warp_idx() { return __shfl_sync(0xffffffffu, (int)(threadIdx.x / 32), 0); }
 // D[tmem] (+)= A[smem] * B[smem], bf16 inputs, fp32 accumulate
 __device__ __forceinline__ void umma_bf16_ss(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
   asm volatile(

@@ -42,6 +42,11 @@ struct UmmaParams {
   uint32_t a_bytes, b_bytes;
   int ntaps[2];
   TapEntry taps[2][kMaxTaps];
+  // halo mode (stride 1, several taps): ONE activation tile of ft + (h_max - h_min) frames per 64-channel block serves every tap
+  // through row-shifted descriptors; the weight tiles have their own ring, or stay resident when they all fit
+  int halo, h_min, w_stages, w_resident, nstaging;
+  uint32_t a_stage_bytes, a_halo_bytes;
+  int a_off16[kMaxTaps];   // descriptor offset (16-byte units) of each tap's first row inside the halo tile
   // epilogue
   const float* bias; const float* bias2d; const float* scale; const float* shift;
   int b2_smem;           // bias2d staged in shared memory as [V][bn+4] floats (only when n_tiles == 1)
@@ -69,24 +74,27 @@ conv_gemm_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_c
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // 1024-byte aligned carve-up (dynamic smem base is only guaranteed 16-byte aligned)
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-  uint8_t* smem_a = smem;                                        // stages x 16 KB
-  uint8_t* smem_b = smem_a + (size_t)p.stages * kATileBytes;     // stages x bn*128 B (multiple of 1024)
-  uint8_t* staging = smem_b + (size_t)p.stages * p.b_bytes;      // 2 x 16 KB
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(staging + 2 * kStagingBytes);
-  uint64_t* empty_bar = full_bar + p.stages;
-  uint64_t* tfull_bar = empty_bar + p.stages;
-  uint64_t* tempty_bar = tfull_bar + 2;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+  uint8_t* smem_a = smem;                                        // stages x a_stage_bytes (16 KB, or the halo tile)
+  uint8_t* smem_b = smem_a + (size_t)p.stages * p.a_stage_bytes; // w_stages x bn*128 B (multiple of 1024)
+  uint8_t* staging = smem_b + (size_t)p.w_stages * p.b_bytes;    // nstaging x 16 KB
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(staging + (size_t)p.nstaging * kStagingBytes);
+  uint64_t* empty_bar = full_bar + 8;
+  uint64_t* tfull_bar = full_bar + 16;
+  uint64_t* tempty_bar = full_bar + 18;
+  uint64_t* wfull_bar = full_bar + 20;                           // [16] halo mode: weight ring
+  uint64_t* wempty_bar = full_bar + 36;                          // [16]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(full_bar + 52);
   float* b2_tab = reinterpret_cast<float*>(tmem_slot + 4);       // 16-byte aligned: barriers start on a 1024-byte boundary
   float* stat_acc = b2_tab + (p.b2_smem ? p.v * (p.bn + 4) : 0);  // [2][n_out]
   float* vsum_acc = stat_acc + (p.stat_partials ? 2 * p.n_out : 0);   // [V][n_out]
 
-  const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
+  const int warp = uniform_warp_idx(), lane = threadIdx.x % 32;
 
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&map_in); prefetch_tmap(&map_w); prefetch_tmap(&map_out);
     for (int s = 0; s < p.stages; ++s) { mbar_init(full_bar + s, 1); mbar_init(empty_bar + s, 1); }
     for (int a = 0; a < 2; ++a) { mbar_init(tfull_bar + a, 1); mbar_init(tempty_bar + a, 128); }
+    for (int a = 0; a < 16; ++a) { mbar_init(wfull_bar + a, 1); mbar_init(wempty_bar + a, 1); }
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc(tmem_slot, p.tmem_cols);
@@ -97,7 +105,48 @@ conv_gemm_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_c
 
   if (warp == 0) {
     // ===================== TMA producer =====================
-    if (lane == 0) {
+    // the whole warp runs the loops (uniform registers for coordinates and addresses); one elected lane arms the barrier and issues
+    if (p.halo) {
+      const int nt = p.ntaps[0];
+      if (p.w_resident) {                          // every (channel block, tap) weight tile, once
+        if (elect_one()) mbar_expect_tx(wfull_bar, (uint32_t)(nt * p.kblocks_c) * p.b_bytes);
+        __syncwarp();
+        for (int kb = 0; kb < p.kblocks_c; ++kb)
+          for (int ti = 0; ti < nt; ++ti)
+            if (elect_one()) tma_load_3d(&map_w, smem_b + (size_t)(kb * nt + ti) * p.b_bytes, wfull_bar, kb * 64, 0, p.taps[0][ti].w_tap);
+      }
+      // two cursors over the (tile, channel block) units: activation tiles run `lead` units ahead of the weight tiles
+      int a_tile = blockIdx.x, a_kb = 0, w_tile = blockIdx.x, w_kb = 0;
+      int stage = 0; uint32_t phase = 0; int ws = 0; uint32_t wph = 0;
+      auto issue_a = [&]() {
+        if (a_tile >= p.total_tiles) return;
+        const TileCoord tc = decode_tile(p, a_tile);
+        mbar_wait(empty_bar + stage, phase ^ 1);
+        if (elect_one()) {
+          mbar_expect_tx(full_bar + stage, p.a_halo_bytes);
+          tma_load_5d(&map_in, smem_a + (size_t)stage * p.a_stage_bytes, full_bar + stage, a_kb * 64, 0, 0, tc.j0 + p.h_min, tc.b);
+        }
+        if (++stage == p.stages) { stage = 0; phase ^= 1; }
+        if (++a_kb == p.kblocks_c) { a_kb = 0; a_tile += gridDim.x; }
+      };
+      const int lead = p.w_resident ? p.stages - 1 : p.stages - 2;
+      for (int i = 0; i <= lead; ++i) issue_a();
+      while (w_tile < p.total_tiles) {
+        if (!p.w_resident) {
+          const TileCoord tc = decode_tile(p, w_tile);
+          for (int ti = 0; ti < nt; ++ti) {
+            mbar_wait(wempty_bar + ws, wph ^ 1);
+            if (elect_one()) {
+              mbar_expect_tx(wfull_bar + ws, p.b_bytes);
+              tma_load_3d(&map_w, smem_b + (size_t)ws * p.b_bytes, wfull_bar + ws, w_kb * 64, tc.n_t * p.bn, p.taps[0][ti].w_tap);
+            }
+            if (++ws == p.w_stages) { ws = 0; wph ^= 1; }
+          }
+        }
+        if (++w_kb == p.kblocks_c) { w_kb = 0; w_tile += gridDim.x; }
+        issue_a();
+      }
+    } else {
       int stage = 0; uint32_t phase = 0;
       for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
         const TileCoord tc = decode_tile(p, tile);
@@ -106,9 +155,11 @@ conv_gemm_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_c
           const TapEntry te = p.taps[tc.ph][ti];
           for (int kb = 0; kb < p.kblocks_c; ++kb) {
             mbar_wait(empty_bar + stage, phase ^ 1);
-            mbar_expect_tx(full_bar + stage, p.a_bytes + p.b_bytes);
-            tma_load_5d(&map_in, smem_a + (size_t)stage * kATileBytes, full_bar + stage, kb * 64, 0, te.parity, tc.j0 + te.h_off, tc.b);
-            tma_load_3d(&map_w, smem_b + (size_t)stage * p.b_bytes, full_bar + stage, kb * 64, tc.n_t * p.bn, te.w_tap);
+            if (elect_one()) {
+              mbar_expect_tx(full_bar + stage, p.a_bytes + p.b_bytes);
+              tma_load_5d(&map_in, smem_a + (size_t)stage * p.a_stage_bytes, full_bar + stage, kb * 64, 0, te.parity, tc.j0 + te.h_off, tc.b);
+              tma_load_3d(&map_w, smem_b + (size_t)stage * p.b_bytes, full_bar + stage, kb * 64, tc.n_t * p.bn, te.w_tap);
+            }
             if (++stage == p.stages) { stage = 0; phase ^= 1; }
           }
         }
@@ -116,7 +167,46 @@ conv_gemm_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_c
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
-    if (lane == 0) {
+    // the whole warp runs the loop, one elected lane issues (see umma_bf16_ss_elect)
+    if (p.halo) {
+      const uint32_t idesc = make_idesc_bf16(128, p.bn, 0, 0);
+      const uint64_t a_d0 = make_smem_desc_sw128(smem_u32(smem_a), 16, 1024);
+      const uint64_t w_d0 = make_smem_desc_sw128(smem_u32(smem_b), 16, 1024);
+      const uint32_t a_step = p.a_stage_bytes >> 4, w_step = p.b_bytes >> 4;
+      const int nt = p.ntaps[0];
+      int stage = 0; uint32_t phase = 0; int ws = 0; uint32_t wph = 0;
+      int as = 0; uint32_t aphase = 0;
+      if (p.w_resident) { mbar_wait(wfull_bar, 0); tc_fence_after(); }
+      for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
+        mbar_wait(tempty_bar + as, aphase ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + (uint32_t)(as * p.bn);
+        for (int kb = 0; kb < p.kblocks_c; ++kb) {
+          mbar_wait(full_bar + stage, phase);
+          tc_fence_after();
+          const uint64_t a_st = a_d0 + (uint64_t)((uint32_t)stage * a_step);
+          for (int ti = 0; ti < nt; ++ti) {
+            uint64_t bdesc;
+            if (p.w_resident) {
+              bdesc = w_d0 + (uint64_t)((uint32_t)(kb * nt + ti) * w_step);
+            } else {
+              mbar_wait(wfull_bar + ws, wph);
+              tc_fence_after();
+              bdesc = w_d0 + (uint64_t)((uint32_t)ws * w_step);
+            }
+            const uint64_t adesc = a_st + (uint64_t)(uint32_t)p.a_off16[ti];      // this tap's rows: a row shift inside the halo tile
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+              umma_bf16_ss_elect(d_tmem, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc, (kb | ti | k) != 0 ? 1u : 0u);
+            if (!p.w_resident) { umma_commit_elect(wempty_bar + ws); if (++ws == p.w_stages) { ws = 0; wph ^= 1; } }
+          }
+          umma_commit_elect(empty_bar + stage);
+          if (++stage == p.stages) { stage = 0; phase ^= 1; }
+        }
+        umma_commit_elect(tfull_bar + as);
+        if (++as == 2) { as = 0; aphase ^= 1; }
+      }
+    } else {
       const uint32_t idesc = make_idesc_bf16(128, p.bn, 0, 0);
       int stage = 0; uint32_t phase = 0;
       int as = 0; uint32_t aphase = 0;
@@ -129,15 +219,15 @@ conv_gemm_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_c
         for (int kb = 0; kb < nkb; ++kb) {
           mbar_wait(full_bar + stage, phase);
           tc_fence_after();
-          const uint64_t adesc = make_smem_desc_sw128(smem_u32(smem_a + (size_t)stage * kATileBytes), 16, 1024);
+          const uint64_t adesc = make_smem_desc_sw128(smem_u32(smem_a + (size_t)stage * p.a_stage_bytes), 16, 1024);
           const uint64_t bdesc = make_smem_desc_sw128(smem_u32(smem_b + (size_t)stage * p.b_bytes), 16, 1024);
 #pragma unroll
           for (int k = 0; k < 4; ++k)   // 4 x (K = 16 bf16 = 32 bytes) inside the 128-byte swizzle atom
-            umma_bf16_ss(d_tmem, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc, (kb | k) != 0 ? 1u : 0u);
-          umma_commit(empty_bar + stage);          // frees the smem stage when these MMAs retire
+            umma_bf16_ss_elect(d_tmem, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc, (kb | k) != 0 ? 1u : 0u);
+          umma_commit_elect(empty_bar + stage);          // frees the smem stage when these MMAs retire
           if (++stage == p.stages) { stage = 0; phase ^= 1; }
         }
-        umma_commit(tfull_bar + as);               // accumulator ready for the epilogue
+        umma_commit_elect(tfull_bar + as);               // accumulator ready for the epilogue
         if (++as == 2) { as = 0; aphase ^= 1; }
       }
     }
@@ -163,9 +253,9 @@ conv_gemm_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_c
       const bool row_valid = row < p.ft * p.v && jj < p.t_out_ph;
       const long long grow = ((long long)tc.b * p.t_out + (long long)jj * p.phases + tc.ph) * p.v + vv;   // global output row
       for (int ch = 0; ch < p.bn / 64; ++ch, ++chunk_ctr) {
-        uint8_t* stg = staging + (chunk_ctr & 1) * kStagingBytes;
-        if (chunk_ctr >= 2) {
-          if (et == 0) tma_store_wait_read<1>();   // the store that last read this buffer has drained
+        uint8_t* stg = staging + (p.nstaging == 2 ? (chunk_ctr & 1) * kStagingBytes : 0);
+        if (chunk_ctr >= p.nstaging) {
+          if (et == 0) { if (p.nstaging == 2) tma_store_wait_read<1>(); else tma_store_wait_read<0>(); }   // the store that last read this buffer has drained
           asm volatile("bar.sync 1, 128;" ::: "memory");
         }
 #pragma unroll
@@ -392,17 +482,51 @@ int32_t launch_conv_gemm_umma(const ConvGeom& g, const bf16* in, const bf16* w, 
   }
   p.a_bytes = (uint32_t)(p.ft * g.v * 128);
   p.b_bytes = (uint32_t)(p.bn * 128);
-  const size_t stage_bytes = kATileBytes + p.b_bytes;
   p.b2_smem = (ep.bias2d && p.n_tiles == 1) ? 1 : 0;
   p.stat_partials = ep.stat_partials; p.vsum = ep.vsum;
   const size_t b2_bytes = (p.b2_smem ? (size_t)g.v * (p.bn + 4) * sizeof(float) : 0) +
                           (ep.stat_partials ? 2 * (size_t)g.n_out * sizeof(float) : 0) +
                           (ep.vsum ? (size_t)g.v * g.n_out * sizeof(float) : 0);
-  const size_t fixed = 2 * kStagingBytes + 1024 /*align slack*/ + 512 /*barriers*/ + b2_bytes;
-  int stages = (int)((220 * 1024 - fixed) / stage_bytes);
-  if (stages > 8) stages = 8;
-  if (stages < 2) { set_error("umma conv-gemm: not enough shared memory for 2 stages"); return STGCN_ERR_UNSUPPORTED; }
-  p.stages = stages;
+  const size_t budget = 220 * 1024 - (1024 /*align slack*/ + 512 /*barriers*/ + b2_bytes);
+  p.nstaging = 2; p.a_stage_bytes = kATileBytes; p.halo = 0;
+  static const bool no_halo = getenv("STGCN_NO_HALO") != nullptr;
+  int hf = p.ft;
+  if (!no_halo && s == 1 && p.ntaps[0] > 1) {
+    // stride 1: all taps read frame-shifted windows of one (ft + span)-frame tile
+    int hmin = p.taps[0][0].h_off, hmax = hmin;
+    for (int i = 1; i < p.ntaps[0]; ++i) { hmin = std::min(hmin, p.taps[0][i].h_off); hmax = std::max(hmax, p.taps[0][i].h_off); }
+    const int span = hmax - hmin;
+    const size_t a_stage = (((size_t)span * g.v + 128) * 128 + 1023) / 1024 * 1024;   // the last tap still reads 128 rows
+    const size_t w_all = (size_t)p.ntaps[0] * p.kblocks_c * p.b_bytes;
+    bool ok = p.ft + span <= 256;
+    int a_st = 0, w_st = 0, nstg = 2, resident = 0;
+    if (ok && p.n_tiles == 1 && w_all <= 80 * 1024) {
+      resident = 1; w_st = p.ntaps[0] * p.kblocks_c;
+      a_st = (int)((budget - 2 * kStagingBytes - w_all) / a_stage);
+      if (a_st < 3 && p.bn == 64) { nstg = 1; a_st = (int)((budget - kStagingBytes - w_all) / a_stage); }   // one chunk per tile: a single staging buffer
+      a_st = std::min(a_st, 4);
+      ok = a_st >= 2;
+    } else if (ok) {
+      const size_t left = budget - 2 * kStagingBytes;
+      a_st = 2;                                   // one halo tile feeds ntaps weight tiles: depth goes to the weight ring
+      if (left < a_st * a_stage + 2 * (size_t)p.b_bytes) ok = false;
+      else w_st = (int)std::min<size_t>(8, (left - a_st * a_stage) / p.b_bytes);
+    }
+    if (ok) {
+      p.halo = 1; p.h_min = hmin; p.stages = a_st; p.w_stages = w_st; p.w_resident = resident; p.nstaging = nstg;
+      p.a_stage_bytes = (uint32_t)a_stage; hf = p.ft + span; p.a_halo_bytes = (uint32_t)(hf * g.v * 128);
+      for (int i = 0; i < p.ntaps[0]; ++i) p.a_off16[i] = (p.taps[0][i].h_off - hmin) * g.v * 8;
+    }
+  }
+  size_t smem;
+  if (!p.halo) {
+    const size_t stage_bytes = kATileBytes + p.b_bytes;
+    int stages = (int)((budget - 2 * kStagingBytes) / stage_bytes);
+    if (stages > 8) stages = 8;
+    if (stages < 2) { set_error("umma conv-gemm: not enough shared memory for 2 stages"); return STGCN_ERR_UNSUPPORTED; }
+    p.stages = stages; p.w_stages = stages;
+  }
+  smem = (size_t)p.stages * p.a_stage_bytes + (size_t)p.w_stages * p.b_bytes + (size_t)p.nstaging * kStagingBytes + 1024 + 512 + b2_bytes;
   uint32_t cols = 32; while (cols < (uint32_t)(2 * p.bn)) cols <<= 1;
   p.tmem_cols = cols;
   p.bias = ep.bias; p.bias2d = ep.bias2d; p.scale = ep.scale; p.shift = ep.shift;
@@ -416,7 +540,7 @@ int32_t launch_conv_gemm_umma(const ConvGeom& g, const bf16* in, const bf16* w, 
     const uint64_t sp = g.dgrad ? 1 : s;
     uint64_t dims[5] = {C, V, sp, (uint64_t)g.t_in / sp, (uint64_t)g.nb};
     uint64_t str[4] = {C * 2, V * C * 2, sp * V * C * 2, (uint64_t)g.t_in * V * C * 2};
-    uint32_t box[5] = {64, (uint32_t)g.v, 1, (uint32_t)p.ft, 1};
+    uint32_t box[5] = {64, (uint32_t)g.v, 1, (uint32_t)hf, 1};
     STGCN_TRY(make_tmap_bf16(&map_in, in, 5, dims, str, box));
   }
   {
@@ -432,7 +556,6 @@ int32_t launch_conv_gemm_umma(const ConvGeom& g, const bf16* in, const bf16* w, 
     uint32_t box[5] = {64, (uint32_t)g.v, 1, (uint32_t)p.ft, 1};
     STGCN_TRY(make_tmap_bf16(&map_out, out, 5, dims, str, box));
   }
-  const size_t smem = (size_t)stages * stage_bytes + fixed;
   static bool attr_set = false;
   if (!attr_set) {
     cudaError_t e = cudaFuncSetAttribute(conv_gemm_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);

@@ -52,7 +52,7 @@ spatial_fused_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_con
   uint64_t* big_bar = sempty + 1;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(big_bar + 1);
   float* btab = reinterpret_cast<float*>(bars + 64);               // [2K][Co] bias vectors (512 B after the barrier block start)
-  const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
+  const int warp = uniform_warp_idx(), lane = threadIdx.x % 32;
 
   {  // padding rows of the activation tiles (never written by TMA) must be finite: they meet BigA's zero columns
     uint4* z = reinterpret_cast<uint4*>(smem_x);
@@ -103,7 +103,7 @@ spatial_fused_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_con
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
-    if (lane == 0) {
+    {   // whole warp runs the issue loop, one elected lane issues (umma_common.cuh)
       const uint32_t idesc1 = make_idesc_bf16(128, 64, 0, 1);        // A = BigA (K-major), B = x tile (MN-major)
       const uint32_t idesc2 = make_idesc_bf16(128, p.wn, 0, 0);      // A = P (K-major), B = weights (K-major)
       mbar_wait(big_bar, 0);
@@ -130,9 +130,9 @@ spatial_fused_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_con
         const uint32_t d = t_tmem + (uint32_t)(tb * 64);
 #pragma unroll
         for (int kk = 0; kk < 8; ++kk)
-          umma_bf16_ss(d, ad0 + (uint64_t)((kk / 4) * (kSpTile >> 4) + (kk % 4) * 2), bd0 + (uint64_t)(kk * 128), idesc1, kk != 0 ? 1u : 0u);
-        umma_commit(tfull + tb);
-        if (++k1 == p.k) { k1 = 0; umma_commit(xempty + xs); if (++xs == p.xs) { xs = 0; xph ^= 1; } }
+          umma_bf16_ss_elect(d, ad0 + (uint64_t)((kk / 4) * (kSpTile >> 4) + (kk % 4) * 2), bd0 + (uint64_t)(kk * 128), idesc1, kk != 0 ? 1u : 0u);
+        umma_commit_elect(tfull + tb);
+        if (++k1 == p.k) { k1 = 0; umma_commit_elect(xempty + xs); if (++xs == p.xs) { xs = 0; xph ^= 1; } }
       };
       if (total > 0) issue1(0);
       int c = 0;                                 // chunk index inside the tile of the next mixing product
@@ -150,12 +150,12 @@ spatial_fused_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_con
           const uint32_t d = s_tmem + (uint32_t)(wp * p.wn);
 #pragma unroll
           for (int kk = 0; kk < 4; ++kk)
-            umma_bf16_ss(d, ad + (uint64_t)(kk * 2), bd + (uint64_t)(kk * 2), idesc2, (c | kk) != 0 ? 1u : 0u);
-          umma_commit(wempty + ws);
+            umma_bf16_ss_elect(d, ad + (uint64_t)(kk * 2), bd + (uint64_t)(kk * 2), idesc2, (c | kk) != 0 ? 1u : 0u);
+          umma_commit_elect(wempty + ws);
           if (++ws == p.wst) { ws = 0; wph ^= 1; }
         }
-        umma_commit(pempty + pb);
-        if (++c == chunks) { c = 0; umma_commit(sfull); sph ^= 1; }
+        umma_commit_elect(pempty + pb);
+        if (++c == chunks) { c = 0; umma_commit_elect(sfull); sph ^= 1; }
       }
     }
   } else {

@@ -55,7 +55,7 @@ wgrad_umma_kernel(const __grid_constant__ CUtensorMap map_dout, const __grid_con
   uint64_t* tempty_bar = tfull_bar + 1;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 1);
   float* tr_base = reinterpret_cast<float*>(full_bar + 32);      // 4 x [32][33] floats, after the barrier block
-  const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
+  const int warp = uniform_warp_idx(), lane = threadIdx.x % 32;
 
   // one-time clear: rows TMA never writes (tile padding) must read as zero, never as NaN bit patterns
   {
@@ -105,7 +105,7 @@ wgrad_umma_kernel(const __grid_constant__ CUtensorMap map_dout, const __grid_con
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
+    {   // whole warp runs the issue loop, one elected lane issues (umma_common.cuh)
       const uint32_t idesc = make_idesc_bf16(128, p.c_tile, 1, 1);
       const uint32_t a_lbo = p.n_slabs == 2 ? (uint32_t)kATile : 0u;   // one slab: rows 64..127 alias rows 0..63 (ignored)
       int stage = 0; uint32_t phase = 0; uint32_t tphase = 0;
@@ -124,13 +124,13 @@ wgrad_umma_kernel(const __grid_constant__ CUtensorMap map_dout, const __grid_con
             const uint64_t bd = make_smem_desc_sw128(b_addr + (uint32_t)G.row_off[t] * 128u, (uint32_t)p.b_slab, 1024);
 #pragma unroll
             for (int k = 0; k < 8; ++k)          // 8 x 16 rows of the 128-row reduction step (2048 B each)
-              umma_bf16_ss(tmem_base + (uint32_t)(t * p.c_tile), ad + (uint64_t)(k * 128), bd + (uint64_t)(k * 128), idesc,
+              umma_bf16_ss_elect(tmem_base + (uint32_t)(t * p.c_tile), ad + (uint64_t)(k * 128), bd + (uint64_t)(k * 128), idesc,
                            (kb > kb0 || k > 0) ? 1u : 0u);
           }
-          umma_commit(empty_bar + stage);
+          umma_commit_elect(empty_bar + stage);
           if (++stage == p.stages) { stage = 0; phase ^= 1; }
         }
-        umma_commit(tfull_bar);
+        umma_commit_elect(tfull_bar);
         tphase ^= 1;
       }
     }
