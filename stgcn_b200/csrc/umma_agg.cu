@@ -145,26 +145,26 @@ agg_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_constan
   const int outs_per_item = p.transpose ? 1 : p.k;
 
   if (warp == 0) {
-    if (lane == 0) {
-      mbar_expect_tx(big_bar, (uint32_t)(p.k * 2 * kTile16K));
+    {   // whole warp runs the loop, one elected lane arms barriers and issues copies
+      mbar_expect_tx_e(big_bar, (uint32_t)(p.k * 2 * kTile16K));
       for (int k = 0; k < p.k; ++k)
-        for (int h = 0; h < 2; ++h) tma_load_2d(&map_big, smem_big + (size_t)(k * 2 + h) * kTile16K, big_bar, h * 64, k * 128);
+        for (int h = 0; h < 2; ++h) tma_load_2d_e(&map_big, smem_big + (size_t)(k * 2 + h) * kTile16K, big_bar, h * 64, k * 128);
       int stage = 0; uint32_t phase = 0; int xs = 0; uint32_t xphase = 0;
       for (int item = blockIdx.x; item < p.total_items; item += gridDim.x) {
         int cch, j0, b; decode(item, cch, j0, b);
         if (p.dA) {                                  // raw-input tile of the same rows / channels: B operand of the dA products
           mbar_wait(xempty_bar + xs, xphase ^ 1);
-          mbar_expect_tx(xfull_bar + xs, (uint32_t)slabs * p.tile_bytes);
+          mbar_expect_tx_e(xfull_bar + xs, (uint32_t)slabs * p.tile_bytes);
           for (int s = 0; s < slabs; ++s)
-            tma_load_5d(&map_x, smem_xb + (size_t)xs * stage_bytes + s * kTile16K, xfull_bar + xs, cch * p.nch + s * 64, 0, 0, j0, b);
+            tma_load_5d_e(&map_x, smem_xb + (size_t)xs * stage_bytes + s * kTile16K, xfull_bar + xs, cch * p.nch + s * 64, 0, 0, j0, b);
           if (++xs == 2) { xs = 0; xphase ^= 1; }
         }
         for (int l = 0; l < loads_per_item; ++l) {
           mbar_wait(empty_bar + stage, phase ^ 1);
-          mbar_expect_tx(full_bar + stage, (uint32_t)slabs * p.tile_bytes);
+          mbar_expect_tx_e(full_bar + stage, (uint32_t)slabs * p.tile_bytes);
           const int col0 = (p.transpose ? l * p.c : 0) + cch * p.nch;
           for (int s = 0; s < slabs; ++s)
-            tma_load_5d(&map_in, smem_x + (size_t)stage * stage_bytes + s * kTile16K, full_bar + stage, col0 + s * 64, 0, 0, j0, b);
+            tma_load_5d_e(&map_in, smem_x + (size_t)stage * stage_bytes + s * kTile16K, full_bar + stage, col0 + s * 64, 0, 0, j0, b);
           if (++stage == p.stages) { stage = 0; phase ^= 1; }
         }
       }
@@ -409,16 +409,16 @@ agg_dA_umma_kernel(const __grid_constant__ CUtensorMap map_dxa, const __grid_con
   const bool have_work = (int)blockIdx.x < p.total_tiles;
 
   if (warp == 0) {
-    if (lane == 0) {
+    {   // whole warp runs the loop, one elected lane arms barriers and issues copies
       int stage = 0; uint32_t phase = 0;
       for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
         const int j0 = (tile % p.m_tiles_per_b) * p.ft, b = tile / p.m_tiles_per_b;
         for (int cb = 0; cb < cbs; ++cb) {
           mbar_wait(empty_bar + stage, phase ^ 1);
-          mbar_expect_tx(full_bar + stage, (uint32_t)(p.k + 1) * p.tile_bytes);
+          mbar_expect_tx_e(full_bar + stage, (uint32_t)(p.k + 1) * p.tile_bytes);
           uint8_t* sb = smem + (size_t)stage * stage_bytes;
-          for (int k = 0; k < p.k; ++k) tma_load_5d(&map_dxa, sb + k * kTile16K, full_bar + stage, k * p.c + cb * 64, 0, 0, j0, b);
-          tma_load_5d(&map_h, sb + p.k * kTile16K, full_bar + stage, cb * 64, 0, 0, j0, b);
+          for (int k = 0; k < p.k; ++k) tma_load_5d_e(&map_dxa, sb + k * kTile16K, full_bar + stage, k * p.c + cb * 64, 0, 0, j0, b);
+          tma_load_5d_e(&map_h, sb + p.k * kTile16K, full_bar + stage, cb * 64, 0, 0, j0, b);
           if (++stage == p.stages) { stage = 0; phase ^= 1; }
         }
       }

@@ -68,6 +68,17 @@ __device__ __forceinline__ void tma_load_2d(const CUtensorMap* m, void* smem_dst
       "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
       : "memory");
 }
+// Warp-converged producer variants: called by all 32 lanes, one elected lane acts (operands stay in uniform registers).
+__device__ __forceinline__ void mbar_expect_tx_e(uint64_t* bar, uint32_t bytes) { if (elect_one()) mbar_expect_tx(bar, bytes); }
+__device__ __forceinline__ void tma_load_5d_e(const CUtensorMap* m, void* smem_dst, uint64_t* bar, int c0, int c1, int c2, int c3, int c4) {
+  if (elect_one()) tma_load_5d(m, smem_dst, bar, c0, c1, c2, c3, c4);
+}
+__device__ __forceinline__ void tma_load_3d_e(const CUtensorMap* m, void* smem_dst, uint64_t* bar, int c0, int c1, int c2) {
+  if (elect_one()) tma_load_3d(m, smem_dst, bar, c0, c1, c2);
+}
+__device__ __forceinline__ void tma_load_2d_e(const CUtensorMap* m, void* smem_dst, uint64_t* bar, int c0, int c1) {
+  if (elect_one()) tma_load_2d(m, smem_dst, bar, c0, c1);
+}
 __device__ __forceinline__ void tma_store_5d(const CUtensorMap* m, const void* smem_src, int c0, int c1, int c2, int c3, int c4) {
   asm volatile("cp.async.bulk.tensor.5d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5, %6}], [%1];" ::"l"(
                    reinterpret_cast<uint64_t>(m)),

@@ -79,23 +79,23 @@ spatial_fused_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_con
 
   if (warp == 0) {
     // ===================== TMA producer =====================
-    if (lane == 0) {
-      mbar_expect_tx(big_bar, (uint32_t)(p.k * 2 * kSpTile));
+    {   // whole warp runs the loop, one elected lane arms barriers and issues copies
+      mbar_expect_tx_e(big_bar, (uint32_t)(p.k * 2 * kSpTile));
       for (int k = 0; k < p.k; ++k)
-        for (int h = 0; h < 2; ++h) tma_load_2d(&map_big, smem_big + (size_t)(k * 2 + h) * kSpTile, big_bar, h * 64, k * 128);
+        for (int h = 0; h < 2; ++h) tma_load_2d_e(&map_big, smem_big + (size_t)(k * 2 + h) * kSpTile, big_bar, h * 64, k * 128);
       int xs = 0; uint32_t xph = 0; int ws = 0; uint32_t wph = 0;
       for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
         const int j0 = (tile % p.m_tiles_per_b) * p.ft, b = tile / p.m_tiles_per_b;
         for (int cc = 0; cc < p.cblocks; ++cc) {
           mbar_wait(xempty + xs, xph ^ 1);
-          mbar_expect_tx(xfull + xs, p.tile_bytes);
-          tma_load_5d(&map_x, smem_x + (size_t)xs * kSpTile, xfull + xs, cc * 64, 0, 0, j0, b);
+          mbar_expect_tx_e(xfull + xs, p.tile_bytes);
+          tma_load_5d_e(&map_x, smem_x + (size_t)xs * kSpTile, xfull + xs, cc * 64, 0, 0, j0, b);
           if (++xs == p.xs) { xs = 0; xph ^= 1; }
           for (int k = 0; k < p.k; ++k)
             for (int wp = 0; wp < p.wparts; ++wp) {
               mbar_wait(wempty + ws, wph ^ 1);
-              mbar_expect_tx(wfull + ws, (uint32_t)w_stage_bytes);
-              tma_load_2d(&map_w, smem_w + (size_t)ws * w_stage_bytes, wfull + ws, k * p.ci + cc * 64, wp * p.wn);
+              mbar_expect_tx_e(wfull + ws, (uint32_t)w_stage_bytes);
+              tma_load_2d_e(&map_w, smem_w + (size_t)ws * w_stage_bytes, wfull + ws, k * p.ci + cc * 64, wp * p.wn);
               if (++ws == p.wst) { ws = 0; wph ^= 1; }
             }
         }

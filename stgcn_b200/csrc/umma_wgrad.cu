@@ -86,7 +86,7 @@ wgrad_umma_kernel(const __grid_constant__ CUtensorMap map_dout, const __grid_con
   };
 
   if (warp == 0) {
-    if (lane == 0) {
+    {   // whole warp runs the loop, one elected lane arms barriers and issues copies
       int stage = 0; uint32_t phase = 0;
       for (int item = blockIdx.x; item < p.total_items; item += gridDim.x) {
         int n_t, c_t, g, kb0, kb1; decode(item, n_t, c_t, g, kb0, kb1);
@@ -94,11 +94,11 @@ wgrad_umma_kernel(const __grid_constant__ CUtensorMap map_dout, const __grid_con
         for (int kb = kb0; kb < kb1; ++kb) {
           const int b = kb / p.jblocks, j0 = (kb % p.jblocks) * p.fj;
           mbar_wait(empty_bar + stage, phase ^ 1);
-          mbar_expect_tx(full_bar + stage, p.a_bytes + p.b_bytes);
+          mbar_expect_tx_e(full_bar + stage, p.a_bytes + p.b_bytes);
           for (int s = 0; s < p.n_slabs; ++s)
-            tma_load_5d(&map_dout, smem_a + (size_t)stage * a_stage + s * kATile, full_bar + stage, n_t * 128 + s * 64, 0, 0, j0, b);
+            tma_load_5d_e(&map_dout, smem_a + (size_t)stage * a_stage + s * kATile, full_bar + stage, n_t * 128 + s * 64, 0, 0, j0, b);
           for (int s = 0; s < p.c_tile / 64; ++s)
-            tma_load_5d(&map_in, smem_b + (size_t)stage * b_stage + s * p.b_slab, full_bar + stage, c_t * p.c_tile + s * 64, 0,
+            tma_load_5d_e(&map_in, smem_b + (size_t)stage * b_stage + s * p.b_slab, full_bar + stage, c_t * p.c_tile + s * 64, 0,
                         G.parity, j0 + G.h_min, b);
           if (++stage == p.stages) { stage = 0; phase ^= 1; }
         }
