@@ -25,7 +25,7 @@ namespace stgcn {
 
 using namespace umma;
 
-constexpr int kUmmaThreads = 192;
+constexpr int kUmmaThreads = 320;          // TMA warp, MMA warp, two epilogue groups of four warps
 constexpr int kMaxTaps = 16;
 constexpr int kATileBytes = 128 * 128;      // 128 rows x 64 bf16
 constexpr int kStagingBytes = 128 * 128;    // 128 rows x 64 bf16 (one TMA-store box)
@@ -76,8 +76,8 @@ conv_gemm_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_c
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   uint8_t* smem_a = smem;                                        // stages x a_stage_bytes (16 KB, or the halo tile)
   uint8_t* smem_b = smem_a + (size_t)p.stages * p.a_stage_bytes; // w_stages x bn*128 B (multiple of 1024)
-  uint8_t* staging = smem_b + (size_t)p.w_stages * p.b_bytes;    // nstaging x 16 KB
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(staging + (size_t)p.nstaging * kStagingBytes);
+  uint8_t* staging = smem_b + (size_t)p.w_stages * p.b_bytes;    // 2 groups x nstaging x 16 KB
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(staging + (size_t)2 * p.nstaging * kStagingBytes);
   uint64_t* empty_bar = full_bar + 8;
   uint64_t* tfull_bar = full_bar + 16;
   uint64_t* tempty_bar = full_bar + 18;
@@ -93,7 +93,7 @@ conv_gemm_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_c
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&map_in); prefetch_tmap(&map_w); prefetch_tmap(&map_out);
     for (int s = 0; s < p.stages; ++s) { mbar_init(full_bar + s, 1); mbar_init(empty_bar + s, 1); }
-    for (int a = 0; a < 2; ++a) { mbar_init(tfull_bar + a, 1); mbar_init(tempty_bar + a, 128); }
+    for (int a = 0; a < 2; ++a) { mbar_init(tfull_bar + a, 1); mbar_init(tempty_bar + a, 256); }
     for (int a = 0; a < 16; ++a) { mbar_init(wfull_bar + a, 1); mbar_init(wempty_bar + a, 1); }
     fence_barrier_init();
   }
@@ -232,19 +232,25 @@ conv_gemm_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_c
       }
     }
   } else {
-    // ===================== epilogue warps (2..5) =====================
+    // ===================== epilogue warps: group 0 = warps 2..5, group 1 = warps 6..9 =====================
+    // the groups take alternate 64-column chunks (alternate tiles when a tile is one chunk); each has its own staging buffers
     const int q = warp % 4;                        // TMEM lane quarter this warp may access
     const int row = q * 32 + lane;                 // tile row == TMEM lane
-    const int et = threadIdx.x - 64;               // 0..127
+    const int grp = (warp - 2) >> 2;               // epilogue group
+    const int et = threadIdx.x - 64 - grp * 128;   // 0..127 inside the group
+    const int bar_a = 1 + 2 * grp, bar_b = 2 + 2 * grp;   // named barriers of this group
+    const int et2 = threadIdx.x - 64;              // 0..255 over both groups
     const int fl = row / p.v, vv = row % p.v;
     int as = 0; uint32_t aphase = 0;
-    int chunk_ctr = 0;
+    int chunk_ctr = 0;                             // chunks this group has staged
+    int gchunk = 0;                                // chunks of the CTA so far (both groups count them)
+    uint8_t* const my_staging = staging + (size_t)grp * p.nstaging * kStagingBytes;
     const int b2_ld = p.bn + 4;                    // row pitch (floats): 16-byte rows, conflict-free across joints
     if (p.b2_smem)
-      for (int i = et; i < p.v * p.bn; i += 128) b2_tab[(i / p.bn) * b2_ld + (i % p.bn)] = __ldg(p.bias2d + i);
-    if (p.stat_partials) for (int i = et; i < 2 * p.n_out; i += 128) stat_acc[i] = 0.f;
-    if (p.vsum) for (int i = et; i < p.v * p.n_out; i += 128) vsum_acc[i] = 0.f;
-    asm volatile("bar.sync 1, 128;" ::: "memory");
+      for (int i = et2; i < p.v * p.bn; i += 256) b2_tab[(i / p.bn) * b2_ld + (i % p.bn)] = __ldg(p.bias2d + i);
+    if (p.stat_partials) for (int i = et2; i < 2 * p.n_out; i += 256) stat_acc[i] = 0.f;
+    if (p.vsum) for (int i = et2; i < p.v * p.n_out; i += 256) vsum_acc[i] = 0.f;
+    asm volatile("bar.sync 5, 256;" ::: "memory");
     for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
       const TileCoord tc = decode_tile(p, tile);
       mbar_wait(tfull_bar + as, aphase);
@@ -252,12 +258,14 @@ conv_gemm_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_c
       const int jj = tc.j0 + fl;
       const bool row_valid = row < p.ft * p.v && jj < p.t_out_ph;
       const long long grow = ((long long)tc.b * p.t_out + (long long)jj * p.phases + tc.ph) * p.v + vv;   // global output row
-      for (int ch = 0; ch < p.bn / 64; ++ch, ++chunk_ctr) {
-        uint8_t* stg = staging + (p.nstaging == 2 ? (chunk_ctr & 1) * kStagingBytes : 0);
+      for (int ch = 0; ch < p.bn / 64; ++ch) {
+        if (((gchunk++) & 1) != grp) continue;
+        uint8_t* stg = my_staging + (size_t)(chunk_ctr & (p.nstaging - 1)) * kStagingBytes;   // nstaging (per group) is 1 or 2
         if (chunk_ctr >= p.nstaging) {
           if (et == 0) { if (p.nstaging == 2) tma_store_wait_read<1>(); else tma_store_wait_read<0>(); }   // the store that last read this buffer has drained
-          asm volatile("bar.sync 1, 128;" ::: "memory");
+          asm volatile("bar.sync %0, 128;" ::"r"(bar_a) : "memory");
         }
+        ++chunk_ctr;
 #pragma unroll
         for (int half = 0; half < 2; ++half) {
           uint32_t r[32];
@@ -332,7 +340,7 @@ conv_gemm_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_c
           }
         }
         fence_proxy_async_smem();                  // generic-proxy smem writes -> visible to the TMA engine
-        asm volatile("bar.sync 2, 128;" ::: "memory");
+        asm volatile("bar.sync %0, 128;" ::"r"(bar_b) : "memory");
         if (et == 0) {
           tma_store_5d(&map_out, stg, tc.n_t * p.bn + ch * 64, 0, tc.ph, tc.j0, tc.b);
           tma_store_commit();
@@ -361,7 +369,7 @@ conv_gemm_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_c
                 const int r = f2 * p.v + v2;
                 sacc += __bfloat162float(*reinterpret_cast<const bf16*>(stg + r * 128 + ((cj ^ (r & 7)) << 4) + ((col & 7) << 1)));
               }
-              vsum_acc[v2 * p.n_out + nbase + col] += sacc;        // (v, col) of a chunk always belongs to this thread
+              atomicAdd(vsum_acc + v2 * p.n_out + nbase + col, sacc);
             }
           }
         }
@@ -372,11 +380,11 @@ conv_gemm_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_c
     }
     if (et == 0) tma_store_wait<0>();
     if (p.stat_partials || p.vsum) {
-      asm volatile("bar.sync 1, 128;" ::: "memory");
+      asm volatile("bar.sync 5, 256;" ::: "memory");
       if (p.stat_partials)
-        for (int i = et; i < 2 * p.n_out; i += 128) p.stat_partials[(size_t)blockIdx.x * 2 * p.n_out + i] = stat_acc[i];
+        for (int i = et2; i < 2 * p.n_out; i += 256) p.stat_partials[(size_t)blockIdx.x * 2 * p.n_out + i] = stat_acc[i];
       if (p.vsum)
-        for (int i = et; i < p.v * p.n_out; i += 128) atomicAdd(p.vsum + i, vsum_acc[i]);
+        for (int i = et2; i < p.v * p.n_out; i += 256) atomicAdd(p.vsum + i, vsum_acc[i]);
     }
   }
   tc_fence_before();
@@ -488,7 +496,7 @@ int32_t launch_conv_gemm_umma(const ConvGeom& g, const bf16* in, const bf16* w, 
                           (ep.stat_partials ? 2 * (size_t)g.n_out * sizeof(float) : 0) +
                           (ep.vsum ? (size_t)g.v * g.n_out * sizeof(float) : 0);
   const size_t budget = 220 * 1024 - (1024 /*align slack*/ + 512 /*barriers*/ + b2_bytes);
-  p.nstaging = 2; p.a_stage_bytes = kATileBytes; p.halo = 0;
+  p.nstaging = 1; p.a_stage_bytes = kATileBytes; p.halo = 0;        // staging buffers PER epilogue group
   static const bool no_halo = getenv("STGCN_NO_HALO") != nullptr;
   int hf = p.ft;
   if (!no_halo && s == 1 && p.ntaps[0] > 1) {
@@ -499,11 +507,10 @@ int32_t launch_conv_gemm_umma(const ConvGeom& g, const bf16* in, const bf16* w, 
     const size_t a_stage = (((size_t)span * g.v + 128) * 128 + 1023) / 1024 * 1024;   // the last tap still reads 128 rows
     const size_t w_all = (size_t)p.ntaps[0] * p.kblocks_c * p.b_bytes;
     bool ok = p.ft + span <= 256;
-    int a_st = 0, w_st = 0, nstg = 2, resident = 0;
+    int a_st = 0, w_st = 0, nstg = 1, resident = 0;
     if (ok && p.n_tiles == 1 && w_all <= 80 * 1024) {
       resident = 1; w_st = p.ntaps[0] * p.kblocks_c;
       a_st = (int)((budget - 2 * kStagingBytes - w_all) / a_stage);
-      if (a_st < 3 && p.bn == 64) { nstg = 1; a_st = (int)((budget - kStagingBytes - w_all) / a_stage); }   // one chunk per tile: a single staging buffer
       a_st = std::min(a_st, 4);
       ok = a_st >= 2;
     } else if (ok) {
@@ -521,12 +528,15 @@ int32_t launch_conv_gemm_umma(const ConvGeom& g, const bf16* in, const bf16* w, 
   size_t smem;
   if (!p.halo) {
     const size_t stage_bytes = kATileBytes + p.b_bytes;
-    int stages = (int)((budget - 2 * kStagingBytes) / stage_bytes);
+    // several 64-column chunks per tile and a short reduction: the TMA-store drain latency, not the MMAs, paces the kernel,
+    // so give the epilogue four staging buffers when the load ring stays at least four deep
+    if ((budget - 4 * kStagingBytes) / stage_bytes >= 3) p.nstaging = 2;
+    int stages = (int)((budget - (size_t)2 * p.nstaging * kStagingBytes) / stage_bytes);
     if (stages > 8) stages = 8;
     if (stages < 2) { set_error("umma conv-gemm: not enough shared memory for 2 stages"); return STGCN_ERR_UNSUPPORTED; }
     p.stages = stages; p.w_stages = stages;
   }
-  smem = (size_t)p.stages * p.a_stage_bytes + (size_t)p.w_stages * p.b_bytes + (size_t)p.nstaging * kStagingBytes + 1024 + 512 + b2_bytes;
+  smem = (size_t)p.stages * p.a_stage_bytes + (size_t)p.w_stages * p.b_bytes + (size_t)2 * p.nstaging * kStagingBytes + 1024 + 512 + b2_bytes;
   uint32_t cols = 32; while (cols < (uint32_t)(2 * p.bn)) cols <<= 1;
   p.tmem_cols = cols;
   p.bias = ep.bias; p.bias2d = ep.bias2d; p.scale = ep.scale; p.shift = ep.shift;

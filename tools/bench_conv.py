@@ -26,5 +26,7 @@ def run(nb, t, v, c, n_out, taps, stride, pad, iters=20):
 
 for shape in [(64, 300, 25, 64, 64, 9, 1, 4), (64, 300, 25, 64, 128, 9, 2, 4), (64, 150, 25, 128, 128, 9, 1, 4),
               (64, 150, 25, 128, 256, 9, 2, 4), (64, 75, 25, 256, 256, 9, 1, 4), (64, 300, 25, 192, 64, 1, 1, 0),
-              (64, 75, 25, 768, 256, 1, 1, 0)]:
-    run(*shape)
+              (64, 75, 25, 768, 256, 1, 1, 0),
+              (64, 300, 25, 64, 192, 1, 1, 0), (64, 150, 25, 128, 384, 1, 1, 0), (64, 75, 25, 256, 768, 1, 1, 0)]:
+    if len(sys.argv) > 1 and str(shape[3]) + 'x' + str(shape[4]) not in sys.argv[1:]: continue
+    run(*shape, iters=int(os.environ.get('ITERS', '20')))
