@@ -50,7 +50,7 @@ class ClockSampler:
         self.rows, self.p = [], None
         try:
             self.p = subprocess.Popen(['nvidia-smi', '-i', str(index), '--query-gpu=' + self.Q,
-                                       '--format=csv,noheader,nounits', '-lms', '100'], stdout=subprocess.PIPE, text=True)
+                                       '--format=csv,noheader,nounits', '-lms', '20'], stdout=subprocess.PIPE, text=True)
             threading.Thread(target=self._read, daemon=True).start()
         except Exception:
             self.p = None
@@ -234,7 +234,6 @@ def main():
     l0 = _lib.launch_count()
     ms_train = timed(lambda i: (flush.zero_(), train_step(*dev_batches[i % n_batches])), args.steps)
     launches = _lib.launch_count() - l0
-    clocks = sampler.stop() if sampler else None
     # the L2 flush is inside the timed region: subtract its own measured cost
     ms_flush = timed(lambda i: flush.zero_(), args.steps)
     ms_step = (ms_train - ms_flush) / args.steps
@@ -245,6 +244,7 @@ def main():
     ms_instr = (timed(lambda i: (flush.zero_(), train_step(*dev_batches[i % n_batches])), args.steps) - ms_flush) / args.steps
     _lib.timing_enable(False)
     prof = _lib.timing_read()
+    clocks = sampler.stop() if sampler else None      # sampled every 20 ms across the timed pass and the instrumented pass
 
     # ---- end to end: pinned host batch -> H2D -> step -> loss D2H ------------------------
     xin = torch.empty_like(dev_batches[0][0]); yin = torch.empty_like(dev_batches[0][1])
@@ -286,10 +286,17 @@ def main():
     fwd_flops, _ = flops_forward_per_neff()
     um = prof.get('umma_conv_gemm')
     roof = None
+    traffic, traffic_src = None, None
+    try:    # DRAM bytes per launch of the same kernel from the committed ncu capture (dram__bytes_read.sum + dram__bytes_write.sum)
+        tj = json.load(open(os.path.join(ROOT, 'profiles', 'traffic.json')))['conv_gemm_umma_kernel']
+        traffic, traffic_src = tj['avg_dram_bytes_per_launch'], tj['source']
+    except Exception:
+        pass
     if um:
         ach = um[1] / (um[0] * 1e-3) / 1e12
         roof = {'bound': 'tensor', 'kernel': 'conv_gemm_umma_kernel', 'achieved': ach, 'peak': peak_tf, 'unit': 'TFLOP/s',
-                'frac': ach / peak_tf, 'traffic': None, 'launches': um[2], 'ms_total': um[0],
+                'frac': ach / peak_tf, 'traffic': traffic, 'traffic_unit': 'DRAM bytes per launch (ncu)', 'traffic_source': traffic_src,
+                'flop_per_launch': um[1] / max(um[2], 1), 'launches': um[2], 'ms_total': um[0],
                 'peak_source': 'MEASURED_PEAKS.json bf16_tflops_sustained' if peaks else 'fallback 1.4 PFLOP/s'}
     out = {'metric': 'ST-GCN training sequences/s (3x300x25x2, 10-layer, fwd+CE+bwd+Adam)', 'value': value, 'unit': 'seq/s',
            'n_gpus': world, 'steps': args.steps, 'warmup': W, 'ms_per_step': ms_step, 'higher_is_better': True,
