@@ -223,11 +223,73 @@ __global__ void __launch_bounds__(kAggThreads) agg_dA_kernel(const T* __restrict
     if (okv[j] >= 0) atomicAdd(dA + okv[j] * V + ow[j], acc[j]);
 }
 
+// Small-C_in form (first block, C_in <= 4, no affine): per frame only K*V*C + V*C values matter, so a batch of 8 frames is staged
+// per barrier pair as zero-padded float4 rows and every thread runs 4-wide dot products for its <= 8 outputs.
+constexpr int kDaFrames = 8;
+template <class T>
+__global__ void __launch_bounds__(kAggThreads) agg_dA_small_kernel(const T* __restrict__ dxa, const T* __restrict__ x, long long frames,
+                                                                   int V, int C, int K, int KC, float* __restrict__ dA) {
+  extern __shared__ float4 sm4[];
+  const int KV = K * V;
+  float4* hs = sm4;                          // [frames][V]
+  float4* gs = sm4 + kDaFrames * V;          // [frames][K*V]
+  const int nout = K * V * V;
+  float acc[kDaPer];
+  int okv[kDaPer], ow[kDaPer];
+#pragma unroll
+  for (int j = 0; j < kDaPer; ++j) {
+    acc[j] = 0.f;
+    int o = threadIdx.x + j * kAggThreads;
+    okv[j] = o < nout ? o / V : -1;
+    ow[j] = o < nout ? o % V : 0;
+  }
+  for (long long f0 = (long long)blockIdx.x * kDaFrames; f0 < frames; f0 += (long long)gridDim.x * kDaFrames) {
+    const int nf = (int)min((long long)kDaFrames, frames - f0);
+    __syncthreads();
+    for (int i = threadIdx.x; i < nf * V; i += blockDim.x) {
+      const T* xp = x + (f0 * V + i) * C;
+      float t[4] = {0.f, 0.f, 0.f, 0.f};
+      for (int c = 0; c < C; ++c) t[c] = ldf(xp + c);
+      hs[i] = make_float4(t[0], t[1], t[2], t[3]);
+    }
+    for (int i = threadIdx.x; i < nf * KV; i += blockDim.x) {
+      const int fb = i / KV, kv = i - fb * KV, k = kv / V, v = kv - k * V;
+      const T* gp = dxa + ((f0 + fb) * V + v) * KC + k * C;
+      float t[4] = {0.f, 0.f, 0.f, 0.f};
+      for (int c = 0; c < C; ++c) t[c] = ldf(gp + c);
+      gs[i] = make_float4(t[0], t[1], t[2], t[3]);
+    }
+    __syncthreads();
+#pragma unroll
+    for (int j = 0; j < kDaPer; ++j) {
+      if (okv[j] >= 0) {
+        float s = acc[j];
+        for (int fb = 0; fb < nf; ++fb) {
+          const float4 g = gs[fb * KV + okv[j]], h = hs[fb * V + ow[j]];
+          s = fmaf(g.x, h.x, fmaf(g.y, h.y, fmaf(g.z, h.z, fmaf(g.w, h.w, s))));
+        }
+        acc[j] = s;
+      }
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < kDaPer; ++j)
+    if (okv[j] >= 0) atomicAdd(dA + okv[j] * V + ow[j], acc[j]);
+}
+
 template <class T>
 int32_t launch_agg_dA(const T* dxa, const T* x, long long frames, int V, int C, int K, const float* a, const float* b,
                       int relu, float* dA, cudaStream_t st, int ld) {
   KernelTimer kt_(KC_AGG_DA, 2.0 * frames * V * V * (double)K * C, st);
   if (K * V * V > kDaPer * kAggThreads) { set_error("agg_dA: K*V*V=%d too large", K * V * V); return STGCN_ERR_UNSUPPORTED; }
+  if (C <= 4 && !a && !relu) {
+    const long long batches = (frames + kDaFrames - 1) / kDaFrames;
+    const int nblk = (int)std::min<long long>(batches, 148 * 4);
+    agg_dA_small_kernel<T><<<nblk, kAggThreads, (size_t)kDaFrames * (V + K * V) * sizeof(float4), st>>>(dxa, x, frames, V, C, K,
+                                                                                                       ld > 0 ? ld : K * C, dA);
+    STGCN_CHECK_LAUNCH("agg_dA_small");
+    return STGCN_OK;
+  }
   int CC = std::min(C, 64);
   size_t smem = (size_t)(V + K * V) * (CC + 1) * sizeof(float);
   int blocks = (int)std::min<long long>(frames, 148 * 4);
@@ -505,14 +567,14 @@ int32_t launch_adjacency_rowsum(const float* A, int K, int V, float* rs, cudaStr
 //   dgamma_c = invstd_c * ( sum_{k,co} W[(k,co),c] * dWraw[(k,co),c]  -  mean_c * dbeta_c )
 //   dW       = dWraw (.) a  +  q (x) b        (in place; the second term is the BN shift travelling through bias2d')
 //   coef     = { mean, a*dbeta/m, a*invstd*dgamma/m }  for the fused  dx = dh' - c1 - (x-mean)*c2   epilogue
-// 32 channels per CTA, 32 row-slices reduced through shared memory.
+// 8 channels per CTA (C_in / 8 CTAs keep the launch latency-bound part short), 128 row-slices reduced through shared memory.
 __global__ void __launch_bounds__(1024) bn1_fold_grads_kernel(const float* __restrict__ W, float* __restrict__ dW,
                                                               const float* __restrict__ stats, const float* __restrict__ t1,
                                                               const float* __restrict__ rowsum_q, int K, int V, int Co, int Ci,
                                                               int training, float inv_m, float* __restrict__ dgamma,
                                                               float* __restrict__ dbeta, float* __restrict__ coef) {
   __shared__ float q[1024];
-  __shared__ float red[2][32][33];
+  __shared__ float red[2][128][9];
   const int KCo = K * Co;
   for (int i = threadIdx.x; i < KCo; i += blockDim.x) {
     const int k = i / Co, co = i % Co;
@@ -521,38 +583,42 @@ __global__ void __launch_bounds__(1024) bn1_fold_grads_kernel(const float* __res
     q[i] = s;
   }
   __syncthreads();
-  const int cl = threadIdx.x & 31, sl = threadIdx.x >> 5, c = blockIdx.x * 32 + cl;
+  const int cl = threadIdx.x & 7, sl = threadIdx.x >> 3, c = blockIdx.x * 8 + cl;
   float s1 = 0.f, s2 = 0.f;
+  float a = 0.f, bsh = 0.f;
   if (c < Ci) {
-    for (int r = sl; r < KCo; r += 32) {
-      const float w = W[(size_t)r * Ci + c];
+    a = stats[2 * Ci + c]; bsh = stats[3 * Ci + c];
+    for (int r = sl; r < KCo; r += 128) {
+      const size_t o = (size_t)r * Ci + c;
+      const float w = W[o], g = dW[o];
       s1 = fmaf(q[r], w, s1);
-      s2 = fmaf(w, dW[(size_t)r * Ci + c], s2);
+      s2 = fmaf(w, g, s2);
+      dW[o] = fmaf(g, a, q[r] * bsh);            // raw-weight gradient: scale + the shift term through bias2d'
     }
   }
   red[0][sl][cl] = s1; red[1][sl][cl] = s2;
   __syncthreads();
-  if (c < Ci) {
-    const float a = stats[2 * Ci + c];
-    const float b = stats[3 * Ci + c];
-    for (int r = sl; r < KCo; r += 32) dW[(size_t)r * Ci + c] = fmaf(dW[(size_t)r * Ci + c], a, q[r] * b);   // + shift term through bias2d'
-    if (sl == 0) {
-      float db = 0.f, sw = 0.f;
-      for (int i = 0; i < 32; ++i) { db += red[0][i][cl]; sw += red[1][i][cl]; }
-      const float mean = stats[c], invstd = stats[Ci + c];
-      const float dg = invstd * (sw - mean * db);
-      dgamma[c] = dg; dbeta[c] = db;
-      coef[c] = mean;
-      coef[Ci + c] = training ? a * db * inv_m : 0.f;
-      coef[2 * Ci + c] = training ? a * invstd * dg * inv_m : 0.f;
-    }
+  if (c < Ci && sl < 2) {                         // slice 0 sums the dbeta partials, slice 1 the dgamma partials, then they meet
+    float acc = 0.f;
+    for (int i = 0; i < 128; ++i) acc += red[sl][i][cl];
+    red[sl][0][cl] = acc;
+  }
+  __syncthreads();
+  if (c < Ci && sl == 0) {
+    const float db = red[0][0][cl], sw = red[1][0][cl];
+    const float mean = stats[c], invstd = stats[Ci + c];
+    const float dg = invstd * (sw - mean * db);
+    dgamma[c] = dg; dbeta[c] = db;
+    coef[c] = mean;
+    coef[Ci + c] = training ? a * db * inv_m : 0.f;
+    coef[2 * Ci + c] = training ? a * invstd * dg * inv_m : 0.f;
   }
 }
 int32_t launch_bn1_fold_grads(const float* W, float* dW, const float* stats, const float* t1, const float* rowsum_q, int K, int V,
                               int Co, int Ci, int training, double rows, float* dgamma, float* dbeta, float* coef, cudaStream_t st) {
   KernelTimer kt_(KC_PACK, 0.0, st);
   if (K * Co > 1024) { set_error("bn1_fold_grads: K*C_out=%d > 1024", K * Co); return STGCN_ERR_UNSUPPORTED; }
-  bn1_fold_grads_kernel<<<cdiv(Ci, 32), 1024, 0, st>>>(W, dW, stats, t1, rowsum_q, K, V, Co, Ci, training, (float)(1.0 / rows), dgamma,
+  bn1_fold_grads_kernel<<<cdiv(Ci, 8), 1024, 0, st>>>(W, dW, stats, t1, rowsum_q, K, V, Co, Ci, training, (float)(1.0 / rows), dgamma,
                                                        dbeta, coef);
   STGCN_CHECK_LAUNCH("bn1_fold_grads");
   return STGCN_OK;

@@ -62,7 +62,21 @@ static int32_t validate(const StgcnBlockDesc* d) {
 static bool fold_ok_desc(const StgcnBlockDesc& d, const Dims& m);
 static bool smallc_ok_desc(const StgcnBlockDesc& d, const Dims& m);
 constexpr int kSmallLd = 64;      // padded K*C_in of the small-C_in path
-template <class T> struct Saved { float* stats1; float* stats2; T* S; T* U; T* XA; };
+// operands the folded-BatchNorm spatial path prepares from (A, W, BN-1 coefficients): block-diagonal adjacency, W.diag(a) and its
+// transpose, bias vectors.  Forward carves them from the saved buffer when there is one, so backward reuses them as they are.
+struct FoldPrep { void* prep; bf16* w2p; bf16* w2pT; float* wb; float* wbb; bool valid; };
+static FoldPrep carve_fold_prep(Arena& a, const Dims& m) {
+  FoldPrep f;
+  const int KCi = m.k * m.ci;
+  f.prep = a.get<uint8_t>(umma_agg_prep_bytes(m.k));
+  f.w2p = a.get<bf16>((size_t)m.co * KCi);
+  f.w2pT = a.get<bf16>((size_t)m.co * KCi);
+  f.wb = a.get<float>((size_t)m.k * m.co);
+  f.wbb = a.get<float>((size_t)m.k * m.co);
+  f.valid = true;
+  return f;
+}
+template <class T> struct Saved { float* stats1; float* stats2; T* S; T* U; T* XA; FoldPrep fp; };
 template <class T> static Saved<T> carve_saved(Arena& a, const StgcnBlockDesc& d, const Dims& m) {
   Saved<T> s;
   s.stats1 = a.get<float>(4 * m.ci);
@@ -71,6 +85,8 @@ template <class T> static Saved<T> carve_saved(Arena& a, const StgcnBlockDesc& d
   s.U = d.residual == STGCN_RES_NONE ? a.get<T>(m.rows_out * m.co) : nullptr;
   // folded-BatchNorm path: the aggregated raw input (rows x K*C_in) is kept so backward does not re-aggregate
   s.XA = fold_ok_desc(d, m) ? a.get<T>(m.rows_in * m.k * m.ci) : (smallc_ok_desc(d, m) ? a.get<T>(m.rows_in * kSmallLd) : nullptr);
+  s.fp.valid = false;
+  if (fold_ok_desc(d, m)) s.fp = carve_fold_prep(a, m);
   return s;
 }
 
@@ -161,11 +177,13 @@ template <class T> static bool fold_ok(const Engine<T>& e, const Dims& m, const 
 }
 template <class T> struct Bn1Fold {      // backward of the folded BatchNorm-1 (spatial_bwd fills dgamma / dbeta / dx itself)
   const float* stats; int training; float* dgamma; float* dbeta; T* dx; bool done; const T* xa_saved;
+  const FoldPrep* prep_saved;   // operands prepared (and kept) by forward, or null
   float* t1_ready;      // per-joint column sums of dS already produced by the temporal dgrad epilogue (or null)
 };
 template <class T>
 static int32_t spatial_fwd(Engine<T>& e, const Dims& m, const T* x, const float* aff_a, const float* aff_b, int relu1,
-                           const float* A, const float* W, const float* Wb, T* S, T* xa_keep = nullptr) {
+                           const float* A, const float* W, const float* Wb, T* S, T* xa_keep = nullptr,
+                           const FoldPrep* keep_prep = nullptr) {
   Arena& ws = e.ws;
   T* XA = xa_keep ? xa_keep : ws.template get<T>(m.rows_in * m.k * m.ci);
   float* b2d = ws.template get<float>((size_t)m.v * m.co);
@@ -191,11 +209,8 @@ static int32_t spatial_fwd(Engine<T>& e, const Dims& m, const T* x, const float*
     if (fold_ok<T>(e, m, aff_a, relu1)) {
       // BatchNorm-1 folded into the 1x1 weights: aggregate the RAW input, GEMM-1 against W.diag(a), shift through bias2d
       const int KCi = m.k * m.ci;
-      void* prep = ws.template get<uint8_t>(umma_agg_prep_bytes(m.k));
-      bf16* w2p = ws.template get<bf16>((size_t)m.co * KCi);
-      bf16* w2pT = ws.template get<bf16>((size_t)m.co * KCi);
-      float* wb = ws.template get<float>((size_t)m.k * m.co);
-      float* wbb = ws.template get<float>((size_t)m.k * m.co);
+      const FoldPrep fp = (keep_prep && keep_prep->valid) ? *keep_prep : carve_fold_prep(ws, m);
+      void* prep = fp.prep; bf16* w2p = fp.w2p; bf16* w2pT = fp.w2pT; float* wb = fp.wb; float* wbb = fp.wbb;
       float* rsum2 = ws.template get<float>((size_t)2 * m.k * m.v);
       float* bvec2 = ws.template get<float>((size_t)2 * m.k * m.co);
       if (ws.dry) return STGCN_OK;
@@ -287,17 +302,17 @@ static int32_t spatial_bwd(Engine<T>& e, const Dims& m, const T* x, const float*
     }
     if (bf && fold_ok<T>(e, m, aff_a, relu1)) {
       bf->done = true;
-      void* prep = ws.template get<uint8_t>(umma_agg_prep_bytes(m.k));
-      bf16* w2p = ws.template get<bf16>((size_t)m.co * KCi);
-      bf16* w2pT = ws.template get<bf16>((size_t)m.co * KCi);
-      float* wb = ws.template get<float>((size_t)m.k * m.co);
-      float* wbb = ws.template get<float>((size_t)m.k * m.co);
+      const bool have_prep = bf->prep_saved && bf->prep_saved->valid;
+      const FoldPrep fp = have_prep ? *bf->prep_saved : carve_fold_prep(ws, m);
+      void* prep = fp.prep; bf16* w2p = fp.w2p; bf16* w2pT = fp.w2pT; float* wb = fp.wb; float* wbb = fp.wbb;
       float* b2d = ws.template get<float>((size_t)m.v * m.co);
       float* coef = ws.template get<float>((size_t)3 * m.ci);
       if (!ws.dry) {
         if (!ws.ok()) return STGCN_ERR_WORKSPACE;
-        STGCN_TRY(launch_build_big_adjacency(A, m.k, m.v, prep, e.st));
-        STGCN_TRY(launch_bn1_fold(W, Wb, A, umma_agg_rowsum_q(prep, m.k), aff_a, aff_b, m.k, m.v, m.co, m.ci, w2p, w2pT, wb, wbb, b2d, e.st));
+        if (!have_prep) {
+          STGCN_TRY(launch_build_big_adjacency(A, m.k, m.v, prep, e.st));
+          STGCN_TRY(launch_bn1_fold(W, Wb, A, umma_agg_rowsum_q(prep, m.k), aff_a, aff_b, m.k, m.v, m.co, m.ci, w2p, w2pT, wb, wbb, b2d, e.st));
+        }
         if (!bf->xa_saved) STGCN_TRY(launch_agg_fwd_umma(x, m.n, m.t, m.v, m.ci, m.k, prep, nullptr, nullptr, XA, e.st));   // else kept by forward
         cudaMemsetAsync(dA, 0, sizeof(float) * (size_t)m.k * m.v * m.v, e.st);
         if (!have_t1) {
@@ -376,7 +391,7 @@ static int32_t block_forward_t(const StgcnBlockDesc& d, const T* x, const StgcnB
   Saved<T> S;
   const bool keep = saved_mem != nullptr || ws.dry;
   if (saved_mem) S = carve_saved<T>(sv, d, m);
-  else { S.stats1 = ws.get<float>(4 * m.ci); S.stats2 = ws.get<float>(4 * m.co); S.S = ws.get<T>(m.rows_in * m.co); S.U = nullptr; S.XA = nullptr; }
+  else { S.stats1 = ws.get<float>(4 * m.ci); S.stats2 = ws.get<float>(4 * m.co); S.S = ws.get<T>(m.rows_in * m.co); S.U = nullptr; S.XA = nullptr; S.fp.valid = false; }
   float* partials = ws.get<float>(stat_partials_bytes(std::max(m.ci, m.co)) / sizeof(float));
   Engine<T> e{d, ws, st};
   const bool res = d.residual != STGCN_RES_NONE;
@@ -392,7 +407,7 @@ static int32_t block_forward_t(const StgcnBlockDesc& d, const T* x, const StgcnB
       STGCN_TRY(launch_bn_eval_coeffs(m.ci, P.bn1_weight, P.bn1_bias, P.bn1_running_mean, P.bn1_running_var, d.bn_eps, S.stats1, st));
     }
   }
-  STGCN_TRY(spatial_fwd<T>(e, m, x, S.stats1 + 2 * m.ci, S.stats1 + 3 * m.ci, relu1, P.A, P.W, P.W_bias, S.S, saved_mem ? S.XA : nullptr));
+  STGCN_TRY(spatial_fwd<T>(e, m, x, S.stats1 + 2 * m.ci, S.stats1 + 3 * m.ci, relu1, P.A, P.W, P.W_bias, S.S, saved_mem ? S.XA : nullptr, saved_mem ? &S.fp : nullptr));
 
   // temporal weights: packed [tap][n=co][c=ci] = Wt[(co*Co+ci)*gamma + tap]
   const WIndex wiT = widx(kNoDiv, 0, (long long)m.co * m.gamma, kNoDiv, 0, m.gamma, 1);
@@ -507,7 +522,7 @@ static int32_t block_backward_t(const StgcnBlockDesc& d, const T* x, const T* y,
     STGCN_TRY(launch_bn_bwd_finalize(partials, nblk, m.co, sums2, G.bn2_weight, G.bn2_bias, st));
     STGCN_TRY(launch_bn_bwd_apply<T>(dTin, S.S, S.stats2, sums2, m.rows_in, m.co, 1, d.training, 0.f, 0, 0, dS, st));
   }
-  Bn1Fold<T> bf{S.stats1, d.training, G.bn1_weight, G.bn1_bias, dx, false, S.XA, t1_ready ? t1 : nullptr};
+  Bn1Fold<T> bf{S.stats1, d.training, G.bn1_weight, G.bn1_bias, dx, false, S.XA, &S.fp, t1_ready ? t1 : nullptr};
   STGCN_TRY(spatial_bwd<T>(e, m, x, S.stats1 + 2 * m.ci, S.stats1 + 3 * m.ci, relu1, P.A, P.W, P.W_bias, dS, dh, G.A, G.W, G.W_bias, &bf));
   if (!ws.dry && !bf.done) {
     STGCN_TRY(launch_bn_bwd_reduce<T>(dh, x, S.stats1, m.rows_in, m.ci, 0, 0.f, 0, 0, partials, &nblk, st));
