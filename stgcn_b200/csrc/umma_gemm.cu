@@ -68,9 +68,18 @@ __device__ __forceinline__ TileCoord decode_tile(const UmmaParams& p, int tile) 
   return t;
 }
 
+// PLAIN = no epilogue option at all (every data-gradient GEMM): the option code folds away, which matters because the epilogue
+// warps are bound by dependent-issue latency (about 10 cycles per instruction with two warps per scheduler)
+template <bool PLAIN>
 __global__ void __launch_bounds__(kUmmaThreads, 1)
 conv_gemm_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_constant__ CUtensorMap map_w,
                       const __grid_constant__ CUtensorMap map_out, const __grid_constant__ UmmaParams p) {
+  const float* const o_bias = PLAIN ? nullptr : p.bias; const float* const o_bias2d = PLAIN ? nullptr : p.bias2d;
+  const float* const o_scale = PLAIN ? nullptr : p.scale; const float* const o_shift = PLAIN ? nullptr : p.shift;
+  const bf16* const o_residual = PLAIN ? nullptr : p.residual;
+  float* const o_stat_partials = PLAIN ? nullptr : p.stat_partials; float* const o_vsum = PLAIN ? nullptr : p.vsum;
+  const int o_b2_smem = PLAIN ? 0 : p.b2_smem, o_relu = PLAIN ? 0 : p.relu;
+  const float o_dropout_p = PLAIN ? 0.f : p.dropout_p;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // 1024-byte aligned carve-up (dynamic smem base is only guaranteed 16-byte aligned)
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -85,8 +94,8 @@ conv_gemm_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_c
   uint64_t* wempty_bar = full_bar + 36;                          // [16]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(full_bar + 52);
   float* b2_tab = reinterpret_cast<float*>(tmem_slot + 4);       // 16-byte aligned: barriers start on a 1024-byte boundary
-  float* stat_acc = b2_tab + (p.b2_smem ? p.v * (p.bn + 4) : 0);  // [2][n_out]
-  float* vsum_acc = stat_acc + (p.stat_partials ? 2 * p.n_out : 0);   // [V][n_out]
+  float* stat_acc = b2_tab + (o_b2_smem ? p.v * (p.bn + 4) : 0);  // [2][n_out]
+  float* vsum_acc = stat_acc + (o_stat_partials ? 2 * p.n_out : 0);   // [V][n_out]
 
   const int warp = uniform_warp_idx(), lane = threadIdx.x % 32;
 
@@ -246,10 +255,10 @@ conv_gemm_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_c
     int gchunk = 0;                                // chunks of the CTA so far (both groups count them)
     uint8_t* const my_staging = staging + (size_t)grp * p.nstaging * kStagingBytes;
     const int b2_ld = p.bn + 4;                    // row pitch (floats): 16-byte rows, conflict-free across joints
-    if (p.b2_smem)
-      for (int i = et2; i < p.v * p.bn; i += 256) b2_tab[(i / p.bn) * b2_ld + (i % p.bn)] = __ldg(p.bias2d + i);
-    if (p.stat_partials) for (int i = et2; i < 2 * p.n_out; i += 256) stat_acc[i] = 0.f;
-    if (p.vsum) for (int i = et2; i < p.v * p.n_out; i += 256) vsum_acc[i] = 0.f;
+    if (o_b2_smem)
+      for (int i = et2; i < p.v * p.bn; i += 256) b2_tab[(i / p.bn) * b2_ld + (i % p.bn)] = __ldg(o_bias2d + i);
+    if (o_stat_partials) for (int i = et2; i < 2 * p.n_out; i += 256) stat_acc[i] = 0.f;
+    if (o_vsum) for (int i = et2; i < p.v * p.n_out; i += 256) vsum_acc[i] = 0.f;
     asm volatile("bar.sync 5, 256;" ::: "memory");
     for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
       const TileCoord tc = decode_tile(p, tile);
@@ -266,39 +275,40 @@ conv_gemm_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_c
           asm volatile("bar.sync %0, 128;" ::"r"(bar_a) : "memory");
         }
         ++chunk_ctr;
+        uint32_t r2[2][32];                        // both 32-column halves in flight before the first use
+        tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * p.bn + ch * 64), r2[0]);
+        tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * p.bn + ch * 64 + 32), r2[1]);
+        tmem_ld_wait();
 #pragma unroll
         for (int half = 0; half < 2; ++half) {
-          uint32_t r[32];
           const int col0 = ch * 64 + half * 32;    // column inside the bn-wide tile
-          tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * p.bn + col0), r);
-          tmem_ld_wait();
-          const int n0 = tc.n_t * p.bn + col0;     // global output channel of r[0]
+          const int n0 = tc.n_t * p.bn + col0;     // global output channel of the first value
           float f[32];
 #pragma unroll
-          for (int i = 0; i < 32; ++i) f[i] = __uint_as_float(r[i]);
-          if (p.bias) {
-            const float4* bp = reinterpret_cast<const float4*>(p.bias + n0);
+          for (int i = 0; i < 32; ++i) f[i] = __uint_as_float(r2[half][i]);
+          if (o_bias) {
+            const float4* bp = reinterpret_cast<const float4*>(o_bias + n0);
 #pragma unroll
             for (int g = 0; g < 8; ++g) {
               const float4 t = __ldg(bp + g);
               f[g * 4 + 0] += t.x; f[g * 4 + 1] += t.y; f[g * 4 + 2] += t.z; f[g * 4 + 3] += t.w;
             }
           }
-          if (p.b2_smem) {
+          if (o_b2_smem) {
             const float4* b2 = reinterpret_cast<const float4*>(b2_tab + vv * b2_ld + col0);
 #pragma unroll
             for (int g = 0; g < 8; ++g) {
               const float4 t = b2[g];
               f[g * 4 + 0] += t.x; f[g * 4 + 1] += t.y; f[g * 4 + 2] += t.z; f[g * 4 + 3] += t.w;
             }
-          } else if (p.bias2d) {
-            const float* b2 = p.bias2d + (size_t)vv * p.n_out + n0;
+          } else if (o_bias2d) {
+            const float* b2 = o_bias2d + (size_t)vv * p.n_out + n0;
 #pragma unroll
             for (int i = 0; i < 32; ++i) f[i] += __ldg(b2 + i);
           }
-          if (p.scale) {
-            const float4* sp = reinterpret_cast<const float4*>(p.scale + n0);
-            const float4* hp = reinterpret_cast<const float4*>(p.shift + n0);
+          if (o_scale) {
+            const float4* sp = reinterpret_cast<const float4*>(o_scale + n0);
+            const float4* hp = reinterpret_cast<const float4*>(o_shift + n0);
 #pragma unroll
             for (int g = 0; g < 8; ++g) {
               const float4 a4 = __ldg(sp + g), b4 = __ldg(hp + g);
@@ -306,8 +316,8 @@ conv_gemm_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_c
               f[g * 4 + 2] = fmaf(a4.z, f[g * 4 + 2], b4.z); f[g * 4 + 3] = fmaf(a4.w, f[g * 4 + 3], b4.w);
             }
           }
-          if (p.residual && row_valid) {
-            const uint4* rp = reinterpret_cast<const uint4*>(p.residual + (size_t)grow * p.n_out + n0);
+          if (o_residual && row_valid) {
+            const uint4* rp = reinterpret_cast<const uint4*>(o_residual + (size_t)grow * p.n_out + n0);
 #pragma unroll
             for (int g = 0; g < 4; ++g) {
               uint4 u = __ldg(rp + g);
@@ -316,14 +326,14 @@ conv_gemm_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_c
               for (int e = 0; e < 4; ++e) { f[g * 8 + 2 * e] += __low2float(h[e]); f[g * 8 + 2 * e + 1] += __high2float(h[e]); }
             }
           }
-          if (p.relu) {
+          if (o_relu) {
 #pragma unroll
             for (int i = 0; i < 32; ++i) f[i] = fmaxf(f[i], 0.f);
           }
-          if (p.dropout_p > 0.f && row_valid) {
+          if (o_dropout_p > 0.f && row_valid) {
             const uint64_t o = (uint64_t)grow * p.n_out + n0;
 #pragma unroll
-            for (int i = 0; i < 32; ++i) f[i] *= dropout_scale(p.seed, p.offset, o + i, p.dropout_p, p.inv_keep);
+            for (int i = 0; i < 32; ++i) f[i] *= dropout_scale(p.seed, p.offset, o + i, o_dropout_p, p.inv_keep);
           }
           // bf16 pack and 128B-swizzled store: 16-byte chunk j of row lands at chunk (j ^ (row & 7))
 #pragma unroll
@@ -345,11 +355,11 @@ conv_gemm_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_c
           tma_store_5d(&map_out, stg, tc.n_t * p.bn + ch * 64, 0, tc.ph, tc.j0, tc.b);
           tma_store_commit();
         }
-        if (p.stat_partials || p.vsum) {
+        if (o_stat_partials || o_vsum) {
           // column reductions of the tile as stored (bf16), read back from the swizzled staging image
           const int vframes = min(p.ft, p.t_out_ph - tc.j0);
           const int nbase = tc.n_t * p.bn + ch * 64;
-          if (p.stat_partials) {
+          if (o_stat_partials) {
             const int col = et & 63, r0 = (et >> 6) * 64, r1 = min(r0 + 64, vframes * p.v);
             const uint8_t* cp = stg + ((col & 7) << 1);
             const int cj = col >> 3;
@@ -361,7 +371,7 @@ conv_gemm_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_c
             atomicAdd(stat_acc + nbase + col, s1);                 // two row-halves share a column
             atomicAdd(stat_acc + p.n_out + nbase + col, s2);
           }
-          if (p.vsum) {
+          if (o_vsum) {
             for (int o = et; o < p.v * 64; o += 128) {
               const int v2 = o >> 6, col = o & 63, cj = col >> 3;
               float sacc = 0.f;
@@ -379,12 +389,12 @@ conv_gemm_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_c
       if (++as == 2) { as = 0; aphase ^= 1; }
     }
     if (et == 0) tma_store_wait<0>();
-    if (p.stat_partials || p.vsum) {
+    if (o_stat_partials || o_vsum) {
       asm volatile("bar.sync 5, 256;" ::: "memory");
-      if (p.stat_partials)
-        for (int i = et2; i < 2 * p.n_out; i += 256) p.stat_partials[(size_t)blockIdx.x * 2 * p.n_out + i] = stat_acc[i];
-      if (p.vsum)
-        for (int i = et2; i < p.v * p.n_out; i += 256) atomicAdd(p.vsum + i, vsum_acc[i]);
+      if (o_stat_partials)
+        for (int i = et2; i < 2 * p.n_out; i += 256) o_stat_partials[(size_t)blockIdx.x * 2 * p.n_out + i] = stat_acc[i];
+      if (o_vsum)
+        for (int i = et2; i < p.v * p.n_out; i += 256) atomicAdd(o_vsum + i, vsum_acc[i]);
     }
   }
   tc_fence_before();
@@ -568,12 +578,15 @@ int32_t launch_conv_gemm_umma(const ConvGeom& g, const bf16* in, const bf16* w, 
   }
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(conv_gemm_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    cudaError_t e = cudaFuncSetAttribute(conv_gemm_umma_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_gemm_umma_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     if (e != cudaSuccess) { set_error("cudaFuncSetAttribute(smem) failed: %s", cudaGetErrorString(e)); return STGCN_ERR_CUDA; }
     attr_set = true;
   }
   const int grid = std::min(p.total_tiles, num_sms());
-  conv_gemm_umma_kernel<<<grid, kUmmaThreads, smem, st>>>(map_in, map_w, map_out, p);
+  const bool plain = !ep.bias && !ep.bias2d && !ep.scale && !ep.residual && !ep.relu && !(ep.dropout_p > 0.f) && !ep.stat_partials && !ep.vsum;
+  if (plain) conv_gemm_umma_kernel<true><<<grid, kUmmaThreads, smem, st>>>(map_in, map_w, map_out, p);
+  else conv_gemm_umma_kernel<false><<<grid, kUmmaThreads, smem, st>>>(map_in, map_w, map_out, p);
   STGCN_CHECK_LAUNCH("conv_gemm_umma");
   return STGCN_OK;
 }

@@ -9,14 +9,14 @@ def run(nb, t, v, c, n_out, taps, stride, pad, iters=20):
     t_out = (t + 2 * pad - taps) // stride + 1
     x = torch.randn(nb, t, v, c, device='cuda').bfloat16()
     w = (torch.randn(taps, n_out, c, device='cuda') / (c * taps) ** 0.5).bfloat16()
-    bias = torch.randn(n_out, device='cuda')
+    bias = None if os.environ.get('NOBIAS') else torch.randn(n_out, device='cuda')
     out = torch.empty(nb, t_out, v, n_out, device='cuda', dtype=torch.bfloat16)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device='cuda')
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(iters)]
     for i in range(iters + 3):
         flush.zero_()
         if i >= 3: ev[i - 3][0].record()
-        L.check(L.lib().stgcn_umma_conv_gemm(nb, t, t_out, v, c, n_out, taps, stride, pad, L.ptr(x), L.ptr(w), L.ptr(bias),
+        L.check(L.lib().stgcn_umma_conv_gemm(nb, t, t_out, v, c, n_out, taps, stride, pad, L.ptr(x), L.ptr(w), L.ptr(bias) if bias is not None else None,
                                              L.ptr(out), L.stream_ptr()), 'umma_conv_gemm')
         if i >= 3: ev[i - 3][1].record()
     torch.cuda.synchronize()
