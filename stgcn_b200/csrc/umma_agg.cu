@@ -78,6 +78,7 @@ static int num_sms_agg() {
   return n;
 }
 
+constexpr int kAggU2Threads = 320;    // agg_umma_kernel: TMA warp, MMA warp, two epilogue groups of four warps
 struct AggParams {
   int nb, t, v, ft, c, k, nch;            // nch = channels per work item (64 or 128)
   int c_chunks, m_tiles_per_b, total_items, stages;
@@ -91,10 +92,14 @@ struct AggParams {
 };
 
 // smem: bigA (K x 32 KB) | stages x (nch/64 x 16 KB) | staging 2 x 16 KB | barriers
-__global__ void __launch_bounds__(kAggUThreads, 1)
+// MODE bits (compile time, so unused epilogue options cost no instructions: the epilogue warps are dependent-issue bound):
+//   1 transposed (backward)   2 dA products ride along   4 forward affine   8 ReLU mask   16 fused BatchNorm-1 backward
+template <int MODE>
+__global__ void __launch_bounds__(kAggU2Threads, 1)
 agg_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_constant__ CUtensorMap map_big,
                 const __grid_constant__ CUtensorMap map_out, const __grid_constant__ CUtensorMap map_x,
                 const __grid_constant__ AggParams p) {
+  constexpr bool TR = (MODE & 1) != 0, DA = (MODE & 2) != 0, AFF = (MODE & 4) != 0, MASKH = (MODE & 8) != 0, BNB = (MODE & 16) != 0;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   const int slabs = p.nch / 64;
@@ -102,7 +107,7 @@ agg_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_constan
   uint8_t* smem_big = smem;                                          // [k][2 halves of 64 cols][128 rows x 128 B]
   uint8_t* smem_x = smem_big + (size_t)p.k * 2 * kTile16K;
   uint8_t* smem_xb = smem_x + (size_t)p.stages * stage_bytes;        // dA mode: 2 x stage_bytes ring of raw-input tiles
-  uint8_t* staging = smem_xb + (p.dA ? 2 * (size_t)stage_bytes : 0);
+  uint8_t* staging = smem_xb + (DA ? 2 * (size_t)stage_bytes : 0);
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(staging + 2 * kTile16K);
   uint64_t* empty_bar = full_bar + p.stages;
   uint64_t* tfull_bar = empty_bar + p.stages;
@@ -114,18 +119,18 @@ agg_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_constan
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(done_bar + 1);
   float* aff_tab = reinterpret_cast<float*>(full_bar + 32);          // [3][C] per-channel epilogue coefficients
   float* da_tab = aff_tab + 3 * p.c;                                 // dA mode: [K][V][V] CTA-local sums
-  if (p.dA) for (int i = threadIdx.x; i < p.k * p.v * p.v; i += kAggUThreads) da_tab[i] = 0.f;
+  if (DA) for (int i = threadIdx.x; i < p.k * p.v * p.v; i += kAggU2Threads) da_tab[i] = 0.f;
   const int warp = uniform_warp_idx(), lane = threadIdx.x % 32;
 
   {  // padding rows of the activation tiles must be finite (they meet BigA's zero columns)
     uint4* z = reinterpret_cast<uint4*>(smem_x);
-    const int n16 = (p.stages + (p.dA ? 2 : 0)) * stage_bytes / 16;
-    for (int i = threadIdx.x; i < n16; i += kAggUThreads) z[i] = make_uint4(0, 0, 0, 0);
+    const int n16 = (p.stages + (DA ? 2 : 0)) * stage_bytes / 16;
+    for (int i = threadIdx.x; i < n16; i += kAggU2Threads) z[i] = make_uint4(0, 0, 0, 0);
   }
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&map_in); prefetch_tmap(&map_big); prefetch_tmap(&map_out); prefetch_tmap(&map_x);
     for (int s = 0; s < p.stages; ++s) { mbar_init(full_bar + s, 1); mbar_init(empty_bar + s, 1); }
-    for (int a = 0; a < 2; ++a) { mbar_init(tfull_bar + a, 1); mbar_init(tempty_bar + a, 128); mbar_init(xfull_bar + a, 1); mbar_init(xempty_bar + a, 129); }
+    for (int a = 0; a < 2; ++a) { mbar_init(tfull_bar + a, 1); mbar_init(tempty_bar + a, 256); mbar_init(xfull_bar + a, 1); mbar_init(xempty_bar + a, 129); }
     mbar_init(big_bar, 1); mbar_init(done_bar, 1);
     fence_barrier_init();
   }
@@ -141,8 +146,8 @@ agg_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_constan
     j0 = (item % p.m_tiles_per_b) * p.ft; b = item / p.m_tiles_per_b;
   };
   // forward: 1 load, K accumulations (K outputs).  transpose: K loads, 1 output.
-  const int loads_per_item = p.transpose ? p.k : 1;
-  const int outs_per_item = p.transpose ? 1 : p.k;
+  const int loads_per_item = TR ? p.k : 1;
+  const int outs_per_item = TR ? 1 : p.k;
 
   if (warp == 0) {
     {   // whole warp runs the loop, one elected lane arms barriers and issues copies
@@ -152,7 +157,7 @@ agg_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_constan
       int stage = 0; uint32_t phase = 0; int xs = 0; uint32_t xphase = 0;
       for (int item = blockIdx.x; item < p.total_items; item += gridDim.x) {
         int cch, j0, b; decode(item, cch, j0, b);
-        if (p.dA) {                                  // raw-input tile of the same rows / channels: B operand of the dA products
+        if (DA) {                                  // raw-input tile of the same rows / channels: B operand of the dA products
           mbar_wait(xempty_bar + xs, xphase ^ 1);
           mbar_expect_tx_e(xfull_bar + xs, (uint32_t)slabs * p.tile_bytes);
           for (int s = 0; s < slabs; ++s)
@@ -162,7 +167,7 @@ agg_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_constan
         for (int l = 0; l < loads_per_item; ++l) {
           mbar_wait(empty_bar + stage, phase ^ 1);
           mbar_expect_tx_e(full_bar + stage, (uint32_t)slabs * p.tile_bytes);
-          const int col0 = (p.transpose ? l * p.c : 0) + cch * p.nch;
+          const int col0 = (TR ? l * p.c : 0) + cch * p.nch;
           for (int s = 0; s < slabs; ++s)
             tma_load_5d_e(&map_in, smem_x + (size_t)stage * stage_bytes + s * kTile16K, full_bar + stage, col0 + s * 64, 0, 0, j0, b);
           if (++stage == p.stages) { stage = 0; phase ^= 1; }
@@ -181,22 +186,22 @@ agg_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_constan
       const uint64_t xb_d0 = make_smem_desc_sw128(smem_u32(smem_xb), 16, 1024);
       int stage = 0; uint32_t phase = 0; int as = 0; uint32_t aphase = 0; int xs = 0; uint32_t xphase = 0; bool g_first = true;
       for (int item = blockIdx.x; item < p.total_items; item += gridDim.x) {
-        if (p.transpose) { mbar_wait(tempty_bar + as, aphase ^ 1); tc_fence_after(); }
-        if (p.dA) { mbar_wait(xfull_bar + xs, xphase); tc_fence_after(); }
+        if (TR) { mbar_wait(tempty_bar + as, aphase ^ 1); tc_fence_after(); }
+        if (DA) { mbar_wait(xfull_bar + xs, xphase); tc_fence_after(); }
         for (int k = 0; k < p.k; ++k) {
-          if (!p.transpose) { mbar_wait(tempty_bar + as, aphase ^ 1); tc_fence_after(); }
-          if (p.transpose || k == 0) { mbar_wait(full_bar + stage, phase); tc_fence_after(); }
+          if (!TR) { mbar_wait(tempty_bar + as, aphase ^ 1); tc_fence_after(); }
+          if (TR || k == 0) { mbar_wait(full_bar + stage, phase); tc_fence_after(); }
           // shared-memory descriptors are affine in the address (field = addr >> 4): one base each, then constant offsets
           const uint32_t st16 = (uint32_t)(stage * (stage_bytes >> 4));
           const uint64_t ad0 = big_d0 + (uint64_t)(k * (2 * kTile16K >> 4));
           const uint64_t bd0 = x_d0 + (uint64_t)st16;
           const uint32_t d_tmem = tmem_base + (uint32_t)(as * p.nch);
-          const uint32_t acc0 = (p.transpose && k != 0) ? 1u : 0u;
+          const uint32_t acc0 = (TR && k != 0) ? 1u : 0u;
 #pragma unroll
           for (int kk = 0; kk < 8; ++kk)           // reduction over the 128 tile rows, 16 per instruction
             umma_bf16_ss_elect(d_tmem, ad0 + (uint64_t)((kk / 4) * (kTile16K >> 4) + (kk % 4) * 2), bd0 + (uint64_t)(kk * 128), idesc,
                          kk != 0 ? 1u : acc0);
-          if (p.dA) {
+          if (DA) {
             // G_k[(f,v)][(f',w)] += sum_c dXA_k[(f,v),c] * x[(f',w),c]: the SAME tile images read K-major; the FT diagonal
             // V x V blocks (f == f') are folded into dA at the end of the kernel
             const uint64_t ga0 = xk_d0 + (uint64_t)st16;
@@ -208,57 +213,65 @@ agg_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_constan
                              gb0 + (uint64_t)(s2 * (kTile16K >> 4) + kk * 2), idesc_da, (g_first && s2 == 0 && kk == 0) ? 0u : 1u);
             }
           }
-          if (p.transpose || k == p.k - 1) { umma_commit_elect(empty_bar + stage); if (++stage == p.stages) { stage = 0; phase ^= 1; } }
-          if (!p.transpose) { umma_commit_elect(tfull_bar + as); if (++as == 2) { as = 0; aphase ^= 1; } }
+          if (TR || k == p.k - 1) { umma_commit_elect(empty_bar + stage); if (++stage == p.stages) { stage = 0; phase ^= 1; } }
+          if (!TR) { umma_commit_elect(tfull_bar + as); if (++as == 2) { as = 0; aphase ^= 1; } }
         }
-        if (p.transpose) { umma_commit_elect(tfull_bar + as); if (++as == 2) { as = 0; aphase ^= 1; } }
-        if (p.dA) { umma_commit_elect(xempty_bar + xs); if (++xs == 2) { xs = 0; xphase ^= 1; } g_first = false; }
+        if (TR) { umma_commit_elect(tfull_bar + as); if (++as == 2) { as = 0; aphase ^= 1; } }
+        if (DA) { umma_commit_elect(xempty_bar + xs); if (++xs == 2) { xs = 0; xphase ^= 1; } g_first = false; }
       }
-      if (p.dA) umma_commit_elect(done_bar);
+      if (DA) umma_commit_elect(done_bar);
     }
   } else {
-    const int q = warp % 4, row = q * 32 + lane, et = threadIdx.x - 64;
+    // two epilogue groups (warps 2..5 and 6..9) take alternate 64-column chunks; each has its own staging buffer and barriers
+    const int grp = (warp - 2) >> 2;
+    const int q = warp % 4, row = q * 32 + lane, et = threadIdx.x - 64 - grp * 128;
+    const int bar_a = 1 + 2 * grp, bar_b = 2 + 2 * grp;
+    uint8_t* const stg = staging + grp * kTile16K;
+    int gchunk = 0;                                // chunks of the CTA so far (both groups count them)
     const int fl = row / p.v, vv = row % p.v;
-    const int c_out_total = p.transpose ? p.c : p.k * p.c;
+    const int c_out_total = TR ? p.c : p.k * p.c;
     int as = 0; uint32_t aphase = 0; int chunk_ctr = 0; int xslot = 0; uint32_t xph = 0;
-    const bool affine = !p.transpose && p.aff_a;
-    const bool bnb = p.transpose && p.bn_coef;
+    constexpr bool affine = AFF;
+    constexpr bool bnb = BNB;
     if (affine) {
-      for (int i = et; i < p.c; i += 128) { aff_tab[i] = __ldg(p.aff_a + i); aff_tab[p.c + i] = __ldg(p.aff_b + i); }
-      asm volatile("bar.sync 1, 128;" ::: "memory");
+      for (int i = et; i < p.c; i += 128) { aff_tab[i] = __ldg(p.aff_a + i); aff_tab[p.c + i] = __ldg(p.aff_b + i); }   // both groups write the same values
+      asm volatile("bar.sync %0, 128;" ::"r"(bar_a) : "memory");
     } else if (bnb) {
       // dx = dh' - c1 - (x - mean) * c2 = (dh' + d0) - c2 * x  with d0 = mean * c2 - c1: two coefficients per channel
       for (int i = et; i < p.c; i += 128) {
         const float mu = __ldg(p.bn_coef + i), c1 = __ldg(p.bn_coef + p.c + i), c2 = __ldg(p.bn_coef + 2 * p.c + i);
         aff_tab[i] = mu * c2 - c1; aff_tab[p.c + i] = -c2;
       }
-      asm volatile("bar.sync 1, 128;" ::: "memory");
+      asm volatile("bar.sync %0, 128;" ::"r"(bar_a) : "memory");
     }
     for (int item = blockIdx.x; item < p.total_items; item += gridDim.x) {
       int cch, j0, b; decode(item, cch, j0, b);
       const bool row_valid = row < p.ft * p.v && (j0 + fl) < p.t;
       const long long grow = ((long long)b * p.t + j0 + fl) * p.v + vv;
-      if (p.dA) mbar_wait(xfull_bar + xslot, xph);      // acquire the TMA-written raw-input tile for generic reads (already complete)
+      const bool mine_item = ((gchunk & 1) == grp);   // dA mode: an item is one chunk, so one group owns its raw-input tile
+      if (DA && mine_item) mbar_wait(xfull_bar + xslot, xph);      // acquire the TMA-written raw-input tile for generic reads
       for (int o = 0; o < outs_per_item; ++o) {
         mbar_wait(tfull_bar + as, aphase);
         tc_fence_after();
-        const float rs = (!p.transpose && p.aff_b && row_valid) ? p.rowsum[o * p.v + vv] : 0.f;
-        for (int ch = 0; ch < slabs; ++ch, ++chunk_ctr) {
-          uint8_t* stg = staging + (chunk_ctr & 1) * kTile16K;
-          if (chunk_ctr >= 2) {
-            if (et == 0) tma_store_wait_read<1>();
-            asm volatile("bar.sync 1, 128;" ::: "memory");
+        const float rs = (AFF && row_valid) ? p.rowsum[o * p.v + vv] : 0.f;
+        for (int ch = 0; ch < slabs; ++ch) {
+          if (((gchunk++) & 1) != grp) continue;
+          if (chunk_ctr >= 1) {
+            if (et == 0) tma_store_wait_read<0>();       // this group's previous store (two chunks ago) has drained
+            asm volatile("bar.sync %0, 128;" ::"r"(bar_a) : "memory");
           }
+          ++chunk_ctr;
+          uint32_t r2[2][32];                           // both 32-column halves in flight before the first use
+          tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * p.nch + ch * 64), r2[0]);
+          tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * p.nch + ch * 64 + 32), r2[1]);
+          tmem_ld_wait();
 #pragma unroll
           for (int half = 0; half < 2; ++half) {
-            uint32_t r[32];
             const int col0 = ch * 64 + half * 32;
-            tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * p.nch + col0), r);
-            tmem_ld_wait();
-            const int c0 = cch * p.nch + col0;          // channel of r[0]
+            const int c0 = cch * p.nch + col0;          // channel of the first value
             float f[32];
 #pragma unroll
-            for (int i = 0; i < 32; ++i) f[i] = __uint_as_float(r[i]);
+            for (int i = 0; i < 32; ++i) f[i] = __uint_as_float(r2[half][i]);
             if (affine) {
               const float4* ta = reinterpret_cast<const float4*>(aff_tab + c0);
               const float4* tb = reinterpret_cast<const float4*>(aff_tab + p.c + c0);
@@ -269,7 +282,7 @@ agg_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_constan
                 f[g * 4 + 2] = fmaf(a4.z, f[g * 4 + 2], b4.z * rs); f[g * 4 + 3] = fmaf(a4.w, f[g * 4 + 3], b4.w * rs);
               }
             }
-            if (p.transpose && p.mask_h && row_valid) {
+            if (MASKH && row_valid) {
               const uint4* hp = reinterpret_cast<const uint4*>(p.mask_h + (size_t)grow * p.c + c0);
 #pragma unroll
               for (int g = 0; g < 4; ++g) {
@@ -290,7 +303,7 @@ agg_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_constan
               const float4* n24 = reinterpret_cast<const float4*>(aff_tab + p.c + c0);
 #pragma unroll
               for (int g = 0; g < 4; ++g) {
-                const uint4 u = p.dA ? *reinterpret_cast<const uint4*>(xsm + (((half * 4 + g) ^ (row & 7)) << 4)) : __ldg(xp + g);
+                const uint4 u = DA ? *reinterpret_cast<const uint4*>(xsm + (((half * 4 + g) ^ (row & 7)) << 4)) : __ldg(xp + g);
                 const __nv_bfloat162* x2 = reinterpret_cast<const __nv_bfloat162*>(&u);
                 float xv[8];
 #pragma unroll
@@ -318,9 +331,9 @@ agg_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_constan
             }
           }
           fence_proxy_async_smem();
-          asm volatile("bar.sync 2, 128;" ::: "memory");
+          asm volatile("bar.sync %0, 128;" ::"r"(bar_b) : "memory");
           if (et == 0) {
-            const int oc = (p.transpose ? 0 : o * p.c) + cch * p.nch + ch * 64;
+            const int oc = (TR ? 0 : o * p.c) + cch * p.nch + ch * 64;
             tma_store_5d(&map_out, stg, oc, 0, 0, j0, b);
             tma_store_commit();
           }
@@ -329,17 +342,17 @@ agg_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_constan
         mbar_arrive(tempty_bar + as);
         if (++as == 2) { as = 0; aphase ^= 1; }
       }
-      if (p.dA) { mbar_arrive(xempty_bar + xslot); if ((xslot ^= 1) == 0) xph ^= 1; }     // done reading the raw-input tile
+      if (DA) { if (mine_item) mbar_arrive(xempty_bar + xslot); if ((xslot ^= 1) == 0) xph ^= 1; }     // done reading the raw-input tile
       (void)c_out_total;
     }
     if (et == 0) tma_store_wait<0>();
-    if (p.dA) {                                    // fold the FT diagonal V x V blocks of every G_k into dA
+    if (DA) asm volatile("bar.sync 7, 256;" ::: "memory");          // every epilogue thread is done with the raw-input ring
+    if (DA && grp == 0) {                        // fold the FT diagonal V x V blocks of every G_k into dA
       mbar_wait(done_bar, 0);
       tc_fence_after();
       // every load has landed and every product has completed: the activation ring is free and holds the unfolded blocks,
       // fold_tab[k][f][v][w] = G_k[(f,v)][(f,w)] written with plain stores (each thread owns its row), then summed over f
       float* fold_tab = reinterpret_cast<float*>(smem_x);
-      asm volatile("bar.sync 1, 128;" ::: "memory");                 // every epilogue thread is done with the raw-input ring
       const int vv2 = p.v * p.v;
       for (int k = 0; k < p.k; ++k) {
         float* mine = fold_tab + ((size_t)(k * p.ft + fl) * p.v + vv) * p.v - fl * p.v;   // indexed by the tile column
@@ -518,13 +531,24 @@ static int32_t launch_agg_common(int transpose, const bf16* in, int nb, int t, i
     STGCN_TRY(make_tmap_bf16(&map_big, transpose ? prep.bigT : prep.big, 2, dims, str, box));
   }
   const size_t smem = fixed + (size_t)stages * stage_bytes;
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(agg_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-    if (e != cudaSuccess) { set_error("cudaFuncSetAttribute failed: %s", cudaGetErrorString(e)); return STGCN_ERR_CUDA; }
-    attr_set = true;
+  const int mode = (transpose ? 1 : 0) | (dA ? 2 : 0) | ((!transpose && aff_a) ? 4 : 0) | ((transpose && mask_h) ? 8 : 0) |
+                   ((transpose && bn_coef) ? 16 : 0);
+  const int grid = std::min(p.total_items, num_sms_agg());
+#define STGCN_AGG_CASE(M)                                                                                                  \
+  case M: {                                                                                                                \
+    static bool attr_set = false;                                                                                          \
+    if (!attr_set) {                                                                                                       \
+      cudaError_t e = cudaFuncSetAttribute(agg_umma_kernel<M>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);   \
+      if (e != cudaSuccess) { set_error("cudaFuncSetAttribute failed: %s", cudaGetErrorString(e)); return STGCN_ERR_CUDA; } \
+      attr_set = true;                                                                                                     \
+    }                                                                                                                      \
+    agg_umma_kernel<M><<<grid, kAggU2Threads, smem, st>>>(map_in, map_big, map_out, map_x, p);                              \
+  } break;
+  switch (mode) {
+    STGCN_AGG_CASE(0) STGCN_AGG_CASE(4) STGCN_AGG_CASE(1) STGCN_AGG_CASE(9) STGCN_AGG_CASE(17) STGCN_AGG_CASE(19)
+    default: set_error("umma agg: epilogue combination %d not instantiated", mode); return STGCN_ERR_UNSUPPORTED;
   }
-  agg_umma_kernel<<<std::min(p.total_items, num_sms_agg()), kAggUThreads, smem, st>>>(map_in, map_big, map_out, map_x, p);
+#undef STGCN_AGG_CASE
   STGCN_CHECK_LAUNCH("agg_umma");
   return STGCN_OK;
 }
