@@ -215,15 +215,17 @@ static int32_t spatial_fwd(Engine<T>& e, const Dims& m, const T* x, const float*
       float* bvec2 = ws.template get<float>((size_t)2 * m.k * m.co);
       if (ws.dry) return STGCN_OK;
       if (!ws.ok()) return STGCN_ERR_WORKSPACE;
-      // The single-kernel aggregation + mixing path is opt-in: measured on B200 it is still behind the two-kernel pair
-      // (per-chunk MMA -> epilogue -> MMA latency chain), see DESIGN.md section 8.
-      static const bool want_fused = getenv("STGCN_FUSED_SPATIAL") != nullptr;
+      // Single-kernel aggregation + mixing: default when XA is not wanted by a backward pass (inference: no XA round trip through
+      // HBM, measured 0.78 vs 0.92 ms per 32 sequences); with the XA store it only ties the two-kernel pair, which then stays the
+      // default.  STGCN_FUSED_SPATIAL=1 / =0 forces it on / off.
+      static const char* fused_env = getenv("STGCN_FUSED_SPATIAL");
+      const bool want_fused = fused_env ? (fused_env[0] != '0') : (xa_keep == nullptr);
       const bool fused = want_fused && umma_spatial_supported(m.v, m.ci, m.co, m.k);
       STGCN_TRY(launch_build_big_adjacency(A, m.k, m.v, prep, e.st));
       STGCN_TRY(launch_bn1_fold(W, Wb, A, umma_agg_rowsum_q(prep, m.k), aff_a, aff_b, m.k, m.v, m.co, m.ci, w2p, w2pT, wb, wbb, b2d, e.st, 0,
                                 rsum2, bvec2));
       if (fused)     // one kernel: aggregation -> (TMEM -> bf16 smem) -> channel mixing; XA goes to HBM only when backward wants it
-        return launch_spatial_fused(x, m.n, m.t, m.v, m.ci, m.co, m.k, umma_agg_big(prep, m.k), w2p, rsum2, bvec2, xa_keep, S, e.st);
+        return launch_spatial_fused(x, m.n, m.t, m.v, m.ci, m.co, m.k, umma_agg_big(prep, m.k), w2p, b2d, xa_keep, S, e.st);
       STGCN_TRY(launch_agg_fwd_umma(x, m.n, m.t, m.v, m.ci, m.k, prep, nullptr, nullptr, XA, e.st));
       GemmEpilogue ep; ep.bias2d = b2d;
       return e.gemm_packed(geom(m.n, m.t, m.t, m.v, KCi, m.co, 1, 1, 0, 0), XA, w2p, ep, S);

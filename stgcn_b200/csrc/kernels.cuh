@@ -115,7 +115,7 @@ int32_t launch_agg_dA_umma(const bf16* dxa, const bf16* h, int nb, int t, int v,
 // umma_spatial.cu  (fused aggregation + 1x1 channel mixing, forward)
 bool umma_spatial_supported(int v, int ci, int co, int k);
 int32_t launch_spatial_fused(const bf16* x, int nb, int t, int v, int ci, int co, int k, const bf16* big, const bf16* w2p,
-                             const float* rsum, const float* bvec, bf16* xa, bf16* s_out, cudaStream_t st);
+                             const float* b2d, bf16* xa, bf16* s_out, cudaStream_t st);
 const bf16* umma_agg_big(const void* prep, int k);
 
 // head_kernels.cu

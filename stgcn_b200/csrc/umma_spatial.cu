@@ -28,8 +28,8 @@ struct SpParams {
   int xs, wst;                 // ring depths
   uint32_t tmem_cols, tile_bytes;
   int write_xa;
-  const float* rsum;           // [2K][V]  : rowsum(A)_k[v] (k < K), rowsum(bf16 A)_k[v] (K <= k < 2K)
-  const float* bvec;           // [2K][Co] : Wb[k][co]      (k < K), (W b1)[k][co]       (K <= k < 2K)
+  int ns;                      // output accumulators in TMEM (2 when 128 + 2*Co <= 512 columns)
+  const float* b2d;            // [V][Co] joint bias table bias2d' (bias2d_fold_kernel)
 };
 
 __global__ void __launch_bounds__(kSpThreads, 1)
@@ -48,10 +48,10 @@ spatial_fused_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_con
   uint64_t* wfull = xempty + p.xs;   uint64_t* wempty = wfull + p.wst;
   uint64_t* tfull = wempty + p.wst;  uint64_t* tempty = tfull + 2;
   uint64_t* pfull = tempty + 2;      uint64_t* pempty = pfull + 2;
-  uint64_t* sfull = pempty + 2;      uint64_t* sempty = sfull + 1;
-  uint64_t* big_bar = sempty + 1;
+  uint64_t* sfull = pempty + 2;      uint64_t* sempty = sfull + 2;
+  uint64_t* big_bar = sempty + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(big_bar + 1);
-  float* btab = reinterpret_cast<float*>(bars + 64);               // [2K][Co] bias vectors (512 B after the barrier block start)
+  float* b2_tab = reinterpret_cast<float*>(bars + 64);             // [V][Co+4] joint bias table (512 B after the barrier block start)
   const int warp = uniform_warp_idx(), lane = threadIdx.x % 32;
 
   {  // padding rows of the activation tiles (never written by TMA) must be finite: they meet BigA's zero columns
@@ -64,7 +64,8 @@ spatial_fused_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_con
     for (int s = 0; s < p.xs; ++s) { mbar_init(xfull + s, 1); mbar_init(xempty + s, 1); }
     for (int s = 0; s < p.wst; ++s) { mbar_init(wfull + s, 1); mbar_init(wempty + s, 1); }
     for (int a = 0; a < 2; ++a) { mbar_init(tfull + a, 1); mbar_init(tempty + a, 128); mbar_init(pfull + a, 1); mbar_init(pempty + a, 1); }
-    mbar_init(sfull, 1); mbar_init(sempty, 256); mbar_init(big_bar, 1);
+    for (int a = 0; a < 2; ++a) { mbar_init(sfull + a, 1); mbar_init(sempty + a, 256); }
+    mbar_init(big_bar, 1);
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc(tmem_slot, p.tmem_cols);
@@ -118,7 +119,7 @@ spatial_fused_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_con
       for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) ++my_tiles;
       const int total = my_tiles * chunks;
       int xs = 0; uint32_t xph = 0; int ws = 0; uint32_t wph = 0;
-      uint32_t sph = 0;
+      uint32_t sph = 0; int sb = 0;             // per-accumulator phase bits, current output accumulator
       int k1 = 0;                                // partition index of the next aggregation product
       auto issue1 = [&](int g) {                 // T[g & 1] = BigA_k . x_cc
         const int tb = g & 1;
@@ -139,7 +140,7 @@ spatial_fused_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_con
       for (int g = 0; g < total; ++g) {
         if (g + 1 < total) issue1(g + 1);
         const int pb = g & 1;
-        if (c == 0) { mbar_wait(sempty, sph ^ 1); }                  // previous tile's output has left TMEM
+        if (c == 0) { mbar_wait(sempty + sb, ((sph >> sb) & 1u) ^ 1u); }   // the tile that last used this accumulator has left TMEM
         mbar_wait(pfull + pb, (uint32_t)((g >> 1) & 1));
         tc_fence_after();
         const uint64_t ad = p_d0 + (uint64_t)(pb * (kSpTile >> 4));
@@ -147,7 +148,7 @@ spatial_fused_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_con
           mbar_wait(wfull + ws, wph);
           tc_fence_after();
           const uint64_t bd = w_d0 + (uint64_t)(ws * w_step);
-          const uint32_t d = s_tmem + (uint32_t)(wp * p.wn);
+          const uint32_t d = s_tmem + (uint32_t)(sb * p.co + wp * p.wn);
 #pragma unroll
           for (int kk = 0; kk < 4; ++kk)
             umma_bf16_ss_elect(d, ad + (uint64_t)(kk * 2), bd + (uint64_t)(kk * 2), idesc2, (c | kk) != 0 ? 1u : 0u);
@@ -155,7 +156,7 @@ spatial_fused_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_con
           if (++ws == p.wst) { ws = 0; wph ^= 1; }
         }
         umma_commit_elect(pempty + pb);
-        if (++c == chunks) { c = 0; umma_commit_elect(sfull); sph ^= 1; }
+        if (++c == chunks) { c = 0; umma_commit_elect(sfull + sb); sph ^= (1u << sb); if (++sb == p.ns) sb = 0; }
       }
     }
   } else {
@@ -167,13 +168,12 @@ spatial_fused_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_con
     const int vv = row % p.v;
     const int bar_a = 1 + grp * 2, bar_b = 2 + grp * 2;
     auto gsync = [&](int id) { asm volatile("bar.sync %0, 128;" ::"r"(id) : "memory"); };
-    for (int i = et; i < 2 * p.k * p.co; i += 128) btab[i] = __ldg(p.bvec + i);       // both groups write the same values
-    float rs[8];
-#pragma unroll
-    for (int i = 0; i < 8; ++i) rs[i] = (i < 2 * p.k && row < p.ft * p.v) ? __ldg(p.rsum + i * p.v + vv) : 0.f;
+    const int b2_ld = p.co + 4;                     // row pitch (floats): 16-byte rows, conflict-free across joints
+    for (int i = et; i < p.v * p.co; i += 128) b2_tab[(i / p.co) * b2_ld + (i % p.co)] = __ldg(p.b2d + i);   // both groups write the same values
     gsync(bar_a);
+    const float* const my_b2 = b2_tab + (row < p.ft * p.v ? vv : 0) * b2_ld;
     int g = 0;
-    uint32_t sph = 0;
+    uint32_t sph = 0; int sb = 0; int och = 0;      // output-accumulator phase bits / index, output chunks so far
     uint8_t* const my_p = smem_p + (size_t)grp * kSpTile;
     for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
       const int j0 = (tile % p.m_tiles_per_b) * p.ft, b = tile / p.m_tiles_per_b;
@@ -215,32 +215,26 @@ spatial_fused_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_con
       }
       // ---- output tile: S -> + bias2d' -> bf16 -> staging (this group's P buffer, idle now) -> TMA store; the two groups
       //      take alternate 64-column chunks ----
-      mbar_wait(sfull, sph); sph ^= 1;
+      mbar_wait(sfull + sb, (sph >> sb) & 1u); sph ^= (1u << sb);
       tc_fence_after();
-      for (int ch = grp; ch < p.co / 64; ch += 2) {
+      const uint32_t s_cur = s_tmem + (uint32_t)(sb * p.co);
+      for (int ch = 0; ch < p.co / 64; ++ch) {
+        if (((och + ch) & 1) != grp) continue;
         if (et == 0) tma_store_wait_read<0>();                  // XA store / previous output chunk done reading the buffer
         gsync(bar_a);
+        uint32_t r2[2][32];                                     // both 32-column halves in flight before the first use
+        tmem_ld_32x32(s_cur + ((uint32_t)(q * 32) << 16) + (uint32_t)(ch * 64), r2[0]);
+        tmem_ld_32x32(s_cur + ((uint32_t)(q * 32) << 16) + (uint32_t)(ch * 64 + 32), r2[1]);
+        tmem_ld_wait();
 #pragma unroll
         for (int half = 0; half < 2; ++half) {
-          uint32_t r[32];
-          const int col0 = ch * 64 + half * 32;
-          tmem_ld_32x32(s_tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)col0, r);
-          tmem_ld_wait();
+          const float4* b2 = reinterpret_cast<const float4*>(my_b2 + ch * 64 + half * 32);
           float f[32];
 #pragma unroll
-          for (int i = 0; i < 32; ++i) f[i] = __uint_as_float(r[i]);
-#pragma unroll
-          for (int kk = 0; kk < 8; ++kk) {
-            if (kk < 2 * p.k) {                                   // bias2d'[v][n] = sum_kk rs[kk][v] * bvec[kk][n]  (rank 2K)
-              const float4* bv = reinterpret_cast<const float4*>(btab + kk * p.co + col0);
-              const float rk = rs[kk];
-#pragma unroll
-              for (int g4 = 0; g4 < 8; ++g4) {
-                const float4 t4 = bv[g4];
-                f[g4 * 4 + 0] = fmaf(rk, t4.x, f[g4 * 4 + 0]); f[g4 * 4 + 1] = fmaf(rk, t4.y, f[g4 * 4 + 1]);
-                f[g4 * 4 + 2] = fmaf(rk, t4.z, f[g4 * 4 + 2]); f[g4 * 4 + 3] = fmaf(rk, t4.w, f[g4 * 4 + 3]);
-              }
-            }
+          for (int g4 = 0; g4 < 8; ++g4) {
+            const float4 t4 = b2[g4];
+            f[g4 * 4 + 0] = __uint_as_float(r2[half][g4 * 4 + 0]) + t4.x; f[g4 * 4 + 1] = __uint_as_float(r2[half][g4 * 4 + 1]) + t4.y;
+            f[g4 * 4 + 2] = __uint_as_float(r2[half][g4 * 4 + 2]) + t4.z; f[g4 * 4 + 3] = __uint_as_float(r2[half][g4 * 4 + 3]) + t4.w;
           }
 #pragma unroll
           for (int g4 = 0; g4 < 4; ++g4) {
@@ -259,8 +253,9 @@ spatial_fused_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_con
         gsync(bar_b);
         if (et == 0) { tma_store_5d(&map_out, my_p, ch * 64, 0, 0, j0, b); tma_store_commit(); }
       }
+      och += p.co / 64;
       tc_fence_before();
-      mbar_arrive(sempty);                                       // the output accumulator may be overwritten
+      mbar_arrive(sempty + sb); if (++sb == p.ns) sb = 0;                                       // the output accumulator may be overwritten
       // this group's staging store must have finished READING the buffer before its next chunk refills it
       if (et == 0) tma_store_wait_read<0>();
       gsync(bar_a);
@@ -287,7 +282,7 @@ static SpPlan sp_plan(int v, int ci, int co, int k) {
   SpPlan pl; pl.ok = false;
   if (ci % 64 != 0 || co % 64 != 0 || co > 256 || v < 4 || v > 32 || k < 1 || k > 3) return pl;
   pl.wn = co % 128 == 0 ? 128 : 64; pl.wparts = co / pl.wn;
-  const size_t fixed = (size_t)k * 2 * kSpTile + 2 * kSpTile + 1024 + 512 + (size_t)2 * k * co * sizeof(float);
+  const size_t fixed = (size_t)k * 2 * kSpTile + 2 * kSpTile + 1024 + 512 + (size_t)v * (co + 4) * sizeof(float);
   for (int xs = 3; xs >= 2 && !pl.ok; --xs)
     for (int wst = 4; wst >= 2 && !pl.ok; --wst) {
       if (wst < pl.wparts) continue;
@@ -305,9 +300,9 @@ static int num_sms_sp() {
 }
 
 // x (nb,t,v,ci) -> s (nb,t,v,co); xa (nb,t,v,k*ci) written too when non-null.  big = bf16 block-diagonal A (build_big_adjacency),
-// w2p = bf16 [co][k*ci] folded weights, rsum [2k][v], bvec [2k][co] (see SpParams).
+// w2p = bf16 [co][k*ci] folded weights, b2d = fp32 [v][co] joint bias table.
 int32_t launch_spatial_fused(const bf16* x, int nb, int t, int v, int ci, int co, int k, const bf16* big, const bf16* w2p,
-                             const float* rsum, const float* bvec, bf16* xa, bf16* s_out, cudaStream_t st) {
+                             const float* b2d, bf16* xa, bf16* s_out, cudaStream_t st) {
   KernelTimer kt_(KC_UMMA_SPATIAL, 2.0 * nb * t * v * (double)k * ci * (co + v), st);
   const SpPlan pl = sp_plan(v, ci, co, k);
   if (!pl.ok) { set_error("fused spatial: unsupported shape V=%d Ci=%d Co=%d K=%d", v, ci, co, k); return STGCN_ERR_UNSUPPORTED; }
@@ -315,9 +310,10 @@ int32_t launch_spatial_fused(const bf16* x, int nb, int t, int v, int ci, int co
   p.nb = nb; p.t = t; p.v = v; p.ft = 128 / v; p.ci = ci; p.co = co; p.k = k;
   p.m_tiles_per_b = cdiv(t, p.ft); p.total_tiles = p.m_tiles_per_b * nb;
   p.cblocks = ci / 64; p.wn = pl.wn; p.wparts = pl.wparts; p.xs = pl.xs; p.wst = pl.wst;
-  uint32_t cols = 32; while (cols < (uint32_t)(128 + co)) cols <<= 1;
+  p.ns = (128 + 2 * co <= 512) ? 2 : 1;
+  uint32_t cols = 32; while (cols < (uint32_t)(128 + p.ns * co)) cols <<= 1;
   p.tmem_cols = cols; p.tile_bytes = (uint32_t)(p.ft * v * 128);
-  p.write_xa = xa != nullptr; p.rsum = rsum; p.bvec = bvec;
+  p.write_xa = xa != nullptr; p.b2d = b2d;
   CUtensorMap map_x, map_big, map_w, map_xa, map_out;
   STGCN_TRY(sp_act_map(&map_x, x, ci, v, t, nb, p.ft));
   STGCN_TRY(sp_act_map(&map_out, s_out, co, v, t, nb, p.ft));

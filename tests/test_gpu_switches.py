@@ -14,12 +14,14 @@ pytestmark = pytest.mark.gpu
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-@pytest.mark.parametrize('var', ['STGCN_FUSED_SPATIAL', 'STGCN_NO_HALO', 'STGCN_SPLIT_DA', 'STGCN_NO_FUSED_STATS', 'STGCN_FUSED_VSUM'])
+@pytest.mark.parametrize('var', ['STGCN_FUSED_SPATIAL=1', 'STGCN_FUSED_SPATIAL=0', 'STGCN_NO_HALO=1', 'STGCN_SPLIT_DA=1',
+                                 'STGCN_NO_FUSED_STATS=1', 'STGCN_FUSED_VSUM=1'])
 def test_switched_path_is_parity_green(var):
     if os.environ.get('STGCN_SWITCH_CHILD'):
         pytest.skip('child run')
     env = dict(os.environ, STGCN_SWITCH_CHILD='1')
-    env[var] = '1'
+    name, value = var.split('=')
+    env[name] = value
     r = subprocess.run([sys.executable, '-m', 'pytest', os.path.join(ROOT, 'tests', 'test_gpu_block.py'),
                         os.path.join(ROOT, 'tests', 'test_gpu_umma.py'), '-q', '-x', '-m', 'gpu', '-k', 'bfloat16 or umma_conv_gemm'],
                        cwd=ROOT, env=env, capture_output=True, text=True, timeout=900)
