@@ -1,14 +1,16 @@
 #!/bin/bash
-# Round checkpoint: full bench line, ncu launch list, DRAM traffic of every conv_gemm launch of one step, full capture of 6 launches.
+# Round checkpoint: full bench line, ncu launch list, DRAM traffic of every conv_gemm launch of one step, full capture of a few launches.
 set -u
 mkdir -p gpurun_out
-CMD="python bench.py --only-train --steps 2 --warmup 3 --no-cpu-baseline"
+rm -f gpurun_out/*.ncu-rep
+CMD="python bench.py --only-train --steps 1 --warmup 3 --no-cpu-baseline"
 timeout 600 python bench.py > gpurun_out/bench_full.log 2>&1; echo "bench rc=$?" >> gpurun_out/bench_full.log
 timeout 300 $CMD > gpurun_out/plain.log 2>&1 &&
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 4000 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu_list.log 2>&1
 echo "list rc=$?" >> gpurun_out/ncu_list.log
-timeout 600 ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum,gpu__time_duration.sum --clock-control none -k regex:conv_gemm_umma -s 114 -c 38 --csv --log-file gpurun_out/conv_gemm_traffic.csv $CMD > gpurun_out/ncu_traffic.log 2>&1
+# one training step launches 39 conv_gemm kernels (10 mixing + 10 temporal forward, 10 temporal + 9 mixing data gradients); skip 3 warm-up steps
+timeout 600 ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum,gpu__time_duration.sum --clock-control none -k regex:conv_gemm_umma -s 117 -c 39 --csv --log-file gpurun_out/conv_gemm_traffic.csv $CMD > gpurun_out/ncu_traffic.log 2>&1
 echo "traffic rc=$?" >> gpurun_out/ncu_traffic.log
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:conv_gemm_umma -s 119 -c 6 -o gpurun_out/prof_conv_gemm $CMD > gpurun_out/ncu_full.log 2>&1
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:conv_gemm_umma -s 117 -c 8 -o gpurun_out/prof_conv_gemm $CMD > gpurun_out/ncu_full.log 2>&1
 echo "full rc=$?" >> gpurun_out/ncu_full.log
 tail -n 2 gpurun_out/bench_full.log gpurun_out/ncu_list.log gpurun_out/ncu_traffic.log gpurun_out/ncu_full.log | cut -c1-300
