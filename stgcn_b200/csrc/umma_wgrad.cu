@@ -24,15 +24,17 @@ using namespace umma;
 constexpr int kWgThreads = 192;
 constexpr int kWgMaxGroups = 8;
 constexpr int kWgMaxTapsPerGroup = 8;
-constexpr int kMaxSlabRows = 232;              // 4*25 + 128 = 228 -> multiple of 8
+constexpr int kMaxSlabRows = 392;              // (taps - 1) * V + 128 rows, multiple of 8 (8*32 + 128 = 384 for V = 32)
 constexpr int kATile = 128 * 128;              // 128 rows x 64 ch bf16
 
-struct WgGroup { int ntaps; int parity; int h_min; int w_tap[kWgMaxTapsPerGroup]; int row_off[kWgMaxTapsPerGroup]; };
+// stacked mode (n_out == 64): accumulator rows 0..63 hold tap w_tap[t], rows 64..127 tap w_tap2[t] (the next frame offset, or -1)
+struct WgGroup { int ntaps; int parity; int h_min; int w_tap[kWgMaxTapsPerGroup]; int row_off[kWgMaxTapsPerGroup]; int w_tap2[kWgMaxTapsPerGroup]; };
 
 struct WgParams {
   int nb, v, fj, jblocks;            // frames per reduction step, steps per sample
   int n_out, c, n_tiles, c_tiles, c_tile, n_slabs;   // n_slabs: 64-wide slabs of dout per tile (1 or 2)
   int ngroups, splits, kblocks_total, total_items;
+  int stacked;                       // 64 output channels: the second dout slab is the SAME channels one frame earlier -> two taps per MMA
   int stages;
   uint32_t tmem_cols, a_bytes, b_bytes;
   int b_slab;                        // bytes of one 64-channel input slab (rows * 128, rows % 8 == 0)
@@ -96,7 +98,8 @@ wgrad_umma_kernel(const __grid_constant__ CUtensorMap map_dout, const __grid_con
           mbar_wait(empty_bar + stage, phase ^ 1);
           mbar_expect_tx_e(full_bar + stage, p.a_bytes + p.b_bytes);
           for (int s = 0; s < p.n_slabs; ++s)
-            tma_load_5d_e(&map_dout, smem_a + (size_t)stage * a_stage + s * kATile, full_bar + stage, n_t * 128 + s * 64, 0, 0, j0, b);
+            tma_load_5d_e(&map_dout, smem_a + (size_t)stage * a_stage + s * kATile, full_bar + stage,
+                          p.stacked ? 0 : n_t * 128 + s * 64, 0, 0, p.stacked ? j0 - s : j0, b);
           for (int s = 0; s < p.c_tile / 64; ++s)
             tma_load_5d_e(&map_in, smem_b + (size_t)stage * b_stage + s * p.b_slab, full_bar + stage, c_t * p.c_tile + s * 64, 0,
                         G.parity, j0 + G.h_min, b);
@@ -143,11 +146,13 @@ wgrad_umma_kernel(const __grid_constant__ CUtensorMap map_dout, const __grid_con
       const WgGroup& G = p.groups[g];
       mbar_wait(tfull_bar, tphase);
       tc_fence_after();
-      const int n0 = n_t * 128 + q * 32;          // first output channel of this warp's rows
-      const int rows_ok = (kb1 > kb0) ? max(0, min(32, min(p.n_slabs * 64 - q * 32, p.n_out - n0))) : 0;
-      if (rows_ok > 0) {
+      const int n0 = p.stacked ? (q & 1) * 32 : n_t * 128 + q * 32;          // first output channel of this warp's rows
+      const int rows_all = (kb1 > kb0) ? (p.stacked ? 32 : max(0, min(32, min(p.n_slabs * 64 - q * 32, p.n_out - n0)))) : 0;
+      if (rows_all > 0) {
         for (int t = 0; t < G.ntaps; ++t) {
-          float* dst = p.packed + ((size_t)G.w_tap[t] * p.n_out + n0) * p.c + (size_t)c_t * p.c_tile + lane;
+          const int tap = (p.stacked && q >= 2) ? G.w_tap2[t] : G.w_tap[t];
+          const int rows_ok = tap >= 0 ? rows_all : 0;
+          float* dst = p.packed + ((size_t)max(tap, 0) * p.n_out + n0) * p.c + (size_t)c_t * p.c_tile + lane;
           for (int cc = 0; cc < p.c_tile; cc += 32) {
             uint32_t r[32];
             tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(t * p.c_tile + cc), r);
@@ -204,9 +209,11 @@ int32_t launch_wgrad_umma(const ConvGeom& g, const bf16* dout, const bf16* in, c
   if (!umma_wgrad_supported(g)) { set_error("umma wgrad: unsupported geometry"); return STGCN_ERR_UNSUPPORTED; }
   WgParams p; memset(&p, 0, sizeof(p));
   const int s = g.stride;
-  p.nb = g.nb; p.v = g.v; p.fj = 128 / g.v; p.jblocks = cdiv(g.t_out, p.fj);
+  p.stacked = (g.n_out == 64 && g.taps > 1 && getenv("STGCN_NO_TAP_STACK") == nullptr) ? 1 : 0;
+  // stacked: one extra reduction step per sample so that the frame-shifted slab also covers the last output frame
+  p.nb = g.nb; p.v = g.v; p.fj = 128 / g.v; p.jblocks = cdiv(g.t_out + p.stacked, p.fj);
   p.n_out = g.n_out; p.c = g.c;
-  p.n_tiles = cdiv(g.n_out, 128); p.n_slabs = g.n_out >= 128 ? 2 : 1;
+  p.n_tiles = cdiv(g.n_out, 128); p.n_slabs = (g.n_out >= 128 || p.stacked) ? 2 : 1;
   if (g.n_out % 128 != 0 && g.n_out > 64) { set_error("umma wgrad: n_out must be 64 or a multiple of 128"); return STGCN_ERR_UNSUPPORTED; }
   // tap groups: same input parity, consecutive frame offsets, at most `tg_max` taps (TMEM: taps*c_tile <= 512 columns)
   if (g.taps == 1) p.c_tile = g.c % 256 == 0 ? 256 : (g.c % 192 == 0 ? 192 : (g.c % 128 == 0 ? 128 : 64));
@@ -222,6 +229,23 @@ int32_t launch_wgrad_umma(const ConvGeom& g, const bf16* dout, const bf16* in, c
       if (r == par) { taps_p[np] = tap; hoff_p[np] = (d - r) / s; ++np; }
     }
     if (!np) continue;
+    if (p.stacked) {      // entries are PAIRS of consecutive frame offsets (taps_p is ordered by offset, step 1)
+      const int npair = cdiv(np, 2);
+      int ng = cdiv(npair, tg_max), per = cdiv(npair, ng);
+      for (int i0 = 0; i0 < npair; i0 += per) {
+        if (p.ngroups >= kWgMaxGroups) { set_error("umma wgrad: too many tap groups"); return STGCN_ERR_UNSUPPORTED; }
+        WgGroup& G = p.groups[p.ngroups++];
+        G.ntaps = std::min(per, npair - i0); G.parity = par; G.h_min = hoff_p[2 * i0];
+        for (int i = 0; i < G.ntaps; ++i) {
+          const int a = 2 * (i0 + i);
+          G.w_tap[i] = taps_p[a]; G.row_off[i] = (hoff_p[a] - G.h_min) * g.v;
+          G.w_tap2[i] = (a + 1 < np && hoff_p[a + 1] == hoff_p[a] + 1) ? taps_p[a + 1] : -1;
+          if (a + 1 < np && G.w_tap2[i] < 0) { set_error("umma wgrad: taps of one parity are not consecutive"); return STGCN_ERR_UNSUPPORTED; }
+        }
+        span_max = std::max(span_max, hoff_p[2 * (i0 + G.ntaps - 1)] - G.h_min);
+      }
+      continue;
+    }
     int ng = cdiv(np, tg_max), per = cdiv(np, ng);
     for (int i0 = 0; i0 < np; i0 += per) {
       if (p.ngroups >= kWgMaxGroups) { set_error("umma wgrad: too many tap groups"); return STGCN_ERR_UNSUPPORTED; }

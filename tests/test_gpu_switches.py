@@ -15,7 +15,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
 @pytest.mark.parametrize('var', ['STGCN_FUSED_SPATIAL=1', 'STGCN_FUSED_SPATIAL=0', 'STGCN_NO_HALO=1', 'STGCN_SPLIT_DA=1',
-                                 'STGCN_NO_FUSED_STATS=1', 'STGCN_FUSED_VSUM=1'])
+                                 'STGCN_NO_FUSED_STATS=1', 'STGCN_FUSED_VSUM=1', 'STGCN_NO_TAP_STACK=1'])
 def test_switched_path_is_parity_green(var):
     if os.environ.get('STGCN_SWITCH_CHILD'):
         pytest.skip('child run')
