@@ -108,6 +108,18 @@ size_t stgcn_block_workspace_bytes(const StgcnBlockDesc* desc, int32_t backward)
 int32_t stgcn_block_forward(const StgcnBlockDesc* desc, const void* x, const StgcnBlockParams* params,
                             void* y, void* saved, void* workspace, size_t workspace_bytes, void* stream);
 
+/* Inference with frozen parameters (no reference counterpart: the reference re-derives nothing, it calls cuDNN per layer).
+ * Everything that depends only on the parameters -- eval-mode BatchNorm tables (st_graphconv.py:34,46), the BatchNorm-1-folded
+ * 1x1 weights, the joint-bias table, the block-diagonal adjacency operand and the packed temporal weights -- is computed once by
+ * stgcn_block_prepare into a caller-owned device buffer of stgcn_block_prepared_bytes(desc) bytes; stgcn_block_forward_prepared
+ * then runs SpatialTemporalConv.forward (eval mode, default block) as two kernels.  The buffer does not depend on n or t.
+ * stgcn_block_prepared_bytes returns 0 when the block has no prepared path (training mode, fp32, residual block, C_in % 64 != 0);
+ * callers then use stgcn_block_forward.  The caller must prepare again whenever a parameter or a running statistic changes. */
+size_t stgcn_block_prepared_bytes(const StgcnBlockDesc* desc);
+int32_t stgcn_block_prepare(const StgcnBlockDesc* desc, const StgcnBlockParams* params, void* prepared, void* stream);
+int32_t stgcn_block_forward_prepared(const StgcnBlockDesc* desc, const void* x, const StgcnBlockParams* params, const void* prepared,
+                                     void* y, void* workspace, size_t workspace_bytes, void* stream);
+
 /* Autograd of the above (reference: torch autograd over st_graphconv.py:85-109).
  *   dy (n,t_out,v,c_out) -> dx (n,t,v,c_in) (may be NULL: first block) + grads. */
 int32_t stgcn_block_backward(const StgcnBlockDesc* desc, const void* x, const void* y,

@@ -50,6 +50,11 @@ def _declare(lib):
     lib.stgcn_block_workspace_bytes.restype = sz; lib.stgcn_block_workspace_bytes.argtypes = [D, i32]
     lib.stgcn_block_forward.restype = i32
     lib.stgcn_block_forward.argtypes = [D, _P, C.POINTER(BlockParams), _P, _P, _P, sz, _P]
+    lib.stgcn_block_prepared_bytes.restype = sz; lib.stgcn_block_prepared_bytes.argtypes = [D]
+    lib.stgcn_block_prepare.restype = i32
+    lib.stgcn_block_prepare.argtypes = [D, C.POINTER(BlockParams), _P, _P]
+    lib.stgcn_block_forward_prepared.restype = i32
+    lib.stgcn_block_forward_prepared.argtypes = [D, _P, C.POINTER(BlockParams), _P, _P, _P, sz, _P]
     lib.stgcn_block_backward.restype = i32
     lib.stgcn_block_backward.argtypes = [D, _P, _P, C.POINTER(BlockParams), _P, _P, _P, C.POINTER(BlockGrads), _P, sz, _P]
     lib.stgcn_spatial_workspace_bytes.restype = sz; lib.stgcn_spatial_workspace_bytes.argtypes = [D, i32]

@@ -77,6 +77,18 @@ static FoldPrep carve_fold_prep(Arena& a, const Dims& m) {
   return f;
 }
 template <class T> struct Saved { float* stats1; float* stats2; T* S; T* U; T* XA; FoldPrep fp; };
+// Inference with frozen parameters (stgcn_block_prepare / stgcn_block_forward_prepared): everything that depends only on the
+// parameters -- eval BatchNorm coefficient tables, folded spatial operands, joint-bias table, packed temporal weights.
+struct Prepared { float* stats1; float* stats2; FoldPrep fp; float* b2d; bf16* wt; };
+static Prepared carve_prepared(Arena& a, const Dims& m) {
+  Prepared q;
+  q.stats1 = a.get<float>(4 * m.ci);
+  q.stats2 = a.get<float>(4 * m.co);
+  q.fp = carve_fold_prep(a, m);
+  q.b2d = a.get<float>((size_t)m.v * m.co);
+  q.wt = a.get<bf16>((size_t)m.gamma * m.co * m.co);
+  return q;
+}
 template <class T> static Saved<T> carve_saved(Arena& a, const StgcnBlockDesc& d, const Dims& m) {
   Saved<T> s;
   s.stats1 = a.get<float>(4 * m.ci);
@@ -183,10 +195,11 @@ template <class T> struct Bn1Fold {      // backward of the folded BatchNorm-1 (
 template <class T>
 static int32_t spatial_fwd(Engine<T>& e, const Dims& m, const T* x, const float* aff_a, const float* aff_b, int relu1,
                            const float* A, const float* W, const float* Wb, T* S, T* xa_keep = nullptr,
-                           const FoldPrep* keep_prep = nullptr) {
+                           const FoldPrep* keep_prep = nullptr, const float* b2d_ready = nullptr) {
   Arena& ws = e.ws;
   T* XA = xa_keep ? xa_keep : ws.template get<T>(m.rows_in * m.k * m.ci);
   float* b2d = ws.template get<float>((size_t)m.v * m.co);
+  if (b2d_ready) b2d = const_cast<float*>(b2d_ready);      // operands prepared ahead of time (keep_prep holds the rest)
   bool tc_agg = false;
   if constexpr (std::is_same<T, bf16>::value) tc_agg = e.want_umma() && umma_agg_supported(m.v, m.ci, m.k);
   if constexpr (std::is_same<T, bf16>::value) {
@@ -221,9 +234,11 @@ static int32_t spatial_fwd(Engine<T>& e, const Dims& m, const T* x, const float*
       static const char* fused_env = getenv("STGCN_FUSED_SPATIAL");
       const bool want_fused = fused_env ? (fused_env[0] != '0') : (xa_keep == nullptr);
       const bool fused = want_fused && umma_spatial_supported(m.v, m.ci, m.co, m.k);
-      STGCN_TRY(launch_build_big_adjacency(A, m.k, m.v, prep, e.st));
-      STGCN_TRY(launch_bn1_fold(W, Wb, A, umma_agg_rowsum_q(prep, m.k), aff_a, aff_b, m.k, m.v, m.co, m.ci, w2p, w2pT, wb, wbb, b2d, e.st, 0,
-                                rsum2, bvec2));
+      if (!b2d_ready) {
+        STGCN_TRY(launch_build_big_adjacency(A, m.k, m.v, prep, e.st));
+        STGCN_TRY(launch_bn1_fold(W, Wb, A, umma_agg_rowsum_q(prep, m.k), aff_a, aff_b, m.k, m.v, m.co, m.ci, w2p, w2pT, wb, wbb, b2d, e.st, 0,
+                                  rsum2, bvec2));
+      }
       if (fused)     // one kernel: aggregation -> (TMEM -> bf16 smem) -> channel mixing; XA goes to HBM only when backward wants it
         return launch_spatial_fused(x, m.n, m.t, m.v, m.ci, m.co, m.k, umma_agg_big(prep, m.k), w2p, b2d, xa_keep, S, e.st);
       STGCN_TRY(launch_agg_fwd_umma(x, m.n, m.t, m.v, m.ci, m.k, prep, nullptr, nullptr, XA, e.st));
@@ -465,6 +480,39 @@ static int32_t block_forward_t(const StgcnBlockDesc& d, const T* x, const StgcnB
 }
 
 // ---------------------------------------------------------------------------
+// inference with frozen parameters: prepare once, then two large kernels per block
+// ---------------------------------------------------------------------------
+static bool prepared_ok(const StgcnBlockDesc& d, const Dims& m) {
+  if (d.training || d.dtype != STGCN_BF16 || d.residual != STGCN_RES_NONE || !fold_ok_desc(d, m)) return false;
+  return umma_conv_gemm_supported(geom(m.n, m.t, m.to, m.v, m.co, m.co, m.gamma, m.stride, m.pad, 0));
+}
+static int32_t block_prepare(const StgcnBlockDesc& d, const StgcnBlockParams& P, void* prepared_mem, cudaStream_t st) {
+  const Dims m = dims_of(d);
+  if (!prepared_ok(d, m)) { set_error("block_prepare: this block has no prepared path (needs eval mode, bf16, default block, C_in % 64 == 0)"); return STGCN_ERR_UNSUPPORTED; }
+  Arena pa(prepared_mem, ~(size_t)0);
+  const Prepared q = carve_prepared(pa, m);
+  STGCN_TRY(launch_bn_eval_coeffs(m.ci, P.bn1_weight, P.bn1_bias, P.bn1_running_mean, P.bn1_running_var, d.bn_eps, q.stats1, st));
+  STGCN_TRY(launch_bn_eval_coeffs(m.co, P.bn2_weight, P.bn2_bias, P.bn2_running_mean, P.bn2_running_var, d.bn_eps, q.stats2, st));
+  STGCN_TRY(launch_build_big_adjacency(P.A, m.k, m.v, q.fp.prep, st));
+  STGCN_TRY(launch_bn1_fold(P.W, P.W_bias, P.A, umma_agg_rowsum_q(q.fp.prep, m.k), q.stats1 + 2 * m.ci, q.stats1 + 3 * m.ci, m.k, m.v, m.co,
+                            m.ci, q.fp.w2p, q.fp.w2pT, q.fp.wb, q.fp.wbb, q.b2d, st));
+  const WIndex wiT = widx(kNoDiv, 0, (long long)m.co * m.gamma, kNoDiv, 0, m.gamma, 1);
+  return launch_pack_weights<bf16>(P.Wt, wiT, m.gamma, m.co, m.co, q.wt, st);
+}
+static int32_t block_forward_prepared(const StgcnBlockDesc& d, const bf16* x, const StgcnBlockParams& P, const void* prepared_mem, bf16* y,
+                                      Arena& ws, cudaStream_t st) {
+  const Dims m = dims_of(d);
+  if (!prepared_ok(d, m)) { set_error("block_forward_prepared: this block has no prepared path"); return STGCN_ERR_UNSUPPORTED; }
+  Arena pa(const_cast<void*>(prepared_mem), ~(size_t)0);
+  const Prepared q = carve_prepared(pa, m);
+  bf16* Sbuf = ws.get<bf16>(m.rows_in * m.co);
+  Engine<bf16> e{d, ws, st};
+  STGCN_TRY(spatial_fwd<bf16>(e, m, x, q.stats1 + 2 * m.ci, q.stats1 + 3 * m.ci, 0, P.A, P.W, P.W_bias, Sbuf, nullptr, &q.fp, q.b2d));
+  GemmEpilogue ep; ep.bias = P.Wt_bias; ep.scale = q.stats2 + 2 * m.co; ep.shift = q.stats2 + 3 * m.co; ep.relu = 1;   // BN-2 + ReLU in the epilogue
+  return e.gemm_packed(geom(m.n, m.t, m.to, m.v, m.co, m.co, m.gamma, m.stride, m.pad, 0), Sbuf, q.wt, ep, y);
+}
+
+// ---------------------------------------------------------------------------
 // block backward
 // ---------------------------------------------------------------------------
 template <class T>
@@ -624,6 +672,31 @@ int32_t stgcn_block_forward(const StgcnBlockDesc* d, const void* x, const StgcnB
   cudaStream_t st = (cudaStream_t)stream;
   if (d->dtype == STGCN_F32) return block_forward_t<float>(*d, (const float*)x, *P, (float*)y, saved, ws, st);
   return block_forward_t<bf16>(*d, (const bf16*)x, *P, (bf16*)y, saved, ws, st);
+}
+
+size_t stgcn_block_prepared_bytes(const StgcnBlockDesc* d) {
+  if (validate(d) != STGCN_OK) return 0;
+  const Dims m = dims_of(*d);
+  if (!prepared_ok(*d, m)) return 0;
+  Arena dry(nullptr, 0);
+  carve_prepared(dry, m);
+  return dry.off + 256;
+}
+
+int32_t stgcn_block_prepare(const StgcnBlockDesc* d, const StgcnBlockParams* P, void* prepared, void* stream) {
+  STGCN_TRY(validate(d));
+  STGCN_TRY(check_ptrs(prepared, P, prepared));
+  return block_prepare(*d, *P, prepared, (cudaStream_t)stream);
+}
+
+int32_t stgcn_block_forward_prepared(const StgcnBlockDesc* d, const void* x, const StgcnBlockParams* P, const void* prepared, void* y,
+                                     void* workspace, size_t workspace_bytes, void* stream) {
+  STGCN_TRY(validate(d));
+  STGCN_TRY(check_ptrs(x, P, y));
+  if (!prepared) { set_error("null prepared buffer"); return STGCN_ERR_INVALID; }
+  if (!workspace) { set_error("null workspace"); return STGCN_ERR_WORKSPACE; }
+  Arena ws(workspace, workspace_bytes);
+  return block_forward_prepared(*d, (const bf16*)x, *P, prepared, (bf16*)y, ws, (cudaStream_t)stream);
 }
 
 int32_t stgcn_block_backward(const StgcnBlockDesc* d, const void* x, const void* y, const StgcnBlockParams* P, const void* saved,

@@ -66,6 +66,7 @@ class SpatialTemporalConv(nn.Module):
         self.compute_dtype = compute_dtype
         self.flags = 0
         self._calls = 0
+        self._prep_cache = {}      # frozen-parameter inference operands (functional._BlockFn), keyed by tensor versions
 
     def forward(self, f_in):
         sc, tc, b1, b2 = self.spatialConv, self.temporalConv, self.batch_n, self.batch_n_2
@@ -81,11 +82,13 @@ class SpatialTemporalConv(nn.Module):
         if p_drop > 0:
             seed = int(torch.randint(0, 2 ** 62, (1,)).item())
         self._calls += 1
+        if self.training:
+            self._prep_cache.clear()       # running statistics are about to change behind torch's version counters
         cfg = {'dtype': self.compute_dtype, 'c_in': self.C_in, 'c_out': self.C_out, 'gamma': self.gamma,
                'stride': self.temporal_stride, 'pad': self.temporal_padding, 'training': self.training,
                'residual': self._res_mode, 'dropout_p': p_drop, 'eps': b1.eps,
                'momentum': 0.1 if b1.momentum is None else b1.momentum, 'seed': seed, 'need_grad': need_grad,
-               'flags': self.flags}
+               'flags': self.flags, 'prep_cache': self._prep_cache}
         buffers = (b1.running_mean, b1.running_var, b1.num_batches_tracked,
                    b2.running_mean, b2.running_var, b2.num_batches_tracked)
         return Fn.block_forward(f_in, cfg, buffers, params)

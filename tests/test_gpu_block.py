@@ -220,3 +220,37 @@ def test_first_block_without_input_gradient(training):
             assert float(v.abs().max()) <= 1e-5 * float(gy.abs().sum())
             continue
         assert rel_err(v.reshape(ref.shape), ref) < ptol, k
+
+
+def test_prepared_inference_tracks_parameter_changes():
+    """Frozen-parameter inference (stgcn_block_prepare / _forward_prepared) must equal the unprepared call, re-prepare when a
+    parameter changes in place and after a training step moved the running statistics."""
+    torch.manual_seed(11)
+    A = torch.rand(3, 25, 25) * 0.2
+    m = build_block(64, 128, A, 2, False, dtype=torch.bfloat16)
+    x = torch.randn(4, 64, 20, 25).cuda()
+
+    def both():
+        m.eval()
+        with torch.no_grad():
+            cache = m._prep_cache
+            y_p = m(x).float()
+            assert m._prep_cache.get('blob') is not None          # the prepared path really ran
+            y_p2 = m(x).float()                                    # cached operands
+            m._prep_cache = None
+            y_u = m(x).float()
+            m._prep_cache = cache
+        assert torch.equal(y_p, y_p2)
+        assert rel_err(y_p.cpu(), y_u.cpu()) < 1e-6
+        return y_p
+
+    y0 = both()
+    with torch.no_grad():
+        m.batch_n.weight.mul_(1.5)
+        m.temporalConv.bias.add_(0.25)
+    y1 = both()
+    assert rel_err(y1.cpu(), y0.cpu()) > 1e-3
+    m.train()
+    m(x * 3 + 1)                                                   # moves the running statistics through raw pointers
+    y2 = both()
+    assert rel_err(y2.cpu(), y1.cpu()) > 1e-3
