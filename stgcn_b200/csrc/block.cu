@@ -492,7 +492,8 @@ static int32_t block_prepare(const StgcnBlockDesc& d, const StgcnBlockParams& P,
   Arena pa(prepared_mem, ~(size_t)0);
   const Prepared q = carve_prepared(pa, m);
   STGCN_TRY(launch_bn_eval_coeffs(m.ci, P.bn1_weight, P.bn1_bias, P.bn1_running_mean, P.bn1_running_var, d.bn_eps, q.stats1, st));
-  STGCN_TRY(launch_bn_eval_coeffs(m.co, P.bn2_weight, P.bn2_bias, P.bn2_running_mean, P.bn2_running_var, d.bn_eps, q.stats2, st));
+  // the temporal conv's bias travels in the BatchNorm-2 shift: the fused epilogue is one fma + ReLU per element
+  STGCN_TRY(launch_bn_eval_coeffs(m.co, P.bn2_weight, P.bn2_bias, P.bn2_running_mean, P.bn2_running_var, d.bn_eps, q.stats2, st, P.Wt_bias));
   STGCN_TRY(launch_build_big_adjacency(P.A, m.k, m.v, q.fp.prep, st));
   STGCN_TRY(launch_bn1_fold(P.W, P.W_bias, P.A, umma_agg_rowsum_q(q.fp.prep, m.k), q.stats1 + 2 * m.ci, q.stats1 + 3 * m.ci, m.k, m.v, m.co,
                             m.ci, q.fp.w2p, q.fp.w2pT, q.fp.wb, q.fp.wbb, q.b2d, st));
@@ -508,7 +509,7 @@ static int32_t block_forward_prepared(const StgcnBlockDesc& d, const bf16* x, co
   bf16* Sbuf = ws.get<bf16>(m.rows_in * m.co);
   Engine<bf16> e{d, ws, st};
   STGCN_TRY(spatial_fwd<bf16>(e, m, x, q.stats1 + 2 * m.ci, q.stats1 + 3 * m.ci, 0, P.A, P.W, P.W_bias, Sbuf, nullptr, &q.fp, q.b2d));
-  GemmEpilogue ep; ep.bias = P.Wt_bias; ep.scale = q.stats2 + 2 * m.co; ep.shift = q.stats2 + 3 * m.co; ep.relu = 1;   // BN-2 + ReLU in the epilogue
+  GemmEpilogue ep; ep.scale = q.stats2 + 2 * m.co; ep.shift = q.stats2 + 3 * m.co; ep.relu = 1;   // conv bias + BN-2 + ReLU in the epilogue
   return e.gemm_packed(geom(m.n, m.t, m.to, m.v, m.co, m.co, m.gamma, m.stride, m.pad, 0), Sbuf, q.wt, ep, y);
 }
 

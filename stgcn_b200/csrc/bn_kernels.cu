@@ -231,7 +231,7 @@ bn_finalize_kernel(const float* __restrict__ partials, int nblk, int C, double c
 
 __global__ void bn_eval_coeffs_kernel(int C, const float* __restrict__ gamma, const float* __restrict__ beta,
                                       const float* __restrict__ rm, const float* __restrict__ rv, float eps,
-                                      float* __restrict__ stats) {
+                                      float* __restrict__ stats, const float* __restrict__ pre_bias) {
   int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= C) return;
   float invstd = rsqrtf(rv[c] + eps);
@@ -239,7 +239,8 @@ __global__ void bn_eval_coeffs_kernel(int C, const float* __restrict__ gamma, co
   stats[0 * C + c] = rm[c];
   stats[1 * C + c] = invstd;
   stats[2 * C + c] = a;
-  stats[3 * C + c] = beta[c] - a * rm[c];
+  // pre_bias: a per-channel bias added BEFORE the normalisation (the producing conv's) folded into the shift
+  stats[3 * C + c] = beta[c] - a * rm[c] + (pre_bias ? a * pre_bias[c] : 0.f);
 }
 
 int32_t launch_bn_finalize(const float* partials, int nblk, int C, double count, const float* gamma,
@@ -250,8 +251,8 @@ int32_t launch_bn_finalize(const float* partials, int nblk, int C, double count,
   return STGCN_OK;
 }
 int32_t launch_bn_eval_coeffs(int C, const float* gamma, const float* beta, const float* rm, const float* rv,
-                              float eps, float* stats, cudaStream_t st) {
-  bn_eval_coeffs_kernel<<<cdiv(C, 128), 128, 0, st>>>(C, gamma, beta, rm, rv, eps, stats);
+                              float eps, float* stats, cudaStream_t st, const float* pre_bias) {
+  bn_eval_coeffs_kernel<<<cdiv(C, 128), 128, 0, st>>>(C, gamma, beta, rm, rv, eps, stats, pre_bias);
   STGCN_CHECK_LAUNCH("bn_eval_coeffs");
   return STGCN_OK;
 }

@@ -50,7 +50,7 @@ template <class T> int32_t launch_colstats(const T* x, long long rows, int C, fl
 int32_t launch_bn_finalize(const float* partials, int nblk, int C, double count, const float* gamma, const float* beta,
                            float* rm, float* rv, long long* nbt, float eps, float momentum, float* stats, cudaStream_t st);
 int32_t launch_bn_eval_coeffs(int C, const float* gamma, const float* beta, const float* rm, const float* rv, float eps,
-                              float* stats, cudaStream_t st);
+                              float* stats, cudaStream_t st, const float* pre_bias = nullptr);
 template <class T> int32_t launch_affine_act(const T* x, long long rows, int C, const float* a, const float* b, int relu, float p,
                                             uint64_t seed, uint64_t offset, T* y, cudaStream_t st);
 template <class T> int32_t launch_bn_bwd_reduce(const T* dy, const T* z, const float* stats, long long rows, int C, int relu, float p,

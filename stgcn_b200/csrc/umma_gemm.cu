@@ -68,18 +68,20 @@ __device__ __forceinline__ TileCoord decode_tile(const UmmaParams& p, int tile) 
   return t;
 }
 
-// PLAIN = no epilogue option at all (every data-gradient GEMM): the option code folds away, which matters because the epilogue
-// warps are bound by dependent-issue latency (about 10 cycles per instruction with two warps per scheduler)
-template <bool PLAIN>
+// EPM = compile-time mask of the epilogue options an instantiation keeps (the others fold away).  This matters because the
+// epilogue warps are bound by dependent-issue latency (about 10 cycles per instruction with two warps per scheduler): the
+// option-free instance used by every data-gradient GEMM needs 84 registers and a third of the instructions per chunk.
+constexpr int EP_BIAS = 1, EP_BIAS2D = 2, EP_SCALE = 4, EP_RESID = 8, EP_RELU = 16, EP_DROPOUT = 32, EP_STATS = 64, EP_VSUM = 128, EP_ALL = 255;
+template <int EPM>
 __global__ void __launch_bounds__(kUmmaThreads, 1)
 conv_gemm_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_constant__ CUtensorMap map_w,
                       const __grid_constant__ CUtensorMap map_out, const __grid_constant__ UmmaParams p) {
-  const float* const o_bias = PLAIN ? nullptr : p.bias; const float* const o_bias2d = PLAIN ? nullptr : p.bias2d;
-  const float* const o_scale = PLAIN ? nullptr : p.scale; const float* const o_shift = PLAIN ? nullptr : p.shift;
-  const bf16* const o_residual = PLAIN ? nullptr : p.residual;
-  float* const o_stat_partials = PLAIN ? nullptr : p.stat_partials; float* const o_vsum = PLAIN ? nullptr : p.vsum;
-  const int o_b2_smem = PLAIN ? 0 : p.b2_smem, o_relu = PLAIN ? 0 : p.relu;
-  const float o_dropout_p = PLAIN ? 0.f : p.dropout_p;
+  const float* const o_bias = (EPM & EP_BIAS) ? p.bias : nullptr; const float* const o_bias2d = (EPM & EP_BIAS2D) ? p.bias2d : nullptr;
+  const float* const o_scale = (EPM & EP_SCALE) ? p.scale : nullptr; const float* const o_shift = (EPM & EP_SCALE) ? p.shift : nullptr;
+  const bf16* const o_residual = (EPM & EP_RESID) ? p.residual : nullptr;
+  float* const o_stat_partials = (EPM & EP_STATS) ? p.stat_partials : nullptr; float* const o_vsum = (EPM & EP_VSUM) ? p.vsum : nullptr;
+  const int o_b2_smem = (EPM & EP_BIAS2D) ? p.b2_smem : 0, o_relu = (EPM & EP_RELU) ? p.relu : 0;
+  const float o_dropout_p = (EPM & EP_DROPOUT) ? p.dropout_p : 0.f;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // 1024-byte aligned carve-up (dynamic smem base is only guaranteed 16-byte aligned)
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -578,15 +580,22 @@ int32_t launch_conv_gemm_umma(const ConvGeom& g, const bf16* in, const bf16* w, 
   }
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(conv_gemm_umma_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_gemm_umma_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    cudaError_t e = cudaSuccess;
+#define STGCN_CG_ATTR(M) if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_gemm_umma_kernel<M>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    STGCN_CG_ATTR(0) STGCN_CG_ATTR(EP_BIAS2D) STGCN_CG_ATTR(EP_BIAS | EP_STATS) STGCN_CG_ATTR(EP_SCALE | EP_RELU)
+    STGCN_CG_ATTR(EP_BIAS | EP_SCALE | EP_RELU) STGCN_CG_ATTR(EP_ALL)
+#undef STGCN_CG_ATTR
     if (e != cudaSuccess) { set_error("cudaFuncSetAttribute(smem) failed: %s", cudaGetErrorString(e)); return STGCN_ERR_CUDA; }
     attr_set = true;
   }
   const int grid = std::min(p.total_tiles, num_sms());
-  const bool plain = !ep.bias && !ep.bias2d && !ep.scale && !ep.residual && !ep.relu && !(ep.dropout_p > 0.f) && !ep.stat_partials && !ep.vsum;
-  if (plain) conv_gemm_umma_kernel<true><<<grid, kUmmaThreads, smem, st>>>(map_in, map_w, map_out, p);
-  else conv_gemm_umma_kernel<false><<<grid, kUmmaThreads, smem, st>>>(map_in, map_w, map_out, p);
+  const int need = (ep.bias ? EP_BIAS : 0) | (ep.bias2d ? EP_BIAS2D : 0) | (ep.scale ? EP_SCALE : 0) | (ep.residual ? EP_RESID : 0) |
+                   (ep.relu ? EP_RELU : 0) | (ep.dropout_p > 0.f ? EP_DROPOUT : 0) | (ep.stat_partials ? EP_STATS : 0) | (ep.vsum ? EP_VSUM : 0);
+  // the leanest instantiation that keeps every requested option
+#define STGCN_CG_TRY(M) if ((need & ~(M)) == 0) { conv_gemm_umma_kernel<M><<<grid, kUmmaThreads, smem, st>>>(map_in, map_w, map_out, p); } else
+  STGCN_CG_TRY(0) STGCN_CG_TRY(EP_BIAS2D) STGCN_CG_TRY(EP_BIAS | EP_STATS) STGCN_CG_TRY(EP_SCALE | EP_RELU)
+  STGCN_CG_TRY(EP_BIAS | EP_SCALE | EP_RELU) { conv_gemm_umma_kernel<EP_ALL><<<grid, kUmmaThreads, smem, st>>>(map_in, map_w, map_out, p); }
+#undef STGCN_CG_TRY
   STGCN_CHECK_LAUNCH("conv_gemm_umma");
   return STGCN_OK;
 }

@@ -241,7 +241,7 @@ def test_prepared_inference_tracks_parameter_changes():
             y_u = m(x).float()
             m._prep_cache = cache
         assert torch.equal(y_p, y_p2)
-        assert rel_err(y_p.cpu(), y_u.cpu()) < 1e-6
+        assert rel_err(y_p.cpu(), y_u.cpu()) < 8e-3              # same math, the conv bias rides in the BN shift: bf16 ulp flips only
         return y_p
 
     y0 = both()
