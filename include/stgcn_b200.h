@@ -108,6 +108,18 @@ size_t stgcn_block_workspace_bytes(const StgcnBlockDesc* desc, int32_t backward)
 int32_t stgcn_block_forward(const StgcnBlockDesc* desc, const void* x, const StgcnBlockParams* params,
                             void* y, void* saved, void* workspace, size_t workspace_bytes, void* stream);
 
+/* Chained blocks (training): the BatchNorm-1 batch statistics of block i+1 (st_graphconv.py:34, :98) are column statistics of
+ * block i's output, which block i's last pass can produce for free.  Same as stgcn_block_forward, plus
+ *   x_colstats / x_colstats_nblk : per-CTA partial column sums of x written by the call that produced x (NULL / 0: none)
+ *   y_colstats / y_colstats_nblk : buffer of stgcn_colstats_bytes(c_out) bytes to receive the partials of y; *nblk is set to
+ *                                  the number of partial rows written, 0 when this path cannot produce them (dropout, residual
+ *                                  block, eval mode) -- the consumer then computes its own statistics.
+ * The statistics describe y as stored; they are stale once y is modified. */
+size_t stgcn_colstats_bytes(int32_t channels);
+int32_t stgcn_block_forward_chain(const StgcnBlockDesc* desc, const void* x, const StgcnBlockParams* params, void* y, void* saved,
+                                  void* workspace, size_t workspace_bytes, const float* x_colstats, int32_t x_colstats_nblk,
+                                  float* y_colstats, int32_t* y_colstats_nblk, void* stream);
+
 /* Inference with frozen parameters (no reference counterpart: the reference re-derives nothing, it calls cuDNN per layer).
  * Everything that depends only on the parameters -- eval-mode BatchNorm tables (st_graphconv.py:34,46), the BatchNorm-1-folded
  * 1x1 weights, the joint-bias table, the block-diagonal adjacency operand and the packed temporal weights -- is computed once by

@@ -50,6 +50,9 @@ def _declare(lib):
     lib.stgcn_block_workspace_bytes.restype = sz; lib.stgcn_block_workspace_bytes.argtypes = [D, i32]
     lib.stgcn_block_forward.restype = i32
     lib.stgcn_block_forward.argtypes = [D, _P, C.POINTER(BlockParams), _P, _P, _P, sz, _P]
+    lib.stgcn_colstats_bytes.restype = sz; lib.stgcn_colstats_bytes.argtypes = [i32]
+    lib.stgcn_block_forward_chain.restype = i32
+    lib.stgcn_block_forward_chain.argtypes = [D, _P, C.POINTER(BlockParams), _P, _P, _P, sz, _P, i32, _P, C.POINTER(i32), _P]
     lib.stgcn_block_prepared_bytes.restype = sz; lib.stgcn_block_prepared_bytes.argtypes = [D]
     lib.stgcn_block_prepare.restype = i32
     lib.stgcn_block_prepare.argtypes = [D, C.POINTER(BlockParams), _P, _P]

@@ -402,7 +402,11 @@ static int32_t spatial_bwd(Engine<T>& e, const Dims& m, const T* x, const float*
 // ---------------------------------------------------------------------------
 template <class T>
 static int32_t block_forward_t(const StgcnBlockDesc& d, const T* x, const StgcnBlockParams& P, T* y, void* saved_mem,
-                               Arena& ws, cudaStream_t st) {
+                               Arena& ws, cudaStream_t st, const float* x_cs = nullptr, int x_cs_n = 0, float* y_cs = nullptr,
+                               int* y_cs_n = nullptr) {
+  // x_cs / y_cs: chained blocks (stgcn_block_forward_chain) -- column statistics of x handed over by the producer of x, and of
+  // y produced for the consumer of y, so BatchNorm-1 of the next block needs no pass of its own
+  if (y_cs_n) *y_cs_n = 0;
   const Dims m = dims_of(d);
   Arena sv(saved_mem, ~(size_t)0);
   Saved<T> S;
@@ -417,8 +421,10 @@ static int32_t block_forward_t(const StgcnBlockDesc& d, const T* x, const StgcnB
   if (!ws.dry) {
     if (!ws.ok()) { set_error("workspace too small"); return STGCN_ERR_WORKSPACE; }
     if (d.training) {
-      STGCN_TRY(launch_colstats<T>(x, m.rows_in, m.ci, partials, &nblk, st));
-      STGCN_TRY(launch_bn_finalize(partials, nblk, m.ci, (double)m.rows_in, P.bn1_weight, P.bn1_bias, P.bn1_running_mean,
+      const float* part1 = partials;
+      if (x_cs && x_cs_n > 0) { part1 = x_cs; nblk = x_cs_n; }
+      else STGCN_TRY(launch_colstats<T>(x, m.rows_in, m.ci, partials, &nblk, st));
+      STGCN_TRY(launch_bn_finalize(part1, nblk, m.ci, (double)m.rows_in, P.bn1_weight, P.bn1_bias, P.bn1_running_mean,
                                    P.bn1_running_var, (long long*)P.bn1_num_batches_tracked, d.bn_eps, d.bn_momentum, S.stats1, st));
     } else {
       STGCN_TRY(launch_bn_eval_coeffs(m.ci, P.bn1_weight, P.bn1_bias, P.bn1_running_mean, P.bn1_running_var, d.bn_eps, S.stats1, st));
@@ -448,7 +454,8 @@ static int32_t block_forward_t(const StgcnBlockDesc& d, const T* x, const StgcnB
         STGCN_TRY(launch_bn_eval_coeffs(m.co, P.bn2_weight, P.bn2_bias, P.bn2_running_mean, P.bn2_running_var, d.bn_eps, S.stats2, st));
       }
       const float p = d.training ? d.dropout_p : 0.f;
-      return launch_affine_act<T>(U, m.rows_out, m.co, S.stats2 + 2 * m.co, S.stats2 + 3 * m.co, 1, p, d.seed, d.offset, y, st);
+      return launch_affine_act<T>(U, m.rows_out, m.co, S.stats2 + 2 * m.co, S.stats2 + 3 * m.co, 1, p, d.seed, d.offset, y, st,
+                                  d.training ? y_cs : nullptr, y_cs_n);
     }
     // inference: BN2 + ReLU folded into the temporal GEMM's epilogue, U never exists
     if (!ws.dry) STGCN_TRY(launch_bn_eval_coeffs(m.co, P.bn2_weight, P.bn2_bias, P.bn2_running_mean, P.bn2_running_var, d.bn_eps, S.stats2, st));
@@ -673,6 +680,28 @@ int32_t stgcn_block_forward(const StgcnBlockDesc* d, const void* x, const StgcnB
   cudaStream_t st = (cudaStream_t)stream;
   if (d->dtype == STGCN_F32) return block_forward_t<float>(*d, (const float*)x, *P, (float*)y, saved, ws, st);
   return block_forward_t<bf16>(*d, (const bf16*)x, *P, (bf16*)y, saved, ws, st);
+}
+
+size_t stgcn_colstats_bytes(int32_t channels) { return channels > 0 ? stat_partials_bytes(channels) : 0; }
+
+int32_t stgcn_block_forward_chain(const StgcnBlockDesc* d, const void* x, const StgcnBlockParams* P, void* y, void* saved,
+                                  void* workspace, size_t workspace_bytes, const float* x_colstats, int32_t x_colstats_nblk,
+                                  float* y_colstats, int32_t* y_colstats_nblk, void* stream) {
+  STGCN_TRY(validate(d));
+  STGCN_TRY(check_ptrs(x, P, y));
+  if (!workspace) { set_error("null workspace"); return STGCN_ERR_WORKSPACE; }
+  if (d->residual == STGCN_RES_CONV && (!P->Wr || !P->Wr_bias)) { set_error("conv residual needs Wr / Wr_bias"); return STGCN_ERR_INVALID; }
+  if (y_colstats && !y_colstats_nblk) { set_error("y_colstats needs y_colstats_nblk"); return STGCN_ERR_INVALID; }
+  Arena ws(workspace, workspace_bytes);
+  cudaStream_t st = (cudaStream_t)stream;
+  int nb = 0;
+  int32_t rc;
+  if (d->dtype == STGCN_F32)
+    rc = block_forward_t<float>(*d, (const float*)x, *P, (float*)y, saved, ws, st, x_colstats, x_colstats_nblk, y_colstats, &nb);
+  else
+    rc = block_forward_t<bf16>(*d, (const bf16*)x, *P, (bf16*)y, saved, ws, st, x_colstats, x_colstats_nblk, y_colstats, &nb);
+  if (y_colstats_nblk) *y_colstats_nblk = nb;
+  return rc;
 }
 
 size_t stgcn_block_prepared_bytes(const StgcnBlockDesc* d) {

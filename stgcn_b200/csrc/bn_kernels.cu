@@ -307,6 +307,48 @@ __global__ void __launch_bounds__(256) affine_act_fast_kernel(const T* __restric
   }
   if (i < total) { float v0[VEC]; ldv(x + i, v0); apply(v0); stv(y + i, v0); }
 }
+// Same pass, additionally producing the column sums / sums of squares of the STORED output as per-CTA partials
+// [blockIdx][2][C] (the layout bn_finalize reads): the BatchNorm-1 batch statistics of the next block, without its own pass.
+template <class T>
+__global__ void __launch_bounds__(256) affine_act_stats_kernel(const T* __restrict__ x, long long total, int C,
+                                                               const float* __restrict__ a, const float* __restrict__ b,
+                                                               int relu, T* __restrict__ y, float* __restrict__ partials) {
+  constexpr int VEC = VecN<T>::N;
+  extern __shared__ float sm[];                       // [2][rows per sweep][C]
+  long long i = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * VEC;
+  const long long step = (long long)gridDim.x * blockDim.x * VEC;
+  const int c = (int)(i % C);
+  float ca[VEC], cb[VEC], s1[VEC], s2[VEC];
+#pragma unroll
+  for (int j = 0; j < VEC; ++j) { ca[j] = a ? a[c + j] : 1.f; cb[j] = a ? b[c + j] : 0.f; s1[j] = 0.f; s2[j] = 0.f; }
+  auto apply = [&](float (&v)[VEC]) {
+#pragma unroll
+    for (int j = 0; j < VEC; ++j) {
+      float t = fmaf(ca[j], v[j], cb[j]);
+      t = relu ? fmaxf(t, 0.f) : t;
+      t = roundf_as(t, y);                            // statistics of the value as stored
+      v[j] = t; s1[j] += t; s2[j] = fmaf(t, t, s2[j]);
+    }
+  };
+  for (; i + step < total; i += 2 * step) {
+    float v0[VEC], v1[VEC];
+    ldv(x + i, v0); ldv(x + i + step, v1);
+    apply(v0); apply(v1);
+    stv(y + i, v0); stv(y + i + step, v1);
+  }
+  if (i < total) { float v0[VEC]; ldv(x + i, v0); apply(v0); stv(y + i, v0); }
+  const int rps = (256 * VEC) / C, myr = (threadIdx.x * VEC) / C;
+  float* a1 = sm; float* a2 = sm + rps * C;
+#pragma unroll
+  for (int j = 0; j < VEC; ++j) { a1[myr * C + c + j] = s1[j]; a2[myr * C + c + j] = s2[j]; }
+  __syncthreads();
+  for (int cc = threadIdx.x; cc < C; cc += 256) {
+    float t1 = 0.f, t2 = 0.f;
+    for (int rr = 0; rr < rps; ++rr) { t1 += a1[rr * C + cc]; t2 += a2[rr * C + cc]; }
+    partials[((size_t)blockIdx.x * 2 + 0) * C + cc] = t1;
+    partials[((size_t)blockIdx.x * 2 + 1) * C + cc] = t2;
+  }
+}
 template <class T> static bool elementwise_fast_ok(long long total, int C) {
   return (256 * VecN<T>::N) % C == 0 && C % VecN<T>::N == 0 && total % VecN<T>::N == 0;
 }
@@ -316,11 +358,16 @@ static int elementwise_blocks(long long total, int vec) {
 
 template <class T>
 int32_t launch_affine_act(const T* x, long long rows, int C, const float* a, const float* b, int relu, float p,
-                          uint64_t seed, uint64_t offset, T* y, cudaStream_t st) {
+                          uint64_t seed, uint64_t offset, T* y, cudaStream_t st, float* out_partials, int* out_nblk) {
   KernelTimer kt_(KC_ELEMWISE, (double)rows * C, st);
   long long total = rows * C;
   float inv_keep = p > 0.f ? 1.f / (1.f - p) : 1.f;
-  if (p == 0.f && elementwise_fast_ok<T>(total, C)) {
+  if (out_nblk) *out_nblk = 0;
+  if (out_partials && out_nblk && p == 0.f && elementwise_fast_ok<T>(total, C)) {
+    const int nb = std::min(elementwise_blocks(total, VecN<T>::N), kMaxStatBlocks);
+    affine_act_stats_kernel<T><<<nb, 256, 2 * 256 * VecN<T>::N * sizeof(float), st>>>(x, total, C, a, b, relu, y, out_partials);
+    *out_nblk = nb;
+  } else if (p == 0.f && elementwise_fast_ok<T>(total, C)) {
     affine_act_fast_kernel<T><<<elementwise_blocks(total, VecN<T>::N), 256, 0, st>>>(x, total, C, a, b, relu, y);
   } else if (C % 4 == 0) {
     int blocks = (int)std::min<long long>((total / 4 + 255) / 256, 148 * 16);
@@ -332,8 +379,8 @@ int32_t launch_affine_act(const T* x, long long rows, int C, const float* a, con
   STGCN_CHECK_LAUNCH("affine_act");
   return STGCN_OK;
 }
-template int32_t launch_affine_act<float>(const float*, long long, int, const float*, const float*, int, float, uint64_t, uint64_t, float*, cudaStream_t);
-template int32_t launch_affine_act<bf16>(const bf16*, long long, int, const float*, const float*, int, float, uint64_t, uint64_t, bf16*, cudaStream_t);
+template int32_t launch_affine_act<float>(const float*, long long, int, const float*, const float*, int, float, uint64_t, uint64_t, float*, cudaStream_t, float*, int*);
+template int32_t launch_affine_act<bf16>(const bf16*, long long, int, const float*, const float*, int, float, uint64_t, uint64_t, bf16*, cudaStream_t, float*, int*);
 
 // ---------------------------------------------------------------------------
 // backward of  y = drop(relu?(a*z + b))  w.r.t. the BN:

@@ -51,8 +51,10 @@ int32_t launch_bn_finalize(const float* partials, int nblk, int C, double count,
                            float* rm, float* rv, long long* nbt, float eps, float momentum, float* stats, cudaStream_t st);
 int32_t launch_bn_eval_coeffs(int C, const float* gamma, const float* beta, const float* rm, const float* rv, float eps,
                               float* stats, cudaStream_t st, const float* pre_bias = nullptr);
+// out_partials / out_nblk (optional): also produce per-CTA column statistics of the stored output (see affine_act_stats_kernel)
 template <class T> int32_t launch_affine_act(const T* x, long long rows, int C, const float* a, const float* b, int relu, float p,
-                                            uint64_t seed, uint64_t offset, T* y, cudaStream_t st);
+                                            uint64_t seed, uint64_t offset, T* y, cudaStream_t st, float* out_partials = nullptr,
+                                            int* out_nblk = nullptr);
 template <class T> int32_t launch_bn_bwd_reduce(const T* dy, const T* z, const float* stats, long long rows, int C, int relu, float p,
                                                uint64_t seed, uint64_t offset, float* partials, int* nblk, cudaStream_t st);
 int32_t launch_bn_bwd_finalize(const float* partials, int nblk, int C, float* sums, float* dgamma, float* dbeta, cudaStream_t st);

@@ -84,8 +84,16 @@ class _BlockFn(torch.autograd.Function):
             L.check(lib.stgcn_block_forward_prepared(C.byref(d), L.ptr(xp), C.byref(P), L.ptr(blob), L.ptr(y), L.ptr(ws),
                                                      ws.numel(), L.stream_ptr(x.device)), 'block_forward_prepared')
         else:
-            L.check(lib.stgcn_block_forward(C.byref(d), L.ptr(xp), C.byref(P), L.ptr(y), L.ptr(saved), L.ptr(ws),
-                                            ws.numel(), L.stream_ptr(x.device)), 'block_forward')
+            # chained blocks: column statistics of x handed over by the block that produced it, and those of y for the next one
+            xs = cfg.get('x_stats')
+            ys = None
+            if cfg['training'] and cfg['residual'] == L.RES_NONE and cfg['dropout_p'] == 0.0:
+                ys = torch.empty(lib.stgcn_colstats_bytes(cfg['c_out']) // 4, dtype=torch.float32, device=x.device)
+            nb = C.c_int32(0)
+            L.check(lib.stgcn_block_forward_chain(C.byref(d), L.ptr(xp), C.byref(P), L.ptr(y), L.ptr(saved), L.ptr(ws), ws.numel(),
+                                                  L.ptr(xs[0]) if xs else None, xs[1] if xs else 0, L.ptr(ys), C.byref(nb),
+                                                  L.stream_ptr(x.device)), 'block_forward')
+            cfg['y_stats'] = (ys, nb.value) if (ys is not None and nb.value > 0) else None
         if need_grad:
             ctx.d = d
             ctx.buffers = buffers

@@ -91,4 +91,14 @@ class SpatialTemporalConv(nn.Module):
                'flags': self.flags, 'prep_cache': self._prep_cache}
         buffers = (b1.running_mean, b1.running_var, b1.num_batches_tracked,
                    b2.running_mean, b2.running_var, b2.num_batches_tracked)
-        return Fn.block_forward(f_in, cfg, buffers, params)
+        # chained blocks: the block that produced f_in may have left its column statistics on the tensor (valid only for this
+        # very tensor, unmodified since, and only used for training-mode BatchNorm-1)
+        cs = getattr(f_in, '_stgcn_colstats', None)
+        if (cs is not None and self.training and cs[2] == f_in._version and cs[3] == self.compute_dtype
+                and f_in.dtype == self.compute_dtype and cs[4] == self.C_in):
+            cfg['x_stats'] = (cs[0], cs[1])
+        y = Fn.block_forward(f_in, cfg, buffers, params)
+        ys = cfg.get('y_stats')
+        if ys is not None:
+            y._stgcn_colstats = (ys[0], ys[1], y._version, self.compute_dtype, self.C_out)
+        return y

@@ -254,3 +254,35 @@ def test_prepared_inference_tracks_parameter_changes():
     m(x * 3 + 1)                                                   # moves the running statistics through raw pointers
     y2 = both()
     assert rel_err(y2.cpu(), y1.cpu()) > 1e-3
+
+
+@pytest.mark.parametrize('dtype', [torch.float32, torch.bfloat16], ids=['float32', 'bfloat16'])
+def test_chained_column_statistics_match_own_pass(dtype):
+    """Block i hands the column statistics of its output to block i+1 (stgcn_block_forward_chain): same BatchNorm-1 result as
+    block i+1 reducing its input itself, and the hand-over is dropped when the tensor is modified in between."""
+    torch.manual_seed(5)
+    A = torch.rand(3, 25, 25) * 0.2
+    b1 = build_block(64, 64, A, 1, False, dtype=dtype).train()
+    b2 = build_block(64, 128, A, 2, False, dtype=dtype).train()
+    x = torch.randn(4, 64, 20, 25).cuda()
+    sd = {k: v.clone() for k, v in b2.state_dict().items()}
+
+    def run(chain, touch=False):
+        b2.load_state_dict(sd)
+        y1 = b1(x)
+        assert hasattr(y1, '_stgcn_colstats')
+        if touch:
+            y1.mul_(1.0)                                   # bumps the version counter: the statistics must be ignored
+        if not chain:
+            del y1._stgcn_colstats
+        y2 = b2(y1)
+        return y2.float().detach().cpu(), b2.batch_n.running_mean.clone().cpu(), b2.batch_n.running_var.clone().cpu()
+
+    with torch.no_grad():
+        ya, ma, va = run(True)
+        yb, mb, vb = run(False)
+        yc, mc, vc = run(True, touch=True)
+    tol = 1e-5 if dtype == torch.float32 else 8e-3
+    assert rel_err(ya, yb) < tol
+    assert rel_err(ma, mb) < 1e-5 and rel_err(va, vb) < 1e-5
+    assert rel_err(yc, yb) < tol and rel_err(mc, mb) < 1e-5
