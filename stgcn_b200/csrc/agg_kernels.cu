@@ -21,6 +21,7 @@ __global__ void __launch_bounds__(kAggThreads) agg_fwd_kernel(const T* __restric
                                                               const float* __restrict__ A, const float* __restrict__ aff_a,
                                                               const float* __restrict__ aff_b, int relu, int FB,
                                                               T* __restrict__ xa) {
+  pdl_enter();
   extern __shared__ float sm[];
   float* As = sm;                         // [K][V][kVP]
   float* hs = sm + K * V * kVP;           // [FB][V][C]
@@ -83,7 +84,7 @@ int32_t launch_agg_fwd(const T* x, long long frames, int V, int C, int K, const 
   bool& attr = std::is_same<T, float>::value ? attr_f : attr_b;
   if (!attr) { cudaFuncSetAttribute(agg_fwd_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024); attr = true; }
   int blocks = (int)std::min<long long>((frames + FB - 1) / FB, 148 * 4);
-  agg_fwd_kernel<T><<<blocks, kAggThreads, smem, st>>>(x, frames, V, C, K, A, a, b, relu, FB, xa);
+  launch_k(agg_fwd_kernel<T>, blocks, kAggThreads, smem, st, x, frames, V, C, K, A, a, b, relu, FB, xa);
   STGCN_CHECK_LAUNCH("agg_fwd");
   return STGCN_OK;
 }
@@ -99,6 +100,7 @@ __global__ void __launch_bounds__(kAggThreads) agg_bwd_kernel(const T* __restric
                                                               const float* __restrict__ A, const T* __restrict__ x,
                                                               const float* __restrict__ aff_a, const float* __restrict__ aff_b,
                                                               int relu, T* __restrict__ dh) {
+  pdl_enter();
   extern __shared__ float sm[];
   float* At = sm;                         // [K][W=V][kVP over v]  (transposed)
   for (int i = threadIdx.x; i < K * V * kVP; i += blockDim.x) {
@@ -155,7 +157,7 @@ int32_t launch_agg_bwd(const T* dxa, long long frames, int V, int C, int K, cons
   if (V > kVP || K > 4) { set_error("agg_bwd: V=%d K=%d unsupported", V, K); return STGCN_ERR_UNSUPPORTED; }
   size_t smem = (size_t)K * V * kVP * sizeof(float);
   int blocks = (int)std::min<long long>((frames * C + kAggThreads - 1) / kAggThreads, 148 * 8);
-  agg_bwd_kernel<T><<<blocks, kAggThreads, smem, st>>>(dxa, frames, V, C, K, A, x, a, b, relu, dh);
+  launch_k(agg_bwd_kernel<T>, blocks, kAggThreads, smem, st, dxa, frames, V, C, K, A, x, a, b, relu, dh);
   STGCN_CHECK_LAUNCH("agg_bwd");
   return STGCN_OK;
 }
@@ -176,6 +178,7 @@ __global__ void __launch_bounds__(kAggThreads) agg_dA_kernel(const T* __restrict
                                                              int V, int C, int K, const float* __restrict__ aff_a,
                                                              const float* __restrict__ aff_b, int relu, int CC, int KC,
                                                              float* __restrict__ dA) {
+  pdl_enter();
   extern __shared__ float sm[];
   const int KV = K * V;
   float* hs = sm;                          // [V][CC+1]
@@ -229,6 +232,7 @@ constexpr int kDaFrames = 8;
 template <class T>
 __global__ void __launch_bounds__(kAggThreads) agg_dA_small_kernel(const T* __restrict__ dxa, const T* __restrict__ x, long long frames,
                                                                    int V, int C, int K, int KC, float* __restrict__ dA) {
+  pdl_enter();
   extern __shared__ float4 sm4[];
   const int KV = K * V;
   float4* hs = sm4;                          // [frames][V]
@@ -285,7 +289,7 @@ int32_t launch_agg_dA(const T* dxa, const T* x, long long frames, int V, int C, 
   if (C <= 4 && !a && !relu) {
     const long long batches = (frames + kDaFrames - 1) / kDaFrames;
     const int nblk = (int)std::min<long long>(batches, 148 * 4);
-    agg_dA_small_kernel<T><<<nblk, kAggThreads, (size_t)kDaFrames * (V + K * V) * sizeof(float4), st>>>(dxa, x, frames, V, C, K,
+    launch_k(agg_dA_small_kernel<T>, nblk, kAggThreads, (size_t)kDaFrames * (V + K * V) * sizeof(float4), st, dxa, x, frames, V, C, K,
                                                                                                        ld > 0 ? ld : K * C, dA);
     STGCN_CHECK_LAUNCH("agg_dA_small");
     return STGCN_OK;
@@ -293,7 +297,7 @@ int32_t launch_agg_dA(const T* dxa, const T* x, long long frames, int V, int C, 
   int CC = std::min(C, 64);
   size_t smem = (size_t)(V + K * V) * (CC + 1) * sizeof(float);
   int blocks = (int)std::min<long long>(frames, 148 * 4);
-  agg_dA_kernel<T><<<blocks, kAggThreads, smem, st>>>(dxa, x, frames, V, C, K, a, b, relu, CC, ld > 0 ? ld : K * C, dA);
+  launch_k(agg_dA_kernel<T>, blocks, kAggThreads, smem, st, dxa, x, frames, V, C, K, a, b, relu, CC, ld > 0 ? ld : K * C, dA);
   STGCN_CHECK_LAUNCH("agg_dA");
   return STGCN_OK;
 }
@@ -306,6 +310,7 @@ template int32_t launch_agg_dA<bf16>(const bf16*, const bf16*, long long, int, i
 // ---------------------------------------------------------------------------
 template <class T>
 __global__ void __launch_bounds__(256) vcolsum_kernel(const T* __restrict__ ds, long long frames, int VC, float* __restrict__ t1) {
+  pdl_enter();
   int e = blockIdx.y * 256 + threadIdx.x;
   if (e >= VC) return;
   float s = 0.f;
@@ -316,6 +321,7 @@ __global__ void __launch_bounds__(256) vcolsum_kernel(const T* __restrict__ ds, 
 // in flight
 template <class T>
 __global__ void __launch_bounds__(256) vcolsum_vec_kernel(const T* __restrict__ ds, long long frames, int VC, float* __restrict__ t1) {
+  pdl_enter();
   constexpr int VEC = VecN<T>::N;
   const int e = (blockIdx.y * 256 + threadIdx.x) * VEC;
   if (e >= VC) return;
@@ -351,10 +357,10 @@ int32_t launch_vcolsum(const T* ds, long long frames, int V, int C, float* t1, c
     const int by = cdiv(VC / VEC, 256);
     // few, long-running CTAs: the final atomics contend bx-way per address
     const int bx = (int)std::max<long long>(1, std::min<long long>(frames / 16, (148 * 2 + by - 1) / by));
-    vcolsum_vec_kernel<T><<<dim3((unsigned)bx, (unsigned)by), 256, 0, st>>>(ds, frames, VC, t1);
+    launch_k(vcolsum_vec_kernel<T>, dim3((unsigned)bx, (unsigned)by), 256, 0, st, ds, frames, VC, t1);
   } else {
     dim3 grid((unsigned)std::min<long long>(frames, 64), (unsigned)cdiv(VC, 256));
-    vcolsum_kernel<T><<<grid, 256, 0, st>>>(ds, frames, VC, t1);
+    launch_k(vcolsum_kernel<T>, grid, 256, 0, st, ds, frames, VC, t1);
   }
   STGCN_CHECK_LAUNCH("vcolsum");
   return STGCN_OK;
@@ -375,6 +381,7 @@ __device__ __forceinline__ void adjacency_rowsums(const float* __restrict__ A, i
 // bias2d[v][co] = sum_k rowsum_k[v] * bias[k*Co+co]   (bias of W passes through A, st_graphconv.py:148-150)
 __global__ void __launch_bounds__(256) bias2d_kernel(const float* __restrict__ A, const float* __restrict__ bias, int K, int V, int Co,
                                                      float* __restrict__ out) {
+  pdl_enter();
   __shared__ float rs[128];
   adjacency_rowsums(A, K, V, rs);
   int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -385,7 +392,7 @@ __global__ void __launch_bounds__(256) bias2d_kernel(const float* __restrict__ A
   out[i] = s;
 }
 int32_t launch_bias2d(const float* A, const float* bias, int K, int V, int Co, float* out, cudaStream_t st) {
-  bias2d_kernel<<<cdiv(V * Co, 256), 256, 0, st>>>(A, bias, K, V, Co, out);
+  launch_k(bias2d_kernel, cdiv(V * Co, 256), 256, 0, st, A, bias, K, V, Co, out);
   STGCN_CHECK_LAUNCH("bias2d");
   return STGCN_OK;
 }
@@ -396,6 +403,7 @@ __global__ void __launch_bounds__(256) spatial_bias_grads_kernel(const float* __
                                                                  const float* __restrict__ bias, const float* __restrict__ bias_dA,
                                                                  int K, int V, int Co, int nb_bias,
                                                                  float* __restrict__ dbias, float* __restrict__ dA) {
+  pdl_enter();
   __shared__ float rs[128];
   __shared__ float wsum[8];
   if ((int)blockIdx.x < nb_bias) {
@@ -426,7 +434,7 @@ __global__ void __launch_bounds__(256) spatial_bias_grads_kernel(const float* __
 int32_t launch_spatial_bias_grads(const float* t1, const float* A, const float* bias, int K, int V, int Co, float* dbias,
                                   float* dA, cudaStream_t st, const float* bias_dA) {
   const int nb_bias = cdiv(K * Co, 256);
-  spatial_bias_grads_kernel<<<nb_bias + K * V, 256, 0, st>>>(t1, A, bias, bias_dA, K, V, Co, nb_bias, dbias, dA);
+  launch_k(spatial_bias_grads_kernel, nb_bias + K * V, 256, 0, st, t1, A, bias, bias_dA, K, V, Co, nb_bias, dbias, dA);
   STGCN_CHECK_LAUNCH("spatial_bias_grads");
   return STGCN_OK;
 }
@@ -444,6 +452,7 @@ int32_t launch_spatial_bias_grads(const float* t1, const float* A, const float* 
 __global__ void __launch_bounds__(128) bn1_fold_weights_kernel(const float* __restrict__ W, const float* __restrict__ a,
                                                                const float* __restrict__ b, int K, int Co, int Ci, int ld,
                                                                bf16* __restrict__ w2p, bf16* __restrict__ w2pT, float* __restrict__ wb) {
+  pdl_enter();
   __shared__ float red[4];
   const int r = blockIdx.x, k = r / Co, co = r % Co;
   float part = 0.f;
@@ -463,6 +472,7 @@ __global__ void __launch_bounds__(256) bias2d_fold_kernel(const float* __restric
                                                           const float* __restrict__ Wb, const float* __restrict__ wb, int K, int V, int Co,
                                                           float* __restrict__ out, float* __restrict__ wbb,
                                                           float* __restrict__ rsum2, float* __restrict__ bvec2) {
+  pdl_enter();
   __shared__ float rs[128];
   adjacency_rowsums(A, K, V, rs);
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -486,9 +496,9 @@ int32_t launch_bn1_fold(const float* W, const float* Wb, const float* A, const f
     cudaMemsetAsync(w2p, 0, sizeof(bf16) * (size_t)Co * ld, st);
     cudaMemsetAsync(w2pT, 0, sizeof(bf16) * (size_t)Co * ld, st);
   }
-  bn1_fold_weights_kernel<<<K * Co, 128, 0, st>>>(W, a, b, K, Co, Ci, ld, w2p, w2pT, wb);
+  launch_k(bn1_fold_weights_kernel, K * Co, 128, 0, st, W, a, b, K, Co, Ci, ld, w2p, w2pT, wb);
   STGCN_CHECK_LAUNCH("bn1_fold_weights");
-  bias2d_fold_kernel<<<cdiv(std::max(V, K) * Co, 256), 256, 0, st>>>(A, rowsum_q, Wb, wb, K, V, Co, bias2d, wbb, rsum2, bvec2);
+  launch_k(bias2d_fold_kernel, cdiv(std::max(V, K) * Co, 256), 256, 0, st, A, rowsum_q, Wb, wb, K, V, Co, bias2d, wbb, rsum2, bvec2);
   STGCN_CHECK_LAUNCH("bias2d_fold");
   return STGCN_OK;
 }
@@ -501,6 +511,7 @@ int32_t launch_bn1_fold(const float* W, const float* Wb, const float* A, const f
 template <class T>
 __global__ void __launch_bounds__(256) agg_small_fwd_kernel(const T* __restrict__ x, long long frames, int V, int C, int K, int ld,
                                                             const float* __restrict__ A, int FB, T* __restrict__ xa) {
+  pdl_enter();
   extern __shared__ float sm[];
   float* As = sm;                   // [K][V][V]
   float* xs = sm + K * V * V;       // [FB][V][C]
@@ -541,7 +552,7 @@ int32_t launch_agg_small_fwd(const T* x, long long frames, int V, int C, int K, 
   const int FB = std::max(1, 256 / V);
   const size_t smem = ((size_t)K * V * V + (size_t)FB * V * C) * sizeof(float);
   const int blocks = (int)std::min<long long>((frames + FB - 1) / FB, 148 * 8);
-  agg_small_fwd_kernel<T><<<blocks, 256, smem, st>>>(x, frames, V, C, K, ld, A, FB, xa);
+  launch_k(agg_small_fwd_kernel<T>, blocks, 256, smem, st, x, frames, V, C, K, ld, A, FB, xa);
   STGCN_CHECK_LAUNCH("agg_small_fwd");
   return STGCN_OK;
 }
@@ -549,6 +560,7 @@ template int32_t launch_agg_small_fwd<float>(const float*, long long, int, int, 
 template int32_t launch_agg_small_fwd<bf16>(const bf16*, long long, int, int, int, int, const float*, bf16*, cudaStream_t);
 
 __global__ void adjacency_rowsum_kernel(const float* __restrict__ A, int KV, int V, float* __restrict__ rs) {
+  pdl_enter();
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= KV) return;
   float s = 0.f;
@@ -556,7 +568,7 @@ __global__ void adjacency_rowsum_kernel(const float* __restrict__ A, int KV, int
   rs[i] = s;
 }
 int32_t launch_adjacency_rowsum(const float* A, int K, int V, float* rs, cudaStream_t st) {
-  adjacency_rowsum_kernel<<<cdiv(K * V, 128), 128, 0, st>>>(A, K * V, V, rs);
+  launch_k(adjacency_rowsum_kernel, cdiv(K * V, 128), 128, 0, st, A, K * V, V, rs);
   STGCN_CHECK_LAUNCH("adjacency_rowsum");
   return STGCN_OK;
 }
@@ -573,6 +585,7 @@ __global__ void __launch_bounds__(1024) bn1_fold_grads_kernel(const float* __res
                                                               const float* __restrict__ rowsum_q, int K, int V, int Co, int Ci,
                                                               int training, float inv_m, float* __restrict__ dgamma,
                                                               float* __restrict__ dbeta, float* __restrict__ coef) {
+  pdl_enter();
   __shared__ float q[1024];
   __shared__ float red[2][128][9];
   const int KCo = K * Co;
@@ -618,7 +631,7 @@ int32_t launch_bn1_fold_grads(const float* W, float* dW, const float* stats, con
                               int Co, int Ci, int training, double rows, float* dgamma, float* dbeta, float* coef, cudaStream_t st) {
   KernelTimer kt_(KC_PACK, 0.0, st);
   if (K * Co > 1024) { set_error("bn1_fold_grads: K*C_out=%d > 1024", K * Co); return STGCN_ERR_UNSUPPORTED; }
-  bn1_fold_grads_kernel<<<cdiv(Ci, 8), 1024, 0, st>>>(W, dW, stats, t1, rowsum_q, K, V, Co, Ci, training, (float)(1.0 / rows), dgamma,
+  launch_k(bn1_fold_grads_kernel, cdiv(Ci, 8), 1024, 0, st, W, dW, stats, t1, rowsum_q, K, V, Co, Ci, training, (float)(1.0 / rows), dgamma,
                                                        dbeta, coef);
   STGCN_CHECK_LAUNCH("bn1_fold_grads");
   return STGCN_OK;

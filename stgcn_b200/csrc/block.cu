@@ -11,6 +11,7 @@
 namespace stgcn {
 
 std::atomic<uint64_t> g_launches{0};
+bool pdl_enabled() { static const bool on = getenv("STGCN_NO_PDL") == nullptr; return on; }
 static thread_local char g_err[512] = "";
 void set_error(const char* fmt, ...) {
   va_list ap; va_start(ap, fmt); vsnprintf(g_err, sizeof(g_err), fmt, ap); va_end(ap);

@@ -19,6 +19,7 @@ constexpr int kMaxStatBlocks = 148 * 4;
 // ---------------------------------------------------------------------------
 template <int VEC, class F>
 __global__ void __launch_bounds__(kStatThreads) colreduce_kernel(long long rows, int C, F f, float* __restrict__ partials) {
+  pdl_enter();
   extern __shared__ float sm[];               // [2][rows_per_step][C] folded below
   const int cv = C / VEC;                     // vectors per row
   const int rps = kStatThreads / cv;          // rows per step (>=1, host guarantees cv <= 256)
@@ -83,6 +84,7 @@ template <class T, int MODE>
 __global__ void __launch_bounds__(kStatThreads) colreduce_fast_kernel(const T* __restrict__ x, const T* __restrict__ z,
                                                                       const float* __restrict__ stats, int relu, long long rows,
                                                                       int C, float* __restrict__ partials) {
+  pdl_enter();
   constexpr int VEC = VecN<T>::N;
   extern __shared__ float sm[];
   const int cv = C / VEC, rps = kStatThreads / cv, tid = threadIdx.x;
@@ -147,7 +149,7 @@ static void launch_colreduce_fast(const T* x, const T* z, const float* stats, in
   long long b = (rows + rps - 1) / rps; b = (b + 7) / 8;
   if (b < 1) b = 1; if (b > kMaxStatBlocks) b = kMaxStatBlocks;
   *nblk = (int)b;
-  colreduce_fast_kernel<T, MODE><<<(int)b, kStatThreads, 2 * rps * C * sizeof(float), st>>>(x, z, stats, relu, rows, C, partials);
+  launch_k(colreduce_fast_kernel<T, MODE>, (int)b, kStatThreads, 2 * rps * C * sizeof(float), st, x, z, stats, relu, rows, C, partials);
 }
 
 size_t stat_partials_bytes(int C) { return (size_t)kMaxStatBlocks * 2 * C * sizeof(float); }
@@ -161,12 +163,12 @@ int32_t launch_colstats(const T* x, long long rows, int C, float* partials, int*
   } else if (C % 4 == 0) {
     int nb = stat_blocks(rows, C, 4); *nblk = nb;
     int rps = kStatThreads / (C / 4);
-    colreduce_kernel<4><<<nb, kStatThreads, 2 * rps * C * sizeof(float), st>>>(rows, C, FwdStatF<T, 4>{x, C}, partials);
+    launch_k(colreduce_kernel<4, FwdStatF<T, 4>>, nb, kStatThreads, 2 * rps * C * sizeof(float), st, rows, C, FwdStatF<T, 4>{x, C}, partials);
   } else {
     if (C > 256) { set_error("colstats: C=%d not a multiple of 4 and > 256", C); return STGCN_ERR_UNSUPPORTED; }
     int nb = stat_blocks(rows, C, 1); *nblk = nb;
     int rps = kStatThreads / C;
-    colreduce_kernel<1><<<nb, kStatThreads, 2 * rps * C * sizeof(float), st>>>(rows, C, FwdStatF<T, 1>{x, C}, partials);
+    launch_k(colreduce_kernel<1, FwdStatF<T, 1>>, nb, kStatThreads, 2 * rps * C * sizeof(float), st, rows, C, FwdStatF<T, 1>{x, C}, partials);
   }
   STGCN_CHECK_LAUNCH("colstats");
   return STGCN_OK;
@@ -209,6 +211,7 @@ bn_finalize_kernel(const float* __restrict__ partials, int nblk, int C, double c
                    const float* __restrict__ gamma, const float* __restrict__ beta,
                    float* running_mean, float* running_var, long long* nbt,
                    float eps, float momentum, float* __restrict__ stats) {
+  pdl_enter();
   if (blockIdx.x == 0 && threadIdx.x == 0 && nbt) *nbt += 1;
   double s1, s2;
   if (!reduce_partials_32x32(partials, nblk, C, s1, s2)) return;
@@ -232,6 +235,7 @@ bn_finalize_kernel(const float* __restrict__ partials, int nblk, int C, double c
 __global__ void bn_eval_coeffs_kernel(int C, const float* __restrict__ gamma, const float* __restrict__ beta,
                                       const float* __restrict__ rm, const float* __restrict__ rv, float eps,
                                       float* __restrict__ stats, const float* __restrict__ pre_bias) {
+  pdl_enter();
   int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= C) return;
   float invstd = rsqrtf(rv[c] + eps);
@@ -246,13 +250,13 @@ __global__ void bn_eval_coeffs_kernel(int C, const float* __restrict__ gamma, co
 int32_t launch_bn_finalize(const float* partials, int nblk, int C, double count, const float* gamma,
                            const float* beta, float* rm, float* rv, long long* nbt, float eps, float momentum,
                            float* stats, cudaStream_t st) {
-  bn_finalize_kernel<<<cdiv(C, 32), kFinThreads, 0, st>>>(partials, nblk, C, count, gamma, beta, rm, rv, nbt, eps, momentum, stats);
+  launch_k(bn_finalize_kernel, cdiv(C, 32), kFinThreads, 0, st, partials, nblk, C, count, gamma, beta, rm, rv, nbt, eps, momentum, stats);
   STGCN_CHECK_LAUNCH("bn_finalize");
   return STGCN_OK;
 }
 int32_t launch_bn_eval_coeffs(int C, const float* gamma, const float* beta, const float* rm, const float* rv,
                               float eps, float* stats, cudaStream_t st, const float* pre_bias) {
-  bn_eval_coeffs_kernel<<<cdiv(C, 128), 128, 0, st>>>(C, gamma, beta, rm, rv, eps, stats, pre_bias);
+  launch_k(bn_eval_coeffs_kernel, cdiv(C, 128), 128, 0, st, C, gamma, beta, rm, rv, eps, stats, pre_bias);
   STGCN_CHECK_LAUNCH("bn_eval_coeffs");
   return STGCN_OK;
 }
@@ -265,6 +269,7 @@ __global__ void __launch_bounds__(256) affine_act_kernel(const T* __restrict__ x
                                                          const float* __restrict__ a, const float* __restrict__ b,
                                                          int relu, float p, float inv_keep, uint64_t seed,
                                                          uint64_t offset, T* __restrict__ y) {
+  pdl_enter();
   long long i = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * VEC;
   const long long step = (long long)gridDim.x * blockDim.x * VEC;
   for (; i < total; i += step) {
@@ -288,6 +293,7 @@ template <class T>
 __global__ void __launch_bounds__(256) affine_act_fast_kernel(const T* __restrict__ x, long long total, int C,
                                                               const float* __restrict__ a, const float* __restrict__ b,
                                                               int relu, T* __restrict__ y) {
+  pdl_enter();
   constexpr int VEC = VecN<T>::N;
   long long i = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * VEC;
   const long long step = (long long)gridDim.x * blockDim.x * VEC;
@@ -313,6 +319,7 @@ template <class T>
 __global__ void __launch_bounds__(256) affine_act_stats_kernel(const T* __restrict__ x, long long total, int C,
                                                                const float* __restrict__ a, const float* __restrict__ b,
                                                                int relu, T* __restrict__ y, float* __restrict__ partials) {
+  pdl_enter();
   constexpr int VEC = VecN<T>::N;
   extern __shared__ float sm[];                       // [2][rows per sweep][C]
   long long i = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * VEC;
@@ -365,16 +372,16 @@ int32_t launch_affine_act(const T* x, long long rows, int C, const float* a, con
   if (out_nblk) *out_nblk = 0;
   if (out_partials && out_nblk && p == 0.f && elementwise_fast_ok<T>(total, C)) {
     const int nb = std::min(elementwise_blocks(total, VecN<T>::N), kMaxStatBlocks);
-    affine_act_stats_kernel<T><<<nb, 256, 2 * 256 * VecN<T>::N * sizeof(float), st>>>(x, total, C, a, b, relu, y, out_partials);
+    launch_k(affine_act_stats_kernel<T>, nb, 256, 2 * 256 * VecN<T>::N * sizeof(float), st, x, total, C, a, b, relu, y, out_partials);
     *out_nblk = nb;
   } else if (p == 0.f && elementwise_fast_ok<T>(total, C)) {
-    affine_act_fast_kernel<T><<<elementwise_blocks(total, VecN<T>::N), 256, 0, st>>>(x, total, C, a, b, relu, y);
+    launch_k(affine_act_fast_kernel<T>, elementwise_blocks(total, VecN<T>::N), 256, 0, st, x, total, C, a, b, relu, y);
   } else if (C % 4 == 0) {
     int blocks = (int)std::min<long long>((total / 4 + 255) / 256, 148 * 16);
-    affine_act_kernel<T, 4><<<blocks, 256, 0, st>>>(x, total, C, a, b, relu, p, inv_keep, seed, offset, y);
+    launch_k(affine_act_kernel<T, 4>, blocks, 256, 0, st, x, total, C, a, b, relu, p, inv_keep, seed, offset, y);
   } else {
     int blocks = (int)std::min<long long>((total + 255) / 256, 148 * 16);
-    affine_act_kernel<T, 1><<<blocks, 256, 0, st>>>(x, total, C, a, b, relu, p, inv_keep, seed, offset, y);
+    launch_k(affine_act_kernel<T, 1>, blocks, 256, 0, st, x, total, C, a, b, relu, p, inv_keep, seed, offset, y);
   }
   STGCN_CHECK_LAUNCH("affine_act");
   return STGCN_OK;
@@ -415,12 +422,12 @@ int32_t launch_bn_bwd_reduce(const T* dy, const T* z, const float* stats, long l
   } else if (C % 4 == 0) {
     int nb = stat_blocks(rows, C, 4); *nblk = nb;
     int rps = kStatThreads / (C / 4);
-    colreduce_kernel<4><<<nb, kStatThreads, 2 * rps * C * sizeof(float), st>>>(
+    launch_k(colreduce_kernel<4, BwdRedF<T, 4>>, nb, kStatThreads, 2 * rps * C * sizeof(float), st,
         rows, C, BwdRedF<T, 4>{dy, z, stats, C, relu, p, inv_keep, seed, offset}, partials);
   } else {
     int nb = stat_blocks(rows, C, 1); *nblk = nb;
     int rps = kStatThreads / C;
-    colreduce_kernel<1><<<nb, kStatThreads, 2 * rps * C * sizeof(float), st>>>(
+    launch_k(colreduce_kernel<1, BwdRedF<T, 1>>, nb, kStatThreads, 2 * rps * C * sizeof(float), st,
         rows, C, BwdRedF<T, 1>{dy, z, stats, C, relu, p, inv_keep, seed, offset}, partials);
   }
   STGCN_CHECK_LAUNCH("bn_bwd_reduce");
@@ -433,6 +440,7 @@ template int32_t launch_bn_bwd_reduce<bf16>(const bf16*, const bf16*, const floa
 __global__ void __launch_bounds__(kFinThreads)
 bn_bwd_finalize_kernel(const float* __restrict__ partials, int nblk, int C, float* __restrict__ sums,
                        float* __restrict__ dgamma, float* __restrict__ dbeta) {
+  pdl_enter();
   double s1, s2;
   if (!reduce_partials_32x32(partials, nblk, C, s1, s2)) return;
   const int c = blockIdx.x * 32 + (threadIdx.x & 31);
@@ -441,7 +449,7 @@ bn_bwd_finalize_kernel(const float* __restrict__ partials, int nblk, int C, floa
   if (dbeta) dbeta[c] = (float)s1;
 }
 int32_t launch_bn_bwd_finalize(const float* partials, int nblk, int C, float* sums, float* dgamma, float* dbeta, cudaStream_t st) {
-  bn_bwd_finalize_kernel<<<cdiv(C, 32), kFinThreads, 0, st>>>(partials, nblk, C, sums, dgamma, dbeta);
+  launch_k(bn_bwd_finalize_kernel, cdiv(C, 32), kFinThreads, 0, st, partials, nblk, C, sums, dgamma, dbeta);
   STGCN_CHECK_LAUNCH("bn_bwd_finalize");
   return STGCN_OK;
 }
@@ -452,6 +460,7 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const T* __restrict__
                                                            long long total, int C, int relu, int training, float inv_m,
                                                            float p, float inv_keep, uint64_t seed, uint64_t offset,
                                                            T* __restrict__ dz) {
+  pdl_enter();
   long long i = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * VEC;
   const long long step = (long long)gridDim.x * blockDim.x * VEC;
   for (; i < total; i += step) {
@@ -476,6 +485,7 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_fast_kernel(const T* __restr
                                                                 const float* __restrict__ stats, const float* __restrict__ sums,
                                                                 long long total, int C, int relu, int training, float inv_m,
                                                                 T* __restrict__ dz) {
+  pdl_enter();
   constexpr int VEC = VecN<T>::N;
   long long i = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * VEC;
   const long long step = (long long)gridDim.x * blockDim.x * VEC;
@@ -513,14 +523,14 @@ int32_t launch_bn_bwd_apply(const T* dy, const T* z, const float* stats, const f
   float inv_keep = p > 0.f ? 1.f / (1.f - p) : 1.f;
   float inv_m = 1.0f / (float)rows;
   if (p == 0.f && elementwise_fast_ok<T>(total, C)) {
-    bn_bwd_apply_fast_kernel<T><<<elementwise_blocks(total, VecN<T>::N), 256, 0, st>>>(dy, z, stats, sums, total, C, relu, training,
+    launch_k(bn_bwd_apply_fast_kernel<T>, elementwise_blocks(total, VecN<T>::N), 256, 0, st, dy, z, stats, sums, total, C, relu, training,
                                                                                          inv_m, dz);
   } else if (C % 4 == 0) {
     int blocks = (int)std::min<long long>((total / 4 + 255) / 256, 148 * 16);
-    bn_bwd_apply_kernel<T, 4><<<blocks, 256, 0, st>>>(dy, z, stats, sums, total, C, relu, training, inv_m, p, inv_keep, seed, offset, dz);
+    launch_k(bn_bwd_apply_kernel<T, 4>, blocks, 256, 0, st, dy, z, stats, sums, total, C, relu, training, inv_m, p, inv_keep, seed, offset, dz);
   } else {
     int blocks = (int)std::min<long long>((total + 255) / 256, 148 * 16);
-    bn_bwd_apply_kernel<T, 1><<<blocks, 256, 0, st>>>(dy, z, stats, sums, total, C, relu, training, inv_m, p, inv_keep, seed, offset, dz);
+    launch_k(bn_bwd_apply_kernel<T, 1>, blocks, 256, 0, st, dy, z, stats, sums, total, C, relu, training, inv_m, p, inv_keep, seed, offset, dz);
   }
   STGCN_CHECK_LAUNCH("bn_bwd_apply");
   return STGCN_OK;
@@ -536,6 +546,7 @@ template int32_t launch_bn_bwd_apply<bf16>(const bf16*, const bf16*, const float
 template <class T, int VEC>
 __global__ void __launch_bounds__(256) relu_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ out, long long total,
                                                        float inv_keep, T* __restrict__ dz) {
+  pdl_enter();
   long long i = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * VEC;
   const long long step = (long long)gridDim.x * blockDim.x * VEC;
   for (; i < total; i += step) {
@@ -552,10 +563,10 @@ int32_t launch_relu_bwd(const T* dy, const T* out, long long total, float p, T* 
   float inv_keep = p > 0.f ? 1.f / (1.f - p) : 1.f;
   if (total % 4 == 0) {
     int blocks = (int)std::min<long long>((total / 4 + 255) / 256, 148 * 16);
-    relu_bwd_kernel<T, 4><<<blocks, 256, 0, st>>>(dy, out, total, inv_keep, dz);
+    launch_k(relu_bwd_kernel<T, 4>, blocks, 256, 0, st, dy, out, total, inv_keep, dz);
   } else {
     int blocks = (int)std::min<long long>((total + 255) / 256, 148 * 16);
-    relu_bwd_kernel<T, 1><<<blocks, 256, 0, st>>>(dy, out, total, inv_keep, dz);
+    launch_k(relu_bwd_kernel<T, 1>, blocks, 256, 0, st, dy, out, total, inv_keep, dz);
   }
   STGCN_CHECK_LAUNCH("relu_bwd");
   return STGCN_OK;
@@ -566,6 +577,7 @@ template int32_t launch_relu_bwd<bf16>(const bf16*, const bf16*, long long, floa
 // dst = a + b (residual identity gradient merge), and cast
 template <class TS, class TD>
 __global__ void __launch_bounds__(256) cast_kernel(const TS* __restrict__ s, TD* __restrict__ d, size_t n) {
+  pdl_enter();
   size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   for (; i < n; i += (size_t)gridDim.x * blockDim.x) stf(d + i, ldf(s + i));
 }
@@ -573,7 +585,7 @@ template <class TS, class TD>
 int32_t launch_cast(const TS* s, TD* d, size_t n, cudaStream_t st) {
   int blocks = (int)std::min<size_t>((n + 255) / 256, 148 * 16);
   if (blocks < 1) blocks = 1;
-  cast_kernel<TS, TD><<<blocks, 256, 0, st>>>(s, d, n);
+  launch_k(cast_kernel<TS, TD>, blocks, 256, 0, st, s, d, n);
   STGCN_CHECK_LAUNCH("cast");
   return STGCN_OK;
 }
@@ -584,6 +596,7 @@ template int32_t launch_cast<bf16, bf16>(const bf16*, bf16*, size_t, cudaStream_
 
 template <class T>
 __global__ void __launch_bounds__(256) add_inplace_kernel(T* __restrict__ d, const T* __restrict__ s, size_t n) {
+  pdl_enter();
   size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   for (; i < n; i += (size_t)gridDim.x * blockDim.x) stf(d + i, ldf(d + i) + ldf(s + i));
 }
@@ -592,7 +605,7 @@ int32_t launch_add_inplace(T* d, const T* s, size_t n, cudaStream_t st) {
   KernelTimer kt_(KC_ELEMWISE, (double)n, st);
   int blocks = (int)std::min<size_t>((n + 255) / 256, 148 * 16);
   if (blocks < 1) blocks = 1;
-  add_inplace_kernel<T><<<blocks, 256, 0, st>>>(d, s, n);
+  launch_k(add_inplace_kernel<T>, blocks, 256, 0, st, d, s, n);
   STGCN_CHECK_LAUNCH("add_inplace");
   return STGCN_OK;
 }

@@ -34,6 +34,28 @@ inline void count_launch(int n = 1) { g_launches.fetch_add((uint64_t)n, std::mem
     if (rc__ != STGCN_OK) return rc__; \
   } while (0)
 
+// ---- programmatic dependent launch ------------------------------------------------------------------------------
+// Every kernel of the library is launched with cudaLaunchAttributeProgrammaticStreamSerialization (launch_k) and starts with
+// pdl_trigger() -- "my dependents may be scheduled as soon as all my CTAs are running" -- followed, before its first global
+// memory access, by pdl_wait(), which returns once the preceding grid in the stream has completed and flushed.  A kernel's
+// launch latency, CTA ramp and on-chip prologue (barrier init, TMEM allocation, descriptor prefetch) then overlap the tail
+// of its predecessor.  Since every kernel waits before touching memory, completion order stays transitive along the stream.
+// STGCN_NO_PDL=1 launches without the attribute (both instructions are then no-ops).
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_enter() { pdl_trigger(); pdl_wait(); }
+bool pdl_enabled();
+template <class... KArgs, class... Args>
+inline void launch_k(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr; cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);       // errors surface through STGCN_CHECK_LAUNCH (cudaGetLastError)
+}
+
 // ---- element access ---------------------------------------------------------
 __device__ __forceinline__ float ldf(const float* p) { return *p; }
 __device__ __forceinline__ float ldf(const bf16* p) { return __bfloat162float(*p); }

@@ -26,6 +26,7 @@ __device__ __forceinline__ void load_row_vec(const T* base, long long row, int C
 template <class T>
 __global__ void __launch_bounds__(256) conv_gemm_simt_kernel(ConvGeom g, const T* __restrict__ in, const float* __restrict__ w,
                                                              GemmEpilogue ep, T* __restrict__ out) {
+  pdl_enter();
   __shared__ __align__(16) float As[BK][LDS_];
   __shared__ __align__(16) float Bs[BK][LDS_];
   const int tid = threadIdx.x, tx = tid % 16, ty = tid / 16;
@@ -100,7 +101,7 @@ int32_t launch_conv_gemm_simt(const ConvGeom& g, const T* in, const float* w, co
   KernelTimer kt_(KC_SIMT_GEMM, 2.0 * g.nb * g.t_out * g.v * (double)g.c * g.n_out * g.taps, st);
   long long rows = (long long)g.nb * g.t_out * g.v;
   dim3 grid((unsigned)cdiv(rows, BM), (unsigned)cdiv(g.n_out, BN));
-  conv_gemm_simt_kernel<T><<<grid, 256, 0, st>>>(g, in, w, ep, out);
+  launch_k(conv_gemm_simt_kernel<T>, grid, 256, 0, st, g, in, w, ep, out);
   STGCN_CHECK_LAUNCH("conv_gemm_simt");
   return STGCN_OK;
 }
@@ -115,6 +116,7 @@ template int32_t launch_conv_gemm_simt<bf16>(const ConvGeom&, const bf16*, const
 template <class T>
 __global__ void __launch_bounds__(256) wgrad_simt_kernel(ConvGeom g, const T* __restrict__ dout, const T* __restrict__ in,
                                                          long long rows_per_chunk, int c_tiles, WIndex wi, float* __restrict__ dw) {
+  pdl_enter();
   __shared__ __align__(16) float Ds[BK][LDS_];   // [row k][n]
   __shared__ __align__(16) float Is[BK][LDS_];   // [row k][c]
   const int tid = threadIdx.x, tx = tid % 16, ty = tid / 16;
@@ -180,7 +182,7 @@ int32_t launch_wgrad_simt(const ConvGeom& g, const T* dout, const T* in, const W
   long long rpc = ((rows + chunks - 1) / chunks + BK - 1) / BK * BK;
   chunks = (rows + rpc - 1) / rpc;
   dim3 grid((unsigned)chunks, (unsigned)(n_tiles * c_tiles), (unsigned)g.taps);
-  wgrad_simt_kernel<T><<<grid, 256, 0, st>>>(g, dout, in, rpc, c_tiles, wi, dw);
+  launch_k(wgrad_simt_kernel<T>, grid, 256, 0, st, g, dout, in, rpc, c_tiles, wi, dw);
   STGCN_CHECK_LAUNCH("wgrad_simt");
   return STGCN_OK;
 }
@@ -193,6 +195,7 @@ template int32_t launch_wgrad_simt<bf16>(const ConvGeom&, const bf16*, const bf1
 template <class TD>
 __global__ void __launch_bounds__(256) pack_weights_kernel(const float* __restrict__ src, WIndex wi, int taps, int n_out, int c,
                                                            int round_bf16, TD* __restrict__ dst) {
+  pdl_enter();
   size_t total = (size_t)taps * n_out * c;
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
     int cc = (int)(i % c); size_t r = i / c; int n = (int)(r % n_out); int tap = (int)(r / n_out);
@@ -206,7 +209,7 @@ int32_t launch_pack_weights(const float* src, const WIndex& wi, int taps, int n_
   KernelTimer kt_(KC_PACK, 0.0, st);
   size_t total = (size_t)taps * n_out * c;
   int blocks = (int)std::min<size_t>((total + 255) / 256, 148 * 4);
-  pack_weights_kernel<TD><<<blocks, 256, 0, st>>>(src, wi, taps, n_out, c, round_bf16, dst);
+  launch_k(pack_weights_kernel<TD>, blocks, 256, 0, st, src, wi, taps, n_out, c, round_bf16, dst);
   STGCN_CHECK_LAUNCH("pack_weights");
   return STGCN_OK;
 }
@@ -215,6 +218,7 @@ template int32_t launch_pack_weights<bf16>(const float*, const WIndex&, int, int
 
 // column sums (bias gradients): out[c] = scale * sum_r x[r][c], via the stats partials
 __global__ void colsum_finalize_kernel(const float* __restrict__ partials, int nblk, int C, float* __restrict__ out) {
+  pdl_enter();
   int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= C) return;
   double s = 0;
@@ -226,7 +230,7 @@ int32_t launch_colsum(const T* x, long long rows, int C, float* partials, float*
   KernelTimer kt_(KC_BN_STATS, 0.0, st);
   int nblk = 0;
   STGCN_TRY(launch_colstats<T>(x, rows, C, partials, &nblk, st));
-  colsum_finalize_kernel<<<cdiv(C, 128), 128, 0, st>>>(partials, nblk, C, out);
+  launch_k(colsum_finalize_kernel, cdiv(C, 128), 128, 0, st, partials, nblk, C, out);
   STGCN_CHECK_LAUNCH("colsum_finalize");
   return STGCN_OK;
 }

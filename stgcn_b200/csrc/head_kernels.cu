@@ -9,6 +9,7 @@ namespace stgcn {
 // pooled[n][c] = mean_{t,v} feat[n][t][v][c]; grid (n, row-splits), atomics into zeroed pooled
 template <class T>
 __global__ void __launch_bounds__(256) pool_kernel(const T* __restrict__ feat, int rows, int C, float inv_rows, float* __restrict__ pooled) {
+  pdl_enter();
   const int n = blockIdx.x;
   const T* f = feat + (size_t)n * rows * C;
   for (int c = threadIdx.x; c < C; c += blockDim.x) {
@@ -21,6 +22,7 @@ __global__ void __launch_bounds__(256) pool_kernel(const T* __restrict__ feat, i
 // vector form: a thread owns one 16-byte channel group of one sample and strides over rows, 4 loads in flight
 template <class T>
 __global__ void __launch_bounds__(256) pool_vec_kernel(const T* __restrict__ feat, int rows, int C, float inv_rows, float* __restrict__ pooled) {
+  pdl_enter();
   constexpr int VEC = VecN<T>::N;
   const int n = blockIdx.x, cv = C / VEC, lanes = 256 / cv;        // host guarantees cv <= 256
   const int myc = (threadIdx.x % cv) * VEC, myr = threadIdx.x / cv;
@@ -48,6 +50,7 @@ __global__ void __launch_bounds__(256) pool_vec_kernel(const T* __restrict__ fea
 }
 template <class T>
 __global__ void __launch_bounds__(256) pool_bwd_vec_kernel(const float* __restrict__ dpooled, int rows, int C, float inv_rows, T* __restrict__ dfeat) {
+  pdl_enter();
   constexpr int VEC = VecN<T>::N;
   const int n = blockIdx.x, cv = C / VEC, lanes = 256 / cv;
   const int myc = (threadIdx.x % cv) * VEC, myr = threadIdx.x / cv;
@@ -61,6 +64,7 @@ __global__ void __launch_bounds__(256) pool_bwd_vec_kernel(const float* __restri
 
 __global__ void __launch_bounds__(128) fc_kernel(const float* __restrict__ pooled, const float* __restrict__ w, const float* __restrict__ b,
                                                  int N, int C, int classes, float* __restrict__ logits) {
+  pdl_enter();
   int warp = (blockIdx.x * blockDim.x + threadIdx.x) / 32, lane = threadIdx.x % 32;
   if (warp >= N * classes) return;
   int n = warp / classes, j = warp % classes;
@@ -79,12 +83,12 @@ int32_t head_forward(int dtype, int n, int t, int v, int c, int classes, const v
   const int vec = dtype == STGCN_F32 ? 4 : 8;
   if (c % vec == 0 && c / vec <= 256) {
     dim3 gv((unsigned)n, (unsigned)std::max(1, std::min(rows / 16, cdiv(148 * 8, n))));
-    if (dtype == STGCN_F32) pool_vec_kernel<float><<<gv, 256, 0, st>>>((const float*)feat, rows, c, 1.f / rows, pooled);
-    else pool_vec_kernel<bf16><<<gv, 256, 0, st>>>((const bf16*)feat, rows, c, 1.f / rows, pooled);
-  } else if (dtype == STGCN_F32) pool_kernel<float><<<grid, 256, 0, st>>>((const float*)feat, rows, c, 1.f / rows, pooled);
-  else pool_kernel<bf16><<<grid, 256, 0, st>>>((const bf16*)feat, rows, c, 1.f / rows, pooled);
+    if (dtype == STGCN_F32) launch_k(pool_vec_kernel<float>, gv, 256, 0, st, (const float*)feat, rows, c, 1.f / rows, pooled);
+    else launch_k(pool_vec_kernel<bf16>, gv, 256, 0, st, (const bf16*)feat, rows, c, 1.f / rows, pooled);
+  } else if (dtype == STGCN_F32) launch_k(pool_kernel<float>, grid, 256, 0, st, (const float*)feat, rows, c, 1.f / rows, pooled);
+  else launch_k(pool_kernel<bf16>, grid, 256, 0, st, (const bf16*)feat, rows, c, 1.f / rows, pooled);
   STGCN_CHECK_LAUNCH("pool");
-  fc_kernel<<<cdiv((long long)n * classes * 32, 128), 128, 0, st>>>(pooled, fcw, fcb, n, c, classes, logits);
+  launch_k(fc_kernel, cdiv((long long)n * classes * 32, 128), 128, 0, st, pooled, fcw, fcb, n, c, classes, logits);
   STGCN_CHECK_LAUNCH("fc");
   return STGCN_OK;
 }
@@ -92,6 +96,7 @@ int32_t head_forward(int dtype, int n, int t, int v, int c, int classes, const v
 // dpooled[n][c] = sum_j dlogits[n][j] w[j][c]
 __global__ void __launch_bounds__(256) fc_bwd_data_kernel(const float* __restrict__ dlogits, const float* __restrict__ w, int N, int C,
                                                           int classes, float* __restrict__ dpooled) {
+  pdl_enter();
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= N * C) return;
   int n = i / C, c = i % C;
@@ -102,6 +107,7 @@ __global__ void __launch_bounds__(256) fc_bwd_data_kernel(const float* __restric
 // dw[j][c] = sum_n dlogits[n][j] pooled[n][c] ; db[j] = sum_n dlogits[n][j]
 __global__ void __launch_bounds__(256) fc_bwd_weight_kernel(const float* __restrict__ dlogits, const float* __restrict__ pooled, int N, int C,
                                                             int classes, float* __restrict__ dw, float* __restrict__ db) {
+  pdl_enter();
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < classes * C) {
     int j = i / C, c = i % C;
@@ -118,6 +124,7 @@ __global__ void __launch_bounds__(256) fc_bwd_weight_kernel(const float* __restr
 template <class T>
 __global__ void __launch_bounds__(256) pool_bwd_kernel(const float* __restrict__ dpooled, int rows, int C, float inv_rows, size_t total,
                                                        T* __restrict__ dfeat) {
+  pdl_enter();
   size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   for (; i < total; i += (size_t)gridDim.x * blockDim.x) {
     int c = (int)(i % C);
@@ -131,20 +138,20 @@ int32_t head_backward(int dtype, int n, int t, int v, int c, int classes, const 
                       const float* dlogits, void* dfeat, float* dfcw, float* dfcb, cudaStream_t st) {
   KernelTimer kt_(KC_HEAD, 0.0, st);
   int rows = t * v;
-  fc_bwd_weight_kernel<<<cdiv((long long)classes * c, 256), 256, 0, st>>>(dlogits, pooled, n, c, classes, dfcw, dfcb);
+  launch_k(fc_bwd_weight_kernel, cdiv((long long)classes * c, 256), 256, 0, st, dlogits, pooled, n, c, classes, dfcw, dfcb);
   STGCN_CHECK_LAUNCH("fc_bwd_weight");
   float* dpooled = const_cast<float*>(pooled);
-  fc_bwd_data_kernel<<<cdiv((long long)n * c, 256), 256, 0, st>>>(dlogits, fcw, n, c, classes, dpooled);
+  launch_k(fc_bwd_data_kernel, cdiv((long long)n * c, 256), 256, 0, st, dlogits, fcw, n, c, classes, dpooled);
   STGCN_CHECK_LAUNCH("fc_bwd_data");
   size_t total = (size_t)n * rows * c;
   int blocks = (int)std::min<size_t>((total + 255) / 256, 148 * 16);
   const int vec = dtype == STGCN_F32 ? 4 : 8;
   if (c % vec == 0 && c / vec <= 256) {
     dim3 gv((unsigned)n, (unsigned)std::max(1, std::min(rows / 16, cdiv(148 * 8, n))));
-    if (dtype == STGCN_F32) pool_bwd_vec_kernel<float><<<gv, 256, 0, st>>>(dpooled, rows, c, 1.f / rows, (float*)dfeat);
-    else pool_bwd_vec_kernel<bf16><<<gv, 256, 0, st>>>(dpooled, rows, c, 1.f / rows, (bf16*)dfeat);
-  } else if (dtype == STGCN_F32) pool_bwd_kernel<float><<<blocks, 256, 0, st>>>(dpooled, rows, c, 1.f / rows, total, (float*)dfeat);
-  else pool_bwd_kernel<bf16><<<blocks, 256, 0, st>>>(dpooled, rows, c, 1.f / rows, total, (bf16*)dfeat);
+    if (dtype == STGCN_F32) launch_k(pool_bwd_vec_kernel<float>, gv, 256, 0, st, dpooled, rows, c, 1.f / rows, (float*)dfeat);
+    else launch_k(pool_bwd_vec_kernel<bf16>, gv, 256, 0, st, dpooled, rows, c, 1.f / rows, (bf16*)dfeat);
+  } else if (dtype == STGCN_F32) launch_k(pool_bwd_kernel<float>, blocks, 256, 0, st, dpooled, rows, c, 1.f / rows, total, (float*)dfeat);
+  else launch_k(pool_bwd_kernel<bf16>, blocks, 256, 0, st, dpooled, rows, c, 1.f / rows, total, (bf16*)dfeat);
   STGCN_CHECK_LAUNCH("pool_bwd");
   return STGCN_OK;
 }

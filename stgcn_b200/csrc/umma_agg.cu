@@ -31,6 +31,7 @@ constexpr int kTile16K = 128 * 128;     // one [128 rows][64 bf16] tile image
 // ---------------------------------------------------------------------------
 __global__ void build_big_adjacency_kernel(const float* __restrict__ A, int K, int V, int FT, bf16* __restrict__ big,
                                            bf16* __restrict__ bigT, float* __restrict__ rowsum) {
+  pdl_enter();
   const int total = K * 128 * 128;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
     const int c = i % 128, r = (i / 128) % 128, k = i / (128 * 128);
@@ -65,7 +66,7 @@ AggPrep carve_agg_prep(void* mem, int K) {
 int32_t launch_build_big_adjacency(const float* A, int K, int V, void* prep_mem, cudaStream_t st) {
   KernelTimer kt_(KC_PACK, 0.0, st);
   AggPrep a = carve_agg_prep(prep_mem, K);
-  build_big_adjacency_kernel<<<cdiv(K * 128 * 128, 256), 256, 0, st>>>(A, K, V, 128 / V, a.big, a.bigT, a.rowsum);
+  launch_k(build_big_adjacency_kernel, cdiv(K * 128 * 128, 256), 256, 0, st, A, K, V, 128 / V, a.big, a.bigT, a.rowsum);
   STGCN_CHECK_LAUNCH("build_big_adjacency");
   return STGCN_OK;
 }
@@ -100,6 +101,7 @@ agg_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_constan
                 const __grid_constant__ CUtensorMap map_out, const __grid_constant__ CUtensorMap map_x,
                 const __grid_constant__ AggParams p) {
   constexpr bool TR = (MODE & 1) != 0, DA = (MODE & 2) != 0, AFF = (MODE & 4) != 0, MASKH = (MODE & 8) != 0, BNB = (MODE & 16) != 0;
+  pdl_trigger();
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   const int slabs = p.nch / 64;
@@ -139,6 +141,7 @@ agg_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_constan
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  pdl_wait();                       // everything above (barriers, TMEM, descriptor prefetch) overlaps the previous kernel's tail
   const uint32_t tmem_base = *tmem_slot;
 
   auto decode = [&](int item, int& cch, int& j0, int& b) {
@@ -397,6 +400,7 @@ struct DaParams {
 __global__ void __launch_bounds__(kAggUThreads, 1)
 agg_dA_umma_kernel(const __grid_constant__ CUtensorMap map_dxa, const __grid_constant__ CUtensorMap map_h,
                    const __grid_constant__ DaParams p) {
+  pdl_trigger();
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   const int stage_bytes = (p.k + 1) * kTile16K;
@@ -417,6 +421,7 @@ agg_dA_umma_kernel(const __grid_constant__ CUtensorMap map_dxa, const __grid_con
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  pdl_wait();                       // everything above (barriers, TMEM, descriptor prefetch) overlaps the previous kernel's tail
   const uint32_t tmem_base = *tmem_slot;
   const int cbs = p.c / 64;
   const bool have_work = (int)blockIdx.x < p.total_tiles;
@@ -542,7 +547,7 @@ static int32_t launch_agg_common(int transpose, const bf16* in, int nb, int t, i
       if (e != cudaSuccess) { set_error("cudaFuncSetAttribute failed: %s", cudaGetErrorString(e)); return STGCN_ERR_CUDA; } \
       attr_set = true;                                                                                                     \
     }                                                                                                                      \
-    agg_umma_kernel<M><<<grid, kAggU2Threads, smem, st>>>(map_in, map_big, map_out, map_x, p);                              \
+    launch_k(agg_umma_kernel<M>, grid, kAggU2Threads, smem, st, map_in, map_big, map_out, map_x, p);                              \
   } break;
   switch (mode) {
     STGCN_AGG_CASE(0) STGCN_AGG_CASE(4) STGCN_AGG_CASE(1) STGCN_AGG_CASE(9) STGCN_AGG_CASE(17) STGCN_AGG_CASE(19)
@@ -590,7 +595,7 @@ int32_t launch_agg_dA_umma(const bf16* dxa, const bf16* h, int nb, int t, int v,
     if (e != cudaSuccess) { set_error("cudaFuncSetAttribute failed: %s", cudaGetErrorString(e)); return STGCN_ERR_CUDA; }
     attr_set = true;
   }
-  agg_dA_umma_kernel<<<std::min(p.total_tiles, num_sms_agg()), kAggUThreads, smem, st>>>(map_dxa, map_h, p);
+  launch_k(agg_dA_umma_kernel, std::min(p.total_tiles, num_sms_agg()), kAggUThreads, smem, st, map_dxa, map_h, p);
   STGCN_CHECK_LAUNCH("agg_dA_umma");
   return STGCN_OK;
 }

@@ -82,6 +82,7 @@ conv_gemm_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_c
   float* const o_stat_partials = (EPM & EP_STATS) ? p.stat_partials : nullptr; float* const o_vsum = (EPM & EP_VSUM) ? p.vsum : nullptr;
   const int o_b2_smem = (EPM & EP_BIAS2D) ? p.b2_smem : 0, o_relu = (EPM & EP_RELU) ? p.relu : 0;
   const float o_dropout_p = (EPM & EP_DROPOUT) ? p.dropout_p : 0.f;
+  pdl_trigger();
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // 1024-byte aligned carve-up (dynamic smem base is only guaranteed 16-byte aligned)
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -112,6 +113,7 @@ conv_gemm_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_c
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  pdl_wait();                       // everything above (barriers, TMEM, descriptor prefetch) overlaps the previous kernel's tail
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
@@ -592,9 +594,9 @@ int32_t launch_conv_gemm_umma(const ConvGeom& g, const bf16* in, const bf16* w, 
   const int need = (ep.bias ? EP_BIAS : 0) | (ep.bias2d ? EP_BIAS2D : 0) | (ep.scale ? EP_SCALE : 0) | (ep.residual ? EP_RESID : 0) |
                    (ep.relu ? EP_RELU : 0) | (ep.dropout_p > 0.f ? EP_DROPOUT : 0) | (ep.stat_partials ? EP_STATS : 0) | (ep.vsum ? EP_VSUM : 0);
   // the leanest instantiation that keeps every requested option
-#define STGCN_CG_TRY(M) if ((need & ~(M)) == 0) { conv_gemm_umma_kernel<M><<<grid, kUmmaThreads, smem, st>>>(map_in, map_w, map_out, p); } else
+#define STGCN_CG_TRY(M) if ((need & ~(M)) == 0) { launch_k(conv_gemm_umma_kernel<M>, grid, kUmmaThreads, smem, st, map_in, map_w, map_out, p); } else
   STGCN_CG_TRY(0) STGCN_CG_TRY(EP_BIAS2D) STGCN_CG_TRY(EP_BIAS | EP_STATS) STGCN_CG_TRY(EP_SCALE | EP_RELU)
-  STGCN_CG_TRY(EP_BIAS | EP_SCALE | EP_RELU) { conv_gemm_umma_kernel<EP_ALL><<<grid, kUmmaThreads, smem, st>>>(map_in, map_w, map_out, p); }
+  STGCN_CG_TRY(EP_BIAS | EP_SCALE | EP_RELU) { launch_k(conv_gemm_umma_kernel<EP_ALL>, grid, kUmmaThreads, smem, st, map_in, map_w, map_out, p); }
 #undef STGCN_CG_TRY
   STGCN_CHECK_LAUNCH("conv_gemm_umma");
   return STGCN_OK;

@@ -17,6 +17,7 @@ struct ProbeParams { int mode; int row_off; int base_off; int a_rows; };
 __global__ void __launch_bounds__(128, 1)
 umma_probe_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                   const __grid_constant__ ProbeParams p, float* __restrict__ d_out) {
+  pdl_trigger();
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   // A region: up to 512 rows x 128 B (mode 1: two slabs of 256 rows); B region: 128 rows x 128 B
@@ -30,6 +31,7 @@ umma_probe_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  pdl_wait();                       // everything above (barriers, TMEM, descriptor prefetch) overlaps the previous kernel's tail
   const uint32_t tmem_base = *tmem_slot;
   if (threadIdx.x == 0) {
     if (p.mode == 0) {
@@ -94,7 +96,7 @@ extern "C" int32_t stgcn_umma_probe(int32_t mode, int32_t row_off, int32_t base_
   ProbeParams p{mode, row_off, base_off, a_rows};
   const size_t smem = 512 * 128 + 128 * 128 + 1024 + 256;
   cudaFuncSetAttribute(umma_probe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  umma_probe_kernel<<<1, 128, smem, (cudaStream_t)stream>>>(ma, mb, p, d);
+  launch_k(umma_probe_kernel, 1, 128, smem, (cudaStream_t)stream, ma, mb, p, d);
   STGCN_CHECK_LAUNCH("umma_probe");
   return STGCN_OK;
 }

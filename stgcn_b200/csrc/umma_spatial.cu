@@ -36,6 +36,7 @@ __global__ void __launch_bounds__(kSpThreads, 1)
 spatial_fused_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_big,
                      const __grid_constant__ CUtensorMap map_w, const __grid_constant__ CUtensorMap map_xa,
                      const __grid_constant__ CUtensorMap map_out, const __grid_constant__ SpParams p) {
+  pdl_trigger();
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   const int w_stage_bytes = p.wn * 128;
@@ -73,6 +74,7 @@ spatial_fused_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_con
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  pdl_wait();                       // everything above (barriers, TMEM, descriptor prefetch) overlaps the previous kernel's tail
   const uint32_t tmem_base = *tmem_slot;
   const uint32_t t_tmem = tmem_base;                 // 2 x 64 columns: aggregation accumulators
   const uint32_t s_tmem = tmem_base + 128;           // Co columns: the output tile
@@ -332,7 +334,7 @@ int32_t launch_spatial_fused(const bf16* x, int nb, int t, int v, int ci, int co
     if (e != cudaSuccess) { set_error("cudaFuncSetAttribute failed: %s", cudaGetErrorString(e)); return STGCN_ERR_CUDA; }
     attr_set = true;
   }
-  spatial_fused_kernel<<<std::min(p.total_tiles, num_sms_sp()), kSpThreads, pl.smem, st>>>(map_x, map_big, map_w, map_xa, map_out, p);
+  launch_k(spatial_fused_kernel, std::min(p.total_tiles, num_sms_sp()), kSpThreads, pl.smem, st, map_x, map_big, map_w, map_xa, map_out, p);
   STGCN_CHECK_LAUNCH("spatial_fused");
   return STGCN_OK;
 }

@@ -45,6 +45,7 @@ struct WgParams {
 __global__ void __launch_bounds__(kWgThreads, 1)
 wgrad_umma_kernel(const __grid_constant__ CUtensorMap map_dout, const __grid_constant__ CUtensorMap map_in,
                   const __grid_constant__ WgParams p) {
+  pdl_trigger();
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   const int a_stage = p.n_slabs * kATile;
@@ -76,6 +77,7 @@ wgrad_umma_kernel(const __grid_constant__ CUtensorMap map_dout, const __grid_con
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  pdl_wait();                       // everything above (barriers, TMEM, descriptor prefetch) overlaps the previous kernel's tail
   const uint32_t tmem_base = *tmem_slot;
 
   // item -> (n_t, c_t, group, split)
@@ -180,6 +182,7 @@ wgrad_umma_kernel(const __grid_constant__ CUtensorMap map_dout, const __grid_con
 // packed [taps][n][c] -> the reference's parameter layout
 __global__ void __launch_bounds__(256) wgrad_unpack_kernel(const float* __restrict__ packed, WIndex wi, int taps, int n_out, int c,
                                                            int c_valid, float* __restrict__ dw) {
+  pdl_enter();
   size_t total = (size_t)taps * n_out * c;
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
     int cc = (int)(i % c); size_t r = i / c; int n = (int)(r % n_out); int tap = (int)(r / n_out);
@@ -298,10 +301,10 @@ int32_t launch_wgrad_umma(const ConvGeom& g, const bf16* dout, const bf16* in, c
     attr_set = true;
   }
   const int grid = std::min(p.total_items, num_sms_wg());
-  wgrad_umma_kernel<<<grid, kWgThreads, smem, st>>>(map_dout, map_in, p);
+  launch_k(wgrad_umma_kernel, grid, kWgThreads, smem, st, map_dout, map_in, p);
   STGCN_CHECK_LAUNCH("wgrad_umma");
   size_t total = umma_wgrad_workspace_floats(g);
-  wgrad_unpack_kernel<<<(int)std::min<size_t>((total + 255) / 256, 148 * 4), 256, 0, st>>>(packed_ws, wi, g.taps, g.n_out, g.c, c_valid < 0 ? g.c : c_valid, dw);
+  launch_k(wgrad_unpack_kernel, (int)std::min<size_t>((total + 255) / 256, 148 * 4), 256, 0, st, packed_ws, wi, g.taps, g.n_out, g.c, c_valid < 0 ? g.c : c_valid, dw);
   STGCN_CHECK_LAUNCH("wgrad_unpack");
   return STGCN_OK;
 }
