@@ -147,6 +147,7 @@ def main():
     ap.add_argument('--seqs-per-gpu', type=int, default=32)
     ap.add_argument('--dtype', default='bf16', choices=['bf16', 'f32'])
     ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--eager', action='store_true', help='A/B aid: launch the step kernel by kernel instead of replaying its CUDA graph')
     ap.add_argument('--only-train', action='store_true', help='profiling aid: skip the e2e and inference legs')
     ap.add_argument('--only-infer', action='store_true', help='profiling aid: time the eval-mode forward only')
     args = ap.parse_args()
@@ -169,7 +170,9 @@ def main():
     dt = torch.bfloat16 if args.dtype == 'bf16' else torch.float32
     torch.manual_seed(0)
     model = L_STGCN(hparams(), compute_dtype=dt, A=sane_adjacency()).to(dev).train()
-    opt = torch.optim.Adam(model.parameters(), lr=0.01, fused=True)
+    from stgcn_b200 import cross_entropy
+    from stgcn_b200.optim import Adam
+    opt = Adam(model.parameters(), lr=0.01)                 # one launch per 64 parameter tensors (stgcn_adam_step)
     reducer = GradBucketReducer(model.parameters(), 3) if world > 1 else None
     n_batches = 4                                           # distinct resident batches: 4 x S x 2 x 300x25x3 fp32
     dev_batches = [synthetic_batch(S, 100 + rank * 10 + i, dev) for i in range(n_batches)]
@@ -178,25 +181,36 @@ def main():
 
     def train_step(x, y):
         opt.zero_grad(set_to_none=True)
-        loss = torch.nn.functional.cross_entropy(model(x), y)
+        loss = cross_entropy(model(x), y)
         loss.backward()
         if reducer is not None:
             reducer.finish()
         opt.step()
         return loss
 
+    cap = [None]
+
+    def step_fn(x, y):
+        """The public training step: the captured CUDA graph of train_step (stgcn_b200.CapturedTrainStep), or train_step itself."""
+        return cap[0](x, y) if cap[0] is not None else train_step(x, y)
+
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
+    host_ms = [0.0]
+
     def timed(fn, steps):
-        """K steps bracketed by barrier+sync, device-timed with CUDA events; max over ranks."""
+        """K steps bracketed by barrier+sync, device-timed with CUDA events; max over ranks.  host_ms[0] = wall time the host
+        needed to ENQUEUE the K steps (when it is close to the device time, the step is launch-bound)."""
         barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
+        t0 = time.perf_counter()
         for i in range(steps):
             fn(i)
+        host_ms[0] = (time.perf_counter() - t0) * 1e3
         e1.record()
         barrier()
         ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
@@ -230,10 +244,19 @@ def main():
     # ---- device-resident training -------------------------------------------------------
     for i in range(W):
         train_step(*dev_batches[i % n_batches])
+    l0 = _lib.launch_count()
+    if not args.eager:
+        from stgcn_b200 import CapturedTrainStep
+        cap[0] = CapturedTrainStep(model, opt, *dev_batches[0], reducer=reducer)      # warm-up steps inside are undone
+    launches_per_step = (_lib.launch_count() - l0) // 3 if cap[0] is not None else None  # 2 warm-up steps + the captured one
+    for i in range(W):
+        step_fn(*dev_batches[i % n_batches])
     sampler = ClockSampler(local) if rank == 0 else None
     l0 = _lib.launch_count()
-    ms_train = timed(lambda i: (flush.zero_(), train_step(*dev_batches[i % n_batches])), args.steps)
-    launches = _lib.launch_count() - l0
+    ms_train = timed(lambda i: (flush.zero_(), step_fn(*dev_batches[i % n_batches])), args.steps)
+    host_enqueue_ms = host_ms[0] / args.steps
+    # a replayed graph launches the captured kernels without passing through the library's host counter
+    launches = launches_per_step * args.steps if cap[0] is not None else _lib.launch_count() - l0
     # the L2 flush is inside the timed region: subtract its own measured cost
     ms_flush = timed(lambda i: flush.zero_(), args.steps)
     ms_step = (ms_train - ms_flush) / args.steps
@@ -261,7 +284,7 @@ def main():
             pf.push(host_batches[k % n_batches])
         pf.push(host_batches[(k + 1) % n_batches])
         xin, yin = pf.pop()
-        loss = train_step(xin, yin)
+        loss = step_fn(xin, yin)
         pf.done()
         e2e_k[0] = k + 1
         # device -> host read of every step's loss through pinned memory; the host blocks on the PREVIOUS step's copy (deferred
@@ -280,6 +303,7 @@ def main():
     if args.only_train:
         if rank == 0:
             print(json.dumps({'value': value, 'ms_per_step': ms_step, 'ms_per_step_instrumented': ms_instr, 'gpu_launches': launches,
+                              'host_enqueue_ms_per_step': host_enqueue_ms, 'step_mode': 'eager' if args.eager else 'cuda_graph',
                               'kernel_ms_per_step': {k: round(v[0] / args.steps, 4) for k, v in prof.items()}}))
         if world > 1:
             dist.destroy_process_group()
@@ -334,7 +358,8 @@ def main():
                    'ms_per_step': ms_e2e},
            'infer': {'value': S * world / (ms_inf * 1e-3), 'unit': 'seq/s', 'ms_per_step': ms_inf,
                      'model_tflops': fwd_flops * S * M_PERSONS * world / (ms_inf * 1e-3) / 1e12},
-           'gpu_launches': launches, 'clocks': clocks, 'roofline': roof, 'ms_per_step_instrumented': ms_instr,
+           'gpu_launches': launches, 'step_mode': 'eager launches' if args.eager else 'one CUDA graph per step (CapturedTrainStep)',
+           'host_enqueue_ms_per_step': host_enqueue_ms, 'clocks': clocks, 'roofline': roof, 'ms_per_step_instrumented': ms_instr,
            'kernel_ms_per_step': {k: round(v[0] / args.steps, 4) for k, v in sorted(prof.items(), key=lambda kv: -kv[1][0])}}
     if not args.no_cpu_baseline and world == 1:
         r = subprocess.run([sys.executable, os.path.abspath(__file__), '--impl', 'reference', '--steps', '2', '--warmup', '1'],

@@ -158,6 +158,24 @@ int32_t stgcn_head_backward(int32_t dtype, int32_t n, int32_t t, int32_t v, int3
                             const float* pooled, const float* fc_weight, const float* dlogits,
                             void* dfeat, float* dfc_weight, float* dfc_bias, void* stream);
 
+/* Loss of the reference's training_step (src/lightning_model.py:202: F.cross_entropy(output, y), mean reduction).
+ * One launch: loss[0] = mean over rows with labels[r] != ignore_index of (logsumexp(logits[r]) - logits[r][labels[r]]) and
+ * dlogits_unit = d loss / d logits (n,classes) for an incoming gradient of 1.  _backward scales it by grad_loss[0] (device). */
+int32_t stgcn_cross_entropy_forward(int32_t n, int32_t classes, const float* logits, const int64_t* labels,
+                                    int64_t ignore_index, float* loss, float* dlogits_unit, void* stream);
+int32_t stgcn_cross_entropy_backward(int32_t n, int32_t classes, const float* dlogits_unit, const float* grad_loss,
+                                     float* dlogits, void* stream);
+
+/* Optimizer of the reference (src/lightning_model.py:196-197: optim.Adam(self.parameters(), lr)): one step of torch.optim.Adam
+ * (no amsgrad, L2 weight decay) over `count` fp32 tensors.  The four tables are HOST arrays of DEVICE pointers, sizes[i] =
+ * elements of tensor i.  The step number lives on the DEVICE: step_state points to 16 bytes {int64 step; float[2] scratch}
+ * (zero-initialised by the caller).  A one-thread kernel advances it by one (step == 0) or sets it to `step` (step >= 1) and forms
+ * the bias corrections in double before the update runs, so a CUDA graph of the training step replays correctly.
+ * One update launch per 64 tensors. */
+int32_t stgcn_adam_step(int32_t count, float* const* params, const float* const* grads, float* const* exp_avg,
+                        float* const* exp_avg_sq, const int64_t* sizes, double lr, double beta1, double beta2, double eps,
+                        double weight_decay, int64_t step, void* step_state, void* stream);
+
 /* Layout helpers: fp32 (n,t,v,c) <-> dtype (n,t,v,c) casts on device. */
 int32_t stgcn_cast(int32_t src_dtype, int32_t dst_dtype, const void* src, void* dst, size_t count, void* stream);
 

@@ -216,6 +216,28 @@ def cross_entropy(logits, labels):
     return (lse - picked).mean()
 
 
+def cross_entropy_grad(logits, labels):
+    """d cross_entropy / d logits for an incoming gradient of 1: (softmax - onehot) / N."""
+    p = torch.softmax(logits, dim=1)
+    oh = torch.zeros_like(p)
+    oh[torch.arange(logits.shape[0]), labels] = 1.0
+    return (p - oh) / logits.shape[0]
+
+
+def adam_step(p, g, m, v, step, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.0):
+    """One step of torch.optim.Adam (no amsgrad) -- the optimizer of lightning_model.py:196-197 -- written out.
+    Returns the new (p, m, v); `step` is the 1-based step number.  Pinned against torch.optim.Adam in
+    tests/test_oracle_train.py."""
+    b1, b2 = betas
+    g = g + weight_decay * p
+    m = m + (1.0 - b1) * (g - m)
+    v = b2 * v + (1.0 - b2) * g * g
+    bc1 = 1.0 - b1 ** step
+    bc2 = 1.0 - b2 ** step
+    denom = v.sqrt() / (bc2 ** 0.5) + eps
+    return p - (lr / bc1) * (m / denom), m, v
+
+
 # ----------------------------------------------------------------------------
 # explicit backward of the default (non-residual) block -- restates what autograd
 # does for the reference, in the factorisation the CUDA kernels use

@@ -2,5 +2,8 @@
 from . import graph  # noqa: F401
 from .modules import SpatialConv, SpatialTemporalConv  # noqa: F401
 from .model import L_STGCN, STGCN  # noqa: F401
+from . import optim  # noqa: F401
+from .functional import cross_entropy  # noqa: F401
+from .training import CapturedTrainStep  # noqa: F401
 
-__all__ = ['SpatialConv', 'SpatialTemporalConv', 'L_STGCN', 'STGCN', 'graph']
+__all__ = ['SpatialConv', 'SpatialTemporalConv', 'L_STGCN', 'STGCN', 'graph', 'optim', 'cross_entropy', 'CapturedTrainStep']

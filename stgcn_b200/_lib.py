@@ -69,6 +69,12 @@ def _declare(lib):
     lib.stgcn_head_forward.argtypes = [i32] * 6 + [_P] * 5 + [_P]
     lib.stgcn_head_backward.restype = i32
     lib.stgcn_head_backward.argtypes = [i32] * 6 + [_P] * 6 + [_P]
+    lib.stgcn_cross_entropy_forward.restype = i32
+    lib.stgcn_cross_entropy_forward.argtypes = [i32, i32, _P, _P, C.c_int64, _P, _P, _P]
+    lib.stgcn_cross_entropy_backward.restype = i32
+    lib.stgcn_cross_entropy_backward.argtypes = [i32, i32, _P, _P, _P, _P]
+    lib.stgcn_adam_step.restype = i32
+    lib.stgcn_adam_step.argtypes = [i32, _P, _P, _P, _P, _P] + [C.c_double] * 5 + [C.c_int64, _P, _P]
     lib.stgcn_cast.restype = i32; lib.stgcn_cast.argtypes = [i32, i32, _P, _P, sz, _P]
     lib.stgcn_umma_conv_gemm.restype = i32
     lib.stgcn_umma_conv_gemm.argtypes = [i32] * 9 + [_P] * 4 + [_P]

@@ -219,3 +219,41 @@ class _HeadFn(torch.autograd.Function):
 
 def head_forward(feat, fcw, fcb):
     return _HeadFn.apply(feat, fcw, fcb)
+
+
+class _CrossEntropyFn(torch.autograd.Function):
+    """F.cross_entropy(output, y), mean reduction (lightning_model.py:202): loss and d loss / d logits in one launch."""
+
+    @staticmethod
+    def forward(ctx, logits, labels, ignore_index):
+        L.require_cuda(logits, 'logits')
+        L.require_cuda(labels, 'labels')
+        if logits.dim() != 2 or labels.dim() != 1 or labels.shape[0] != logits.shape[0]:
+            raise RuntimeError('stgcn_b200.cross_entropy: logits (N,classes) and labels (N,) expected')
+        if labels.dtype != torch.int64:
+            raise RuntimeError('stgcn_b200.cross_entropy: labels must be int64 class indices')
+        lib = L.lib()
+        lg = _f32(logits)
+        lb = labels.contiguous()
+        n, classes = lg.shape
+        loss = torch.empty((), dtype=torch.float32, device=lg.device)
+        dl = torch.empty_like(lg)
+        L.check(lib.stgcn_cross_entropy_forward(n, classes, L.ptr(lg), L.ptr(lb), int(ignore_index), L.ptr(loss), L.ptr(dl),
+                                                L.stream_ptr(lg.device)), 'cross_entropy_forward')
+        ctx.save_for_backward(dl)
+        ctx.in_dtype = logits.dtype
+        return loss
+
+    @staticmethod
+    def backward(ctx, gloss):
+        (dl,) = ctx.saved_tensors
+        lib = L.lib()
+        g = gloss.contiguous().float()
+        out = torch.empty_like(dl)
+        L.check(lib.stgcn_cross_entropy_backward(dl.shape[0], dl.shape[1], L.ptr(dl), L.ptr(g), L.ptr(out),
+                                                 L.stream_ptr(dl.device)), 'cross_entropy_backward')
+        return out.to(ctx.in_dtype), None, None
+
+
+def cross_entropy(logits, labels, ignore_index=-100):
+    return _CrossEntropyFn.apply(logits, labels, ignore_index)

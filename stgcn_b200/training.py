@@ -1,0 +1,90 @@
+"""One training step of the drop-in model as ONE CUDA graph.
+
+The reference's step is Lightning's `training_step` + `optimizer.step()` (src/lightning_model.py:196-205): forward,
+F.cross_entropy, backward, Adam.  Here that is ~260 kernel launches of 10-60 us each; issued one by one from Python the
+host needs about as long to enqueue them as the B200 needs to run them.  `CapturedTrainStep` records the whole step once
+(zero_grad -> forward -> loss -> backward -> gradient all-reduce -> optimizer) with `torch.cuda.graph` and replays it per
+batch: one `cudaGraphLaunch` per step, the programmatic-dependent-launch edges between the library's kernels included.
+
+    step = CapturedTrainStep(model, optimizer, example_x, example_y)       # model.train(), stgcn_b200.optim.Adam
+    for x, y in loader:                                                     # device tensors of the example's shape / dtype
+        loss = step(x, y)                                                   # 0-dim device tensor, valid until the next call
+
+What makes the step capturable: the library never synchronises or allocates, BatchNorm's running statistics and
+`num_batches_tracked` are advanced by kernels, and the optimizer keeps its step number on the device.  The two warm-up
+steps that precede capture run on the example batch and are UNDONE afterwards (parameters, buffers and optimizer state are
+restored in place), so constructing the object does not train the model.
+"""
+import torch
+
+from .functional import cross_entropy
+
+
+class CapturedTrainStep:
+    def __init__(self, model, optimizer, example_x, example_y, loss_fn=cross_entropy, reducer=None, warmup=2):
+        if not example_x.is_cuda:
+            raise RuntimeError('stgcn_b200.CapturedTrainStep: CUDA tensors required (there is no CPU path)')
+        if not model.training:
+            raise RuntimeError('stgcn_b200.CapturedTrainStep: put the model in train() mode first')
+        self.model, self.opt, self.loss_fn, self.reducer = model, optimizer, loss_fn, reducer
+        self._blocks = [m for m in model.modules() if hasattr(m, '_prep_cache')]
+        if any(getattr(m, 'dropout', None) is not None and m.dropout.p > 0 for m in self._blocks):
+            raise RuntimeError('stgcn_b200.CapturedTrainStep: dropout draws its seed on the host per call; a captured step would '
+                               'replay one mask (use the eager step with dropout_rate > 0)')
+        self.x = torch.empty_like(example_x)
+        self.y = torch.empty_like(example_y)
+        self.x.copy_(example_x); self.y.copy_(example_y)
+        dev = example_x.device
+        # ---- warm-up (sizes the scratch arena, creates optimizer state), then undo it in place ---------------------------
+        saved = [t.detach().clone() for t in self._model_tensors()]
+        opt_saved = {p: {k: v.clone() for k, v in st.items() if torch.is_tensor(v)} for p, st in optimizer.state.items()}
+        dev_saved = {k: t.clone() for k, t in getattr(optimizer, '_dev_step', {}).items()}
+        n_warm = max(1, warmup)
+        side = torch.cuda.Stream(device=dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(side):
+            for _ in range(n_warm):
+                self._eager_step()
+        torch.cuda.current_stream(dev).wait_stream(side)
+        with torch.no_grad():
+            for t, s in zip(self._model_tensors(), saved):
+                t.copy_(s)
+            for p, st in optimizer.state.items():           # state created by the warm-up starts from zero, like a fresh optimizer
+                for k, v in st.items():
+                    if torch.is_tensor(v):
+                        old = opt_saved.get(p, {}).get(k)
+                        v.copy_(old) if old is not None else v.zero_()
+            for k, t in getattr(optimizer, '_dev_step', {}).items():     # device-resident step numbers (stgcn_b200.optim.Adam)
+                if k in dev_saved:
+                    t.copy_(dev_saved[k])
+                else:
+                    t[0] -= n_warm
+        # ---- capture ----------------------------------------------------------------------------------------------------------
+        optimizer.zero_grad(set_to_none=True)
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph):
+            self.loss = self._eager_step()
+
+    def _model_tensors(self):
+        return list(self.model.parameters()) + list(self.model.buffers())
+
+    def _eager_step(self):
+        self.opt.zero_grad(set_to_none=True)
+        loss = self.loss_fn(self.model(self.x), self.y)
+        loss.backward()
+        if self.reducer is not None:
+            self.reducer.finish()
+        self.opt.step()
+        return loss.detach()
+
+    def __call__(self, x, y):
+        """Copy the batch into the captured input buffers (device or pinned-host source, stream-ordered) and replay."""
+        if x.shape != self.x.shape or y.shape != self.y.shape:
+            raise RuntimeError('stgcn_b200.CapturedTrainStep: batch shape %s differs from the captured %s' %
+                               (tuple(x.shape), tuple(self.x.shape)))
+        self.x.copy_(x, non_blocking=True)
+        self.y.copy_(y, non_blocking=True)
+        self.graph.replay()
+        for m in self._blocks:            # parameters and running statistics changed behind torch's version counters
+            m._prep_cache.clear()
+        return self.loss
