@@ -23,6 +23,8 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 T_FRAMES, V_JOINTS, C_IN, M_PERSONS, CLASSES, K_PART = 300, 25, 3, 2, 60, 3
+METRIC = 'ST-GCN training sequences/s (3x300x25x2, 10-layer, fwd+CE+bwd+Adam)'
+WORKLOAD = 'BASELINE cfg4: 10-layer ST-GCN (64x4,128x3,256x3) training, V=25 K=3 60 classes'
 LAYERS = [(3, 64, 1), (64, 64, 1), (64, 64, 1), (64, 64, 1), (64, 128, 2), (128, 128, 1), (128, 128, 1),
           (128, 256, 2), (256, 256, 1), (256, 256, 1)]
 
@@ -130,10 +132,11 @@ def run_reference(args):
     dt = (time.perf_counter() - t0) / steps
     val = seqs / dt
     sample = '%d sequences (N_eff=%d) x 3x300x25, fwd+CE+bwd+Adam fp32, %d steps' % (seqs, seqs * 2, steps)
-    print(json.dumps({'impl': 'reference', 'metric': 'ST-GCN training sequences/s', 'value': val, 'unit': 'seq/s',
+    print(json.dumps({'impl': 'reference', 'metric': METRIC, 'value': val, 'unit': 'seq/s',
                       'n_gpus': args.gpus, 'steps': steps, 'warmup': 1, 'ms_per_step': dt * 1e3, 'higher_is_better': True,
                       'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
-                      'config': {'workload': 'cfg4 10-layer ST-GCN training step, CPU sample', 'seqs_per_step': seqs},
+                      'config': {'workload': WORKLOAD, 'seqs_per_step': seqs, 'T': T_FRAMES,
+                                 'note': 'reference arm: CPU port of the path (oracle), bounded sample of the same workload'},
                       'cpu_baseline': {'value': val, 'unit': 'seq/s', 'cores': cores, 'kind': 'port', 'sample': sample},
                       'e2e': {'value': val, 'unit': 'seq/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0}}))
 
@@ -190,6 +193,19 @@ def main():
 
     cap = [None]
 
+    def leave():
+        """End of a rank.  Every collective of the run is behind us (the last one is the MAX all-reduce of the last timed region), so
+        ranks leave independently.  With a captured step the NCCL communicator is still referenced by a live CUDA graph and tearing
+        it down (destroy_process_group / interpreter shutdown) was observed to hang: release the graph, drain the device and exit
+        the process directly."""
+        sys.stdout.flush(); sys.stderr.flush()
+        if world > 1:
+            torch.cuda.synchronize()
+            if cap[0] is None:
+                dist.destroy_process_group()
+            else:
+                os._exit(0)
+
     def step_fn(x, y):
         """The public training step: the captured CUDA graph of train_step (stgcn_b200.CapturedTrainStep), or train_step itself."""
         return cap[0](x, y) if cap[0] is not None else train_step(x, y)
@@ -237,9 +253,7 @@ def main():
         if rank == 0:
             print(json.dumps({'infer_seq_s': S * world / (ms_inf * 1e-3), 'ms_per_step': ms_inf, 'gpu_launches': launches,
                               'kernel_ms_per_step': {k: round(v[0] / args.steps, 4) for k, v in prof.items()}}))
-        if world > 1:
-            dist.destroy_process_group()
-        return
+        return leave()
 
     # ---- device-resident training -------------------------------------------------------
     for i in range(W):
@@ -305,9 +319,7 @@ def main():
             print(json.dumps({'value': value, 'ms_per_step': ms_step, 'ms_per_step_instrumented': ms_instr, 'gpu_launches': launches,
                               'host_enqueue_ms_per_step': host_enqueue_ms, 'step_mode': 'eager' if args.eager else 'cuda_graph',
                               'kernel_ms_per_step': {k: round(v[0] / args.steps, 4) for k, v in prof.items()}}))
-        if world > 1:
-            dist.destroy_process_group()
-        return
+        return leave()
     for i in range(2):
         e2e_step(i)
     ms_e2e = timed(e2e_step, args.steps) / args.steps
@@ -322,9 +334,7 @@ def main():
     model.train()
 
     if rank != 0:
-        if world > 1:
-            dist.destroy_process_group()
-        return
+        return leave()
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, 'MEASURED_PEAKS.json')))
@@ -346,10 +356,10 @@ def main():
                 'frac': ach / peak_tf, 'traffic': traffic, 'traffic_unit': 'DRAM bytes per launch (ncu)', 'traffic_source': traffic_src,
                 'flop_per_launch': um[1] / max(um[2], 1), 'launches': um[2], 'ms_total': um[0],
                 'peak_source': 'MEASURED_PEAKS.json bf16_tflops_sustained' if peaks else 'fallback 1.4 PFLOP/s'}
-    out = {'metric': 'ST-GCN training sequences/s (3x300x25x2, 10-layer, fwd+CE+bwd+Adam)', 'value': value, 'unit': 'seq/s',
+    out = {'metric': METRIC, 'value': value, 'unit': 'seq/s',
            'n_gpus': world, 'steps': args.steps, 'warmup': W, 'ms_per_step': ms_step, 'higher_is_better': True,
            'scaling': 'weak', 'vs_baseline': None, 'dtype': args.dtype, 'data': 'synthetic',
-           'config': {'workload': 'BASELINE cfg4: 10-layer ST-GCN (64x4,128x3,256x3) training, V=25 K=3 60 classes',
+           'config': {'workload': WORKLOAD,
                       'seqs_per_gpu': S, 'n_eff_per_gpu': S * M_PERSONS, 'global_batch_seqs': S * world, 'T': T_FRAMES,
                       'parallelism': 'dp%d' % world, 'l2': 'flushed (160 MB write) between timed steps, flush time subtracted',
                       'bn': 'per-replica statistics'},
@@ -369,8 +379,7 @@ def main():
         except Exception:
             out['cpu_baseline'] = {'error': (r.stderr or r.stdout)[-300:]}
     print(json.dumps(out))
-    if world > 1:
-        dist.destroy_process_group()
+    leave()
 
 
 if __name__ == '__main__':
