@@ -320,8 +320,9 @@ __global__ void __launch_bounds__(256) vcolsum_kernel(const T* __restrict__ ds, 
 // vector form: one thread owns one 16-byte group of consecutive (v,c) elements and strides over frames with 4 independent loads
 // in flight
 template <class T>
-__global__ void __launch_bounds__(256) vcolsum_vec_kernel(const T* __restrict__ ds, long long frames, int VC, float* __restrict__ t1) {
+__global__ void __launch_bounds__(256) vcolsum_vec_kernel(const T* __restrict__ ds, long long frames, int VC, float* __restrict__ t1, int rev) {
   pdl_enter();
+  auto F = [&](long long q) { return rev ? frames - 1 - q : q; };         // ping-pong traversal (common.cuh)
   constexpr int VEC = VecN<T>::N;
   const int e = (blockIdx.y * 256 + threadIdx.x) * VEC;
   if (e >= VC) return;
@@ -333,12 +334,12 @@ __global__ void __launch_bounds__(256) vcolsum_vec_kernel(const T* __restrict__ 
   for (; f + 7 * step < frames; f += 8 * step) {
     float a[8][VEC];
 #pragma unroll
-    for (int u = 0; u < 8; ++u) ldv(ds + (f + u * step) * VC + e, a[u]);
+    for (int u = 0; u < 8; ++u) ldv(ds + F(f + u * step) * VC + e, a[u]);
 #pragma unroll
     for (int i = 0; i < VEC; ++i) s[i] += ((a[0][i] + a[1][i]) + (a[2][i] + a[3][i])) + ((a[4][i] + a[5][i]) + (a[6][i] + a[7][i]));
   }
   for (; f < frames; f += step) {
-    float a[VEC]; ldv(ds + f * VC + e, a);
+    float a[VEC]; ldv(ds + F(f) * VC + e, a);
 #pragma unroll
     for (int i = 0; i < VEC; ++i) s[i] += a[i];
   }
@@ -357,7 +358,7 @@ int32_t launch_vcolsum(const T* ds, long long frames, int V, int C, float* t1, c
     const int by = cdiv(VC / VEC, 256);
     // few, long-running CTAs: the final atomics contend bx-way per address
     const int bx = (int)std::max<long long>(1, std::min<long long>(frames / 16, (148 * 2 + by - 1) / by));
-    launch_k(vcolsum_vec_kernel<T>, dim3((unsigned)bx, (unsigned)by), 256, 0, st, ds, frames, VC, t1);
+    launch_k(vcolsum_vec_kernel<T>, dim3((unsigned)bx, (unsigned)by), 256, 0, st, ds, frames, VC, t1, next_direction());
   } else {
     dim3 grid((unsigned)std::min<long long>(frames, 64), (unsigned)cdiv(VC, 256));
     launch_k(vcolsum_kernel<T>, grid, 256, 0, st, ds, frames, VC, t1);

@@ -11,6 +11,13 @@
 namespace stgcn {
 
 std::atomic<uint64_t> g_launches{0};
+int next_direction() {
+  static const bool on = getenv("STGCN_NO_PINGPONG") == nullptr;
+  static thread_local int dir = 0;
+  if (!on) return 0;
+  dir ^= 1;
+  return dir;
+}
 bool pdl_enabled() { static const bool on = getenv("STGCN_NO_PDL") == nullptr; return on; }
 static thread_local char g_err[512] = "";
 void set_error(const char* fmt, ...) {

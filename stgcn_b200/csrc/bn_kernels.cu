@@ -83,7 +83,7 @@ static int stat_blocks(long long rows, int C, int vec) {
 template <class T, int MODE>
 __global__ void __launch_bounds__(kStatThreads) colreduce_fast_kernel(const T* __restrict__ x, const T* __restrict__ z,
                                                                       const float* __restrict__ stats, int relu, long long rows,
-                                                                      int C, float* __restrict__ partials) {
+                                                                      int C, float* __restrict__ partials, int rev) {
   pdl_enter();
   constexpr int VEC = VecN<T>::N;
   extern __shared__ float sm[];
@@ -110,21 +110,22 @@ __global__ void __launch_bounds__(kStatThreads) colreduce_fast_kernel(const T* _
   };
   if (active) {
     const long long step = (long long)gridDim.x * rps;
+    auto R = [&](long long q) { return rev ? rows - 1 - q : q; };       // ping-pong traversal (common.cuh)
     long long r = (long long)blockIdx.x * rps + myr;
     for (; r + 3 * step < rows; r += 4 * step) {
       float g[4][VEC], zz[4][VEC];
 #pragma unroll
       for (int u = 0; u < 4; ++u) {
-        ldv(x + (r + u * step) * C + myc, g[u]);
-        if (MODE == 1) ldv(z + (r + u * step) * C + myc, zz[u]);
+        ldv(x + R(r + u * step) * C + myc, g[u]);
+        if (MODE == 1) ldv(z + R(r + u * step) * C + myc, zz[u]);
       }
 #pragma unroll
       for (int u = 0; u < 4; ++u) accum(g[u], MODE == 1 ? zz[u] : g[u]);
     }
     for (; r < rows; r += step) {
       float g[VEC], zz[VEC];
-      ldv(x + r * C + myc, g);
-      if (MODE == 1) ldv(z + r * C + myc, zz);
+      ldv(x + R(r) * C + myc, g);
+      if (MODE == 1) ldv(z + R(r) * C + myc, zz);
       accum(g, MODE == 1 ? zz : g);
     }
   }
@@ -149,7 +150,7 @@ static void launch_colreduce_fast(const T* x, const T* z, const float* stats, in
   long long b = (rows + rps - 1) / rps; b = (b + 7) / 8;
   if (b < 1) b = 1; if (b > kMaxStatBlocks) b = kMaxStatBlocks;
   *nblk = (int)b;
-  launch_k(colreduce_fast_kernel<T, MODE>, (int)b, kStatThreads, 2 * rps * C * sizeof(float), st, x, z, stats, relu, rows, C, partials);
+  launch_k(colreduce_fast_kernel<T, MODE>, (int)b, kStatThreads, 2 * rps * C * sizeof(float), st, x, z, stats, relu, rows, C, partials, next_direction());
 }
 
 size_t stat_partials_bytes(int C) { return (size_t)kMaxStatBlocks * 2 * C * sizeof(float); }
@@ -292,12 +293,13 @@ __global__ void __launch_bounds__(256) affine_act_kernel(const T* __restrict__ x
 template <class T>
 __global__ void __launch_bounds__(256) affine_act_fast_kernel(const T* __restrict__ x, long long total, int C,
                                                               const float* __restrict__ a, const float* __restrict__ b,
-                                                              int relu, T* __restrict__ y) {
+                                                              int relu, T* __restrict__ y, int rev) {
   pdl_enter();
   constexpr int VEC = VecN<T>::N;
   long long i = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * VEC;
   const long long step = (long long)gridDim.x * blockDim.x * VEC;
-  const int c = (int)(i % C);
+  auto P = [&](long long e) { return rev ? total - VEC - e : e; };       // ping-pong traversal (common.cuh)
+  const int c = (int)(P(i) % C);
   float ca[VEC], cb[VEC];
 #pragma unroll
   for (int j = 0; j < VEC; ++j) { ca[j] = a ? a[c + j] : 1.f; cb[j] = a ? b[c + j] : 0.f; }
@@ -307,24 +309,25 @@ __global__ void __launch_bounds__(256) affine_act_fast_kernel(const T* __restric
   };
   for (; i + step < total; i += 2 * step) {
     float v0[VEC], v1[VEC];
-    ldv(x + i, v0); ldv(x + i + step, v1);
+    ldv(x + P(i), v0); ldv(x + P(i + step), v1);
     apply(v0); apply(v1);
-    stv(y + i, v0); stv(y + i + step, v1);
+    stv(y + P(i), v0); stv(y + P(i + step), v1);
   }
-  if (i < total) { float v0[VEC]; ldv(x + i, v0); apply(v0); stv(y + i, v0); }
+  if (i < total) { float v0[VEC]; ldv(x + P(i), v0); apply(v0); stv(y + P(i), v0); }
 }
 // Same pass, additionally producing the column sums / sums of squares of the STORED output as per-CTA partials
 // [blockIdx][2][C] (the layout bn_finalize reads): the BatchNorm-1 batch statistics of the next block, without its own pass.
 template <class T>
 __global__ void __launch_bounds__(256) affine_act_stats_kernel(const T* __restrict__ x, long long total, int C,
                                                                const float* __restrict__ a, const float* __restrict__ b,
-                                                               int relu, T* __restrict__ y, float* __restrict__ partials) {
+                                                               int relu, T* __restrict__ y, float* __restrict__ partials, int rev) {
   pdl_enter();
   constexpr int VEC = VecN<T>::N;
   extern __shared__ float sm[];                       // [2][rows per sweep][C]
   long long i = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * VEC;
   const long long step = (long long)gridDim.x * blockDim.x * VEC;
-  const int c = (int)(i % C);
+  auto P = [&](long long e) { return rev ? total - VEC - e : e; };       // ping-pong traversal (common.cuh)
+  const int c = (int)(P(i) % C);
   float ca[VEC], cb[VEC], s1[VEC], s2[VEC];
 #pragma unroll
   for (int j = 0; j < VEC; ++j) { ca[j] = a ? a[c + j] : 1.f; cb[j] = a ? b[c + j] : 0.f; s1[j] = 0.f; s2[j] = 0.f; }
@@ -339,11 +342,11 @@ __global__ void __launch_bounds__(256) affine_act_stats_kernel(const T* __restri
   };
   for (; i + step < total; i += 2 * step) {
     float v0[VEC], v1[VEC];
-    ldv(x + i, v0); ldv(x + i + step, v1);
+    ldv(x + P(i), v0); ldv(x + P(i + step), v1);
     apply(v0); apply(v1);
-    stv(y + i, v0); stv(y + i + step, v1);
+    stv(y + P(i), v0); stv(y + P(i + step), v1);
   }
-  if (i < total) { float v0[VEC]; ldv(x + i, v0); apply(v0); stv(y + i, v0); }
+  if (i < total) { float v0[VEC]; ldv(x + P(i), v0); apply(v0); stv(y + P(i), v0); }
   const int rps = (256 * VEC) / C, myr = (threadIdx.x * VEC) / C;
   float* a1 = sm; float* a2 = sm + rps * C;
 #pragma unroll
@@ -372,10 +375,10 @@ int32_t launch_affine_act(const T* x, long long rows, int C, const float* a, con
   if (out_nblk) *out_nblk = 0;
   if (out_partials && out_nblk && p == 0.f && elementwise_fast_ok<T>(total, C)) {
     const int nb = std::min(elementwise_blocks(total, VecN<T>::N), kMaxStatBlocks);
-    launch_k(affine_act_stats_kernel<T>, nb, 256, 2 * 256 * VecN<T>::N * sizeof(float), st, x, total, C, a, b, relu, y, out_partials);
+    launch_k(affine_act_stats_kernel<T>, nb, 256, 2 * 256 * VecN<T>::N * sizeof(float), st, x, total, C, a, b, relu, y, out_partials, next_direction());
     *out_nblk = nb;
   } else if (p == 0.f && elementwise_fast_ok<T>(total, C)) {
-    launch_k(affine_act_fast_kernel<T>, elementwise_blocks(total, VecN<T>::N), 256, 0, st, x, total, C, a, b, relu, y);
+    launch_k(affine_act_fast_kernel<T>, elementwise_blocks(total, VecN<T>::N), 256, 0, st, x, total, C, a, b, relu, y, next_direction());
   } else if (C % 4 == 0) {
     int blocks = (int)std::min<long long>((total / 4 + 255) / 256, 148 * 16);
     launch_k(affine_act_kernel<T, 4>, blocks, 256, 0, st, x, total, C, a, b, relu, p, inv_keep, seed, offset, y);
@@ -484,12 +487,13 @@ template <class T>
 __global__ void __launch_bounds__(256) bn_bwd_apply_fast_kernel(const T* __restrict__ dy, const T* __restrict__ z,
                                                                 const float* __restrict__ stats, const float* __restrict__ sums,
                                                                 long long total, int C, int relu, int training, float inv_m,
-                                                                T* __restrict__ dz) {
+                                                                T* __restrict__ dz, int rev) {
   pdl_enter();
   constexpr int VEC = VecN<T>::N;
   long long i = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * VEC;
   const long long step = (long long)gridDim.x * blockDim.x * VEC;
-  const int c = (int)(i % C);
+  auto P = [&](long long e) { return rev ? total - VEC - e : e; };       // ping-pong traversal (common.cuh)
+  const int c = (int)(P(i) % C);
   float mean[VEC], ca[VEC], cb[VEC], k1[VEC], k2[VEC];
 #pragma unroll
   for (int j = 0; j < VEC; ++j) {
@@ -508,11 +512,11 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_fast_kernel(const T* __restr
   };
   for (; i + step < total; i += 2 * step) {
     float g0[VEC], z0[VEC], g1[VEC], z1[VEC];
-    ldv(dy + i, g0); ldv(z + i, z0); ldv(dy + i + step, g1); ldv(z + i + step, z1);
+    ldv(dy + P(i), g0); ldv(z + P(i), z0); ldv(dy + P(i + step), g1); ldv(z + P(i + step), z1);
     apply(g0, z0); apply(g1, z1);
-    stv(dz + i, g0); stv(dz + i + step, g1);
+    stv(dz + P(i), g0); stv(dz + P(i + step), g1);
   }
-  if (i < total) { float g0[VEC], z0[VEC]; ldv(dy + i, g0); ldv(z + i, z0); apply(g0, z0); stv(dz + i, g0); }
+  if (i < total) { float g0[VEC], z0[VEC]; ldv(dy + P(i), g0); ldv(z + P(i), z0); apply(g0, z0); stv(dz + P(i), g0); }
 }
 
 template <class T>
@@ -524,7 +528,7 @@ int32_t launch_bn_bwd_apply(const T* dy, const T* z, const float* stats, const f
   float inv_m = 1.0f / (float)rows;
   if (p == 0.f && elementwise_fast_ok<T>(total, C)) {
     launch_k(bn_bwd_apply_fast_kernel<T>, elementwise_blocks(total, VecN<T>::N), 256, 0, st, dy, z, stats, sums, total, C, relu, training,
-                                                                                         inv_m, dz);
+                                                                                         inv_m, dz, next_direction());
   } else if (C % 4 == 0) {
     int blocks = (int)std::min<long long>((total / 4 + 255) / 256, 148 * 16);
     launch_k(bn_bwd_apply_kernel<T, 4>, blocks, 256, 0, st, dy, z, stats, sums, total, C, relu, training, inv_m, p, inv_keep, seed, offset, dz);

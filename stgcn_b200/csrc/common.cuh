@@ -45,6 +45,10 @@ __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.lau
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_enter() { pdl_trigger(); pdl_wait(); }
 bool pdl_enabled();
+// Ping-pong traversal: consecutive large kernels of a chain walk their tiles in OPPOSITE directions, so each one starts with the
+// rows its predecessor touched last -- the part of a 61 MB activation tensor that is still resident in the 126 MB L2.  Every
+// participating launcher takes the next direction from this per-thread toggle (STGCN_NO_PINGPONG=1: always ascending).
+int next_direction();
 template <class... KArgs, class... Args>
 inline void launch_k(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
   cudaLaunchConfig_t cfg = {};

@@ -82,7 +82,7 @@ static int num_sms_agg() {
 constexpr int kAggU2Threads = 320;    // agg_umma_kernel: TMA warp, MMA warp, two epilogue groups of four warps
 struct AggParams {
   int nb, t, v, ft, c, k, nch;            // nch = channels per work item (64 or 128)
-  int c_chunks, m_tiles_per_b, total_items, stages;
+  int c_chunks, m_tiles_per_b, total_items, stages, rev;
   uint32_t tmem_cols, tile_bytes;
   int transpose;                           // 0: fwd (K outputs), 1: bwd (sum over k)
   const float* aff_a; const float* aff_b;  // fwd epilogue affine (may be null)
@@ -145,6 +145,7 @@ agg_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_constan
   const uint32_t tmem_base = *tmem_slot;
 
   auto decode = [&](int item, int& cch, int& j0, int& b) {
+    if (p.rev) item = p.total_items - 1 - item;
     cch = item % p.c_chunks; item /= p.c_chunks;
     j0 = (item % p.m_tiles_per_b) * p.ft; b = item / p.m_tiles_per_b;
   };
@@ -512,6 +513,7 @@ static int32_t launch_agg_common(int transpose, const bf16* in, int nb, int t, i
   if (!umma_agg_supported(v, c, k)) { set_error("umma agg: unsupported shape V=%d C=%d K=%d", v, c, k); return STGCN_ERR_UNSUPPORTED; }
   AggPrep prep = carve_agg_prep(const_cast<void*>(prep_mem), k);
   AggParams p; memset(&p, 0, sizeof(p));
+  p.rev = next_direction();
   p.nb = nb; p.t = t; p.v = v; p.ft = 128 / v; p.c = c; p.k = k; p.transpose = transpose;
   p.nch = (c % 128 == 0 && !dA) ? 128 : 64;          // dA mode keeps a second tile ring in shared memory: 64-channel items
   p.dA = dA;

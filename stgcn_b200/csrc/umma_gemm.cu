@@ -37,6 +37,7 @@ struct UmmaParams {
   int t_out_ph;          // output frames per phase
   int t_out;             // total output frames (row index for residual / dropout)
   int n_out, bn, n_tiles, kblocks_c, m_tiles_per_b, total_tiles;
+  int rev;               // walk the tiles from the last to the first (ping-pong traversal, common.cuh)
   int stages;
   uint32_t tmem_cols;
   uint32_t a_bytes, b_bytes;
@@ -61,6 +62,7 @@ struct UmmaParams {
 struct TileCoord { int n_t, ph, j0, b; };
 __device__ __forceinline__ TileCoord decode_tile(const UmmaParams& p, int tile) {
   TileCoord t;
+  if (p.rev) tile = p.total_tiles - 1 - tile;
   t.n_t = tile % p.n_tiles; tile /= p.n_tiles;
   t.ph = tile % p.phases; tile /= p.phases;
   t.j0 = (tile % p.m_tiles_per_b) * p.ft;
@@ -478,6 +480,7 @@ int32_t launch_conv_gemm_umma(const ConvGeom& g, const bf16* in, const bf16* w, 
     set_error("umma conv-gemm: bias / scale / shift must be 16-byte aligned"); return STGCN_ERR_INVALID;
   }
   UmmaParams p; memset(&p, 0, sizeof(p));
+  p.rev = next_direction();
   const int s = g.stride;
   p.nb = g.nb; p.v = g.v; p.ft = 128 / g.v; p.t_out = g.t_out; p.n_out = g.n_out;
   p.bn = pick_bn(g.n_out); p.n_tiles = g.n_out / p.bn; p.kblocks_c = g.c / 64;

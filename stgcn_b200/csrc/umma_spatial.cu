@@ -22,7 +22,7 @@ constexpr int kSpTile = 128 * 128;          // one [128 rows][64 bf16] tile imag
 
 struct SpParams {
   int nb, t, v, ft, ci, co, k;
-  int m_tiles_per_b, total_tiles;
+  int m_tiles_per_b, total_tiles, rev;
   int cblocks;                 // ci / 64
   int wn, wparts;              // weight stage rows (<=128) and stages per (k, cc) chunk (co / wn)
   int xs, wst;                 // ring depths
@@ -88,7 +88,8 @@ spatial_fused_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_con
         for (int h = 0; h < 2; ++h) tma_load_2d_e(&map_big, smem_big + (size_t)(k * 2 + h) * kSpTile, big_bar, h * 64, k * 128);
       int xs = 0; uint32_t xph = 0; int ws = 0; uint32_t wph = 0;
       for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
-        const int j0 = (tile % p.m_tiles_per_b) * p.ft, b = tile / p.m_tiles_per_b;
+        const int tl = p.rev ? p.total_tiles - 1 - tile : tile;
+      const int j0 = (tl % p.m_tiles_per_b) * p.ft, b = tl / p.m_tiles_per_b;
         for (int cc = 0; cc < p.cblocks; ++cc) {
           mbar_wait(xempty + xs, xph ^ 1);
           mbar_expect_tx_e(xfull + xs, p.tile_bytes);
@@ -178,7 +179,8 @@ spatial_fused_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_con
     uint32_t sph = 0; int sb = 0; int och = 0;      // output-accumulator phase bits / index, output chunks so far
     uint8_t* const my_p = smem_p + (size_t)grp * kSpTile;
     for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
-      const int j0 = (tile % p.m_tiles_per_b) * p.ft, b = tile / p.m_tiles_per_b;
+      const int tl = p.rev ? p.total_tiles - 1 - tile : tile;
+      const int j0 = (tl % p.m_tiles_per_b) * p.ft, b = tl / p.m_tiles_per_b;
       int cc = 0, k = -1;
       for (int c = 0; c < chunks; ++c, ++g) {
         if (++k == p.k) { k = 0; ++cc; }
@@ -309,6 +311,7 @@ int32_t launch_spatial_fused(const bf16* x, int nb, int t, int v, int ci, int co
   const SpPlan pl = sp_plan(v, ci, co, k);
   if (!pl.ok) { set_error("fused spatial: unsupported shape V=%d Ci=%d Co=%d K=%d", v, ci, co, k); return STGCN_ERR_UNSUPPORTED; }
   SpParams p; memset(&p, 0, sizeof(p));
+  p.rev = next_direction();
   p.nb = nb; p.t = t; p.v = v; p.ft = 128 / v; p.ci = ci; p.co = co; p.k = k;
   p.m_tiles_per_b = cdiv(t, p.ft); p.total_tiles = p.m_tiles_per_b * nb;
   p.cblocks = ci / 64; p.wn = pl.wn; p.wparts = pl.wparts; p.xs = pl.xs; p.wst = pl.wst;

@@ -35,7 +35,7 @@ struct WgParams {
   int n_out, c, n_tiles, c_tiles, c_tile, n_slabs;   // n_slabs: 64-wide slabs of dout per tile (1 or 2)
   int ngroups, splits, kblocks_total, total_items;
   int stacked;                       // 64 output channels: the second dout slab is the SAME channels one frame earlier -> two taps per MMA
-  int stages;
+  int stages, rev;
   uint32_t tmem_cols, a_bytes, b_bytes;
   int b_slab;                        // bytes of one 64-channel input slab (rows * 128, rows % 8 == 0)
   WgGroup groups[kWgMaxGroups];
@@ -82,6 +82,7 @@ wgrad_umma_kernel(const __grid_constant__ CUtensorMap map_dout, const __grid_con
 
   // item -> (n_t, c_t, group, split)
   auto decode = [&](int item, int& n_t, int& c_t, int& g, int& kb0, int& kb1) {
+    if (p.rev) item = p.total_items - 1 - item;
     n_t = item % p.n_tiles; item /= p.n_tiles;
     c_t = item % p.c_tiles; item /= p.c_tiles;
     g = item % p.ngroups; item /= p.ngroups;
@@ -211,6 +212,7 @@ int32_t launch_wgrad_umma(const ConvGeom& g, const bf16* dout, const bf16* in, c
   KernelTimer kt_(KC_UMMA_WGRAD, 2.0 * g.nb * g.t_out * g.v * (double)g.c * g.n_out * g.taps, st);
   if (!umma_wgrad_supported(g)) { set_error("umma wgrad: unsupported geometry"); return STGCN_ERR_UNSUPPORTED; }
   WgParams p; memset(&p, 0, sizeof(p));
+  p.rev = next_direction();
   const int s = g.stride;
   p.stacked = (g.n_out == 64 && g.taps > 1 && getenv("STGCN_NO_TAP_STACK") == nullptr) ? 1 : 0;
   // stacked: one extra reduction step per sample so that the frame-shifted slab also covers the last output frame

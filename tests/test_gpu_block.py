@@ -282,7 +282,9 @@ def test_chained_column_statistics_match_own_pass(dtype):
         ya, ma, va = run(True)
         yb, mb, vb = run(False)
         yc, mc, vc = run(True, touch=True)
-    tol = 1e-5 if dtype == torch.float32 else 8e-3
+    # bf16: the two runs reduce in different orders (and walk their tiles in opposite directions), so stored values may differ
+    # by a bf16 ulp or two; the bound is the bf16 path's 2e-2
+    tol = 1e-5 if dtype == torch.float32 else 2e-2
     assert rel_err(ya, yb) < tol
     assert rel_err(ma, mb) < 1e-5 and rel_err(va, vb) < 1e-5
     assert rel_err(yc, yb) < tol and rel_err(mc, mb) < 1e-5
