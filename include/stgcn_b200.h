@@ -176,6 +176,16 @@ int32_t stgcn_adam_step(int32_t count, float* const* params, const float* const*
                         float* const* exp_avg_sq, const int64_t* sizes, double lr, double beta1, double beta2, double eps,
                         double weight_decay, int64_t step, void* step_state, void* stream);
 
+/* Input pipeline in front of block 0: loop-padding collate (loopy_pad_collate_fn / pad_array_with_loops, src/data/util.py:12-47),
+ * the 2-D affine augmentation (augment_data, src/data/augmentation.py:8-69) and the cast to the storage type, one launch.
+ * `packed` holds the n ragged sequences back to back in fp32: sequence i is lengths[i] frames of v*c values starting at element
+ * offsets[i] (offsets / lengths are DEVICE arrays).  out (n, t_out, v, c) of `dtype`: out[i][t] = seq_i[t mod lengths[i]]
+ * (np.pad mode='wrap'); with xform != NULL (device, n x 4 floats = the T[:2,:2] block of the reference's 3x3 matrix, row major)
+ * the first two channels of every joint become (x T00 + y T10, x T01 + y T11) -- np.dot(frames, T) with a zero homogeneous
+ * coordinate, so T's translation entries never act, exactly as in the reference. */
+int32_t stgcn_collate_pad_augment(int32_t dtype, int32_t n, int32_t t_out, int32_t v, int32_t c, const float* packed,
+                                  const int64_t* offsets, const int32_t* lengths, const float* xform, void* out, void* stream);
+
 /* Layout helpers: fp32 (n,t,v,c) <-> dtype (n,t,v,c) casts on device. */
 int32_t stgcn_cast(int32_t src_dtype, int32_t dst_dtype, const void* src, void* dst, size_t count, void* stream);
 

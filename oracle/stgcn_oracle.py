@@ -216,6 +216,62 @@ def cross_entropy(logits, labels):
     return (lse - picked).mean()
 
 
+# ----------------------------------------------------------------------------
+# input pipeline in front of block 0 (numpy, like the reference's own code)
+# ----------------------------------------------------------------------------
+
+def pad_with_loops(x, target_len):
+    """pad_array_with_loops, src/data/util.py:12-30: np.pad(mode='wrap') on the time axis of (N,T,V,C) = frame t repeats
+    frame t mod T."""
+    import numpy as np
+    t = x.shape[1]
+    if t >= target_len:
+        return x
+    idx = np.arange(target_len) % t
+    return x[:, idx]
+
+
+def loopy_pad_collate(batch):
+    """loopy_pad_collate_fn, src/data/util.py:33-47: batch = [(f_in (N_i,T_i,V,C), labels (N_i,)), ...] -> (sum N_i, T*, V, C), labels."""
+    import numpy as np
+    t_max = max(x.shape[1] for x, _ in batch)
+    return (np.concatenate([pad_with_loops(x, t_max) for x, _ in batch]), np.concatenate([np.asarray(l) for _, l in batch]))
+
+
+AUG_ROTATIONS = [15, -15, 5, -5, 10, -10]           # src/data/augmentation.py:15-17
+AUG_TRANSLATIONS = [[5, 5], [0, 5], [5, 0]]
+AUG_SCALES = [1.05, 1.1, 0.95]
+
+
+def augmentation_matrix(rng):
+    """The 3x3 matrix augment_data draws (src/data/augmentation.py:19-48), same sequence of `rng` calls: two of
+    {rotation, translation, scaling, flip} with replacement, composed in that fixed order by left multiplication."""
+    import numpy as np
+    chosen = rng.choice(['rotation', 'translation', 'scaling', 'flip'], 2)
+    T = np.eye(3)
+    if 'rotation' in chosen:
+        th = np.radians(rng.choice(AUG_ROTATIONS))
+        c, s = np.cos(th), np.sin(th)
+        T = np.array([[c, s, 0], [-s, c, 0], [0, 0, 1]]).dot(T)
+    if 'translation' in chosen:
+        tx, ty = AUG_TRANSLATIONS[rng.choice(range(3))]
+        T = np.array([[1, 0, tx], [0, 1, ty], [0, 0, 1]]).dot(T)
+    if 'scaling' in chosen:
+        f = rng.choice(AUG_SCALES)
+        T = np.array([[f, 0, 0], [0, f, 0], [0, 0, 1]]).dot(T)
+    if 'flip' in chosen:
+        T = np.array([[-1, 0, 0], [0, 1, 0], [0, 0, 1]]).dot(T)
+    return T
+
+
+def augment_apply(seqs, T):
+    """_transform_sequence, src/data/augmentation.py:53-66: (x, y, 0) . T, first two components kept -- the homogeneous
+    coordinate is 0, so only T[:2,:2] acts."""
+    import numpy as np
+    seqs = np.asarray(seqs)
+    return seqs[..., :2] @ np.asarray(T)[:2, :2]
+
+
 def cross_entropy_grad(logits, labels):
     """d cross_entropy / d logits for an incoming gradient of 1: (softmax - onehot) / N."""
     p = torch.softmax(logits, dim=1)

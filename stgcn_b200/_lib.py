@@ -75,6 +75,8 @@ def _declare(lib):
     lib.stgcn_cross_entropy_backward.argtypes = [i32, i32, _P, _P, _P, _P]
     lib.stgcn_adam_step.restype = i32
     lib.stgcn_adam_step.argtypes = [i32, _P, _P, _P, _P, _P] + [C.c_double] * 5 + [C.c_int64, _P, _P]
+    lib.stgcn_collate_pad_augment.restype = i32
+    lib.stgcn_collate_pad_augment.argtypes = [i32] * 5 + [_P] * 5 + [_P]
     lib.stgcn_cast.restype = i32; lib.stgcn_cast.argtypes = [i32, i32, _P, _P, sz, _P]
     lib.stgcn_umma_conv_gemm.restype = i32
     lib.stgcn_umma_conv_gemm.argtypes = [i32] * 9 + [_P] * 4 + [_P]
