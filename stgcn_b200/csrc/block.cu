@@ -139,12 +139,16 @@ template <class T> struct Engine {
     set_error("gemm_packed: geometry not supported by the tcgen05 engine"); return STGCN_ERR_UNSUPPORTED;
   }
   // dw (reference layout, overwritten) = sum over rows of dout (x) in
-  int32_t wgrad(const ConvGeom& g, const T* dout, const T* in, const WIndex& wi, float* dw, size_t dw_floats, int c_valid = -1) {
-    if (want_umma() && umma_wgrad_supported(g) && (g.n_out == 64 || g.n_out % 128 == 0)) {
-      float* packed = ws.template get<float>(umma_wgrad_workspace_floats(g));
+  bool wgrad_on_umma(const ConvGeom& g) const { return want_umma() && umma_wgrad_supported(g) && (g.n_out == 64 || g.n_out % 128 == 0); }
+  // packed_pre: split-K accumulator carved by the caller (packed_zero: and already cleared by an earlier kernel of the chain)
+  int32_t wgrad(const ConvGeom& g, const T* dout, const T* in, const WIndex& wi, float* dw, size_t dw_floats, int c_valid = -1,
+                float* packed_pre = nullptr, bool packed_zero = false) {
+    if (wgrad_on_umma(g)) {
+      float* packed = packed_pre ? packed_pre : ws.template get<float>(umma_wgrad_workspace_floats(g));
       if (ws.dry) return STGCN_OK;
       if (!ws.ok()) { set_error("workspace too small"); return STGCN_ERR_WORKSPACE; }
-      return launch_wgrad_umma(g, reinterpret_cast<const bf16*>(dout), reinterpret_cast<const bf16*>(in), wi, packed, dw, st, c_valid);
+      return launch_wgrad_umma(g, reinterpret_cast<const bf16*>(dout), reinterpret_cast<const bf16*>(in), wi, packed, dw, st, c_valid,
+                               packed_pre && packed_zero);
     }
     if (c_valid >= 0) { set_error("wgrad: padded reduction operand needs the tcgen05 engine"); return STGCN_ERR_UNSUPPORTED; }
     if (ws.dry) return STGCN_OK;
@@ -199,6 +203,9 @@ template <class T> struct Bn1Fold {      // backward of the folded BatchNorm-1 (
   const float* stats; int training; float* dgamma; float* dbeta; T* dx; bool done; const T* xa_saved;
   const FoldPrep* prep_saved;   // operands prepared (and kept) by forward, or null
   float* t1_ready;      // per-joint column sums of dS already produced by the temporal dgrad epilogue (or null)
+  float* t1_buf = nullptr;      // per-joint sum buffer carved by the caller (folded path)
+  float* packed_m = nullptr;    // split-K accumulator of the mixing weight gradient carved by the caller (folded path)
+  bool zeroed = false;          // dA, t1_buf and packed_m were already cleared by an earlier kernel of the chain
 };
 template <class T>
 static int32_t spatial_fwd(Engine<T>& e, const Dims& m, const T* x, const float* aff_a, const float* aff_b, int relu1,
@@ -291,7 +298,7 @@ static int32_t spatial_bwd(Engine<T>& e, const Dims& m, const T* x, const float*
   const int KCi = m.k * m.ci;
   T* XA = ws.template get<T>(m.rows_in * KCi);
   T* dXA = ws.template get<T>(m.rows_in * KCi);
-  float* t1 = (bf && bf->t1_ready) ? bf->t1_ready : ws.template get<float>((size_t)m.v * m.co);
+  float* t1 = (bf && bf->t1_ready) ? bf->t1_ready : ((bf && bf->t1_buf) ? bf->t1_buf : ws.template get<float>((size_t)m.v * m.co));
   const bool have_t1 = bf && bf->t1_ready;
   if constexpr (std::is_same<T, bf16>::value) {
     if (bf && !bf->dx && bf->xa_saved && smallc_ok<T>(e, m, aff_a, relu1)) {
@@ -339,14 +346,15 @@ static int32_t spatial_bwd(Engine<T>& e, const Dims& m, const T* x, const float*
           STGCN_TRY(launch_bn1_fold(W, Wb, A, umma_agg_rowsum_q(prep, m.k), aff_a, aff_b, m.k, m.v, m.co, m.ci, w2p, w2pT, wb, wbb, b2d, e.st));
         }
         if (!bf->xa_saved) STGCN_TRY(launch_agg_fwd_umma(x, m.n, m.t, m.v, m.ci, m.k, prep, nullptr, nullptr, XA, e.st));   // else kept by forward
-        cudaMemsetAsync(dA, 0, sizeof(float) * (size_t)m.k * m.v * m.v, e.st);
+        if (!bf->zeroed) cudaMemsetAsync(dA, 0, sizeof(float) * (size_t)m.k * m.v * m.v, e.st);
         if (!have_t1) {
-          cudaMemsetAsync(t1, 0, sizeof(float) * (size_t)m.v * m.co, e.st);
+          if (!bf->zeroed) cudaMemsetAsync(t1, 0, sizeof(float) * (size_t)m.v * m.co, e.st);
           STGCN_TRY(launch_vcolsum<T>(dS, m.frames_in, m.v, m.co, t1, e.st));
         }
       }
       STGCN_TRY(e.wgrad(geom(m.n, m.t, m.t, m.v, KCi, m.co, 1, 1, 0, 0), dS, bf->xa_saved ? bf->xa_saved : XA,
-                        widx(kNoDiv, 0, m.ci, m.ci, (long long)m.co * m.ci, 1, 0), dW, (size_t)m.k * m.co * m.ci));   // raw: w.r.t. W.diag(a)
+                        widx(kNoDiv, 0, m.ci, m.ci, (long long)m.co * m.ci, 1, 0), dW, (size_t)m.k * m.co * m.ci, -1, bf->packed_m,
+                        bf->zeroed));   // raw: w.r.t. W.diag(a)
       GemmEpilogue ep;
       STGCN_TRY(e.gemm_packed(geom(m.n, m.t, m.t, m.v, m.co, KCi, 1, 1, 0, 0), dS, w2pT, ep, dXA));         // dXA' = dXA (.) a
       if (ws.dry) return STGCN_OK;
@@ -551,14 +559,30 @@ static int32_t block_backward_t(const StgcnBlockDesc& d, const T* x, const T* y,
   const T* tin = S.S;
   T* P2 = res ? ws.get<T>(m.rows_in * m.co) : nullptr;
   T* dS = res ? ws.get<T>(m.rows_in * m.co) : dTin;
+  float* t1 = ws.get<float>((size_t)m.v * m.co);     // per-joint column sums of dS (bias / BN-fold gradients)
+  // accumulators of this chain (split-K weight-gradient tiles, dA, t1, the zero temporal-bias gradient) are cleared by the first
+  // full-grid kernel (bn_bwd_reduce) instead of one memset node each; the buffers are carved here so their addresses are known
+  const ConvGeom g_wt = geom(m.n, m.t, m.to, m.v, m.co, m.co, m.gamma, m.stride, m.pad, 0);
+  const ConvGeom g_wm = geom(m.n, m.t, m.t, m.v, m.k * m.ci, m.co, 1, 1, 0, 0);
+  const bool folded = !res && fold_ok<T>(e, m, S.stats1 + 2 * m.ci, relu1);
+  float* packed_t = (!res && e.wgrad_on_umma(g_wt)) ? ws.get<float>(umma_wgrad_workspace_floats(g_wt)) : nullptr;
+  float* packed_m = (folded && e.wgrad_on_umma(g_wm)) ? ws.get<float>(umma_wgrad_workspace_floats(g_wm)) : nullptr;
+  ZeroJobs zj;
+  if (!res) {
+    if (packed_t) zj.add(packed_t, umma_wgrad_workspace_floats(g_wt));
+    if (packed_m) zj.add(packed_m, umma_wgrad_workspace_floats(g_wm));
+    if (folded) { zj.add(G.A, (size_t)m.k * m.v * m.v); zj.add(t1, (size_t)m.v * m.co); }
+    if (d.training) zj.add(G.Wt_bias, (size_t)m.co);   // a bias before a batch-stat BN has zero gradient
+  }
   if (!ws.dry) {
     if (!ws.ok()) { set_error("workspace too small"); return STGCN_ERR_WORKSPACE; }
     if (!res) {
-      STGCN_TRY(launch_bn_bwd_reduce<T>(dy, S.U, S.stats2, m.rows_out, m.co, 1, p, d.seed, d.offset, partials, &nblk, st));
+      static const bool no_zj = getenv("STGCN_NO_ZEROJOBS") != nullptr;      // A/B switch: one memset node per accumulator
+      STGCN_TRY(launch_bn_bwd_reduce<T>(dy, S.U, S.stats2, m.rows_out, m.co, 1, p, d.seed, d.offset, partials, &nblk, st, no_zj ? nullptr : &zj));
+      if (!zj.done) for (int j = 0; j < zj.count; ++j) cudaMemsetAsync(zj.p[j], 0, sizeof(float) * zj.n[j], st);
       STGCN_TRY(launch_bn_bwd_finalize(partials, nblk, m.co, sums2, G.bn2_weight, G.bn2_bias, st));
       STGCN_TRY(launch_bn_bwd_apply<T>(dy, S.U, S.stats2, sums2, m.rows_out, m.co, 1, d.training, p, d.seed, d.offset, dU, st));
-      if (d.training) cudaMemsetAsync(G.Wt_bias, 0, sizeof(float) * m.co, st);   // a bias before a batch-stat BN has zero gradient
-      else STGCN_TRY(launch_colsum<T>(dU, m.rows_out, m.co, partials, G.Wt_bias, st));
+      if (!d.training) STGCN_TRY(launch_colsum<T>(dU, m.rows_out, m.co, partials, G.Wt_bias, st));
     } else {
       STGCN_TRY(launch_relu_bwd<T>(dy, y, m.rows_out * m.co, p, dU, st));
       STGCN_TRY(launch_colsum<T>(dU, m.rows_out, m.co, partials, G.Wt_bias, st));
@@ -566,10 +590,9 @@ static int32_t block_backward_t(const StgcnBlockDesc& d, const T* x, const T* y,
       tin = P2;
     }
   }
-  STGCN_TRY(e.wgrad(geom(m.n, m.t, m.to, m.v, m.co, m.co, m.gamma, m.stride, m.pad, 0), dU, tin,
-                    widx(kNoDiv, 0, (long long)m.co * m.gamma, kNoDiv, 0, m.gamma, 1), G.Wt, (size_t)m.co * m.co * m.gamma));
+  STGCN_TRY(e.wgrad(g_wt, dU, tin, widx(kNoDiv, 0, (long long)m.co * m.gamma, kNoDiv, 0, m.gamma, 1), G.Wt, (size_t)m.co * m.co * m.gamma,
+                    -1, packed_t, true));
   // temporal dgrad: packed [tap][n=ci][c=co] = Wt[(co*Co+ci)*gamma + tap]
-  float* t1 = ws.get<float>((size_t)m.v * m.co);     // per-joint column sums of dS (bias / BN-fold gradients)
   bool t1_ready = false;
   {
     GemmEpilogue ep;
@@ -589,6 +612,7 @@ static int32_t block_backward_t(const StgcnBlockDesc& d, const T* x, const T* y,
     STGCN_TRY(launch_bn_bwd_apply<T>(dTin, S.S, S.stats2, sums2, m.rows_in, m.co, 1, d.training, 0.f, 0, 0, dS, st));
   }
   Bn1Fold<T> bf{S.stats1, d.training, G.bn1_weight, G.bn1_bias, dx, false, S.XA, &S.fp, t1_ready ? t1 : nullptr};
+  bf.t1_buf = t1; bf.packed_m = packed_m; bf.zeroed = folded && !t1_ready;      // (with STGCN_FUSED_VSUM t1 is cleared right before its producer)
   STGCN_TRY(spatial_bwd<T>(e, m, x, S.stats1 + 2 * m.ci, S.stats1 + 3 * m.ci, relu1, P.A, P.W, P.W_bias, dS, dh, G.A, G.W, G.W_bias, &bf));
   if (!ws.dry && !bf.done) {
     STGCN_TRY(launch_bn_bwd_reduce<T>(dh, x, S.stats1, m.rows_in, m.ci, 0, 0.f, 0, 0, partials, &nblk, st));

@@ -83,8 +83,12 @@ static int stat_blocks(long long rows, int C, int vec) {
 template <class T, int MODE>
 __global__ void __launch_bounds__(kStatThreads) colreduce_fast_kernel(const T* __restrict__ x, const T* __restrict__ z,
                                                                       const float* __restrict__ stats, int relu, long long rows,
-                                                                      int C, float* __restrict__ partials, int rev) {
+                                                                      int C, float* __restrict__ partials, int rev, const ZeroJobs zj) {
   pdl_enter();
+  for (int j = 0; j < zj.count; ++j) {           // side job: clear the accumulators later kernels of the chain add into
+    float* zp = zj.p[j];
+    for (unsigned i = blockIdx.x * kStatThreads + threadIdx.x; i < zj.n[j]; i += gridDim.x * kStatThreads) zp[i] = 0.f;
+  }
   constexpr int VEC = VecN<T>::N;
   extern __shared__ float sm[];
   const int cv = C / VEC, rps = kStatThreads / cv, tid = threadIdx.x;
@@ -145,12 +149,14 @@ __global__ void __launch_bounds__(kStatThreads) colreduce_fast_kernel(const T* _
 template <class T> static bool colreduce_fast_ok(int C) { return C % VecN<T>::N == 0 && C / VecN<T>::N <= kStatThreads; }
 template <class T, int MODE>
 static void launch_colreduce_fast(const T* x, const T* z, const float* stats, int relu, long long rows, int C, float* partials,
-                                  int* nblk, cudaStream_t st) {
+                                  int* nblk, cudaStream_t st, ZeroJobs* zero = nullptr) {
   const int cv = C / VecN<T>::N, rps = kStatThreads / cv;
   long long b = (rows + rps - 1) / rps; b = (b + 7) / 8;
   if (b < 1) b = 1; if (b > kMaxStatBlocks) b = kMaxStatBlocks;
   *nblk = (int)b;
-  launch_k(colreduce_fast_kernel<T, MODE>, (int)b, kStatThreads, 2 * rps * C * sizeof(float), st, x, z, stats, relu, rows, C, partials, next_direction());
+  launch_k(colreduce_fast_kernel<T, MODE>, (int)b, kStatThreads, 2 * rps * C * sizeof(float), st, x, z, stats, relu, rows, C, partials, next_direction(),
+           zero ? *zero : ZeroJobs());
+  if (zero) zero->done = true;
 }
 
 size_t stat_partials_bytes(int C) { return (size_t)kMaxStatBlocks * 2 * C * sizeof(float); }
@@ -417,11 +423,11 @@ struct BwdRedF {
 
 template <class T>
 int32_t launch_bn_bwd_reduce(const T* dy, const T* z, const float* stats, long long rows, int C, int relu, float p,
-                             uint64_t seed, uint64_t offset, float* partials, int* nblk, cudaStream_t st) {
+                             uint64_t seed, uint64_t offset, float* partials, int* nblk, cudaStream_t st, ZeroJobs* zero) {
   KernelTimer kt_(KC_BN_STATS, (double)rows * C, st);
   float inv_keep = p > 0.f ? 1.f / (1.f - p) : 1.f;
   if (p == 0.f && colreduce_fast_ok<T>(C)) {
-    launch_colreduce_fast<T, 1>(dy, z, stats, relu, rows, C, partials, nblk, st);
+    launch_colreduce_fast<T, 1>(dy, z, stats, relu, rows, C, partials, nblk, st, zero);
   } else if (C % 4 == 0) {
     int nb = stat_blocks(rows, C, 4); *nblk = nb;
     int rps = kStatThreads / (C / 4);
@@ -436,8 +442,8 @@ int32_t launch_bn_bwd_reduce(const T* dy, const T* z, const float* stats, long l
   STGCN_CHECK_LAUNCH("bn_bwd_reduce");
   return STGCN_OK;
 }
-template int32_t launch_bn_bwd_reduce<float>(const float*, const float*, const float*, long long, int, int, float, uint64_t, uint64_t, float*, int*, cudaStream_t);
-template int32_t launch_bn_bwd_reduce<bf16>(const bf16*, const bf16*, const float*, long long, int, int, float, uint64_t, uint64_t, float*, int*, cudaStream_t);
+template int32_t launch_bn_bwd_reduce<float>(const float*, const float*, const float*, long long, int, int, float, uint64_t, uint64_t, float*, int*, cudaStream_t, ZeroJobs*);
+template int32_t launch_bn_bwd_reduce<bf16>(const bf16*, const bf16*, const float*, long long, int, int, float, uint64_t, uint64_t, float*, int*, cudaStream_t, ZeroJobs*);
 
 // sums[2][C] = {s1, s2} reduced in double; also emits dgamma = s2, dbeta = s1
 __global__ void __launch_bounds__(kFinThreads)

@@ -44,6 +44,14 @@ struct KernelTimer {     // records an event pair around the launches issued in 
   int idx_; cudaStream_t st_;
 };
 
+// Small fp32 buffers that must be zero before later kernels of a chain accumulate into them (split-K weight-gradient tiles, dA,
+// per-joint sums).  Instead of one memset node each -- which also breaks the programmatic launch chain -- the first full-grid
+// kernel of the chain clears them on the side (bn_bwd_reduce's fast path).
+struct ZeroJobs {
+  float* p[6]; unsigned n[6]; int count = 0; bool done = false;
+  void add(float* ptr, size_t floats) { if (ptr && floats && count < 6) { p[count] = ptr; n[count] = (unsigned)floats; ++count; } }
+};
+
 // bn_kernels.cu
 size_t stat_partials_bytes(int C);
 template <class T> int32_t launch_colstats(const T* x, long long rows, int C, float* partials, int* nblk, cudaStream_t st);
@@ -56,7 +64,8 @@ template <class T> int32_t launch_affine_act(const T* x, long long rows, int C, 
                                             uint64_t seed, uint64_t offset, T* y, cudaStream_t st, float* out_partials = nullptr,
                                             int* out_nblk = nullptr);
 template <class T> int32_t launch_bn_bwd_reduce(const T* dy, const T* z, const float* stats, long long rows, int C, int relu, float p,
-                                               uint64_t seed, uint64_t offset, float* partials, int* nblk, cudaStream_t st);
+                                               uint64_t seed, uint64_t offset, float* partials, int* nblk, cudaStream_t st,
+                                               ZeroJobs* zero = nullptr);
 int32_t launch_bn_bwd_finalize(const float* partials, int nblk, int C, float* sums, float* dgamma, float* dbeta, cudaStream_t st);
 template <class T> int32_t launch_bn_bwd_apply(const T* dy, const T* z, const float* stats, const float* sums, long long rows, int C,
                                               int relu, int training, float p, uint64_t seed, uint64_t offset, T* dz, cudaStream_t st);
@@ -101,7 +110,7 @@ int32_t launch_conv_gemm_umma(const ConvGeom& g, const bf16* in, const bf16* w, 
 bool umma_wgrad_supported(const ConvGeom& g);
 size_t umma_wgrad_workspace_floats(const ConvGeom& g);
 int32_t launch_wgrad_umma(const ConvGeom& g, const bf16* dout, const bf16* in, const WIndex& wi, float* packed_ws, float* dw,
-                          cudaStream_t st, int c_valid = -1);
+                          cudaStream_t st, int c_valid = -1, bool packed_is_zero = false);
 
 // umma_agg.cu  (tensor-core adjacency aggregation, bf16)
 bool umma_agg_supported(int V, int C, int K);

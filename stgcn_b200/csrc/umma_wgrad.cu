@@ -208,7 +208,7 @@ static int num_sms_wg() {
 }
 
 int32_t launch_wgrad_umma(const ConvGeom& g, const bf16* dout, const bf16* in, const WIndex& wi, float* packed_ws, float* dw,
-                          cudaStream_t st, int c_valid) {
+                          cudaStream_t st, int c_valid, bool packed_is_zero) {
   KernelTimer kt_(KC_UMMA_WGRAD, 2.0 * g.nb * g.t_out * g.v * (double)g.c * g.n_out * g.taps, st);
   if (!umma_wgrad_supported(g)) { set_error("umma wgrad: unsupported geometry"); return STGCN_ERR_UNSUPPORTED; }
   WgParams p; memset(&p, 0, sizeof(p));
@@ -279,7 +279,7 @@ int32_t launch_wgrad_umma(const ConvGeom& g, const bf16* dout, const bf16* in, c
   uint32_t cols = 32; while (cols < (uint32_t)(maxt * p.c_tile)) cols <<= 1;
   p.tmem_cols = cols;
   p.packed = packed_ws;
-  cudaMemsetAsync(packed_ws, 0, sizeof(float) * umma_wgrad_workspace_floats(g), st);
+  if (!packed_is_zero) cudaMemsetAsync(packed_ws, 0, sizeof(float) * umma_wgrad_workspace_floats(g), st);
 
   CUtensorMap map_dout, map_in;
   const uint64_t C = g.c, V = g.v, N = g.n_out;

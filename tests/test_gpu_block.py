@@ -286,5 +286,8 @@ def test_chained_column_statistics_match_own_pass(dtype):
     # by a bf16 ulp or two; the bound is the bf16 path's 2e-2
     tol = 1e-5 if dtype == torch.float32 else 2e-2
     assert rel_err(ya, yb) < tol
-    assert rel_err(ma, mb) < 1e-5 and rel_err(va, vb) < 1e-5
-    assert rel_err(yc, yb) < tol and rel_err(mc, mb) < 1e-5
+    # running statistics of block 2's BatchNorm-1 = moments of block 1's STORED output, which in bf16 differs by an ulp here and
+    # there between two runs (see above); in fp32 the two ways of getting them agree to rounding
+    stol = 1e-5 if dtype == torch.float32 else 1e-2
+    assert rel_err(ma, mb) < stol and rel_err(va, vb) < stol
+    assert rel_err(yc, yb) < tol and rel_err(mc, mb) < stol
