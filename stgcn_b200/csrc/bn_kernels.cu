@@ -81,9 +81,9 @@ static int stat_blocks(long long rows, int C, int vec) {
 //   MODE 1: g = dy*[a*z+b > 0 if relu], h = g*(z-mean)*invstd   (BatchNorm backward sums; no dropout)
 // ---------------------------------------------------------------------------
 template <class T, int MODE>
-__global__ void __launch_bounds__(kStatThreads) colreduce_fast_kernel(const T* __restrict__ x, const T* __restrict__ z,
+__global__ void __launch_bounds__(kStatThreads, 2) colreduce_fast_kernel(const T* __restrict__ x, const T* __restrict__ z,
                                                                       const float* __restrict__ stats, int relu, long long rows,
-                                                                      int C, float* __restrict__ partials, int rev, const ZeroJobs zj) {
+                                                                      int C, float* __restrict__ partials, int rev, const __grid_constant__ ZeroJobs zj) {
   pdl_enter();
   for (int j = 0; j < zj.count; ++j) {           // side job: clear the accumulators later kernels of the chain add into
     float* zp = zj.p[j];

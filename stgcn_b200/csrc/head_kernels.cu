@@ -26,27 +26,37 @@ __global__ void __launch_bounds__(256) pool_vec_kernel(const T* __restrict__ fea
   constexpr int VEC = VecN<T>::N;
   const int n = blockIdx.x, cv = C / VEC, lanes = 256 / cv;        // host guarantees cv <= 256
   const int myc = (threadIdx.x % cv) * VEC, myr = threadIdx.x / cv;
-  if (myr >= lanes) return;
+  __shared__ float part[256 * 8];                  // [lanes][C] partial sums of this CTA (lanes * C = 256 * VEC <= 2048)
+  const bool active = myr < lanes;
   const T* f = feat + (size_t)n * rows * C + myc;
   float s[VEC];
 #pragma unroll
   for (int i = 0; i < VEC; ++i) s[i] = 0.f;
-  const int step = gridDim.y * lanes;
-  int r = blockIdx.y * lanes + myr;
-  for (; r + 3 * step < rows; r += 4 * step) {
-    float a[4][VEC];
+  if (active) {
+    const int step = gridDim.y * lanes;
+    int r = blockIdx.y * lanes + myr;
+    for (; r + 3 * step < rows; r += 4 * step) {
+      float a[4][VEC];
 #pragma unroll
-    for (int u = 0; u < 4; ++u) ldv(f + (size_t)(r + u * step) * C, a[u]);
+      for (int u = 0; u < 4; ++u) ldv(f + (size_t)(r + u * step) * C, a[u]);
 #pragma unroll
-    for (int i = 0; i < VEC; ++i) s[i] += (a[0][i] + a[1][i]) + (a[2][i] + a[3][i]);
+      for (int i = 0; i < VEC; ++i) s[i] += (a[0][i] + a[1][i]) + (a[2][i] + a[3][i]);
+    }
+    for (; r < rows; r += step) {
+      float a[VEC]; ldv(f + (size_t)r * C, a);
+#pragma unroll
+      for (int i = 0; i < VEC; ++i) s[i] += a[i];
+    }
+#pragma unroll
+    for (int i = 0; i < VEC; ++i) part[myr * C + myc + i] = s[i];
   }
-  for (; r < rows; r += step) {
-    float a[VEC]; ldv(f + (size_t)r * C, a);
-#pragma unroll
-    for (int i = 0; i < VEC; ++i) s[i] += a[i];
+  __syncthreads();
+  // one atomic per channel per CTA (not per thread): the row lanes of the CTA are folded in shared memory first
+  for (int c = threadIdx.x; c < C; c += 256) {
+    float t = 0.f;
+    for (int l = 0; l < lanes; ++l) t += part[l * C + c];
+    atomicAdd(pooled + (size_t)n * C + c, t * inv_rows);
   }
-#pragma unroll
-  for (int i = 0; i < VEC; ++i) atomicAdd(pooled + (size_t)n * C + myc + i, s[i] * inv_rows);
 }
 template <class T>
 __global__ void __launch_bounds__(256) pool_bwd_vec_kernel(const float* __restrict__ dpooled, int rows, int C, float inv_rows, T* __restrict__ dfeat) {
