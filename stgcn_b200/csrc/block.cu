@@ -6,6 +6,8 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <mutex>
+
 #include "kernels.cuh"
 
 namespace stgcn {
@@ -110,6 +112,30 @@ template <class T> static Saved<T> carve_saved(Arena& a, const StgcnBlockDesc& d
   return s;
 }
 
+// ---- side lane: a second stream per device for work that is off the data-gradient path of a chain (per-joint sums, weight-gradient
+// layout change).  Forked from / joined to the caller's stream with events inside one library call, so the caller never sees it;
+// under CUDA-graph capture the fork/join become graph edges.  STGCN_NO_SIDE=1 keeps everything on the caller's stream.
+struct SideLane { cudaStream_t s = nullptr; cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr}; bool ok = false; };
+static SideLane* side_lane() {
+  static const bool off = getenv("STGCN_NO_SIDE") != nullptr;
+  if (off) return nullptr;
+  static std::mutex mu;
+  static SideLane lanes[64];
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+  std::lock_guard<std::mutex> lk(mu);
+  SideLane& l = lanes[dev];
+  if (!l.s) {
+    cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+    (void)cs;
+    if (cudaStreamCreateWithFlags(&l.s, cudaStreamNonBlocking) != cudaSuccess) { l.s = nullptr; cudaGetLastError(); return nullptr; }
+    l.ok = true;
+    for (int i = 0; i < 4; ++i)
+      if (cudaEventCreateWithFlags(&l.ev[i], cudaEventDisableTiming) != cudaSuccess) { l.ok = false; cudaGetLastError(); }
+  }
+  return l.ok ? &l : nullptr;
+}
+
 // ---- GEMM dispatch: tcgen05 engine for bf16 when the shape fits, else CUDA cores ----
 template <class T> struct Engine {
   const StgcnBlockDesc& d; Arena& ws; cudaStream_t st;
@@ -142,13 +168,13 @@ template <class T> struct Engine {
   bool wgrad_on_umma(const ConvGeom& g) const { return want_umma() && umma_wgrad_supported(g) && (g.n_out == 64 || g.n_out % 128 == 0); }
   // packed_pre: split-K accumulator carved by the caller (packed_zero: and already cleared by an earlier kernel of the chain)
   int32_t wgrad(const ConvGeom& g, const T* dout, const T* in, const WIndex& wi, float* dw, size_t dw_floats, int c_valid = -1,
-                float* packed_pre = nullptr, bool packed_zero = false) {
+                float* packed_pre = nullptr, bool packed_zero = false, cudaStream_t unpack_st = nullptr, cudaEvent_t unpack_ev = nullptr) {
     if (wgrad_on_umma(g)) {
       float* packed = packed_pre ? packed_pre : ws.template get<float>(umma_wgrad_workspace_floats(g));
       if (ws.dry) return STGCN_OK;
       if (!ws.ok()) { set_error("workspace too small"); return STGCN_ERR_WORKSPACE; }
       return launch_wgrad_umma(g, reinterpret_cast<const bf16*>(dout), reinterpret_cast<const bf16*>(in), wi, packed, dw, st, c_valid,
-                               packed_pre && packed_zero);
+                               packed_pre && packed_zero, unpack_st, unpack_ev);
     }
     if (c_valid >= 0) { set_error("wgrad: padded reduction operand needs the tcgen05 engine"); return STGCN_ERR_UNSUPPORTED; }
     if (ws.dry) return STGCN_OK;
@@ -206,6 +232,7 @@ template <class T> struct Bn1Fold {      // backward of the folded BatchNorm-1 (
   float* t1_buf = nullptr;      // per-joint sum buffer carved by the caller (folded path)
   float* packed_m = nullptr;    // split-K accumulator of the mixing weight gradient carved by the caller (folded path)
   bool zeroed = false;          // dA, t1_buf and packed_m were already cleared by an earlier kernel of the chain
+  bool bias_grads_done = false; // dW_bias and the rank-1 part of dA were already issued by the caller (side lane)
 };
 template <class T>
 static int32_t spatial_fwd(Engine<T>& e, const Dims& m, const T* x, const float* aff_a, const float* aff_b, int relu1,
@@ -364,7 +391,7 @@ static int32_t spatial_bwd(Engine<T>& e, const Dims& m, const T* x, const float*
       STGCN_TRY(launch_bn1_fold_grads(W, dW, bf->stats, t1, umma_agg_rowsum_q(prep, m.k), m.k, m.v, m.co, m.ci, bf->training,
                                       (double)m.rows_in, bf->dgamma, bf->dbeta, coef, e.st));
       if (bf->dx) STGCN_TRY(launch_agg_bwd_umma(dXA, m.n, m.t, m.v, m.ci, m.k, prep, nullptr, bf->dx, e.st, x, coef, merged ? dA : nullptr));
-      STGCN_TRY(launch_spatial_bias_grads(t1, A, Wb, m.k, m.v, m.co, dWb, dA, e.st, wbb));
+      if (!bf->bias_grads_done) STGCN_TRY(launch_spatial_bias_grads(t1, A, Wb, m.k, m.v, m.co, dWb, dA, e.st, wbb));
       return STGCN_OK;
     }
   }
@@ -590,8 +617,14 @@ static int32_t block_backward_t(const StgcnBlockDesc& d, const T* x, const T* y,
       tin = P2;
     }
   }
-  STGCN_TRY(e.wgrad(g_wt, dU, tin, widx(kNoDiv, 0, (long long)m.co * m.gamma, kNoDiv, 0, m.gamma, 1), G.Wt, (size_t)m.co * m.co * m.gamma,
-                    -1, packed_t, true));
+  // With the side lane the temporal data gradient goes first; the (HBM-bound) per-joint sums of dS then run beside the
+  // (tensor-bound) temporal weight gradient, whose layout change follows on the side lane as well.
+  SideLane* lane = (!res && folded && packed_t && !ws.dry) ? side_lane() : nullptr;
+  auto temporal_wgrad = [&]() -> int32_t {
+    return e.wgrad(g_wt, dU, tin, widx(kNoDiv, 0, (long long)m.co * m.gamma, kNoDiv, 0, m.gamma, 1), G.Wt, (size_t)m.co * m.co * m.gamma,
+                   -1, packed_t, true, lane ? lane->s : nullptr, lane ? lane->ev[2] : nullptr);
+  };
+  if (!lane) STGCN_TRY(temporal_wgrad());
   // temporal dgrad: packed [tap][n=ci][c=co] = Wt[(co*Co+ci)*gamma + tap]
   bool t1_ready = false;
   {
@@ -606,13 +639,29 @@ static int32_t block_backward_t(const StgcnBlockDesc& d, const T* x, const T* y,
     }
     STGCN_TRY(e.gemm(gd, dU, P.Wt, widx(kNoDiv, 0, m.gamma, kNoDiv, 0, (long long)m.co * m.gamma, 1), ep, dTin));
   }
+  bool side_bias_grads = false;
+  const bool t1_from_epilogue = t1_ready;        // (STGCN_FUSED_VSUM: cleared right before its producer, not by the zero jobs)
+  if (lane) {
+    if (!t1_ready) {
+      cudaEventRecord(lane->ev[0], st); cudaStreamWaitEvent(lane->s, lane->ev[0], 0);
+      STGCN_TRY(launch_vcolsum<T>(dS, m.frames_in, m.v, m.co, t1, lane->s));       // t1 was cleared by the zero jobs / memsets above
+      cudaEventRecord(lane->ev[1], lane->s);
+      if (S.fp.valid) {      // dW_bias and the rank-1 part of dA need only t1 and operands kept by forward (dA takes atomics from both lanes)
+        STGCN_TRY(launch_spatial_bias_grads(t1, P.A, P.W_bias, m.k, m.v, m.co, G.W_bias, G.A, lane->s, S.fp.wbb));
+        side_bias_grads = true;
+      }
+    }
+    STGCN_TRY(temporal_wgrad());                       // caller's stream; its unpack waits on ev[2] on the side lane
+    cudaEventRecord(lane->ev[3], lane->s);             // everything issued to the side lane so far
+    if (!t1_ready) { cudaStreamWaitEvent(st, lane->ev[1], 0); t1_ready = true; }
+  }
   if (res && !ws.dry) {
     STGCN_TRY(launch_bn_bwd_reduce<T>(dTin, S.S, S.stats2, m.rows_in, m.co, 1, 0.f, 0, 0, partials, &nblk, st));
     STGCN_TRY(launch_bn_bwd_finalize(partials, nblk, m.co, sums2, G.bn2_weight, G.bn2_bias, st));
     STGCN_TRY(launch_bn_bwd_apply<T>(dTin, S.S, S.stats2, sums2, m.rows_in, m.co, 1, d.training, 0.f, 0, 0, dS, st));
   }
   Bn1Fold<T> bf{S.stats1, d.training, G.bn1_weight, G.bn1_bias, dx, false, S.XA, &S.fp, t1_ready ? t1 : nullptr};
-  bf.t1_buf = t1; bf.packed_m = packed_m; bf.zeroed = folded && !t1_ready;      // (with STGCN_FUSED_VSUM t1 is cleared right before its producer)
+  bf.t1_buf = t1; bf.packed_m = packed_m; bf.zeroed = folded && !t1_from_epilogue; bf.bias_grads_done = side_bias_grads;      // (with STGCN_FUSED_VSUM t1 is cleared right before its producer)
   STGCN_TRY(spatial_bwd<T>(e, m, x, S.stats1 + 2 * m.ci, S.stats1 + 3 * m.ci, relu1, P.A, P.W, P.W_bias, dS, dh, G.A, G.W, G.W_bias, &bf));
   if (!ws.dry && !bf.done) {
     STGCN_TRY(launch_bn_bwd_reduce<T>(dh, x, S.stats1, m.rows_in, m.ci, 0, 0.f, 0, 0, partials, &nblk, st));
@@ -630,6 +679,7 @@ static int32_t block_backward_t(const StgcnBlockDesc& d, const T* x, const T* y,
       STGCN_TRY(e.gemm(geom(m.n, m.to, m.t, m.v, m.co, m.ci, 1, m.stride, 0, 1), dU, P.Wr, widx(kNoDiv, 0, 1, kNoDiv, 0, m.ci, 0), ep, dx));
     }
   }
+  if (lane) cudaStreamWaitEvent(st, lane->ev[3], 0);     // join: nothing of this call is left on the side lane when it returns
   if (!ws.ok()) { set_error("workspace too small"); return STGCN_ERR_WORKSPACE; }
   return STGCN_OK;
 }

@@ -305,7 +305,10 @@ __global__ void __launch_bounds__(256) affine_act_fast_kernel(const T* __restric
   long long i = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * VEC;
   const long long step = (long long)gridDim.x * blockDim.x * VEC;
   auto P = [&](long long e) { return rev ? total - VEC - e : e; };       // ping-pong traversal (common.cuh)
-  const int c = (int)(P(i) % C);
+  // column group of this thread: total % C == 0, so the mirrored position has column C - VEC - c0 (computed without P(i),
+  // which is negative for threads beyond the data -- their slot must stay their own)
+  const int c0 = (int)(i % C);
+  const int c = rev ? C - VEC - c0 : c0;
   float ca[VEC], cb[VEC];
 #pragma unroll
   for (int j = 0; j < VEC; ++j) { ca[j] = a ? a[c + j] : 1.f; cb[j] = a ? b[c + j] : 0.f; }
@@ -333,7 +336,10 @@ __global__ void __launch_bounds__(256) affine_act_stats_kernel(const T* __restri
   long long i = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * VEC;
   const long long step = (long long)gridDim.x * blockDim.x * VEC;
   auto P = [&](long long e) { return rev ? total - VEC - e : e; };       // ping-pong traversal (common.cuh)
-  const int c = (int)(P(i) % C);
+  // column group of this thread: total % C == 0, so the mirrored position has column C - VEC - c0 (computed without P(i),
+  // which is negative for threads beyond the data -- their slot must stay their own)
+  const int c0 = (int)(i % C);
+  const int c = rev ? C - VEC - c0 : c0;
   float ca[VEC], cb[VEC], s1[VEC], s2[VEC];
 #pragma unroll
   for (int j = 0; j < VEC; ++j) { ca[j] = a ? a[c + j] : 1.f; cb[j] = a ? b[c + j] : 0.f; s1[j] = 0.f; s2[j] = 0.f; }
@@ -499,7 +505,10 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_fast_kernel(const T* __restr
   long long i = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * VEC;
   const long long step = (long long)gridDim.x * blockDim.x * VEC;
   auto P = [&](long long e) { return rev ? total - VEC - e : e; };       // ping-pong traversal (common.cuh)
-  const int c = (int)(P(i) % C);
+  // column group of this thread: total % C == 0, so the mirrored position has column C - VEC - c0 (computed without P(i),
+  // which is negative for threads beyond the data -- their slot must stay their own)
+  const int c0 = (int)(i % C);
+  const int c = rev ? C - VEC - c0 : c0;
   float mean[VEC], ca[VEC], cb[VEC], k1[VEC], k2[VEC];
 #pragma unroll
   for (int j = 0; j < VEC; ++j) {

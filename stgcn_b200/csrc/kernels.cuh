@@ -110,7 +110,8 @@ int32_t launch_conv_gemm_umma(const ConvGeom& g, const bf16* in, const bf16* w, 
 bool umma_wgrad_supported(const ConvGeom& g);
 size_t umma_wgrad_workspace_floats(const ConvGeom& g);
 int32_t launch_wgrad_umma(const ConvGeom& g, const bf16* dout, const bf16* in, const WIndex& wi, float* packed_ws, float* dw,
-                          cudaStream_t st, int c_valid = -1, bool packed_is_zero = false);
+                          cudaStream_t st, int c_valid = -1, bool packed_is_zero = false, cudaStream_t unpack_st = nullptr,
+                          cudaEvent_t unpack_ev = nullptr);
 
 // umma_agg.cu  (tensor-core adjacency aggregation, bf16)
 bool umma_agg_supported(int V, int C, int K);

@@ -208,7 +208,7 @@ static int num_sms_wg() {
 }
 
 int32_t launch_wgrad_umma(const ConvGeom& g, const bf16* dout, const bf16* in, const WIndex& wi, float* packed_ws, float* dw,
-                          cudaStream_t st, int c_valid, bool packed_is_zero) {
+                          cudaStream_t st, int c_valid, bool packed_is_zero, cudaStream_t unpack_st, cudaEvent_t unpack_ev) {
   KernelTimer kt_(KC_UMMA_WGRAD, 2.0 * g.nb * g.t_out * g.v * (double)g.c * g.n_out * g.taps, st);
   if (!umma_wgrad_supported(g)) { set_error("umma wgrad: unsupported geometry"); return STGCN_ERR_UNSUPPORTED; }
   WgParams p; memset(&p, 0, sizeof(p));
@@ -306,7 +306,11 @@ int32_t launch_wgrad_umma(const ConvGeom& g, const bf16* dout, const bf16* in, c
   launch_k(wgrad_umma_kernel, grid, kWgThreads, smem, st, map_dout, map_in, p);
   STGCN_CHECK_LAUNCH("wgrad_umma");
   size_t total = umma_wgrad_workspace_floats(g);
-  launch_k(wgrad_unpack_kernel, (int)std::min<size_t>((total + 255) / 256, 148 * 4), 256, 0, st, packed_ws, wi, g.taps, g.n_out, g.c, c_valid < 0 ? g.c : c_valid, dw);
+  cudaStream_t ust = st;
+  if (unpack_st && unpack_ev) {      // the layout change is off the data-gradient path: let it run beside the next kernels
+    cudaEventRecord(unpack_ev, st); cudaStreamWaitEvent(unpack_st, unpack_ev, 0); ust = unpack_st;
+  }
+  launch_k(wgrad_unpack_kernel, (int)std::min<size_t>((total + 255) / 256, 148 * 4), 256, 0, ust, packed_ws, wi, g.taps, g.n_out, g.c, c_valid < 0 ? g.c : c_valid, dw);
   STGCN_CHECK_LAUNCH("wgrad_unpack");
   return STGCN_OK;
 }

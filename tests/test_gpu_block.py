@@ -291,3 +291,30 @@ def test_chained_column_statistics_match_own_pass(dtype):
     stol = 1e-5 if dtype == torch.float32 else 1e-2
     assert rel_err(ma, mb) < stol and rel_err(va, vb) < stol
     assert rel_err(yc, yb) < tol and rel_err(mc, mb) < stol
+
+
+@pytest.mark.parametrize('dtype', [torch.float32, torch.bfloat16], ids=['float32', 'bfloat16'])
+def test_chained_statistics_equal_moments_of_stored_output_in_both_directions(dtype):
+    """The statistics block i hands to block i+1 are the moments of the output AS STORED, whichever way the element-wise pass
+    walked the tensor (ping-pong traversal) and also when its grid is larger than the tensor (threads beyond the data).  An odd
+    number of participating launches between iterations flips the direction every time."""
+    torch.manual_seed(5)
+    A = torch.rand(3, 25, 25) * 0.2
+    b1 = build_block(64, 64, A, 1, False, dtype=dtype).train()
+    b2 = build_block(64, 128, A, 2, False, dtype=dtype).train()
+    x = torch.randn(4, 64, 20, 25).cuda()
+    sd = {k: v.clone() for k, v in b2.state_dict().items()}
+    with torch.no_grad():
+        for it in range(6):
+            if it in (2, 3):
+                b1(x)
+            b2.load_state_dict(sd)
+            y1 = b1(x)
+            assert hasattr(y1, '_stgcn_colstats')
+            if it % 2:
+                del y1._stgcn_colstats
+            ref_mean = y1.float().mean((0, 2, 3)) * 0.1
+            ref_var = y1.float().var((0, 2, 3), unbiased=True) * 0.1 + 0.9
+            b2(y1)
+            assert rel_err(b2.batch_n.running_mean, ref_mean) < 1e-5, it
+            assert rel_err(b2.batch_n.running_var, ref_var) < 1e-5, it
