@@ -115,7 +115,8 @@ template <class T> static Saved<T> carve_saved(Arena& a, const StgcnBlockDesc& d
 // ---- side lane: a second stream per device for work that is off the data-gradient path of a chain (per-joint sums, weight-gradient
 // layout change).  Forked from / joined to the caller's stream with events inside one library call, so the caller never sees it;
 // under CUDA-graph capture the fork/join become graph edges.  STGCN_NO_SIDE=1 keeps everything on the caller's stream.
-struct SideLane { cudaStream_t s = nullptr; cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr}; bool ok = false; };
+constexpr int kLaneEvents = 6;
+struct SideLane { cudaStream_t s = nullptr; cudaEvent_t ev[kLaneEvents] = {}; bool ok = false; };
 static SideLane* side_lane() {
   static const bool off = getenv("STGCN_NO_SIDE") != nullptr;
   if (off) return nullptr;
@@ -130,7 +131,7 @@ static SideLane* side_lane() {
     (void)cs;
     if (cudaStreamCreateWithFlags(&l.s, cudaStreamNonBlocking) != cudaSuccess) { l.s = nullptr; cudaGetLastError(); return nullptr; }
     l.ok = true;
-    for (int i = 0; i < 4; ++i)
+    for (int i = 0; i < kLaneEvents; ++i)
       if (cudaEventCreateWithFlags(&l.ev[i], cudaEventDisableTiming) != cudaSuccess) { l.ok = false; cudaGetLastError(); }
   }
   return l.ok ? &l : nullptr;
@@ -153,6 +154,22 @@ template <class T> struct Engine {
     if (!ws.ok()) { set_error("workspace too small"); return STGCN_ERR_WORKSPACE; }
     STGCN_TRY(launch_pack_weights<float>(wsrc, wi, g.taps, g.n_out, g.c, wp, st, std::is_same<T, bf16>::value ? 1 : 0));
     return launch_conv_gemm_simt<T>(g, in, wp, ep, out, st);
+  }
+  // Weights packed ahead of their GEMM (they depend on parameters only): on the side lane, beside whatever the caller's stream runs
+  // first, or -- without a lane -- right here.  The buffer is carved in every mode so the dry run plans the same arena.
+  // Use with gemm_packed() after waiting on `done` (recorded on the side lane).
+  bf16* prepack(const ConvGeom& g, const float* wsrc, const WIndex& wi, SideLane* lane, cudaEvent_t fork, cudaEvent_t done, int32_t* rc) {
+    *rc = STGCN_OK;
+    bf16* wp = ws.template get<bf16>((size_t)g.taps * g.n_out * g.c);
+    if (ws.dry || !ws.ok()) return wp;
+    if (lane) {
+      cudaEventRecord(fork, st); cudaStreamWaitEvent(lane->s, fork, 0);
+      *rc = launch_pack_weights<bf16>(wsrc, wi, g.taps, g.n_out, g.c, wp, lane->s);
+      cudaEventRecord(done, lane->s);
+    } else {
+      *rc = launch_pack_weights<bf16>(wsrc, wi, g.taps, g.n_out, g.c, wp, st);
+    }
+    return wp;
   }
   // true when gemm() runs on the tcgen05 engine, whose epilogue can also produce BatchNorm statistics / per-joint sums
   bool gemm_on_umma(const ConvGeom& g) const { return want_umma() && umma_conv_gemm_supported(g); }
@@ -473,11 +490,20 @@ static int32_t block_forward_t(const StgcnBlockDesc& d, const T* x, const StgcnB
       STGCN_TRY(launch_bn_eval_coeffs(m.ci, P.bn1_weight, P.bn1_bias, P.bn1_running_mean, P.bn1_running_var, d.bn_eps, S.stats1, st));
     }
   }
-  STGCN_TRY(spatial_fwd<T>(e, m, x, S.stats1 + 2 * m.ci, S.stats1 + 3 * m.ci, relu1, P.A, P.W, P.W_bias, S.S, saved_mem ? S.XA : nullptr, saved_mem ? &S.fp : nullptr));
-
   // temporal weights: packed [tap][n=co][c=ci] = Wt[(co*Co+ci)*gamma + tap]
   const WIndex wiT = widx(kNoDiv, 0, (long long)m.co * m.gamma, kNoDiv, 0, m.gamma, 1);
   const ConvGeom gt = geom(m.n, m.t, m.to, m.v, m.co, m.co, m.gamma, m.stride, m.pad, 0);
+  // training chain on the tcgen05 engine: the temporal weights are packed on the side lane while BatchNorm-1 and the spatial
+  // convolution run
+  const bool pre_wt = !res && (d.training || keep) && e.gemm_on_umma(gt);
+  SideLane* lane = (pre_wt && !ws.dry) ? side_lane() : nullptr;
+  bf16* wt_pre = nullptr;
+  if (pre_wt) {
+    int32_t rc = STGCN_OK;
+    wt_pre = e.prepack(gt, P.Wt, wiT, lane, lane ? lane->ev[0] : nullptr, lane ? lane->ev[1] : nullptr, &rc);
+    STGCN_TRY(rc);
+  }
+  STGCN_TRY(spatial_fwd<T>(e, m, x, S.stats1 + 2 * m.ci, S.stats1 + 3 * m.ci, relu1, P.A, P.W, P.W_bias, S.S, saved_mem ? S.XA : nullptr, saved_mem ? &S.fp : nullptr));
   if (!res) {
     if (d.training || keep) {
       T* U = S.U ? S.U : ws.get<T>(m.rows_out * m.co);
@@ -485,7 +511,10 @@ static int32_t block_forward_t(const StgcnBlockDesc& d, const T* x, const StgcnB
       static const bool no_fs = getenv("STGCN_NO_FUSED_STATS") != nullptr;
       const bool fused_stats = !no_fs && d.training && e.gemm_on_umma(gt);     // BN-2 statistics ride in the GEMM epilogue
       if (fused_stats) ep.stat_partials = partials;
-      STGCN_TRY(e.gemm(gt, S.S, P.Wt, wiT, ep, U));
+      if (wt_pre) {
+        if (lane) cudaStreamWaitEvent(st, lane->ev[1], 0);            // join: the side lane is empty again
+        STGCN_TRY(e.gemm_packed(gt, S.S, wt_pre, ep, U));
+      } else STGCN_TRY(e.gemm(gt, S.S, P.Wt, wiT, ep, U));
       if (ws.dry) return STGCN_OK;
       if (!ws.ok()) { set_error("workspace too small"); return STGCN_ERR_WORKSPACE; }
       if (d.training) {
@@ -594,6 +623,16 @@ static int32_t block_backward_t(const StgcnBlockDesc& d, const T* x, const T* y,
   const bool folded = !res && fold_ok<T>(e, m, S.stats1 + 2 * m.ci, relu1);
   float* packed_t = (!res && e.wgrad_on_umma(g_wt)) ? ws.get<float>(umma_wgrad_workspace_floats(g_wt)) : nullptr;
   float* packed_m = (folded && e.wgrad_on_umma(g_wm)) ? ws.get<float>(umma_wgrad_workspace_floats(g_wm)) : nullptr;
+  SideLane* lane = (!res && folded && packed_t && !ws.dry) ? side_lane() : nullptr;
+  // temporal data-gradient weights (parameters only): packed on the side lane beside the BatchNorm-2 backward passes
+  const ConvGeom gd = geom(m.n, m.to, m.t, m.v, m.co, m.co, m.gamma, m.stride, m.pad, 1);
+  const WIndex wiD = widx(kNoDiv, 0, m.gamma, kNoDiv, 0, (long long)m.co * m.gamma, 1);
+  bf16* wd_pre = nullptr;
+  if (!res && folded && packed_t && e.gemm_on_umma(gd)) {
+    int32_t rc = STGCN_OK;
+    wd_pre = e.prepack(gd, P.Wt, wiD, lane, lane ? lane->ev[4] : nullptr, lane ? lane->ev[5] : nullptr, &rc);
+    STGCN_TRY(rc);
+  }
   ZeroJobs zj;
   if (!res) {
     if (packed_t) zj.add(packed_t, umma_wgrad_workspace_floats(g_wt));
@@ -619,7 +658,6 @@ static int32_t block_backward_t(const StgcnBlockDesc& d, const T* x, const T* y,
   }
   // With the side lane the temporal data gradient goes first; the (HBM-bound) per-joint sums of dS then run beside the
   // (tensor-bound) temporal weight gradient, whose layout change follows on the side lane as well.
-  SideLane* lane = (!res && folded && packed_t && !ws.dry) ? side_lane() : nullptr;
   auto temporal_wgrad = [&]() -> int32_t {
     return e.wgrad(g_wt, dU, tin, widx(kNoDiv, 0, (long long)m.co * m.gamma, kNoDiv, 0, m.gamma, 1), G.Wt, (size_t)m.co * m.co * m.gamma,
                    -1, packed_t, true, lane ? lane->s : nullptr, lane ? lane->ev[2] : nullptr);
@@ -629,7 +667,6 @@ static int32_t block_backward_t(const StgcnBlockDesc& d, const T* x, const T* y,
   bool t1_ready = false;
   {
     GemmEpilogue ep;
-    const ConvGeom gd = geom(m.n, m.to, m.t, m.v, m.co, m.co, m.gamma, m.stride, m.pad, 1);
     // measured on B200: summing dS in the dgrad epilogue costs more (+60 us per launch) than the separate 30 us pass,
     // so it is off unless STGCN_FUSED_VSUM is set (kept for re-evaluation with a wider epilogue)
     static const bool fv = getenv("STGCN_FUSED_VSUM") != nullptr;
@@ -637,7 +674,10 @@ static int32_t block_backward_t(const StgcnBlockDesc& d, const T* x, const T* y,
       if (!ws.dry) cudaMemsetAsync(t1, 0, sizeof(float) * (size_t)m.v * m.co, st);
       ep.vsum = t1; t1_ready = true;
     }
-    STGCN_TRY(e.gemm(gd, dU, P.Wt, widx(kNoDiv, 0, m.gamma, kNoDiv, 0, (long long)m.co * m.gamma, 1), ep, dTin));
+    if (wd_pre) {
+      if (lane && !ws.dry) cudaStreamWaitEvent(st, lane->ev[5], 0);
+      STGCN_TRY(e.gemm_packed(gd, dU, wd_pre, ep, dTin));
+    } else STGCN_TRY(e.gemm(gd, dU, P.Wt, wiD, ep, dTin));
   }
   bool side_bias_grads = false;
   const bool t1_from_epilogue = t1_ready;        // (STGCN_FUSED_VSUM: cleared right before its producer, not by the zero jobs)
