@@ -122,7 +122,7 @@ def run_reference(args):
         loss = O.cross_entropy(O.model_forward(x, state, cfgs, True), y)
         loss.backward()
         opt.step()
-        return float(loss)
+        return float(loss.detach())
     for _ in range(max(1, min(args.warmup, 1))):
         step()
     steps = max(1, min(args.steps, 3))
