@@ -120,15 +120,11 @@ struct SideLane { cudaStream_t s = nullptr; cudaEvent_t ev[kLaneEvents] = {}; bo
 static SideLane* side_lane() {
   static const bool off = getenv("STGCN_NO_SIDE") != nullptr;
   if (off) return nullptr;
-  static std::mutex mu;
-  static SideLane lanes[64];
+  static thread_local SideLane lanes[64];      // per host thread and device: calls from different threads never share events
   int dev = 0;
   if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
-  std::lock_guard<std::mutex> lk(mu);
   SideLane& l = lanes[dev];
   if (!l.s) {
-    cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
-    (void)cs;
     if (cudaStreamCreateWithFlags(&l.s, cudaStreamNonBlocking) != cudaSuccess) { l.s = nullptr; cudaGetLastError(); return nullptr; }
     l.ok = true;
     for (int i = 0; i < kLaneEvents; ++i)
