@@ -34,3 +34,16 @@ def test_augmentation_matrix_and_transform_match_reference():
         assert np.allclose(sample_augmentation(np.random.RandomState(seed)), T[:2, :2], atol=1e-12), seed
         kinds.add(tuple(np.round(T[:2, :2], 6).reshape(-1)))
     assert len(kinds) >= 6          # the seeds cover rotations, scalings, flips and their combinations
+
+
+def test_device_collate_and_captured_step_refuse_cpu():
+    """No CPU fallback anywhere on the product path: the host-side wrappers raise before touching the library."""
+    import pytest
+    import torch
+    from stgcn_b200.pipeline import DeviceCollate
+    from stgcn_b200.training import CapturedTrainStep
+    with pytest.raises(RuntimeError):
+        DeviceCollate('cpu')([(np.zeros((1, 4, 25, 2), np.float32), np.array([0]))])
+    lin = torch.nn.Linear(4, 2).train()
+    with pytest.raises(RuntimeError):
+        CapturedTrainStep(lin, torch.optim.SGD(lin.parameters(), lr=0.1), torch.zeros(2, 4), torch.zeros(2, dtype=torch.int64))
