@@ -88,3 +88,42 @@ class CapturedTrainStep:
         for m in self._blocks:            # parameters and running statistics changed behind torch's version counters
             m._prep_cache.clear()
         return self.loss
+
+
+class CapturedForward:
+    """Eval-mode forward of the drop-in model as one CUDA graph (frozen parameters: the prepared two-kernels-per-block path).
+
+        fwd = CapturedForward(model.eval(), example_x)
+        logits = fwd(x)              # (N, classes) device tensor, valid until the next call
+
+    Re-capture (construct a new object) after the parameters or the running statistics change: the graph replays the operands
+    prepared at capture time."""
+
+    def __init__(self, model, example_x, warmup=2):
+        if not example_x.is_cuda:
+            raise RuntimeError('stgcn_b200.CapturedForward: CUDA tensors required (there is no CPU path)')
+        if model.training:
+            raise RuntimeError('stgcn_b200.CapturedForward: put the model in eval() mode first')
+        self.model = model
+        self.x = torch.empty_like(example_x)
+        self.x.copy_(example_x)
+        dev = example_x.device
+        side = torch.cuda.Stream(device=dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(side), torch.no_grad():
+            for _ in range(max(1, warmup)):
+                model(self.x)
+        torch.cuda.current_stream(dev).wait_stream(side)
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.no_grad(), torch.cuda.graph(self.graph):
+            self.out = model(self.x)
+        # the graph reads the operands prepared during the warm-up: keep them alive even if the modules drop their caches
+        self._keep = [m._prep_cache.get('blob') for m in model.modules() if hasattr(m, '_prep_cache')]
+
+    def __call__(self, x):
+        if x.shape != self.x.shape:
+            raise RuntimeError('stgcn_b200.CapturedForward: batch shape %s differs from the captured %s' %
+                               (tuple(x.shape), tuple(self.x.shape)))
+        self.x.copy_(x, non_blocking=True)
+        self.graph.replay()
+        return self.out

@@ -151,3 +151,21 @@ def test_captured_train_step_refuses_dropout():
     m = stgcn_b200.L_STGCN(hp, A=torch.randn(3, 25, 25) * 0.1).cuda().train()
     with pytest.raises(RuntimeError):
         stgcn_b200.CapturedTrainStep(m, Adam(m.parameters()), torch.randn(2, 40, 25, 3).cuda(), torch.zeros(2, dtype=torch.int64).cuda())
+
+
+def test_captured_forward_equals_eager_eval_forward():
+    import stgcn_b200
+    model = _small_model(torch.bfloat16)
+    g = torch.Generator().manual_seed(2)
+    xs = [torch.randn(4, 40, 25, 3, generator=g).cuda() for _ in range(3)]
+    with torch.no_grad():
+        model(xs[0])                                   # move the running statistics once
+    model.eval()
+    fwd = stgcn_b200.CapturedForward(model, xs[0])
+    for x in xs:
+        with torch.no_grad():
+            ref = model(x).clone()
+        got = fwd(x)
+        assert float((got - ref).abs().max() / ref.abs().max()) < 1e-2        # same kernels; tiles may be walked the other way round
+    with pytest.raises(RuntimeError):
+        fwd(torch.randn(2, 40, 25, 3).cuda())
