@@ -89,3 +89,22 @@ def test_graph_builder_matches_reference_fixture():
             assert rel_err(A, g[f'A_s{strat}_d{d}']) < 1e-6
     A18 = graph.get_normalized_adjacency_matrices(graph.Strategy.DISTANCE, 2, skeleton='openpose18')
     assert A18.shape == (3, 18, 18)
+
+
+def test_training_tail_and_input_entry_points_validate_arguments_without_gpu():
+    """Argument errors are reported by return code + stgcn_last_error before anything is launched."""
+    from stgcn_b200 import _lib
+    lib = _lib.lib()
+    # Adam: the step state is mandatory (the step number lives on the device)
+    rc = lib.stgcn_adam_step(0, None, None, None, None, None, 1e-3, 0.9, 0.999, 1e-8, 0.0, 0, None, None)
+    assert rc != 0 and b'adam_step' in lib.stgcn_last_error()
+    # cross entropy: shapes and pointers
+    assert lib.stgcn_cross_entropy_forward(0, 60, None, None, -100, None, None, None) != 0
+    assert lib.stgcn_cross_entropy_forward(4, 60, None, None, -100, None, None, None) != 0
+    assert b'cross_entropy' in lib.stgcn_last_error()
+    assert lib.stgcn_cross_entropy_backward(4, 60, None, None, None, None) != 0
+    # collate: bad joint / channel count, null buffers; an empty batch is a no-op
+    assert lib.stgcn_collate_pad_augment(_lib.F32, 2, 10, 0, 3, None, None, None, None, None, None) != 0
+    assert lib.stgcn_collate_pad_augment(_lib.F32, 2, 10, 25, 3, None, None, None, None, None, None) != 0
+    assert b'collate_pad_augment' in lib.stgcn_last_error()
+    assert lib.stgcn_collate_pad_augment(_lib.F32, 0, 10, 25, 3, None, None, None, None, None, None) == 0
