@@ -506,11 +506,61 @@ int32_t launch_bn1_fold(const float* W, const float* Wb, const float* A, const f
 
 // ---------------------------------------------------------------------------
 // small C_in (block 0: 3 coordinates): XA[r][k*C+c] = sum_w A[k,v,w] * x[f,w,c] written as zero-padded rows of
-// `ld` channels (ld = 64) so that GEMM-1 / its gradients run on the tcgen05 engine.  One thread per (frame, joint)
-// row; the frames of a CTA and A are staged in shared memory; every row is one 16-byte-vector burst.
+// `ld` channels (ld = 64) so that GEMM-1 / its gradients run on the tcgen05 engine.  The frames of a CTA and A are staged in
+// shared memory; one thread per (row, partition) forms the C sums from 16-byte coordinate loads, and the rows leave as
+// coalesced 16-byte groups.
 // ---------------------------------------------------------------------------
 template <class T>
 __global__ void __launch_bounds__(256) agg_small_fwd_kernel(const T* __restrict__ x, long long frames, int V, int C, int K, int ld,
+                                                            const float* __restrict__ A, int FB, T* __restrict__ xa) {
+  pdl_enter();
+  extern __shared__ float4 sm4s[];
+  // host guarantees C <= 4 and K*C <= 16
+  float4* xs = sm4s;                                     // [FB][V]     one joint's C coordinates, zero padded to 4
+  float* os = reinterpret_cast<float*>(sm4s + FB * V);   // [FB][V][16] the K*C aggregated values of a row, zero padded to 16
+  float* As = os + FB * V * 16;                          // [K][V][V]
+  for (int i = threadIdx.x; i < K * V * V; i += blockDim.x) As[i] = A[i];
+  constexpr int VEC = VecN<T>::N;
+  const int gpr = ld / VEC;                              // 16-byte groups per output row
+  for (long long f0 = (long long)blockIdx.x * FB; f0 < frames; f0 += (long long)gridDim.x * FB) {
+    const int nf = (int)min((long long)FB, frames - f0);
+    __syncthreads();
+    for (int i = threadIdx.x; i < nf * V; i += blockDim.x) {
+      const T* xp = x + (f0 * V + i) * C;
+      float t[4] = {0.f, 0.f, 0.f, 0.f};
+      for (int c = 0; c < C; ++c) t[c] = ldf(xp + c);
+      xs[i] = make_float4(t[0], t[1], t[2], t[3]);
+    }
+    for (int i = threadIdx.x; i < nf * V * 16; i += blockDim.x) os[i] = 0.f;
+    __syncthreads();
+    // one thread per (row, partition): V steps of one adjacency load and one 16-byte coordinate load
+    for (int it = threadIdx.x; it < nf * V * K; it += blockDim.x) {
+      const int r = it / K, k = it - r * K;
+      const int fl = r / V, v = r - fl * V;
+      const float* ar = As + (k * V + v) * V;
+      const float4* xr = xs + fl * V;
+      float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+      for (int w = 0; w < V; ++w) {
+        const float aw = ar[w]; const float4 q = xr[w];
+        a0 = fmaf(aw, q.x, a0); a1 = fmaf(aw, q.y, a1); a2 = fmaf(aw, q.z, a2); a3 = fmaf(aw, q.w, a3);
+      }
+      float* o = os + r * 16 + k * C;
+      o[0] = a0; if (C > 1) o[1] = a1; if (C > 2) o[2] = a2; if (C > 3) o[3] = a3;
+    }
+    __syncthreads();
+    // coalesced store: consecutive threads write consecutive 16-byte groups, i.e. whole zero-padded rows
+    for (int idx = threadIdx.x; idx < nf * V * gpr; idx += blockDim.x) {
+      const int r = idx / gpr, j0 = (idx - r * gpr) * VEC;
+      float o[VEC];
+#pragma unroll
+      for (int u = 0; u < VEC; ++u) o[u] = (j0 + u < 16) ? os[r * 16 + j0 + u] : 0.f;
+      stv(xa + (f0 * V + r) * (long long)ld + j0, o);
+    }
+  }
+}
+// any C with K*C <= ld: one thread per (frame, joint) row
+template <class T>
+__global__ void __launch_bounds__(256) agg_small_fwd_generic_kernel(const T* __restrict__ x, long long frames, int V, int C, int K, int ld,
                                                             const float* __restrict__ A, int FB, T* __restrict__ xa) {
   pdl_enter();
   extern __shared__ float sm[];
@@ -551,9 +601,14 @@ int32_t launch_agg_small_fwd(const T* x, long long frames, int V, int C, int K, 
   KernelTimer kt_(KC_AGG_FWD, 2.0 * frames * V * V * (double)K * C, st);
   if (K * C > ld || ld % VecN<T>::N != 0) { set_error("agg_small: K*C=%d does not fit ld=%d", K * C, ld); return STGCN_ERR_UNSUPPORTED; }
   const int FB = std::max(1, 256 / V);
-  const size_t smem = ((size_t)K * V * V + (size_t)FB * V * C) * sizeof(float);
   const int blocks = (int)std::min<long long>((frames + FB - 1) / FB, 148 * 8);
-  launch_k(agg_small_fwd_kernel<T>, blocks, 256, smem, st, x, frames, V, C, K, ld, A, FB, xa);
+  if (C <= 4 && K * C <= 16) {
+    const size_t smem = (size_t)FB * V * sizeof(float4) + ((size_t)FB * V * 16 + (size_t)K * V * V) * sizeof(float);
+    launch_k(agg_small_fwd_kernel<T>, blocks, 256, smem, st, x, frames, V, C, K, ld, A, FB, xa);
+  } else {
+    const size_t smem = ((size_t)K * V * V + (size_t)FB * V * C) * sizeof(float);
+    launch_k(agg_small_fwd_generic_kernel<T>, blocks, 256, smem, st, x, frames, V, C, K, ld, A, FB, xa);
+  }
   STGCN_CHECK_LAUNCH("agg_small_fwd");
   return STGCN_OK;
 }
