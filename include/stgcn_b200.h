@@ -79,6 +79,11 @@ typedef struct StgcnBlockParams {
   int64_t* bn2_num_batches_tracked;
   const float* Wr;                                      /* apply_residual.weight (C_out,C_in) or NULL */
   const float* Wr_bias;                                 /* apply_residual.bias (C_out) or NULL */
+  /* nn.Dropout state (st_graphconv.py:53-58), DEVICE resident: rng_state[0] = Philox seed, rng_state[1] = offset.  When non-NULL
+   * (and training with dropout_p > 0) forward takes its mask from this state and advances the offset by ceil(outputs / 4), so a
+   * CUDA graph of the step draws a fresh mask per replay; the state used is kept in `saved` and replayed by backward.  NULL: the
+   * descriptor's seed / offset values are used. */
+  uint64_t* rng_state;
 } StgcnBlockParams;
 
 /* Parameter gradients (fp32, overwritten).  Same shapes as the parameters. */
@@ -185,6 +190,10 @@ int32_t stgcn_adam_step(int32_t count, float* const* params, const float* const*
  * coordinate, so T's translation entries never act, exactly as in the reference. */
 int32_t stgcn_collate_pad_augment(int32_t dtype, int32_t n, int32_t t_out, int32_t v, int32_t c, const float* packed,
                                   const int64_t* offsets, const int32_t* lengths, const float* xform, void* out, void* stream);
+
+/* Keep-scale of nn.Dropout(p) as the library draws it (Philox4x32-10): out[i] = 1/(1-p) if element i of the block output
+ * (flat index over (n,t_out,v,c_out)) is kept under state {seed, offset}, else 0.  For replaying a mask in tests / oracles. */
+int32_t stgcn_dropout_mask(uint64_t seed, uint64_t offset, float p, size_t count, float* out, void* stream);
 
 /* Layout helpers: fp32 (n,t,v,c) <-> dtype (n,t,v,c) casts on device. */
 int32_t stgcn_cast(int32_t src_dtype, int32_t dst_dtype, const void* src, void* dst, size_t count, void* stream);

@@ -482,7 +482,7 @@ def _bn_coeffs(x, gamma, beta, rm, rv, training, update_running, eps=BN_EPS, mom
     return a, beta - a * mean
 
 
-def block_forward_bf16(x, p, cfg: BlockCfg, training: bool, update_running=True, keep_u=True, round_A=None):
+def block_forward_bf16(x, p, cfg: BlockCfg, training: bool, update_running=True, keep_u=True, round_A=None, drop_mask=None):
     """`block_forward` with bf16 storage emulation at the CUDA chain's tensor boundaries
     (x, XA, S, [P2], U, R, y and their gradients; GEMM weights rounded to bf16).
     keep_u=False models the fused inference epilogue where U is never stored."""
@@ -528,7 +528,8 @@ def block_forward_bf16(x, p, cfg: BlockCfg, training: bool, update_running=True,
             u = _q(u)
         a2, b2 = _bn_coeffs(u, p['batch_n_2.weight'], p['batch_n_2.bias'], p.get('batch_n_2.running_mean'),
                             p.get('batch_n_2.running_var'), training, update_running)
-        return _q(torch.relu(u * a2[None, :, None, None] + b2[None, :, None, None]))
+        return _q(dropout(torch.relu(u * a2[None, :, None, None] + b2[None, :, None, None]), cfg.dropout_rate, training,
+                          mask=drop_mask))
     a2, b2 = _bn_coeffs(s, p['batch_n_2.weight'], p['batch_n_2.bias'], p.get('batch_n_2.running_mean'),
                         p.get('batch_n_2.running_var'), training, update_running)
     p2 = _q(torch.relu(s * a2[None, :, None, None] + b2[None, :, None, None]))
@@ -537,7 +538,7 @@ def block_forward_bf16(x, p, cfg: BlockCfg, training: bool, update_running=True,
         r = _q(conv1x1(x, _q(p['apply_residual.weight']), p['apply_residual.bias'], cfg.stride))
     else:
         r = x
-    return _q(torch.relu(u + r))
+    return _q(dropout(torch.relu(u + r), cfg.dropout_rate, training, mask=drop_mask))
 
 
 def model_forward_bf16(x, state, cfgs, training, update_running=True, keep_u=True):

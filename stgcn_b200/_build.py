@@ -27,6 +27,12 @@ def _nvcc():
     return 'nvcc'
 
 
+def have_nvcc():
+    import shutil
+    c = _nvcc()
+    return os.path.exists(c) if os.path.isabs(c) else shutil.which(c) is not None
+
+
 def _digest(paths):
     h = hashlib.sha256()
     for p in sorted(paths):

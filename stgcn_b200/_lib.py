@@ -30,7 +30,7 @@ class BlockParams(C.Structure):
     _fields_ = [(n, _P) for n in ('bn1_weight', 'bn1_bias', 'bn1_running_mean', 'bn1_running_var',
                                   'bn1_num_batches_tracked', 'A', 'W', 'W_bias', 'Wt', 'Wt_bias', 'bn2_weight',
                                   'bn2_bias', 'bn2_running_mean', 'bn2_running_var', 'bn2_num_batches_tracked',
-                                  'Wr', 'Wr_bias')]
+                                  'Wr', 'Wr_bias', 'rng_state')]
 
 
 class BlockGrads(C.Structure):
@@ -78,6 +78,7 @@ def _declare(lib):
     lib.stgcn_collate_pad_augment.restype = i32
     lib.stgcn_collate_pad_augment.argtypes = [i32] * 5 + [_P] * 5 + [_P]
     lib.stgcn_cast.restype = i32; lib.stgcn_cast.argtypes = [i32, i32, _P, _P, sz, _P]
+    lib.stgcn_dropout_mask.restype = i32; lib.stgcn_dropout_mask.argtypes = [u64, u64, C.c_float, sz, _P, _P]
     lib.stgcn_umma_conv_gemm.restype = i32
     lib.stgcn_umma_conv_gemm.argtypes = [i32] * 9 + [_P] * 4 + [_P]
     lib.stgcn_umma_probe.restype = i32
@@ -100,7 +101,9 @@ def lib():
         with _lock:
             if _lib is None:
                 path = _build.LIB
-                if not os.path.exists(path):
+                # built on first use when absent; rebuilt when the sources changed since it was built and a compiler is at hand
+                # (on a box without nvcc the shipped library is used as it is)
+                if not os.path.exists(path) or (not _build.is_fresh() and _build.have_nvcc()):
                     path = _build.build()
                 handle = C.CDLL(path)
                 _declare(handle)
@@ -136,16 +139,31 @@ def require_cuda(t, name):
 
 # one scratch arena per device, grown on demand; stream-ordered reuse across calls
 _ws = {}
+_ws_retired = {}     # device -> arenas that were outgrown: kept alive because captured CUDA graphs may still write into them
 
 
 def workspace(device, nbytes):
     key = (device.index if device.index is not None else torch.cuda.current_device())
     buf = _ws.get(key)
     if buf is None or buf.numel() < nbytes:
-        # grow with head-room so steady state never reallocates (CUDA-graph friendly)
+        # grow with head-room so steady state never reallocates (CUDA-graph friendly).  An outgrown arena is retired, not
+        # freed: a CapturedTrainStep / CapturedForward recorded its address, and replaying that graph after the caching
+        # allocator had handed the memory to someone else would corrupt live tensors silently.
+        if buf is not None:
+            _ws_retired.setdefault(key, []).append(buf)
         buf = torch.empty(int(nbytes * 1.25) + (1 << 20), dtype=torch.uint8, device=device)
         _ws[key] = buf
     return buf
+
+
+def current_workspace(device):
+    """The arena calls on `device` use right now (None before the first call); graph owners keep a reference to it."""
+    return _ws.get(device.index if device.index is not None else torch.cuda.current_device())
+
+
+def release_retired_workspaces():
+    """Free the outgrown arenas.  Only safe once every CUDA graph captured before the last growth has been destroyed."""
+    _ws_retired.clear()
 
 
 def launch_count():

@@ -86,7 +86,7 @@ static FoldPrep carve_fold_prep(Arena& a, const Dims& m) {
   f.valid = true;
   return f;
 }
-template <class T> struct Saved { float* stats1; float* stats2; T* S; T* U; T* XA; FoldPrep fp; };
+template <class T> struct Saved { uint64_t* rng; float* stats1; float* stats2; T* S; T* U; T* XA; FoldPrep fp; };
 // Inference with frozen parameters (stgcn_block_prepare / stgcn_block_forward_prepared): everything that depends only on the
 // parameters -- eval BatchNorm coefficient tables, folded spatial operands, joint-bias table, packed temporal weights.
 struct Prepared { float* stats1; float* stats2; FoldPrep fp; float* b2d; bf16* wt; };
@@ -101,6 +101,7 @@ static Prepared carve_prepared(Arena& a, const Dims& m) {
 }
 template <class T> static Saved<T> carve_saved(Arena& a, const StgcnBlockDesc& d, const Dims& m) {
   Saved<T> s;
+  s.rng = a.get<uint64_t>(2);          // dropout Philox {seed, offset} this call used (replayed by backward)
   s.stats1 = a.get<float>(4 * m.ci);
   s.stats2 = a.get<float>(4 * m.co);
   s.S = a.get<T>(m.rows_in * m.co);
@@ -272,7 +273,8 @@ static int32_t spatial_fwd(Engine<T>& e, const Dims& m, const T* x, const float*
       STGCN_TRY(launch_bn1_fold(W, Wb, A, rs, aff_a, aff_b, m.k, m.v, m.co, m.ci, w2p, w2pT, wb, wbb, b2d, e.st, kSmallLd));
       STGCN_TRY(launch_agg_small_fwd<T>(x, m.frames_in, m.v, m.ci, m.k, kSmallLd, A, XAp, e.st));
       GemmEpilogue ep; ep.bias2d = b2d;
-      return e.gemm_packed(geom(m.n, m.t, m.t, m.v, kSmallLd, m.co, 1, 1, 0, 0), XAp, w2p, ep, S);
+      ConvGeom g1 = geom(m.n, m.t, m.t, m.v, kSmallLd, m.co, 1, 1, 0, 0); g1.c_valid = m.k * m.ci;
+      return e.gemm_packed(g1, XAp, w2p, ep, S);
     }
     if (fold_ok<T>(e, m, aff_a, relu1)) {
       // BatchNorm-1 folded into the 1x1 weights: aggregate the RAW input, GEMM-1 against W.diag(a), shift through bias2d
@@ -365,7 +367,8 @@ static int32_t spatial_bwd(Engine<T>& e, const Dims& m, const T* x, const float*
       STGCN_TRY(e.wgrad(geom(m.n, m.t, m.t, m.v, kSmallLd, m.co, 1, 1, 0, 0), dS, bf->xa_saved,
                         widx(kNoDiv, 0, m.ci, m.ci, (long long)m.co * m.ci, 1, 0), dW, (size_t)m.k * m.co * m.ci, KCi));
       GemmEpilogue ep;
-      STGCN_TRY(e.gemm_packed(geom(m.n, m.t, m.t, m.v, m.co, kSmallLd, 1, 1, 0, 0), dS, w2pT, ep, dXAp));
+      ConvGeom gx = geom(m.n, m.t, m.t, m.v, m.co, kSmallLd, 1, 1, 0, 0); gx.n_valid = KCi;
+      STGCN_TRY(e.gemm_packed(gx, dS, w2pT, ep, dXAp));
       if (ws.dry) return STGCN_OK;
       STGCN_TRY(launch_agg_dA<T>(dXAp, x, m.frames_in, m.v, m.ci, m.k, nullptr, nullptr, 0, dA, e.st, kSmallLd));
       STGCN_TRY(launch_bn1_fold_grads(W, dW, bf->stats, t1, rs, m.k, m.v, m.co, m.ci, bf->training, (double)m.rows_in, bf->dgamma,
@@ -468,14 +471,18 @@ static int32_t block_forward_t(const StgcnBlockDesc& d, const T* x, const StgcnB
   Saved<T> S;
   const bool keep = saved_mem != nullptr || ws.dry;
   if (saved_mem) S = carve_saved<T>(sv, d, m);
-  else { S.stats1 = ws.get<float>(4 * m.ci); S.stats2 = ws.get<float>(4 * m.co); S.S = ws.get<T>(m.rows_in * m.co); S.U = nullptr; S.XA = nullptr; S.fp.valid = false; }
+  else { S.rng = ws.get<uint64_t>(2); S.stats1 = ws.get<float>(4 * m.ci); S.stats2 = ws.get<float>(4 * m.co); S.S = ws.get<T>(m.rows_in * m.co); S.U = nullptr; S.XA = nullptr; S.fp.valid = false; }
   float* partials = ws.get<float>(stat_partials_bytes(std::max(m.ci, m.co)) / sizeof(float));
   Engine<T> e{d, ws, st};
   const bool res = d.residual != STGCN_RES_NONE;
   const int relu1 = res ? 1 : 0;
   int nblk = 0;
+  const bool drop = d.training && d.dropout_p > 0.f;
   if (!ws.dry) {
     if (!ws.ok()) { set_error("workspace too small"); return STGCN_ERR_WORKSPACE; }
+    // dropout state: from the caller's device-resident generator (advanced here by one Philox call per four outputs), else the
+    // descriptor's values; either way the kernels read it from S.rng
+    if (drop) STGCN_TRY(launch_rng_fetch(P.rng_state, d.seed, d.offset, (uint64_t)((m.rows_out * m.co + 3) / 4), S.rng, st));
     if (d.training) {
       const float* part1 = partials;
       if (x_cs && x_cs_n > 0) { part1 = x_cs; nblk = x_cs_n; }
@@ -522,8 +529,8 @@ static int32_t block_forward_t(const StgcnBlockDesc& d, const T* x, const StgcnB
         STGCN_TRY(launch_bn_eval_coeffs(m.co, P.bn2_weight, P.bn2_bias, P.bn2_running_mean, P.bn2_running_var, d.bn_eps, S.stats2, st));
       }
       const float p = d.training ? d.dropout_p : 0.f;
-      return launch_affine_act<T>(U, m.rows_out, m.co, S.stats2 + 2 * m.co, S.stats2 + 3 * m.co, 1, p, d.seed, d.offset, y, st,
-                                  d.training ? y_cs : nullptr, y_cs_n);
+      return launch_affine_act<T>(U, m.rows_out, m.co, S.stats2 + 2 * m.co, S.stats2 + 3 * m.co, 1, p, 0, 0, y, st,
+                                  d.training ? y_cs : nullptr, y_cs_n, drop ? S.rng : nullptr);
     }
     // inference: BN2 + ReLU folded into the temporal GEMM's epilogue, U never exists
     if (!ws.dry) STGCN_TRY(launch_bn_eval_coeffs(m.co, P.bn2_weight, P.bn2_bias, P.bn2_running_mean, P.bn2_running_var, d.bn_eps, S.stats2, st));
@@ -550,7 +557,7 @@ static int32_t block_forward_t(const StgcnBlockDesc& d, const T* x, const StgcnB
     resid = y;
   }
   GemmEpilogue ep; ep.bias = P.Wt_bias; ep.residual = resid; ep.relu = 1;
-  if (d.training) { ep.dropout_p = d.dropout_p; ep.seed = d.seed; ep.offset = d.offset; }
+  if (drop) { ep.dropout_p = d.dropout_p; ep.rng = S.rng; }
   return e.gemm(gt, P2, P.Wt, wiT, ep, y);
 }
 
@@ -640,10 +647,10 @@ static int32_t block_backward_t(const StgcnBlockDesc& d, const T* x, const T* y,
     if (!ws.ok()) { set_error("workspace too small"); return STGCN_ERR_WORKSPACE; }
     if (!res) {
       static const bool no_zj = getenv("STGCN_NO_ZEROJOBS") != nullptr;      // A/B switch: one memset node per accumulator
-      STGCN_TRY(launch_bn_bwd_reduce<T>(dy, S.U, S.stats2, m.rows_out, m.co, 1, p, d.seed, d.offset, partials, &nblk, st, no_zj ? nullptr : &zj));
+      STGCN_TRY(launch_bn_bwd_reduce<T>(dy, S.U, S.stats2, m.rows_out, m.co, 1, p, 0, 0, partials, &nblk, st, no_zj ? nullptr : &zj, p > 0.f ? S.rng : nullptr));
       if (!zj.done) for (int j = 0; j < zj.count; ++j) cudaMemsetAsync(zj.p[j], 0, sizeof(float) * zj.n[j], st);
       STGCN_TRY(launch_bn_bwd_finalize(partials, nblk, m.co, sums2, G.bn2_weight, G.bn2_bias, st));
-      STGCN_TRY(launch_bn_bwd_apply<T>(dy, S.U, S.stats2, sums2, m.rows_out, m.co, 1, d.training, p, d.seed, d.offset, dU, st));
+      STGCN_TRY(launch_bn_bwd_apply<T>(dy, S.U, S.stats2, sums2, m.rows_out, m.co, 1, d.training, p, 0, 0, dU, st, p > 0.f ? S.rng : nullptr));
       if (!d.training) STGCN_TRY(launch_colsum<T>(dU, m.rows_out, m.co, partials, G.Wt_bias, st));
     } else {
       STGCN_TRY(launch_relu_bwd<T>(dy, y, m.rows_out * m.co, p, dU, st));
@@ -933,6 +940,11 @@ int32_t stgcn_umma_conv_gemm(int32_t nb, int32_t t_in, int32_t t_out, int32_t v,
 }
 
 uint64_t stgcn_launch_count(void) { return g_launches.load(); }
+int32_t stgcn_dropout_mask(uint64_t seed, uint64_t offset, float p, size_t count, float* out, void* stream) {
+  if (!out) { set_error("dropout_mask: null output"); return STGCN_ERR_INVALID; }
+  if (p < 0.f || p >= 1.f) { set_error("dropout_mask: p out of range"); return STGCN_ERR_INVALID; }
+  return launch_dropout_mask(seed, offset, p, count, out, (cudaStream_t)stream);
+}
 const char* stgcn_last_error(void) { return g_err; }
 const char* stgcn_version(void) { return "stgcn_b200 0.1 (sm_100a)"; }
 

@@ -279,8 +279,9 @@ template <class T, int VEC>
 __global__ void __launch_bounds__(256) affine_act_kernel(const T* __restrict__ x, long long total, int C,
                                                          const float* __restrict__ a, const float* __restrict__ b,
                                                          int relu, float p, float inv_keep, uint64_t seed,
-                                                         uint64_t offset, T* __restrict__ y) {
+                                                         uint64_t offset, T* __restrict__ y, const uint64_t* __restrict__ rng) {
   pdl_enter();
+  if (rng) { seed = rng[0]; offset = rng[1]; }      // device-resident Philox state (replayable CUDA graphs)
   long long i = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * VEC;
   const long long step = (long long)gridDim.x * blockDim.x * VEC;
   for (; i < total; i += step) {
@@ -384,7 +385,8 @@ static int elementwise_blocks(long long total, int vec) {
 
 template <class T>
 int32_t launch_affine_act(const T* x, long long rows, int C, const float* a, const float* b, int relu, float p,
-                          uint64_t seed, uint64_t offset, T* y, cudaStream_t st, float* out_partials, int* out_nblk) {
+                          uint64_t seed, uint64_t offset, T* y, cudaStream_t st, float* out_partials, int* out_nblk,
+                          const uint64_t* rng) {
   KernelTimer kt_(KC_ELEMWISE, (double)rows * C, st);
   long long total = rows * C;
   float inv_keep = p > 0.f ? 1.f / (1.f - p) : 1.f;
@@ -397,16 +399,16 @@ int32_t launch_affine_act(const T* x, long long rows, int C, const float* a, con
     launch_k(affine_act_fast_kernel<T>, elementwise_blocks(total, VecN<T>::N), 256, 0, st, x, total, C, a, b, relu, y, next_direction());
   } else if (C % 4 == 0) {
     int blocks = (int)std::min<long long>((total / 4 + 255) / 256, 148 * 16);
-    launch_k(affine_act_kernel<T, 4>, blocks, 256, 0, st, x, total, C, a, b, relu, p, inv_keep, seed, offset, y);
+    launch_k(affine_act_kernel<T, 4>, blocks, 256, 0, st, x, total, C, a, b, relu, p, inv_keep, seed, offset, y, rng);
   } else {
     int blocks = (int)std::min<long long>((total + 255) / 256, 148 * 16);
-    launch_k(affine_act_kernel<T, 1>, blocks, 256, 0, st, x, total, C, a, b, relu, p, inv_keep, seed, offset, y);
+    launch_k(affine_act_kernel<T, 1>, blocks, 256, 0, st, x, total, C, a, b, relu, p, inv_keep, seed, offset, y, rng);
   }
   STGCN_CHECK_LAUNCH("affine_act");
   return STGCN_OK;
 }
-template int32_t launch_affine_act<float>(const float*, long long, int, const float*, const float*, int, float, uint64_t, uint64_t, float*, cudaStream_t, float*, int*);
-template int32_t launch_affine_act<bf16>(const bf16*, long long, int, const float*, const float*, int, float, uint64_t, uint64_t, bf16*, cudaStream_t, float*, int*);
+template int32_t launch_affine_act<float>(const float*, long long, int, const float*, const float*, int, float, uint64_t, uint64_t, float*, cudaStream_t, float*, int*, const uint64_t*);
+template int32_t launch_affine_act<bf16>(const bf16*, long long, int, const float*, const float*, int, float, uint64_t, uint64_t, bf16*, cudaStream_t, float*, int*, const uint64_t*);
 
 // ---------------------------------------------------------------------------
 // backward of  y = drop(relu?(a*z + b))  w.r.t. the BN:
@@ -416,9 +418,10 @@ template int32_t launch_affine_act<bf16>(const bf16*, long long, int, const floa
 // ---------------------------------------------------------------------------
 template <class T, int VEC>
 struct BwdRedF {
-  const T* dy; const T* z; const float* stats; int C; int relu; float p; float inv_keep; uint64_t seed, offset;
+  const T* dy; const T* z; const float* stats; int C; int relu; float p; float inv_keep; uint64_t seed, offset; const uint64_t* rng;
   __device__ void operator()(long long r, int c, float (&g)[VEC], float (&h)[VEC]) const {
     float zz[VEC];
+    const uint64_t seed = rng ? rng[0] : this->seed, offset = rng ? rng[1] : this->offset;
     long long i = r * C + c;
     if constexpr (VEC == 4) { ld4(dy + i, g); ld4(z + i, zz); } else { g[0] = ldf(dy + i); zz[0] = ldf(z + i); }
 #pragma unroll
@@ -433,7 +436,8 @@ struct BwdRedF {
 
 template <class T>
 int32_t launch_bn_bwd_reduce(const T* dy, const T* z, const float* stats, long long rows, int C, int relu, float p,
-                             uint64_t seed, uint64_t offset, float* partials, int* nblk, cudaStream_t st, ZeroJobs* zero) {
+                             uint64_t seed, uint64_t offset, float* partials, int* nblk, cudaStream_t st, ZeroJobs* zero,
+                             const uint64_t* rng) {
   KernelTimer kt_(KC_BN_STATS, (double)rows * C, st);
   float inv_keep = p > 0.f ? 1.f / (1.f - p) : 1.f;
   if (p == 0.f && colreduce_fast_ok<T>(C)) {
@@ -442,18 +446,18 @@ int32_t launch_bn_bwd_reduce(const T* dy, const T* z, const float* stats, long l
     int nb = stat_blocks(rows, C, 4); *nblk = nb;
     int rps = kStatThreads / (C / 4);
     launch_k(colreduce_kernel<4, BwdRedF<T, 4>>, nb, kStatThreads, 2 * rps * C * sizeof(float), st,
-        rows, C, BwdRedF<T, 4>{dy, z, stats, C, relu, p, inv_keep, seed, offset}, partials);
+        rows, C, BwdRedF<T, 4>{dy, z, stats, C, relu, p, inv_keep, seed, offset, rng}, partials);
   } else {
     int nb = stat_blocks(rows, C, 1); *nblk = nb;
     int rps = kStatThreads / C;
     launch_k(colreduce_kernel<1, BwdRedF<T, 1>>, nb, kStatThreads, 2 * rps * C * sizeof(float), st,
-        rows, C, BwdRedF<T, 1>{dy, z, stats, C, relu, p, inv_keep, seed, offset}, partials);
+        rows, C, BwdRedF<T, 1>{dy, z, stats, C, relu, p, inv_keep, seed, offset, rng}, partials);
   }
   STGCN_CHECK_LAUNCH("bn_bwd_reduce");
   return STGCN_OK;
 }
-template int32_t launch_bn_bwd_reduce<float>(const float*, const float*, const float*, long long, int, int, float, uint64_t, uint64_t, float*, int*, cudaStream_t, ZeroJobs*);
-template int32_t launch_bn_bwd_reduce<bf16>(const bf16*, const bf16*, const float*, long long, int, int, float, uint64_t, uint64_t, float*, int*, cudaStream_t, ZeroJobs*);
+template int32_t launch_bn_bwd_reduce<float>(const float*, const float*, const float*, long long, int, int, float, uint64_t, uint64_t, float*, int*, cudaStream_t, ZeroJobs*, const uint64_t*);
+template int32_t launch_bn_bwd_reduce<bf16>(const bf16*, const bf16*, const float*, long long, int, int, float, uint64_t, uint64_t, float*, int*, cudaStream_t, ZeroJobs*, const uint64_t*);
 
 // sums[2][C] = {s1, s2} reduced in double; also emits dgamma = s2, dbeta = s1
 __global__ void __launch_bounds__(kFinThreads)
@@ -478,8 +482,9 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const T* __restrict__
                                                            const float* __restrict__ stats, const float* __restrict__ sums,
                                                            long long total, int C, int relu, int training, float inv_m,
                                                            float p, float inv_keep, uint64_t seed, uint64_t offset,
-                                                           T* __restrict__ dz) {
+                                                           T* __restrict__ dz, const uint64_t* __restrict__ rng) {
   pdl_enter();
+  if (rng) { seed = rng[0]; offset = rng[1]; }
   long long i = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * VEC;
   const long long step = (long long)gridDim.x * blockDim.x * VEC;
   for (; i < total; i += step) {
@@ -540,7 +545,8 @@ __global__ void __launch_bounds__(256, 3) bn_bwd_apply_fast_kernel(const T* __re
 
 template <class T>
 int32_t launch_bn_bwd_apply(const T* dy, const T* z, const float* stats, const float* sums, long long rows, int C,
-                            int relu, int training, float p, uint64_t seed, uint64_t offset, T* dz, cudaStream_t st) {
+                            int relu, int training, float p, uint64_t seed, uint64_t offset, T* dz, cudaStream_t st,
+                            const uint64_t* rng) {
   KernelTimer kt_(KC_ELEMWISE, (double)rows * C, st);
   long long total = rows * C;
   float inv_keep = p > 0.f ? 1.f / (1.f - p) : 1.f;
@@ -553,16 +559,16 @@ int32_t launch_bn_bwd_apply(const T* dy, const T* z, const float* stats, const f
                                                                                          inv_m, dz, next_direction());
   } else if (C % 4 == 0) {
     int blocks = (int)std::min<long long>((total / 4 + 255) / 256, 148 * 16);
-    launch_k(bn_bwd_apply_kernel<T, 4>, blocks, 256, 0, st, dy, z, stats, sums, total, C, relu, training, inv_m, p, inv_keep, seed, offset, dz);
+    launch_k(bn_bwd_apply_kernel<T, 4>, blocks, 256, 0, st, dy, z, stats, sums, total, C, relu, training, inv_m, p, inv_keep, seed, offset, dz, rng);
   } else {
     int blocks = (int)std::min<long long>((total + 255) / 256, 148 * 16);
-    launch_k(bn_bwd_apply_kernel<T, 1>, blocks, 256, 0, st, dy, z, stats, sums, total, C, relu, training, inv_m, p, inv_keep, seed, offset, dz);
+    launch_k(bn_bwd_apply_kernel<T, 1>, blocks, 256, 0, st, dy, z, stats, sums, total, C, relu, training, inv_m, p, inv_keep, seed, offset, dz, rng);
   }
   STGCN_CHECK_LAUNCH("bn_bwd_apply");
   return STGCN_OK;
 }
-template int32_t launch_bn_bwd_apply<float>(const float*, const float*, const float*, const float*, long long, int, int, int, float, uint64_t, uint64_t, float*, cudaStream_t);
-template int32_t launch_bn_bwd_apply<bf16>(const bf16*, const bf16*, const float*, const float*, long long, int, int, int, float, uint64_t, uint64_t, bf16*, cudaStream_t);
+template int32_t launch_bn_bwd_apply<float>(const float*, const float*, const float*, const float*, long long, int, int, int, float, uint64_t, uint64_t, float*, cudaStream_t, const uint64_t*);
+template int32_t launch_bn_bwd_apply<bf16>(const bf16*, const bf16*, const float*, const float*, long long, int, int, int, float, uint64_t, uint64_t, bf16*, cudaStream_t, const uint64_t*);
 
 // ---------------------------------------------------------------------------
 // dz = dy * [out > 0] * (1/(1-p) if dropout)    -- backward of the trailing
@@ -637,5 +643,37 @@ int32_t launch_add_inplace(T* d, const T* s, size_t n, cudaStream_t st) {
 }
 template int32_t launch_add_inplace<float>(float*, const float*, size_t, cudaStream_t);
 template int32_t launch_add_inplace<bf16>(bf16*, const bf16*, size_t, cudaStream_t);
+
+// ---------------------------------------------------------------------------
+// dropout random state on the device: {seed, offset}.  Forward copies the state it will use next to `slot` (kept with the
+// tensors saved for backward, so backward replays the same mask) and advances the caller's state by the number of Philox
+// calls the block consumes; a CUDA graph of the step therefore draws a fresh mask at every replay.
+// ---------------------------------------------------------------------------
+__global__ void rng_fetch_kernel(uint64_t* state, uint64_t seed, uint64_t offset, uint64_t advance, uint64_t* slot) {
+  pdl_enter();
+  if (threadIdx.x == 0 && blockIdx.x == 0) {
+    if (state) { slot[0] = state[0]; slot[1] = state[1]; state[1] += advance; }
+    else { slot[0] = seed; slot[1] = offset; }
+  }
+}
+int32_t launch_rng_fetch(uint64_t* state, uint64_t seed, uint64_t offset, uint64_t advance, uint64_t* slot, cudaStream_t st) {
+  launch_k(rng_fetch_kernel, 1, 32, 0, st, state, seed, offset, advance, slot);
+  STGCN_CHECK_LAUNCH("rng_fetch");
+  return STGCN_OK;
+}
+__global__ void __launch_bounds__(256) dropout_mask_kernel(uint64_t seed, uint64_t offset, float p, float inv_keep, size_t n,
+                                                           float* __restrict__ out) {
+  pdl_enter();
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+    out[i] = dropout_scale(seed, offset, (uint64_t)i, p, inv_keep);
+}
+int32_t launch_dropout_mask(uint64_t seed, uint64_t offset, float p, size_t n, float* out, cudaStream_t st) {
+  const float inv_keep = p > 0.f ? 1.f / (1.f - p) : 1.f;
+  int blocks = (int)std::min<size_t>((n + 255) / 256, 148 * 16);
+  if (blocks < 1) blocks = 1;
+  launch_k(dropout_mask_kernel, blocks, 256, 0, st, seed, offset, p, inv_keep, n, out);
+  STGCN_CHECK_LAUNCH("dropout_mask");
+  return STGCN_OK;
+}
 
 }  // namespace stgcn

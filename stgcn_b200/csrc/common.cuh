@@ -150,7 +150,15 @@ struct ConvGeom {      // implicit GEMM over frames: see gemm_simt.cu / umma_gem
   int taps;
   int stride, pad;     // forward: t_in_frame = j*stride - pad + tap
   int dgrad;           // 1: transposed conv: q = j + pad - tap, valid iff q%stride==0, frame = q/stride
+  int c_valid = 0;     // reduction / output channels that carry data when the operand is zero-padded to c / n_out (0 = all):
+  int n_valid = 0;     // only used for the ALGORITHMIC work the timing hooks report
 };
+// algorithmic multiply-adds x 2 of one implicit GEMM: forward 2 rows_out taps c n; the data gradient of a
+// strided conv does the forward's work (its rows are the forward's OUTPUT rows = this geometry's input rows), not taps x its rows
+__host__ inline double conv_algorithmic_flops(const ConvGeom& g) {
+  const double rows = (double)g.nb * (g.dgrad ? g.t_in : g.t_out) * g.v;
+  return 2.0 * rows * g.taps * (double)(g.c_valid > 0 ? g.c_valid : g.c) * (double)(g.n_valid > 0 ? g.n_valid : g.n_out);
+}
 
 __host__ __device__ __forceinline__ int conv_in_frame(const ConvGeom& g, int j, int tap) {
   if (!g.dgrad) {

@@ -73,6 +73,7 @@ __global__ void __launch_bounds__(256) conv_gemm_simt_kernel(ConvGeom g, const T
   }
   // epilogue
   const float inv_keep = ep.dropout_p > 0.f ? 1.f / (1.f - ep.dropout_p) : 1.f;
+  const uint64_t d_seed = ep.rng ? ep.rng[0] : ep.seed, d_off = ep.rng ? ep.rng[1] : ep.offset;
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
     long long r = m0 + ty * 4 + i;
@@ -89,7 +90,7 @@ __global__ void __launch_bounds__(256) conv_gemm_simt_kernel(ConvGeom g, const T
       size_t o = (size_t)r * g.n_out + n;
       if (ep.residual) t += ldf(reinterpret_cast<const T*>(ep.residual) + o);
       if (ep.relu) t = fmaxf(t, 0.f);
-      if (ep.dropout_p > 0.f) t *= dropout_scale(ep.seed, ep.offset, o, ep.dropout_p, inv_keep);
+      if (ep.dropout_p > 0.f) t *= dropout_scale(d_seed, d_off, o, ep.dropout_p, inv_keep);
       if (ep.accumulate) t += ldf(out + o);
       stf(out + o, t);
     }
@@ -98,7 +99,7 @@ __global__ void __launch_bounds__(256) conv_gemm_simt_kernel(ConvGeom g, const T
 
 template <class T>
 int32_t launch_conv_gemm_simt(const ConvGeom& g, const T* in, const float* w, const GemmEpilogue& ep, T* out, cudaStream_t st) {
-  KernelTimer kt_(KC_SIMT_GEMM, 2.0 * g.nb * g.t_out * g.v * (double)g.c * g.n_out * g.taps, st);
+  KernelTimer kt_(KC_SIMT_GEMM, conv_algorithmic_flops(g), st);
   long long rows = (long long)g.nb * g.t_out * g.v;
   dim3 grid((unsigned)cdiv(rows, BM), (unsigned)cdiv(g.n_out, BN));
   launch_k(conv_gemm_simt_kernel<T>, grid, 256, 0, st, g, in, w, ep, out);

@@ -20,6 +20,7 @@ struct GemmEpilogue {
   int accumulate = 0;
   float dropout_p = 0.f;
   uint64_t seed = 0, offset = 0;
+  const uint64_t* rng = nullptr;     // device {seed, offset}: overrides the two values above when set
   float* stat_partials = nullptr;    // tcgen05 engine only: per-CTA column sum / sumsq of the stored output, [grid][2][n_out]
   float* vsum = nullptr;             // tcgen05 engine only: [V][n_out] += per-joint column sums of the stored output
 };
@@ -62,13 +63,16 @@ int32_t launch_bn_eval_coeffs(int C, const float* gamma, const float* beta, cons
 // out_partials / out_nblk (optional): also produce per-CTA column statistics of the stored output (see affine_act_stats_kernel)
 template <class T> int32_t launch_affine_act(const T* x, long long rows, int C, const float* a, const float* b, int relu, float p,
                                             uint64_t seed, uint64_t offset, T* y, cudaStream_t st, float* out_partials = nullptr,
-                                            int* out_nblk = nullptr);
+                                            int* out_nblk = nullptr, const uint64_t* rng = nullptr);
 template <class T> int32_t launch_bn_bwd_reduce(const T* dy, const T* z, const float* stats, long long rows, int C, int relu, float p,
                                                uint64_t seed, uint64_t offset, float* partials, int* nblk, cudaStream_t st,
-                                               ZeroJobs* zero = nullptr);
+                                               ZeroJobs* zero = nullptr, const uint64_t* rng = nullptr);
 int32_t launch_bn_bwd_finalize(const float* partials, int nblk, int C, float* sums, float* dgamma, float* dbeta, cudaStream_t st);
 template <class T> int32_t launch_bn_bwd_apply(const T* dy, const T* z, const float* stats, const float* sums, long long rows, int C,
-                                              int relu, int training, float p, uint64_t seed, uint64_t offset, T* dz, cudaStream_t st);
+                                              int relu, int training, float p, uint64_t seed, uint64_t offset, T* dz, cudaStream_t st,
+                                              const uint64_t* rng = nullptr);
+int32_t launch_rng_fetch(uint64_t* state, uint64_t seed, uint64_t offset, uint64_t advance, uint64_t* slot, cudaStream_t st);
+int32_t launch_dropout_mask(uint64_t seed, uint64_t offset, float p, size_t n, float* out, cudaStream_t st);
 template <class T> int32_t launch_relu_bwd(const T* dy, const T* out, long long total, float p, T* dz, cudaStream_t st);
 template <class TS, class TD> int32_t launch_cast(const TS* s, TD* d, size_t n, cudaStream_t st);
 template <class T> int32_t launch_add_inplace(T* d, const T* s, size_t n, cudaStream_t st);

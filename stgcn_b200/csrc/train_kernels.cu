@@ -47,7 +47,10 @@ __global__ void __launch_bounds__(kCeThreads) cross_entropy_fwd_kernel(const flo
     float se = 0.f;
     for (int j = lane; j < classes; j += 32) se += expf(row[j] - mx);
     se = warp_sum(se);
-    const bool valid = lab != ignore_index;
+    // a label outside [0, classes) that is not ignore_index (torch raises a device assert): no out-of-bounds read here --
+    // the row contributes a NaN to the loss and a zero gradient
+    const bool bad = lab != ignore_index && (lab < 0 || lab >= classes);
+    const bool valid = lab != ignore_index && !bad;
     const float rinv = valid ? inv / se : 0.f;
     for (int j = lane; j < classes; j += 32) {
       float g = expf(row[j] - mx) * rinv;
@@ -55,6 +58,7 @@ __global__ void __launch_bounds__(kCeThreads) cross_entropy_fwd_kernel(const flo
       dlogits[(size_t)r * classes + j] = g;
     }
     if (valid && lane == 0) acc += (logf(se) + mx) - row[lab];
+    if (bad && lane == 0) acc = __int_as_float(0x7fc00000);
   }
   if (lane == 0) s_loss[warp] = acc;
   __syncthreads();

@@ -57,6 +57,7 @@ struct UmmaParams {
   int relu;
   float dropout_p, inv_keep;
   uint64_t seed, offset;
+  const uint64_t* rng;   // device {seed, offset} (overrides the values above)
 };
 
 struct TileCoord { int n_t, ph, j0, b; };
@@ -338,8 +339,9 @@ conv_gemm_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_c
           }
           if (o_dropout_p > 0.f && row_valid) {
             const uint64_t o = (uint64_t)grow * p.n_out + n0;
+            const uint64_t d_seed = p.rng ? p.rng[0] : p.seed, d_off = p.rng ? p.rng[1] : p.offset;
 #pragma unroll
-            for (int i = 0; i < 32; ++i) f[i] *= dropout_scale(p.seed, p.offset, o + i, o_dropout_p, p.inv_keep);
+            for (int i = 0; i < 32; ++i) f[i] *= dropout_scale(d_seed, d_off, o + i, o_dropout_p, p.inv_keep);
           }
           // bf16 pack and 128B-swizzled store: 16-byte chunk j of row lands at chunk (j ^ (row & 7))
 #pragma unroll
@@ -473,7 +475,7 @@ bool umma_conv_gemm_supported(const ConvGeom& g) {
 }
 
 int32_t launch_conv_gemm_umma(const ConvGeom& g, const bf16* in, const bf16* w, const GemmEpilogue& ep, bf16* out, cudaStream_t st) {
-  KernelTimer kt_(KC_UMMA_GEMM, 2.0 * g.nb * g.t_out * g.v * (double)g.c * g.n_out * g.taps, st);
+  KernelTimer kt_(KC_UMMA_GEMM, conv_algorithmic_flops(g), st);
   if (!umma_conv_gemm_supported(g)) { set_error("umma conv-gemm: unsupported geometry"); return STGCN_ERR_UNSUPPORTED; }
   if (ep.accumulate) { set_error("umma conv-gemm: accumulate epilogue unsupported"); return STGCN_ERR_UNSUPPORTED; }
   if (((uintptr_t)ep.bias | (uintptr_t)ep.scale | (uintptr_t)ep.shift) & 15) {
@@ -558,7 +560,7 @@ int32_t launch_conv_gemm_umma(const ConvGeom& g, const bf16* in, const bf16* w, 
   p.tmem_cols = cols;
   p.bias = ep.bias; p.bias2d = ep.bias2d; p.scale = ep.scale; p.shift = ep.shift;
   p.residual = reinterpret_cast<const bf16*>(ep.residual); p.relu = ep.relu;
-  p.dropout_p = ep.dropout_p; p.inv_keep = ep.dropout_p > 0.f ? 1.f / (1.f - ep.dropout_p) : 1.f; p.seed = ep.seed; p.offset = ep.offset;
+  p.dropout_p = ep.dropout_p; p.inv_keep = ep.dropout_p > 0.f ? 1.f / (1.f - ep.dropout_p) : 1.f; p.seed = ep.seed; p.offset = ep.offset; p.rng = ep.rng;
 
   CUtensorMap map_in, map_w, map_out;
   const uint64_t C = g.c, V = g.v, N = g.n_out;

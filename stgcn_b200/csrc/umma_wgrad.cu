@@ -209,7 +209,7 @@ static int num_sms_wg() {
 
 int32_t launch_wgrad_umma(const ConvGeom& g, const bf16* dout, const bf16* in, const WIndex& wi, float* packed_ws, float* dw,
                           cudaStream_t st, int c_valid, bool packed_is_zero, cudaStream_t unpack_st, cudaEvent_t unpack_ev) {
-  KernelTimer kt_(KC_UMMA_WGRAD, 2.0 * g.nb * g.t_out * g.v * (double)g.c * g.n_out * g.taps, st);
+  KernelTimer kt_(KC_UMMA_WGRAD, 2.0 * g.nb * g.t_out * g.v * (double)(c_valid >= 0 ? c_valid : g.c) * g.n_out * g.taps, st);
   if (!umma_wgrad_supported(g)) { set_error("umma wgrad: unsupported geometry"); return STGCN_ERR_UNSUPPORTED; }
   WgParams p; memset(&p, 0, sizeof(p));
   p.rev = next_direction();

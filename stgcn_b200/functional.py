@@ -28,11 +28,23 @@ def _f32(t):
     return t
 
 
+def _grad_out(param, buf):
+    """Tensor a parameter gradient is written to: the caller-provided slice (same element count, fp32, same device) or a new one."""
+    if buf is not None and buf.numel() == param.numel() and buf.dtype == param.dtype and buf.device == param.device:
+        return buf.view(param.shape)
+    return torch.empty_like(param)
+
+
+def grad_buf_of(p):
+    return getattr(p, '_stgcn_grad_buf', None) if p is not None else None
+
+
 class _BlockFn(torch.autograd.Function):
     """SpatialTemporalConv.forward / its autograd (st_graphconv.py:85-109)."""
 
     @staticmethod
     def forward(ctx, x, cfg, buffers, bn1_w, bn1_b, A, W, Wb, Wt, bt, bn2_w, bn2_b, Wr, Wrb):
+        # cfg['rng_state']: int64[2] device tensor {seed, offset} of the block's dropout generator (None without dropout)
         L.require_cuda(x, 'f_in')
         lib = L.lib()
         dt = cfg['dtype']
@@ -53,7 +65,7 @@ class _BlockFn(torch.autograd.Function):
         P = L.BlockParams(L.ptr(_f32(bn1_w)), L.ptr(_f32(bn1_b)), L.ptr(rm1), L.ptr(rv1), L.ptr(nbt1),
                           L.ptr(_f32(A)), L.ptr(_f32(W)), L.ptr(_f32(Wb)), L.ptr(_f32(Wt)), L.ptr(_f32(bt)),
                           L.ptr(_f32(bn2_w)), L.ptr(_f32(bn2_b)), L.ptr(rm2), L.ptr(rv2), L.ptr(nbt2),
-                          L.ptr(_f32(Wr)), L.ptr(_f32(Wrb)))
+                          L.ptr(_f32(Wr)), L.ptr(_f32(Wrb)), L.ptr(cfg.get('rng_state')))
         y = torch.empty((n, t_out, v, cfg['c_out']), dtype=dt, device=x.device)
         saved = None
         if need_grad:
@@ -96,6 +108,7 @@ class _BlockFn(torch.autograd.Function):
             cfg['y_stats'] = (ys, nb.value) if (ys is not None and nb.value > 0) else None
         if need_grad:
             ctx.d = d
+            ctx.grad_bufs = cfg.get('grad_bufs')
             ctx.buffers = buffers
             ctx.x_dtype = x.dtype
             ctx.has_res_conv = Wr is not None
@@ -111,11 +124,13 @@ class _BlockFn(torch.autograd.Function):
         dyp = _to_ntvc(gy, y.dtype)
         P = L.BlockParams(L.ptr(bn1_w), L.ptr(bn1_b), L.ptr(rm1), L.ptr(rv1), L.ptr(nbt1), L.ptr(A), L.ptr(W),
                           L.ptr(Wb), L.ptr(Wt), L.ptr(bt), L.ptr(bn2_w), L.ptr(bn2_b), L.ptr(rm2), L.ptr(rv2),
-                          L.ptr(nbt2), L.ptr(Wr), L.ptr(Wrb))
-        g = {k: torch.empty_like(v) for k, v in (('bn1_w', bn1_w), ('bn1_b', bn1_b), ('A', A), ('W', W), ('Wb', Wb),
-                                                   ('Wt', Wt), ('bt', bt), ('bn2_w', bn2_w), ('bn2_b', bn2_b))}
-        gWr = torch.empty_like(Wr) if Wr is not None else None
-        gWrb = torch.empty_like(Wrb) if Wrb is not None else None
+                          L.ptr(nbt2), L.ptr(Wr), L.ptr(Wrb), None)
+        # gradients go straight into the data-parallel reducer's bucket slices when there are any (parallel.GradBucketReducer)
+        gb = ctx.grad_bufs or [None] * 11
+        g = {k: _grad_out(v, gb[i]) for i, (k, v) in enumerate((('bn1_w', bn1_w), ('bn1_b', bn1_b), ('A', A), ('W', W), ('Wb', Wb),
+                                                                 ('Wt', Wt), ('bt', bt), ('bn2_w', bn2_w), ('bn2_b', bn2_b)))}
+        gWr = _grad_out(Wr, gb[9]) if Wr is not None else None
+        gWrb = _grad_out(Wrb, gb[10]) if Wrb is not None else None
         G = L.BlockGrads(L.ptr(g['bn1_w']), L.ptr(g['bn1_b']), L.ptr(g['A']), L.ptr(g['W']), L.ptr(g['Wb']),
                          L.ptr(g['Wt']), L.ptr(g['bt']), L.ptr(g['bn2_w']), L.ptr(g['bn2_b']), L.ptr(gWr), L.ptr(gWrb))
         dx = torch.empty_like(xp) if ctx.needs_input_grad[0] else None
@@ -199,6 +214,7 @@ class _HeadFn(torch.autograd.Function):
                 'head_forward')
         ctx.shape = (n, t, v, c, classes)
         ctx.dt = fp.dtype
+        ctx.grad_bufs = (grad_buf_of(fcw), grad_buf_of(fcb))
         ctx.save_for_backward(pooled, fcw)
         return logits
 
@@ -209,8 +225,9 @@ class _HeadFn(torch.autograd.Function):
         n, t, v, c, classes = ctx.shape
         gl = gl.contiguous().float()
         dfeat = torch.empty((n, t, v, c), dtype=ctx.dt, device=gl.device)
-        dW = torch.empty_like(fcw)
-        db = torch.empty((classes,), dtype=torch.float32, device=gl.device)
+        dW = _grad_out(fcw, ctx.grad_bufs[0])
+        db = ctx.grad_bufs[1].view(classes) if (ctx.grad_bufs[1] is not None and ctx.grad_bufs[1].numel() == classes) \
+            else torch.empty((classes,), dtype=torch.float32, device=gl.device)
         scratch = pooled.clone()      # head_backward reuses the pooled buffer as scratch
         L.check(lib.stgcn_head_backward(L.dtype_code(ctx.dt), n, t, v, c, classes, L.ptr(scratch), L.ptr(fcw), L.ptr(gl),
                                         L.ptr(dfeat), L.ptr(dW), L.ptr(db), L.stream_ptr(gl.device)), 'head_backward')
@@ -253,6 +270,15 @@ class _CrossEntropyFn(torch.autograd.Function):
         L.check(lib.stgcn_cross_entropy_backward(dl.shape[0], dl.shape[1], L.ptr(dl), L.ptr(g), L.ptr(out),
                                                  L.stream_ptr(dl.device)), 'cross_entropy_backward')
         return out.to(ctx.in_dtype), None, None
+
+
+def dropout_mask(seed, offset, p, count, device):
+    """Keep-scales (1/(1-p) or 0) of `count` consecutive block-output elements under Philox state (seed, offset): what
+    nn.Dropout(p) at st_graphconv.py:108 multiplies by in this library.  Test / oracle helper."""
+    out = torch.empty(int(count), dtype=torch.float32, device=device)
+    L.check(L.lib().stgcn_dropout_mask(int(seed), int(offset), float(p), int(count), L.ptr(out), L.stream_ptr(out.device)),
+            'dropout_mask')
+    return out
 
 
 def cross_entropy(logits, labels, ignore_index=-100):

@@ -91,17 +91,24 @@ def create_adjacency_matrices(strat=Strategy.UNI_LABELING, d=1, distances=None, 
     raise ValueError('unknown partitioning strategy %r' % (strat,))
 
 
-def normalize(matrices, expo=-0.5, alpha=0.001):
+def normalize(matrices, expo=-0.5, alpha=0.001, dense_alpha=True):
+    """dense_alpha=True is the reference (adjacency.py:161-183): alpha is added to EVERY entry of diag(rowsum) before the
+    element-wise power, which makes the result dense with entries ~1e4..1e5.  dense_alpha=False is the textbook
+    D^-1/2 A D^-1/2 the reference's comment intends (alpha on the diagonal only; entries <= 0.5) -- an option beyond the
+    reference, used for the Kinetics-18 benchmark graph."""
     out = torch.empty(len(matrices), matrices[0].shape[0], matrices[0].shape[1])
     for i, A in enumerate(matrices):
-        lam = (torch.diag(A.sum(dim=1)) + alpha) ** expo      # dense: alpha lands off the diagonal too
+        if dense_alpha:
+            lam = (torch.diag(A.sum(dim=1)) + alpha) ** expo      # dense: alpha lands off the diagonal too
+        else:
+            lam = torch.diag((A.sum(dim=1) + alpha) ** expo)
         out[i] = lam @ A @ lam
     return out
 
 
 def get_normalized_adjacency_matrices(strat=Strategy.UNI_LABELING, d=1, alpha=0.001, distance_file=None,
-                                      distances=None, skeleton='body25'):
+                                      distances=None, skeleton='body25', dense_alpha=True):
     if distances is None and distance_file:
         import numpy as np
         distances = np.load(distance_file)
-    return normalize(create_adjacency_matrices(strat, d, distances, skeleton), alpha=alpha)
+    return normalize(create_adjacency_matrices(strat, d, distances, skeleton), alpha=alpha, dense_alpha=dense_alpha)

@@ -15,6 +15,13 @@ from . import _lib as L
 from . import functional as Fn
 
 
+def _momentum(bn):
+    if bn.momentum is None:
+        # torch switches to a cumulative moving average then; the library implements the exponential one only
+        raise RuntimeError('stgcn_b200: BatchNorm2d(momentum=None) (cumulative average) is not supported')
+    return float(bn.momentum)
+
+
 class SpatialConv(nn.Module):
     """Spatial graph convolution, reference st_graphconv.py:111-152.
 
@@ -66,28 +73,41 @@ class SpatialTemporalConv(nn.Module):
         self.compute_dtype = compute_dtype
         self.flags = 0
         self._calls = 0
+        # dropout generator {seed, offset} on the device (advanced by the library, so a captured step draws fresh masks);
+        # non-persistent: the state_dict keeps the reference's keys
+        self.register_buffer('_rng_state', None, persistent=False)
         self._prep_cache = {}      # frozen-parameter inference operands (functional._BlockFn), keyed by tensor versions
+
+    def _ensure_rng(self, device):
+        """Create the device-resident dropout generator on first use: seeded once from torch's CPU generator (so
+        torch.manual_seed makes runs repeatable), never read back by the host."""
+        if self.dropout is not None and (self._rng_state is None or self._rng_state.device != device):
+            self._rng_state = torch.tensor([int(torch.randint(0, 2 ** 62, (1,))), 0], dtype=torch.int64).to(device)
 
     def forward(self, f_in):
         sc, tc, b1, b2 = self.spatialConv, self.temporalConv, self.batch_n, self.batch_n_2
         params = [b1.weight, b1.bias, sc.A, sc.W.weight.view(sc.K * sc.C_out, sc.C_in), sc.W.bias,
                   tc.weight.view(self.C_out, self.C_out, self.gamma), tc.bias, b2.weight, b2.bias]
+        raw = [b1.weight, b1.bias, sc.A, sc.W.weight, sc.W.bias, tc.weight, tc.bias, b2.weight, b2.bias]
         if self._res_mode == L.RES_CONV:
             params += [self.apply_residual.weight.view(self.C_out, self.C_in), self.apply_residual.bias]
+            raw += [self.apply_residual.weight, self.apply_residual.bias]
         else:
             params += [None, None]
+            raw += [None, None]
         need_grad = torch.is_grad_enabled() and (f_in.requires_grad or any(p is not None and p.requires_grad for p in params))
         p_drop = float(self.dropout.p) if (self.dropout is not None and self.training) else 0.0
-        seed = 0
         if p_drop > 0:
-            seed = int(torch.randint(0, 2 ** 62, (1,)).item())
+            self._ensure_rng(f_in.device)
         self._calls += 1
         if self.training:
             self._prep_cache.clear()       # running statistics are about to change behind torch's version counters
         cfg = {'dtype': self.compute_dtype, 'c_in': self.C_in, 'c_out': self.C_out, 'gamma': self.gamma,
                'stride': self.temporal_stride, 'pad': self.temporal_padding, 'training': self.training,
                'residual': self._res_mode, 'dropout_p': p_drop, 'eps': b1.eps,
-               'momentum': 0.1 if b1.momentum is None else b1.momentum, 'seed': seed, 'need_grad': need_grad,
+               'momentum': _momentum(b1), 'seed': 0, 'need_grad': need_grad,
+               'rng_state': self._rng_state if p_drop > 0 else None,
+               'grad_bufs': [Fn.grad_buf_of(q) for q in raw],
                'flags': self.flags, 'prep_cache': self._prep_cache}
         buffers = (b1.running_mean, b1.running_var, b1.num_batches_tracked,
                    b2.running_mean, b2.running_var, b2.num_batches_tracked)

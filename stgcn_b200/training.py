@@ -17,6 +17,7 @@ restored in place), so constructing the object does not train the model.
 """
 import torch
 
+from . import _lib
 from .functional import cross_entropy
 
 
@@ -28,9 +29,8 @@ class CapturedTrainStep:
             raise RuntimeError('stgcn_b200.CapturedTrainStep: put the model in train() mode first')
         self.model, self.opt, self.loss_fn, self.reducer = model, optimizer, loss_fn, reducer
         self._blocks = [m for m in model.modules() if hasattr(m, '_prep_cache')]
-        if any(getattr(m, 'dropout', None) is not None and m.dropout.p > 0 for m in self._blocks):
-            raise RuntimeError('stgcn_b200.CapturedTrainStep: dropout draws its seed on the host per call; a captured step would '
-                               'replay one mask (use the eager step with dropout_rate > 0)')
+        for m in self._blocks:            # dropout state lives on the device and is advanced by the library: every replay draws
+            m._ensure_rng(example_x.device)   # a fresh mask; create it now so the warm-up below can be undone exactly
         self.x = torch.empty_like(example_x)
         self.y = torch.empty_like(example_y)
         self.x.copy_(example_x); self.y.copy_(example_y)
@@ -64,6 +64,18 @@ class CapturedTrainStep:
         self.graph = torch.cuda.CUDAGraph()
         with torch.cuda.graph(self.graph):
             self.loss = self._eager_step()
+        # the graph holds raw addresses inside the library's scratch arena: keep that arena alive for as long as the graph
+        self._workspace = _lib.current_workspace(dev)
+
+    def close(self):
+        """Destroy the captured graph (and with it every reference it holds: NCCL work of the gradient all-reduce, the scratch
+        arena).  Call before `torch.distributed.destroy_process_group()`; the object cannot be called afterwards."""
+        if getattr(self, 'graph', None) is not None:
+            torch.cuda.synchronize()
+            self.graph.reset()
+            self.graph = None
+            self.loss = None
+            self._workspace = None
 
     def _model_tensors(self):
         return list(self.model.parameters()) + list(self.model.buffers())
@@ -82,6 +94,8 @@ class CapturedTrainStep:
         if x.shape != self.x.shape or y.shape != self.y.shape:
             raise RuntimeError('stgcn_b200.CapturedTrainStep: batch shape %s differs from the captured %s' %
                                (tuple(x.shape), tuple(self.x.shape)))
+        if self.graph is None:
+            raise RuntimeError('stgcn_b200.CapturedTrainStep: called after close()')
         self.x.copy_(x, non_blocking=True)
         self.y.copy_(y, non_blocking=True)
         self.graph.replay()
@@ -119,6 +133,7 @@ class CapturedForward:
             self.out = model(self.x)
         # the graph reads the operands prepared during the warm-up: keep them alive even if the modules drop their caches
         self._keep = [m._prep_cache.get('blob') for m in model.modules() if hasattr(m, '_prep_cache')]
+        self._workspace = _lib.current_workspace(dev)      # and the scratch arena whose addresses it recorded
 
     def __call__(self, x):
         if x.shape != self.x.shape:

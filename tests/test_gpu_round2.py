@@ -1,0 +1,302 @@
+"""GPU parity, second set: the reference's features that round 1 left thinly covered.
+
+  * nn.Dropout (st_graphconv.py:53-58,106-109) with the library's Philox mask replayed in the oracle: y, dx, every gradient;
+    a captured training step must draw a fresh mask at every replay;
+  * the STGCN twin (stgcn.py:56-80: softmax output, dropout 0.5, edge-importance masks);
+  * L_STGCN(use_edge_importance=True) (lightning_model.py:53-59): jittered masks scale A at construction, get no gradient;
+  * SpatialConv alone on the bf16 / tcgen05 path (st_graphconv.py:139-152);
+  * residual blocks (st_graphconv.py:60-82) at full frame counts on the tcgen05 path;
+  * a captured graph must survive growth of the library's scratch arena.
+Tolerances: fp32 1e-4, bf16 2e-2 (max|got-ref| / max|ref| per tensor), structurally-zero gradients absolutely.
+"""
+import argparse
+import contextlib
+import io
+
+import numpy as np
+import pytest
+import torch
+
+from _helpers import assert_argmax_consistent, check_dx_kink_tolerant, rel_err
+from oracle import stgcn_oracle as O
+from test_gpu_block import build_block, oracle_block, run_block
+
+pytestmark = pytest.mark.gpu
+TOL = {torch.float32: 1e-4, torch.bfloat16: 2e-2}
+
+
+def _rand_bn(m):
+    with torch.no_grad():
+        for bn in (m.batch_n, m.batch_n_2):
+            bn.weight.uniform_(0.5, 1.5); bn.bias.uniform_(-0.3, 0.3)
+            bn.running_mean.uniform_(-0.2, 0.2); bn.running_var.uniform_(0.6, 1.4)
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# dropout with a replayed mask
+# ---------------------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize('residual', [False, True], ids=['default', 'residual'])
+@pytest.mark.parametrize('dtype', [torch.float32, torch.bfloat16], ids=['float32', 'bfloat16'])
+def test_dropout_replayed_mask_matches_oracle(dtype, residual):
+    """C % 64 == 0, so bf16 runs the tcgen05 chain: dropout in the element-wise pass (default block) and in the temporal GEMM's
+    EP_DROPOUT epilogue (residual block).  The mask the library drew is rebuilt from its (seed, offset) through the C ABI
+    (stgcn_dropout_mask) and handed to the oracle (oracle.dropout(mask=...))."""
+    from stgcn_b200.functional import dropout_mask
+    ci = co = 64; T, V, K, N, p_drop = 24, 25, 3, 3, 0.5
+    torch.manual_seed(4321)
+    A = torch.randn(K, V, V) * 0.2
+    with contextlib.redirect_stdout(io.StringIO()):
+        m = build_block(ci, co, A, 1, residual, dtype=dtype, dropout=p_drop)
+    _rand_bn(m)
+    p = {k: v.detach().cpu().clone() for k, v in m.state_dict().items()}
+    x = torch.randn(N, ci, T, V); gy = torch.randn(N, co, T, V)
+    m.train()
+    m._ensure_rng(torch.device('cuda'))
+    seed, off0 = [int(v) for v in m._rng_state.cpu()]
+    y, dx, grads = run_block(m, x, gy, True)
+    seed1, off1 = [int(v) for v in m._rng_state.cpu()]
+    assert seed1 == seed and off1 == off0 + (N * T * V * co + 3) // 4           # advanced by one Philox call per 4 outputs
+    scale = dropout_mask(seed, off0, p_drop, N * T * V * co, 'cuda').cpu().view(N, T, V, co).permute(0, 3, 1, 2)
+    keep = (scale > 0).float()
+    assert set(torch.unique(scale).tolist()) <= {0.0, 1.0 / (1.0 - p_drop)}
+    assert 0.45 < float(keep.mean()) < 0.55
+    cfg = O.BlockCfg(ci, co, 9, 1, 4, p_drop, residual)
+
+    def oracle(bf16):
+        q = {k: v.clone() for k, v in p.items()}
+        leaves = {}
+        for k, v in q.items():
+            if v.dtype.is_floating_point and 'running' not in k:
+                v.requires_grad_(True); leaves[k] = v
+        xr = x.clone().requires_grad_(True)
+        f = O.block_forward_bf16 if bf16 else O.block_forward
+        yr = f(xr, q, cfg, True, drop_mask=keep)
+        (yr * gy).sum().backward()
+        return yr.detach(), xr.grad, {k: v.grad for k, v in leaves.items()}
+
+    tol = TOL[dtype]
+    y_ref, dx_ref, g_ref = oracle(False)
+    assert rel_err(y, y_ref) < tol
+    dropped_only = float(((y == 0) & (keep == 0)).float().sum() / (keep == 0).float().sum())
+    assert dropped_only == 1.0
+    if dtype == torch.bfloat16:
+        y_ref, dx_ref, g_ref = oracle(True)
+        assert rel_err(y, y_ref) < tol
+    kinks = check_dx_kink_tolerant(dx, dx_ref, tol * 2)
+    flips = int((((y > 0) != (y_ref > 0)) & (keep > 0)).sum())
+    assert flips <= max(2, int(1e-4 * y.numel())), flips
+    ptol = tol * 2 if (kinks == 0 and flips == 0) else 1e-1
+    for k, v in grads.items():
+        if not residual and k == 'temporalConv.bias':
+            assert float(v.abs().max()) <= 1e-5 * float(gy.abs().sum())
+            continue
+        assert rel_err(v.reshape(g_ref[k].shape), g_ref[k]) < ptol, k
+    # a second call draws a different mask; eval mode drops nothing
+    y2, _, _ = run_block(m, x, gy, True)
+    assert float(((y2 == 0) != (y == 0)).float().mean()) > 0.2
+    m.eval()
+    with torch.no_grad():
+        ye = m(x.cuda()).float().cpu()
+    assert float((ye == 0).float().mean()) < 0.75
+
+
+def test_captured_train_step_with_dropout_draws_fresh_masks():
+    """STGCN's default dropout 0.5 (stgcn.py:41-50) inside CapturedTrainStep: every replay advances the device-resident
+    generator, so two replays on the same batch give different losses, and the generator offsets advance by the same amount
+    per step as in eager mode."""
+    from stgcn_b200 import CapturedTrainStep, STGCN
+    from stgcn_b200.optim import Adam
+    torch.manual_seed(0)
+    A = torch.randn(3, 25, 25) * 0.15
+    model = STGCN(3, 9, 10, edge_importance=False, compute_dtype=torch.bfloat16, A=A).cuda().train()
+    opt = Adam(model.parameters(), lr=0.0)                 # lr 0: the only thing that changes between replays is the mask
+    x = torch.randn(4, 40, 25, 3).cuda(); y = torch.tensor([1, 2, 3, 4]).cuda()
+
+    class NLL:
+        def __call__(self, probs, labels):
+            from stgcn_b200 import cross_entropy
+            return cross_entropy(torch.log(probs.clamp_min(1e-12)), labels)
+    step = CapturedTrainStep(model, opt, x, y, loss_fn=NLL())
+    offs0 = [int(b._rng_state[1]) for b in model.conv]
+    l1 = float(step(x, y)); offs1 = [int(b._rng_state[1]) for b in model.conv]
+    l2 = float(step(x, y)); offs2 = [int(b._rng_state[1]) for b in model.conv]
+    assert np.isfinite(l1) and np.isfinite(l2) and l1 != l2
+    assert all(b - a == c - b and b > a for a, b, c in zip(offs0, offs1, offs2))
+    step.close()
+    with pytest.raises(RuntimeError):
+        step(x, y)
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# model variants
+# ---------------------------------------------------------------------------------------------------------------------
+def _hp(**kw):
+    d = dict(C_in=3, nr_classes=60, gamma=9, dropout_rate=0.0, residual=False, use_edge_importance=False,
+             max_mask_jitter=0.001, partitioning=2, d=1, distance_file=None, distances=np.random.RandomState(0).rand(25))
+    d.update(kw)
+    return argparse.Namespace(**d)
+
+
+@pytest.mark.parametrize('dtype', [torch.float32, torch.bfloat16], ids=['float32', 'bfloat16'])
+def test_stgcn_twin_softmax_output_matches_oracle(dtype):
+    """STGCN (stgcn.py:7-80): default dropout 0.5 is inactive in eval mode, output = softmax probabilities."""
+    from stgcn_b200 import STGCN
+    torch.manual_seed(3)
+    A = torch.randn(2, 25, 25) * 0.15
+    model = STGCN(3, 9, 60, edge_importance=True, compute_dtype=dtype, A=A).cuda()
+    assert all(b.dropout is not None and b.dropout.p == 0.5 for b in model.conv)
+    assert len(list(model.Masks)) == 10
+    x = torch.randn(4, 40, 25, 3)
+    model.train()
+    with torch.no_grad():
+        for _ in range(2):
+            model(x.cuda())                       # calibrate the running statistics (dropout active here)
+    model.eval()
+    state = {k: v.detach().cpu().clone() for k, v in model.state_dict().items()}
+    with torch.no_grad():
+        got = model(x.cuda()).float().cpu()
+    ref = O.model_forward(x, state, O.stack_cfgs(3, 9, 0.5, False), False, softmax=True)
+    assert torch.allclose(got.sum(1), torch.ones(4), atol=1e-3)
+    assert rel_err(got, ref) < TOL[dtype]
+    assert_argmax_consistent(got, ref, exact=dtype == torch.float32)
+
+
+@pytest.mark.parametrize('dtype', [torch.float32, torch.bfloat16], ids=['float32', 'bfloat16'])
+def test_edge_importance_masks_scale_A_and_get_no_gradient(dtype):
+    """use_edge_importance=True (lightning_model.py:53-59): each block's A is A * Masks[i] at construction, re-wrapped as a
+    detached leaf (st_graphconv.py:129), so Masks never receive a gradient while spatialConv.A does."""
+    from stgcn_b200 import L_STGCN
+    torch.manual_seed(5)
+    A = torch.randn(3, 25, 25) * 0.15
+    model = L_STGCN(_hp(use_edge_importance=True, max_mask_jitter=0.2), compute_dtype=dtype, A=A)
+    for i, b in enumerate(model.conv):
+        assert torch.allclose(b.spatialConv.A.detach(), A * model.Masks[i].detach())
+        assert not torch.allclose(model.Masks[i].detach(), torch.ones_like(A))
+    state = {k: v.detach().clone() for k, v in model.state_dict().items()}
+    model = model.cuda().train()
+    x = torch.randn(4, 40, 25, 3); labels = torch.tensor([1, 5, 30, 59])
+    logits = model(x.cuda())
+    torch.nn.functional.cross_entropy(logits, labels.cuda()).backward()
+    assert all(mk.grad is None for mk in model.Masks)
+    assert all(b.spatialConv.A.grad is not None and float(b.spatialConv.A.grad.abs().max()) > 0 for b in model.conv)
+    ref = O.model_forward(x, state, O.stack_cfgs(3, 9, 0.0, False), True)
+    assert rel_err(logits, ref) < TOL[dtype]
+
+
+def test_spatial_conv_module_bf16_tcgen05_matches_oracle():
+    """SpatialConv alone with C_in % 64 == 0 in bf16: tensor-core aggregation + tcgen05 1x1 GEMM, and their gradients."""
+    from stgcn_b200 import SpatialConv
+    torch.manual_seed(12)
+    ci, co, T, V, K, N = 64, 128, 20, 25, 3, 3
+    A = torch.randn(K, V, V) * 0.3
+    m = SpatialConv(ci, co, A, compute_dtype=torch.bfloat16).cuda()
+    x = torch.randn(N, ci, T, V)
+    xg = x.cuda().requires_grad_(True)
+    out = m(xg)
+    go = torch.randn(N, co, T, V)
+    (out.float() * go.cuda()).sum().backward()
+    rb = lambda t: t.to(torch.bfloat16).float()
+    # oracle on the operands as the bf16 chain sees them (x, A, W rounded to bf16), fp32 arithmetic
+    Ar = A.clone().requires_grad_(True); W = m.W.weight.detach().cpu().clone().requires_grad_(True)
+    b = m.W.bias.detach().cpu().clone().requires_grad_(True); xr = rb(x).requires_grad_(True)
+    Aq = Ar + (rb(A) - A); Wq = W + (rb(W.detach()) - W.detach())
+    ref = O.spatial_conv(xr, Aq, Wq, b)
+    (ref * rb(go)).sum().backward()
+    tol = TOL[torch.bfloat16]
+    assert rel_err(out, ref) < tol
+    assert rel_err(xg.grad, xr.grad) < tol
+    assert rel_err(m.A.grad, Ar.grad) < tol
+    assert rel_err(m.W.weight.grad, W.grad) < tol
+    assert rel_err(m.W.bias.grad, b.grad) < tol
+    # and against the plain fp32 oracle on the unrounded operands
+    ref32 = O.spatial_conv(x, A, m.W.weight.detach().cpu(), m.W.bias.detach().cpu())
+    assert rel_err(out, ref32) < tol
+
+
+RES_FULL = [
+    # ci, co, T, V, K, stride   (the reference's best configuration is the residual one, report section 5.7)
+    (64, 64, 300, 25, 3, 1),
+    (64, 128, 300, 25, 3, 2),
+]
+
+
+@pytest.mark.parametrize('case', RES_FULL, ids=lambda c: '%d-%d-T%d-V%d-K%d-s%d' % c)
+@pytest.mark.parametrize('dtype', [torch.float32, torch.bfloat16], ids=['float32', 'bfloat16'])
+def test_residual_block_full_frames_matches_oracle(case, dtype):
+    ci, co, T, V, K, s = case
+    torch.manual_seed(321 + ci + co)
+    A = torch.randn(K, V, V) * 0.2
+    with contextlib.redirect_stdout(io.StringIO()):
+        m = build_block(ci, co, A, s, True, dtype=dtype)
+    with torch.no_grad():
+        for bn in (m.batch_n, m.batch_n_2):
+            bn.weight.uniform_(0.5, 1.5); bn.bias.uniform_(-0.3, 0.3)
+    p = {k: v.detach().cpu().clone() for k, v in m.state_dict().items()}
+    N = 2
+    x = torch.randn(N, ci, T, V)
+    T_out = (T - 1) // s + 1
+    gy = torch.randn(N, co, T_out, V)
+    cfg = O.BlockCfg(ci, co, 9, s, 4, 0.0, True)
+    tol = TOL[dtype]
+    y_ref, dx_ref, g_ref, _ = oracle_block(x, gy, p, cfg, True)
+    y, dx, grads = run_block(m, x, gy, True)
+    assert rel_err(y, y_ref) < tol
+    if dtype == torch.bfloat16:
+        y_ref, dx_ref, g_ref, _ = oracle_block(x, gy, p, cfg, True, bf16=True)
+        assert rel_err(y, y_ref) < tol
+    kinks = check_dx_kink_tolerant(dx, dx_ref, tol * 2, max_frames=20)
+    flips = int(((y > 0) != (y_ref > 0)).sum())
+    assert flips <= max(2, int(1e-4 * y.numel())), flips
+    ptol = tol * 2 if (kinks == 0 and flips == 0) else 5e-2
+    for k, v in grads.items():
+        assert rel_err(v.reshape(g_ref[k].shape), g_ref[k]) < ptol, k
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# scratch-arena growth under a live graph
+# ---------------------------------------------------------------------------------------------------------------------
+def test_captured_step_survives_workspace_growth():
+    """Capture a training step at a small shape, then run a LARGER eager forward (the arena grows), then replay: the replayed
+    step must equal an eager step on a twin model (the outgrown arena stays alive for the graph)."""
+    from stgcn_b200 import CapturedTrainStep, L_STGCN, _lib, cross_entropy
+    from stgcn_b200.optim import Adam
+    torch.manual_seed(0)
+    A = torch.randn(3, 25, 25) * 0.15
+    m1 = L_STGCN(_hp(), compute_dtype=torch.bfloat16, A=A).cuda().train()
+    m2 = L_STGCN(_hp(), compute_dtype=torch.bfloat16, A=A).cuda().train()
+    m2.load_state_dict(m1.state_dict())
+    o1, o2 = Adam(m1.parameters(), lr=0.01), Adam(m2.parameters(), lr=0.01)
+    x = torch.randn(4, 32, 25, 3).cuda(); y = torch.tensor([1, 2, 3, 4]).cuda()
+    step = CapturedTrainStep(m1, o1, x, y)
+    before = _lib.current_workspace(x.device)
+    junk = torch.full((256 << 20,), 7, dtype=torch.uint8, device='cuda')      # whatever the allocator hands out next
+    with torch.no_grad():
+        m2.eval(); m2(torch.randn(16, 120, 25, 3).cuda()); m2.train()          # much larger call: the arena must grow
+    assert _lib.current_workspace(x.device) is not before
+    l1 = float(step(x, y))
+    o2.zero_grad(set_to_none=True)
+    loss2 = cross_entropy(m2(x), y); loss2.backward(); o2.step()
+    assert abs(l1 - float(loss2)) < 2e-2 * max(1.0, abs(float(loss2)))
+    for (k, a), (_, b) in zip(m1.named_parameters(), m2.named_parameters()):
+        assert rel_err(a, b) < 2e-2, k
+    assert int(junk[:1024].sum()) == 7 * 1024 and int(junk[-1024:].sum()) == 7 * 1024
+    step.close()
+
+
+def test_cross_entropy_out_of_range_label_poisons_loss_without_oob():
+    import stgcn_b200
+    logits = torch.randn(6, 10).cuda().requires_grad_(True)
+    labels = torch.tensor([1, 2, 10, 3, -1, 4]).cuda()
+    loss = stgcn_b200.cross_entropy(logits, labels)
+    loss.backward()
+    assert torch.isnan(loss)
+    assert torch.isfinite(logits.grad).all()
+    assert float(logits.grad[2].abs().max()) == 0.0 and float(logits.grad[4].abs().max()) == 0.0
+
+
+def test_batchnorm_momentum_none_is_rejected():
+    A = torch.randn(3, 25, 25) * 0.2
+    m = build_block(8, 8, A, 1, False)
+    m.batch_n.momentum = None
+    with pytest.raises(RuntimeError):
+        m(torch.randn(2, 8, 12, 25).cuda())

@@ -49,3 +49,70 @@ def test_bucket_reducer_matches_full_batch_gradients():
         p.join(60)
         assert p.exitcode == 0
     assert err < 1e-6
+
+
+def _model_worker(rank, world, port, out):
+    """The real drop-in model's parameter set (incl. the edge-importance Masks that never get a gradient) through the
+    reducer; arithmetic by the CPU oracle (the product has no CPU path), which is all the reducer needs: autograd gradients
+    arriving at the model's Parameters."""
+    import argparse
+    import numpy as np
+    os.environ.update(MASTER_ADDR='127.0.0.1', MASTER_PORT=str(port))
+    dist.init_process_group('gloo', rank=rank, world_size=world)
+    from oracle import stgcn_oracle as O
+    from stgcn_b200 import L_STGCN
+    from stgcn_b200.parallel import GradBucketReducer, shard_batch
+    torch.manual_seed(0)
+    hp = argparse.Namespace(C_in=3, nr_classes=7, gamma=9, dropout_rate=0.0, residual=False, use_edge_importance=True,
+                            max_mask_jitter=0.01, partitioning=0, d=1, distance_file=None, distances=None)
+    model = L_STGCN(hp, A=torch.randn(2, 25, 25, generator=torch.Generator().manual_seed(3)) * 0.2)
+    names = [n for n, _ in model.named_parameters()]
+    assert any(n.startswith('Masks') for n in names)
+    state = dict(model.state_dict(keep_vars=True))
+    cfgs = O.stack_cfgs(3, 9, 0.0, False)
+    x = torch.randn(4, 12, 25, 3, generator=torch.Generator().manual_seed(1))
+    y = torch.randint(0, 7, (4,), generator=torch.Generator().manual_seed(2))
+
+    def grads_of(xs, ys):
+        model.zero_grad(set_to_none=True)
+        O.cross_entropy(O.model_forward(xs, state, cfgs, True, update_running=False), ys).backward()
+        return {n: (p.grad.clone() if p.grad is not None else None) for n, p in model.named_parameters()}
+
+    ref = None
+    if rank == 0:     # mean over shards of the per-shard gradients (per-replica BatchNorm statistics, SURVEY.md 7.3-3)
+        per = [grads_of(*shard_batch(x, y, r, world)) for r in range(world)]
+        ref = {n: (sum(g[n] for g in per) / world if per[0][n] is not None else None) for n in names}
+    red = GradBucketReducer(model.parameters(), num_buckets=3)
+    assert len(red.buckets) == 3
+    xs, ys = shard_batch(x, y, rank, world)
+    errs = []
+    for step in range(3):      # step 0 learns which gradients arrive; later steps launch buckets as soon as those are in
+        model.zero_grad(set_to_none=True)
+        O.cross_entropy(O.model_forward(xs, state, cfgs, True, update_running=False), ys).backward()
+        early = sum(red.launched)
+        red.finish()
+        if step > 0:
+            assert early >= 2, early                       # the Masks' bucket no longer waits for them
+        if rank == 0:
+            for n, p in model.named_parameters():
+                if n.startswith('Masks'):
+                    assert p.grad is None
+                else:
+                    errs.append(float((p.grad - ref[n]).abs().max() / ref[n].abs().max().clamp_min(1e-12)))
+    if rank == 0:
+        out.put(max(errs))
+    dist.destroy_process_group()
+
+
+def test_bucket_reducer_on_the_real_model_with_edge_importance_masks():
+    ctx = mp.get_context('spawn')
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_model_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    err = q.get(timeout=300)
+    for p in procs:
+        p.join(120)
+        assert p.exitcode == 0
+    assert err < 1e-5
