@@ -85,10 +85,8 @@ def temporal_conv(x, weight, bias, stride_t, pad_t):
     n, c, t, v = x.shape
     gamma = weight.shape[2]
     t_out = (t + 2 * pad_t - gamma) // stride_t + 1
-    xp = torch.zeros(n, c, t + 2 * pad_t, v, dtype=x.dtype)
-    xp = xp + 0  # plain tensor
-    xp = torch.cat([torch.zeros(n, c, pad_t, v, dtype=x.dtype), x,
-                    torch.zeros(n, c, pad_t, v, dtype=x.dtype)], dim=2)
+    zpad = torch.zeros(n, c, pad_t, v, dtype=x.dtype, device=x.device)
+    xp = torch.cat([zpad, x, zpad], dim=2)
     y = None
     for tap in range(gamma):
         # frames  tap + s*j  of the padded input, j = 0..t_out-1

@@ -14,6 +14,10 @@ What makes the step capturable: the library never synchronises or allocates, Bat
 `num_batches_tracked` are advanced by kernels, and the optimizer keeps its step number on the device.  The two warm-up
 steps that precede capture run on the example batch and are UNDONE afterwards (parameters, buffers and optimizer state are
 restored in place), so constructing the object does not train the model.
+
+Drop every autograd graph of earlier EAGER steps on the same parameters before constructing the object (`del loss, logits`):
+while such a graph lives, the parameters' AccumulateGrad nodes stay bound to the stream that step ran on (normally the legacy
+default stream), and capturing backward on the capture stream then fails with cudaErrorStreamCaptureImplicit.
 """
 import torch
 
@@ -42,10 +46,16 @@ class CapturedTrainStep:
         n_warm = max(1, warmup)
         side = torch.cuda.Stream(device=dev)
         side.wait_stream(torch.cuda.current_stream(dev))
-        with torch.cuda.stream(side):
+        import warnings
+        with torch.cuda.stream(side), warnings.catch_warnings(record=True) as caught:
+            warnings.simplefilter('always')
             for _ in range(n_warm):
                 self._eager_step()
         torch.cuda.current_stream(dev).wait_stream(side)
+        stale = any('AccumulateGrad' in str(w.message) and 'stream' in str(w.message) for w in caught)
+        for w in caught:
+            if not ('AccumulateGrad' in str(w.message) and 'stream' in str(w.message)):
+                warnings.warn_explicit(w.message, w.category, w.filename, w.lineno)
         with torch.no_grad():
             for t, s in zip(self._model_tensors(), saved):
                 t.copy_(s)
@@ -59,6 +69,11 @@ class CapturedTrainStep:
                     t.copy_(dev_saved[k])
                 else:
                     t[0] -= n_warm
+        if stale:      # found by the warm-up (it runs on a side stream), BEFORE a capture that would fail and poison the process
+            raise RuntimeError('stgcn_b200.CapturedTrainStep: an autograd graph of an earlier step on these parameters is still '
+                               'alive (e.g. a `loss` or `logits` tensor you kept), which pins their AccumulateGrad nodes to the '
+                               'stream that step ran on; backward cannot be captured on another stream.  Delete those tensors '
+                               '(`del loss, logits`) and construct the object again.')
         # ---- capture ----------------------------------------------------------------------------------------------------------
         optimizer.zero_grad(set_to_none=True)
         self.graph = torch.cuda.CUDAGraph()

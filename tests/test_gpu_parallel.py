@@ -28,12 +28,34 @@ def _hp(edge):
 
 
 def _worker(rank, world, port, edge, out):
+    import threading
+    import traceback
+    # whatever happens below, this process ends: results (or the traceback) go through the queue first, then a watchdog ends
+    # the process if NCCL teardown does not return
+    try:
+        _worker_body(rank, world, port, edge, out)
+    except BaseException:
+        out.put((rank, {'error': traceback.format_exc()[-1500:]}))
+    threading.Timer(20.0, lambda: os._exit(0)).start()
+    try:
+        if dist.is_initialized():
+            dist.destroy_process_group()
+    finally:
+        os._exit(0)
+
+
+def _worker_body(rank, world, port, edge, out):
     import sys
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     for p in (root, os.path.join(root, 'tests')):
         if p not in sys.path:
             sys.path.insert(0, p)
     os.environ.update(MASTER_ADDR='127.0.0.1', MASTER_PORT=str(port))
+    # Two runs of the same bf16 step are compared below.  Consecutive launches normally walk their tiles in alternating
+    # directions (L2 reuse), which changes fp32 reduction order at the 1e-7 level; a 10-block bf16 network amplifies that to
+    # bf16 rounding level (measured, tools/gpu_determinism.py: logits 1.8e-3, gradients 0.18 in L2 between directions, against
+    # identical logits and 5e-3 with the direction fixed).  Fix the direction so the comparison isolates the reducer.
+    os.environ['STGCN_NO_PINGPONG'] = '1'
     torch.cuda.set_device(rank)
     dev = torch.device('cuda', rank)
     dist.init_process_group('nccl', rank=rank, world_size=world, device_id=dev)
@@ -51,17 +73,27 @@ def _worker(rank, world, port, edge, out):
     x = torch.randn(16, 60, 25, 3, generator=g); y = torch.randint(0, 60, (16,), generator=g)
     xs, ys = shard_batch(x, y, rank, world)
     xs, ys = xs.to(dev), ys.to(dev)
-    reducer = GradBucketReducer(model.parameters(), 3)
     cfgs = O.stack_cfgs(3, 9, 0.0, False)
+    # local gradients of this rank's shard by the product alone (no reducer yet), gathered: their mean is what the reducer
+    # must deliver, to fp32 round-off
+    model.zero_grad(set_to_none=True)
+    lg = model(xs); cross_entropy(lg, ys).backward(); del lg
+    names = [k for k, p in model.named_parameters() if p.grad is not None]
+    local = torch.cat([p.grad.flatten() for k, p in model.named_parameters() if p.grad is not None])
+    gathered = [torch.empty_like(local) for _ in range(world)]
+    dist.all_gather(gathered, local)
+    local_mean = sum(gathered) / world
+    model.load_state_dict(state)             # undo the running-statistics update
+    reducer = GradBucketReducer(model.parameters(), 3)
 
-    def oracle_shard(r):
+    def oracle_shard(r, bf16=True):
         st = {k: v.detach().clone() for k, v in state.items()}
         leaves = {}
         for k, v in st.items():
             if v.dtype.is_floating_point and 'running' not in k and not k.startswith('Masks'):
                 v.requires_grad_(True); leaves[k] = v
         xr, yr = shard_batch(x, y, r, world)
-        logits = O.model_forward_bf16(xr.to(dev), st, cfgs, True)
+        logits = (O.model_forward_bf16 if bf16 else O.model_forward)(xr.to(dev), st, cfgs, True)
         O.cross_entropy(logits, yr.to(dev)).backward()
         return logits.detach(), {k: v.grad for k, v in leaves.items()}
 
@@ -73,20 +105,27 @@ def _worker(rank, world, port, edge, out):
     res = {}
     ref_logits, _ = oracle_shard(rank)
     res['logits'] = rel_err(logits.float(), ref_logits)
+    del logits            # the eager step's autograd graph must be gone before a captured step is built (CapturedTrainStep)
     aliased = sum(int(p.grad.data_ptr() == p._stgcn_grad_buf.data_ptr()) for p in model.parameters() if p.grad is not None)
     res['aliased'] = aliased / max(1, sum(1 for p in model.parameters() if p.grad is not None))
+    reduced = torch.cat([p.grad.flatten() for k, p in model.named_parameters() if k in names])
+    res['reduced_vs_mean_of_local'] = float((reduced - local_mean).abs().max() / local_mean.abs().max())
     if rank == 0:
-        per = [oracle_shard(r)[1] for r in range(world)]
-        worst = 0.0
+        # against the checker: mean over shards of the per-shard oracle gradients.  Model-level bf16 gradients
+        # carry the ReLU-flip noise floor (tests/test_gpu_cfg4_parity.py), so the bound is relative to the distance of the
+        # oracle's own bf16 emulation from its fp32 self, in the L2 norm over all gradient elements
+        per16 = [oracle_shard(r, True)[1] for r in range(world)]
+        per32 = [oracle_shard(r, False)[1] for r in range(world)]
+        keys = [k for k in names if not k.endswith('temporalConv.bias')]
         for k, p in model.named_parameters():
             if k.startswith('Masks'):
                 assert p.grad is None
-                continue
-            if k.endswith('temporalConv.bias'):
-                continue
-            ref = sum(q[k] for q in per) / world
-            worst = max(worst, rel_err(p.grad.float(), ref))
-        res['grads_vs_mean_of_shard_oracles'] = worst
+        cat = lambda per: torch.cat([(sum(q[k] for q in per) / world).flatten().double() for k in keys])
+        g16, g32 = cat(per16), cat(per32)
+        mine = torch.cat([p.grad.flatten().double() for k, p in model.named_parameters() if k in keys])
+        l2 = lambda a, b: float((a - b).norm() / b.norm())
+        res['l2_vs_fp32_oracle_mean'] = l2(mine, g32)
+        res['l2_emulation_vs_fp32_oracle_mean'] = l2(g16, g32)
     # replicas must hold identical averaged gradients
     flat = torch.cat([p.grad.flatten() for p in model.parameters() if p.grad is not None])
     other = flat.clone()
@@ -104,14 +143,15 @@ def _worker(rank, world, port, edge, out):
     opt2.zero_grad(set_to_none=True)
     l_e = cross_entropy(model(xs), ys); l_e.backward(); reducer.finish(); opt2.step()
     res['captured_loss_diff'] = abs(l_cap - float(l_e))
-    res['captured_state_diff'] = max(rel_err(cap_state[k], v) for k, v in model.state_dict().items() if v.dtype.is_floating_point)
+    # Adam's first step is lr * sign(g): two correct runs differ by at most 2 lr per weight
+    res['captured_param_absdiff'] = max(float((cap_state[k] - v).abs().max()) for k, v in model.state_dict().items()
+                                        if v.dtype.is_floating_point and 'running' not in k)
     # replicas stay in sync after the step
     w = torch.cat([p.detach().flatten() for p in model.parameters()])
     w0 = w.clone(); dist.broadcast(w0, src=0)
     res['replica_weight_diff'] = float((w - w0).abs().max())
+    torch.cuda.synchronize()
     out.put((rank, res))
-    dist.barrier()
-    dist.destroy_process_group()
 
 
 @pytest.mark.parametrize('edge', [False, True], ids=['plain', 'edge_importance'])
@@ -124,17 +164,22 @@ def test_two_rank_nccl_gradients_match_mean_of_shard_oracles(edge):
     procs = [ctx.Process(target=_worker, args=(r, 2, port, edge, q)) for r in range(2)]
     for p in procs:
         p.start()
-    results = dict(q.get(timeout=600) for _ in range(2))
-    for p in procs:
-        p.join(120)
-        assert p.exitcode == 0
+    try:
+        results = dict(q.get(timeout=240) for _ in range(2))
+    finally:
+        for p in procs:
+            p.join(40)
+            if p.is_alive():
+                p.kill()
     print(results)
     for r in range(2):
         res = results[r]
+        assert 'error' not in res, res['error']
         assert res['logits'] < TOL, res
         assert res['replica_grad_diff'] == 0.0, res
         assert res['replica_weight_diff'] == 0.0, res
         assert res['captured_loss_diff'] < 1e-2, res
-        assert res['captured_state_diff'] < 2e-2, res
+        assert res['captured_param_absdiff'] <= 2.5e-4, res
+        assert res['reduced_vs_mean_of_local'] < 2e-2, res      # measured 5e-3 run to run on one GPU; a lost bucket or a wrong scale is O(1)
         assert res['aliased'] > 0.9, res                      # gradients were written straight into the bucket slices
-    assert results[0]['grads_vs_mean_of_shard_oracles'] < TOL * 2, results[0]
+    assert results[0]['l2_vs_fp32_oracle_mean'] < 1.5 * results[0]['l2_emulation_vs_fp32_oracle_mean'] + TOL, results[0]

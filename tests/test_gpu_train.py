@@ -142,17 +142,6 @@ def test_captured_train_step_matches_eager_steps(dtype):
         assert d < 50 * tol, (k, d)
 
 
-def test_captured_train_step_refuses_dropout():
-    import argparse
-    import stgcn_b200
-    from stgcn_b200.optim import Adam
-    hp = argparse.Namespace(C_in=3, nr_classes=60, gamma=9, dropout_rate=0.5, residual=False, use_edge_importance=False,
-                            max_mask_jitter=0.001, partitioning=2, d=1, distance_file=None, distances=None)
-    m = stgcn_b200.L_STGCN(hp, A=torch.randn(3, 25, 25) * 0.1).cuda().train()
-    with pytest.raises(RuntimeError):
-        stgcn_b200.CapturedTrainStep(m, Adam(m.parameters()), torch.randn(2, 40, 25, 3).cuda(), torch.zeros(2, dtype=torch.int64).cuda())
-
-
 def test_captured_forward_equals_eager_eval_forward():
     import stgcn_b200
     model = _small_model(torch.bfloat16)
