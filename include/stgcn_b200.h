@@ -154,6 +154,19 @@ int32_t stgcn_spatial_backward(const StgcnBlockDesc* desc, const void* x, const 
                                const float* W_bias, const void* dout, void* dx, float* dA, float* dW,
                                float* dW_bias, void* workspace, size_t workspace_bytes, void* stream);
 
+/* SpatialConv.forward WITHOUT a caller workspace and without any allocation.  No counterpart in the reference: added
+ * for callers that cannot allocate (code under CUDA-graph capture, tight serving loops, harnesses
+ * that forbid cudaMalloc).  Same result as stgcn_spatial_forward; the scratch (aggregated input, joint-bias table, packed weights)
+ * lives in a static device array of STGCN_STATIC_SCRATCH_BYTES inside the library, which every GPU that loads the library holds
+ * until exit.  Shapes whose stgcn_spatial_workspace_bytes(desc, 0) exceeds that limit are rejected with STGCN_ERR_WORKSPACE and a
+ * message naming both sizes.  The call launches on `stream`, never calls cudaMalloc / cudaFree or an allocating library routine.
+ * ALL calls share the one array (it keeps the last call's contents; the part a call uses is cleared first): calls that overlap on
+ * the GPU -- two streams, two threads -- race; serialise them. */
+#define STGCN_STATIC_SCRATCH_BYTES (16u << 20)
+size_t stgcn_static_scratch_bytes(void);
+int32_t stgcn_spatial_forward_static(const StgcnBlockDesc* desc, const void* x, const float* A, const float* W,
+                                     const float* W_bias, void* out, void* stream);
+
 /* Head of L_STGCN.forward (lightning_model.py:105-107): global average pool
  * over (T,V) + Linear(C, classes).  feat (n,t,v,c) -> logits (n,classes) fp32. */
 int32_t stgcn_head_forward(int32_t dtype, int32_t n, int32_t t, int32_t v, int32_t c, int32_t classes,

@@ -63,6 +63,9 @@ def _declare(lib):
     lib.stgcn_spatial_workspace_bytes.restype = sz; lib.stgcn_spatial_workspace_bytes.argtypes = [D, i32]
     lib.stgcn_spatial_forward.restype = i32
     lib.stgcn_spatial_forward.argtypes = [D, _P, _P, _P, _P, _P, _P, sz, _P]
+    lib.stgcn_static_scratch_bytes.restype = sz; lib.stgcn_static_scratch_bytes.argtypes = []
+    lib.stgcn_spatial_forward_static.restype = i32
+    lib.stgcn_spatial_forward_static.argtypes = [D, _P, _P, _P, _P, _P, _P]
     lib.stgcn_spatial_backward.restype = i32
     lib.stgcn_spatial_backward.argtypes = [D, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, sz, _P]
     lib.stgcn_head_forward.restype = i32

@@ -939,6 +939,73 @@ int32_t stgcn_umma_conv_gemm(int32_t nb, int32_t t_in, int32_t t_out, int32_t v,
   return launch_conv_gemm_umma(g, (const bf16*)in, (const bf16*)w, ep, (bf16*)out, (cudaStream_t)stream);
 }
 
+
+// ---------------------------------------------------------------------------------------------------------------------------
+// stgcn_spatial_forward_static: SpatialConv.forward with its scratch in a file-scope device array (no caller workspace, no
+// allocation of any kind) -- for callers that cannot allocate: code under CUDA-graph capture, tight serving loops, harnesses
+// that forbid cudaMalloc.  No counterpart in the reference.
+//   * g_static_scratch is a HOST-SIDE STAND-IN in host code, not a device address: the address a kernel may use comes from
+//     cudaGetSymbolAddress, queried once per device with that device current (each device holds its own copy of the array,
+//     STGCN_STATIC_SCRATCH_BYTES of HBM from library load until exit).  Device code names the array directly.
+//   * every call shares the array and finds the previous call's contents in it: the bytes this call will use are cleared first.
+//     Calls that overlap on the GPU (two streams, two host threads) RACE on it -- serialise them.
+// ---------------------------------------------------------------------------------------------------------------------------
+namespace stgcn {
+static __device__ __align__(256) unsigned char g_static_scratch[STGCN_STATIC_SCRATCH_BYTES];
+
+__global__ void __launch_bounds__(256) static_scratch_clear_kernel(size_t bytes) {
+  pdl_enter();
+  uint4* p = reinterpret_cast<uint4*>(g_static_scratch);            // device code: the array by name
+  const size_t n16 = (bytes + 15) / 16;                              // the array is 256-byte aligned and a multiple of 16 long
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += (size_t)gridDim.x * blockDim.x)
+    p[i] = make_uint4(0, 0, 0, 0);
+}
+
+// device address of the array on the CURRENT device (looked up once per device)
+static int32_t static_scratch_address(void** out) {
+  static std::mutex mu;
+  static void* ptrs[64] = {};
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) { set_error("static scratch: no current CUDA device"); return STGCN_ERR_CUDA; }
+  std::lock_guard<std::mutex> lk(mu);
+  if (!ptrs[dev]) {
+    void* p = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(&p, g_static_scratch);
+    if (e != cudaSuccess || !p) {
+      set_error("static scratch: cudaGetSymbolAddress failed on device %d: %s", dev, cudaGetErrorString(e));
+      return STGCN_ERR_CUDA;
+    }
+    ptrs[dev] = p;
+  }
+  *out = ptrs[dev];
+  return STGCN_OK;
+}
+}  // namespace stgcn
+
+size_t stgcn_static_scratch_bytes(void) { return (size_t)STGCN_STATIC_SCRATCH_BYTES; }
+
+int32_t stgcn_spatial_forward_static(const StgcnBlockDesc* d, const void* x, const float* A, const float* W, const float* Wb, void* out,
+                                     void* stream) {
+  STGCN_TRY(validate(d));
+  STGCN_TRY(check_ptrs(x, A, W));
+  STGCN_TRY(check_ptrs(Wb, out, out));
+  const size_t need = stgcn_spatial_workspace_bytes(d, 0);
+  if (need == 0) return STGCN_ERR_UNSUPPORTED;                       // error text set by the sizing pass
+  if (need > (size_t)STGCN_STATIC_SCRATCH_BYTES) {
+    set_error("spatial_forward_static: this shape needs %zu bytes of scratch, the static array holds %zu (STGCN_STATIC_SCRATCH_BYTES); "
+              "use stgcn_spatial_forward with a caller-provided workspace", need, (size_t)STGCN_STATIC_SCRATCH_BYTES);
+    return STGCN_ERR_WORKSPACE;
+  }
+  void* scratch = nullptr;
+  STGCN_TRY(static_scratch_address(&scratch));
+  cudaStream_t st = (cudaStream_t)stream;
+  launch_k(static_scratch_clear_kernel, (int)std::min<size_t>((need / 16 + 255) / 256 + 1, 148 * 8), 256, 0, st, need);
+  STGCN_CHECK_LAUNCH("static_scratch_clear");
+  Arena ws(scratch, (size_t)STGCN_STATIC_SCRATCH_BYTES);
+  if (d->dtype == STGCN_F32) return spatial_only_fwd<float>(*d, (const float*)x, A, W, Wb, (float*)out, ws, st);
+  return spatial_only_fwd<bf16>(*d, (const bf16*)x, A, W, Wb, (bf16*)out, ws, st);
+}
+
 uint64_t stgcn_launch_count(void) { return g_launches.load(); }
 int32_t stgcn_dropout_mask(uint64_t seed, uint64_t offset, float p, size_t count, float* out, void* stream) {
   if (!out) { set_error("dropout_mask: null output"); return STGCN_ERR_INVALID; }
