@@ -402,8 +402,8 @@ def main():
                     'mode': 'eager launches' if args.eager else 'one CUDA graph per forward (CapturedForward)',
                     'l2': 'flushed (160 MB write) between timed steps, flush time subtracted',
                     'model_tflops': tf,
-                    'roofline_step': {'bound': 'tensor', 'achieved': tf, 'peak': peak_tf, 'unit': 'TFLOP/s', 'frac': tf / peak_tf,
-                                      'peak_source': peak_src},
+                    'roofline_step': {'bound': 'tensor', 'achieved': tf / world, 'peak': peak_tf, 'unit': 'TFLOP/s per GPU',
+                                      'frac': tf / world / peak_tf, 'peak_source': peak_src},
                     'roofline': roofline_of(prof, 'umma_conv_gemm', 'conv_gemm_umma_kernel') or roofline_of(prof, 'simt_conv_gemm', 'conv_gemm_simt_kernel'),
                     'e2e': {'value': S * world / (ms_e * 1e-3), 'unit': 'seq/s', 'ms_per_step': ms_e,
                             'h2d_bytes_per_step': hx[0].numel() * hx[0].element_size(), 'd2h_bytes_per_step': out_host.numel() * 4},

@@ -138,7 +138,28 @@ static SideLane* side_lane() {
 template <class T> struct Engine {
   const StgcnBlockDesc& d; Arena& ws; cudaStream_t st;
   bool want_umma() const { return std::is_same<T, bf16>::value && !(d.flags & STGCN_FLAG_FORCE_SIMT); }
+  // fp32 path on the tensor cores: both GEMM operands are split into (hi | mid | lo) bf16 triples by an element-wise pre-pass and
+  // the tcgen05 engines run six products per reduction step with fp32 accumulation in TMEM (error ~1e-6 of the operand scale, an
+  // order inside the fp32 path's 1e-4).  STGCN_FLAG_FORCE_SIMT or STGCN_FP32_SIMT=1 keep the CUDA-core GEMMs (A/B, debugging).
+  bool want_tc32() const {
+    static const bool off = getenv("STGCN_FP32_SIMT") != nullptr;
+    return std::is_same<T, float>::value && !off && !(d.flags & STGCN_FLAG_FORCE_SIMT);
+  }
   int32_t gemm(const ConvGeom& g, const T* in, const float* wsrc, const WIndex& wi, const GemmEpilogue& ep, T* out) {
+    if constexpr (std::is_same<T, float>::value) {
+      if (want_tc32() && umma_conv_gemm_supported(g) && !ep.stat_partials && !ep.vsum) {
+        const long long rows_in = (long long)g.nb * g.t_in * g.v;
+        bf16* in3 = ws.template get<bf16>((size_t)rows_in * 3 * g.c);
+        float* wpf = ws.template get<float>((size_t)g.taps * g.n_out * g.c);
+        bf16* wp3 = ws.template get<bf16>((size_t)g.taps * g.n_out * 3 * g.c);
+        if (ws.dry) return STGCN_OK;
+        if (!ws.ok()) { set_error("workspace too small"); return STGCN_ERR_WORKSPACE; }
+        STGCN_TRY(launch_split_bf16(in, rows_in, g.c, in3, st));
+        STGCN_TRY(launch_pack_weights<float>(wsrc, wi, g.taps, g.n_out, g.c, wpf, st, 0));
+        STGCN_TRY(launch_split_bf16(wpf, (long long)g.taps * g.n_out, g.c, wp3, st));
+        return launch_conv_gemm_umma_split(g, in3, wp3, ep, out, st);
+      }
+    }
     if (want_umma() && umma_conv_gemm_supported(g)) {
       bf16* wp = ws.template get<bf16>((size_t)g.taps * g.n_out * g.c);
       if (ws.dry) return STGCN_OK;
@@ -183,6 +204,19 @@ template <class T> struct Engine {
   // packed_pre: split-K accumulator carved by the caller (packed_zero: and already cleared by an earlier kernel of the chain)
   int32_t wgrad(const ConvGeom& g, const T* dout, const T* in, const WIndex& wi, float* dw, size_t dw_floats, int c_valid = -1,
                 float* packed_pre = nullptr, bool packed_zero = false, cudaStream_t unpack_st = nullptr, cudaEvent_t unpack_ev = nullptr) {
+    if constexpr (std::is_same<T, float>::value) {
+      if (want_tc32() && umma_wgrad_supported(g) && (g.n_out == 64 || g.n_out % 128 == 0) && c_valid < 0) {
+        const long long rows_out = (long long)g.nb * g.t_out * g.v, rows_in = (long long)g.nb * g.t_in * g.v;
+        bf16* d3 = ws.template get<bf16>((size_t)rows_out * 3 * g.n_out);
+        bf16* i3 = ws.template get<bf16>((size_t)rows_in * 3 * g.c);
+        float* packed = ws.template get<float>(umma_wgrad_workspace_floats(g));
+        if (ws.dry) return STGCN_OK;
+        if (!ws.ok()) { set_error("workspace too small"); return STGCN_ERR_WORKSPACE; }
+        STGCN_TRY(launch_split_bf16(dout, rows_out, g.n_out, d3, st));
+        STGCN_TRY(launch_split_bf16(in, rows_in, g.c, i3, st));
+        return launch_wgrad_umma(g, d3, i3, wi, packed, dw, st, -1, false, nullptr, nullptr, 1);
+      }
+    }
     if (wgrad_on_umma(g)) {
       float* packed = packed_pre ? packed_pre : ws.template get<float>(umma_wgrad_workspace_floats(g));
       if (ws.dry) return STGCN_OK;

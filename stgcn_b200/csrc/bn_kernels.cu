@@ -645,6 +645,38 @@ template int32_t launch_add_inplace<float>(float*, const float*, size_t, cudaStr
 template int32_t launch_add_inplace<bf16>(bf16*, const bf16*, size_t, cudaStream_t);
 
 // ---------------------------------------------------------------------------
+// fp32 -> split bf16: x = hi + mid + lo with hi = bf16(x), mid = bf16(x - hi), lo = bf16(x - hi - mid) (24 significand bits
+// together; the subtractions are exact in fp32); rows of [hi | mid | lo]
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) split_bf16_kernel(const float* __restrict__ src, long long rows, int C, bf16* __restrict__ dst) {
+  pdl_enter();
+  const int c4 = C / 4;
+  const long long total = rows * c4;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const long long r = i / c4; const int c = (int)(i - r * c4) * 4;
+    float v[4], hi[4], mid[4], lo[4];
+    ld4(src + r * C + c, v);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      hi[j] = __bfloat162float(__float2bfloat16_rn(v[j]));
+      const float r1 = v[j] - hi[j];
+      mid[j] = __bfloat162float(__float2bfloat16_rn(r1));
+      lo[j] = r1 - mid[j];                 // rounded to bf16 by the store
+    }
+    bf16* d = dst + r * 3 * C + c;
+    st4(d, hi); st4(d + C, mid); st4(d + 2 * C, lo);
+  }
+}
+int32_t launch_split_bf16(const float* src, long long rows, int C, bf16* dst, cudaStream_t st) {
+  KernelTimer kt_(KC_ELEMWISE, (double)rows * C, st);
+  if (C % 4 != 0) { set_error("split_bf16: C %% 4 != 0"); return STGCN_ERR_UNSUPPORTED; }
+  int blocks = (int)std::max<long long>(1, std::min<long long>((rows * (C / 4) + 255) / 256, 148 * 16));
+  launch_k(split_bf16_kernel, blocks, 256, 0, st, src, rows, C, dst);
+  STGCN_CHECK_LAUNCH("split_bf16");
+  return STGCN_OK;
+}
+
+// ---------------------------------------------------------------------------
 // dropout random state on the device: {seed, offset}.  Forward copies the state it will use next to `slot` (kept with the
 // tensors saved for backward, so backward replays the same mask) and advances the caller's state by the number of Philox
 // calls the block consumes; a CUDA graph of the step therefore draws a fresh mask at every replay.

@@ -109,13 +109,17 @@ template <class T> int32_t launch_colsum(const T* x, long long rows, int C, floa
 bool umma_conv_gemm_supported(const ConvGeom& g);
 int umma_conv_gemm_grid(const ConvGeom& g);
 int32_t launch_conv_gemm_umma(const ConvGeom& g, const bf16* in, const bf16* w, const GemmEpilogue& ep, bf16* out, cudaStream_t st);
+// fp32 operands carried as (hi | mid | lo) bf16 triples: in3 [rows][3c], w3 [taps][n_out][3c]; fp32 output (UmmaParams::nterms)
+int32_t launch_conv_gemm_umma_split(const ConvGeom& g, const bf16* in3, const bf16* w3, const GemmEpilogue& ep, float* out, cudaStream_t st);
+// dst[r] = [bf16(x) | bf16(x - hi) | bf16(x - hi - mid)] over the C channels of src[r]   (3C bf16 per row)
+int32_t launch_split_bf16(const float* src, long long rows, int C, bf16* dst, cudaStream_t st);
 
 // umma_wgrad.cu  (tcgen05 weight gradient, bf16, MN-major operands)
 bool umma_wgrad_supported(const ConvGeom& g);
 size_t umma_wgrad_workspace_floats(const ConvGeom& g);
 int32_t launch_wgrad_umma(const ConvGeom& g, const bf16* dout, const bf16* in, const WIndex& wi, float* packed_ws, float* dw,
                           cudaStream_t st, int c_valid = -1, bool packed_is_zero = false, cudaStream_t unpack_st = nullptr,
-                          cudaEvent_t unpack_ev = nullptr);
+                          cudaEvent_t unpack_ev = nullptr, int split = 0);
 
 // umma_agg.cu  (tensor-core adjacency aggregation, bf16)
 bool umma_agg_supported(int V, int C, int K);

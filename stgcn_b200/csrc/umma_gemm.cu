@@ -58,7 +58,29 @@ struct UmmaParams {
   float dropout_p, inv_keep;
   uint64_t seed, offset;
   const uint64_t* rng;   // device {seed, offset} (overrides the values above)
+  // fp32 path on the tensor cores ("split bf16"): every fp32 operand value is carried as hi + mid + lo (three bf16, 24 significand
+  // bits); the input tensor is [rows][3C] = [hi | mid | lo], the weights [tap][n][3C].  The reduction runs over SIX products per
+  // logical 64-channel block -- (part of the activation, part of the weight) = mid.mid, hi.lo, lo.hi, hi.mid, mid.hi, hi.hi,
+  // smallest first; the dropped ones are below 2^-24 relative -- all into the same fp32 accumulator in TMEM.
+  int nterms, c_log;     // nterms: 0 (plain bf16) | 6; c_log = logical 64-channel blocks (kblocks_c = max(nterms,1) * c_log)
+  float* out_f32;        // fp32 output [rows][n_out] written straight from the epilogue (no bf16 staging / TMA store)
+  const float* residual_f32;
+  int accumulate;        // out_f32 += (fp32 output only)
 };
+constexpr int kSplitParts = 3, kSplitTerms = 6;
+__device__ __constant__ int c_term_a[kSplitTerms] = {1, 0, 2, 0, 1, 0};      // activation part of term i
+__device__ __constant__ int c_term_w[kSplitTerms] = {1, 2, 0, 1, 0, 0};      // weight part of term i
+// channel coordinate (elements) of reduction step kb in the activation / weight tensor
+__device__ __forceinline__ int a_col_of(const UmmaParams& p, int kb) {
+  if (!p.nterms) return kb * 64;
+  const int term = kb / p.c_log, cb = kb - term * p.c_log;
+  return (c_term_a[term] * p.c_log + cb) * 64;
+}
+__device__ __forceinline__ int w_col_of(const UmmaParams& p, int kb) {
+  if (!p.nterms) return kb * 64;
+  const int term = kb / p.c_log, cb = kb - term * p.c_log;
+  return (c_term_w[term] * p.c_log + cb) * 64;
+}
 
 struct TileCoord { int n_t, ph, j0, b; };
 __device__ __forceinline__ TileCoord decode_tile(const UmmaParams& p, int tile) {
@@ -75,6 +97,7 @@ __device__ __forceinline__ TileCoord decode_tile(const UmmaParams& p, int tile) 
 // epilogue warps are bound by dependent-issue latency (about 10 cycles per instruction with two warps per scheduler): the
 // option-free instance used by every data-gradient GEMM needs 84 registers and a third of the instructions per chunk.
 constexpr int EP_BIAS = 1, EP_BIAS2D = 2, EP_SCALE = 4, EP_RESID = 8, EP_RELU = 16, EP_DROPOUT = 32, EP_STATS = 64, EP_VSUM = 128, EP_ALL = 255;
+constexpr int EP_F32OUT = 256;      // fp32 output straight from the epilogue (split-bf16 fp32 path); excludes the statistics options
 template <int EPM>
 __global__ void __launch_bounds__(kUmmaThreads, 1)
 conv_gemm_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_constant__ CUtensorMap map_w,
@@ -129,7 +152,7 @@ conv_gemm_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_c
         __syncwarp();
         for (int kb = 0; kb < p.kblocks_c; ++kb)
           for (int ti = 0; ti < nt; ++ti)
-            if (elect_one()) tma_load_3d(&map_w, smem_b + (size_t)(kb * nt + ti) * p.b_bytes, wfull_bar, kb * 64, 0, p.taps[0][ti].w_tap);
+            if (elect_one()) tma_load_3d(&map_w, smem_b + (size_t)(kb * nt + ti) * p.b_bytes, wfull_bar, w_col_of(p, kb), 0, p.taps[0][ti].w_tap);
       }
       // two cursors over the (tile, channel block) units: activation tiles run `lead` units ahead of the weight tiles
       int a_tile = blockIdx.x, a_kb = 0, w_tile = blockIdx.x, w_kb = 0;
@@ -140,7 +163,7 @@ conv_gemm_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_c
         mbar_wait(empty_bar + stage, phase ^ 1);
         if (elect_one()) {
           mbar_expect_tx(full_bar + stage, p.a_halo_bytes);
-          tma_load_5d(&map_in, smem_a + (size_t)stage * p.a_stage_bytes, full_bar + stage, a_kb * 64, 0, 0, tc.j0 + p.h_min, tc.b);
+          tma_load_5d(&map_in, smem_a + (size_t)stage * p.a_stage_bytes, full_bar + stage, a_col_of(p, a_kb), 0, 0, tc.j0 + p.h_min, tc.b);
         }
         if (++stage == p.stages) { stage = 0; phase ^= 1; }
         if (++a_kb == p.kblocks_c) { a_kb = 0; a_tile += gridDim.x; }
@@ -154,7 +177,7 @@ conv_gemm_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_c
             mbar_wait(wempty_bar + ws, wph ^ 1);
             if (elect_one()) {
               mbar_expect_tx(wfull_bar + ws, p.b_bytes);
-              tma_load_3d(&map_w, smem_b + (size_t)ws * p.b_bytes, wfull_bar + ws, w_kb * 64, tc.n_t * p.bn, p.taps[0][ti].w_tap);
+              tma_load_3d(&map_w, smem_b + (size_t)ws * p.b_bytes, wfull_bar + ws, w_col_of(p, w_kb), tc.n_t * p.bn, p.taps[0][ti].w_tap);
             }
             if (++ws == p.w_stages) { ws = 0; wph ^= 1; }
           }
@@ -173,8 +196,8 @@ conv_gemm_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_c
             mbar_wait(empty_bar + stage, phase ^ 1);
             if (elect_one()) {
               mbar_expect_tx(full_bar + stage, p.a_bytes + p.b_bytes);
-              tma_load_5d(&map_in, smem_a + (size_t)stage * p.a_stage_bytes, full_bar + stage, kb * 64, 0, te.parity, tc.j0 + te.h_off, tc.b);
-              tma_load_3d(&map_w, smem_b + (size_t)stage * p.b_bytes, full_bar + stage, kb * 64, tc.n_t * p.bn, te.w_tap);
+              tma_load_5d(&map_in, smem_a + (size_t)stage * p.a_stage_bytes, full_bar + stage, a_col_of(p, kb), 0, te.parity, tc.j0 + te.h_off, tc.b);
+              tma_load_3d(&map_w, smem_b + (size_t)stage * p.b_bytes, full_bar + stage, w_col_of(p, kb), tc.n_t * p.bn, te.w_tap);
             }
             if (++stage == p.stages) { stage = 0; phase ^= 1; }
           }
@@ -277,7 +300,7 @@ conv_gemm_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_c
       for (int ch = 0; ch < p.bn / 64; ++ch) {
         if (((gchunk++) & 1) != grp) continue;
         uint8_t* stg = my_staging + (size_t)(chunk_ctr & (p.nstaging - 1)) * kStagingBytes;   // nstaging (per group) is 1 or 2
-        if (chunk_ctr >= p.nstaging) {
+        if (!(EPM & EP_F32OUT) && chunk_ctr >= p.nstaging) {
           if (et == 0) { if (p.nstaging == 2) tma_store_wait_read<1>(); else tma_store_wait_read<0>(); }   // the store that last read this buffer has drained
           asm volatile("bar.sync %0, 128;" ::"r"(bar_a) : "memory");
         }
@@ -323,7 +346,15 @@ conv_gemm_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_c
               f[g * 4 + 2] = fmaf(a4.z, f[g * 4 + 2], b4.z); f[g * 4 + 3] = fmaf(a4.w, f[g * 4 + 3], b4.w);
             }
           }
-          if (o_residual && row_valid) {
+          if ((EPM & EP_F32OUT) && p.residual_f32 && row_valid) {
+            const float4* rp = reinterpret_cast<const float4*>(p.residual_f32 + (size_t)grow * p.n_out + n0);
+#pragma unroll
+            for (int g = 0; g < 8; ++g) {
+              const float4 t = __ldg(rp + g);
+              f[g * 4 + 0] += t.x; f[g * 4 + 1] += t.y; f[g * 4 + 2] += t.z; f[g * 4 + 3] += t.w;
+            }
+          }
+          if (!(EPM & EP_F32OUT) && o_residual && row_valid) {
             const uint4* rp = reinterpret_cast<const uint4*>(o_residual + (size_t)grow * p.n_out + n0);
 #pragma unroll
             for (int g = 0; g < 4; ++g) {
@@ -343,6 +374,18 @@ conv_gemm_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_c
 #pragma unroll
             for (int i = 0; i < 32; ++i) f[i] *= dropout_scale(d_seed, d_off, o + i, o_dropout_p, p.inv_keep);
           }
+          if (EPM & EP_F32OUT) {       // fp32 rows straight to global memory: 128 contiguous bytes per thread and half-chunk
+            if (row_valid) {
+              float4* op = reinterpret_cast<float4*>(p.out_f32 + (size_t)grow * p.n_out + n0);
+#pragma unroll
+              for (int g = 0; g < 8; ++g) {
+                float4 t = make_float4(f[g * 4 + 0], f[g * 4 + 1], f[g * 4 + 2], f[g * 4 + 3]);
+                if (p.accumulate) { const float4 o4 = op[g]; t.x += o4.x; t.y += o4.y; t.z += o4.z; t.w += o4.w; }
+                op[g] = t;
+              }
+            }
+            continue;
+          }
           // bf16 pack and 128B-swizzled store: 16-byte chunk j of row lands at chunk (j ^ (row & 7))
 #pragma unroll
           for (int g = 0; g < 4; ++g) {
@@ -357,6 +400,7 @@ conv_gemm_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_c
             *reinterpret_cast<uint4*>(stg + row * 128 + ((j ^ (row & 7)) << 4)) = u;
           }
         }
+        if (EPM & EP_F32OUT) continue;            // rows already stored; no staging tile, no statistics on this path
         fence_proxy_async_smem();                  // generic-proxy smem writes -> visible to the TMA engine
         asm volatile("bar.sync %0, 128;" ::"r"(bar_b) : "memory");
         if (et == 0) {
@@ -409,6 +453,8 @@ conv_gemm_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_c
   __syncthreads();
   if (warp == 1) { tc_fence_after(); tmem_dealloc(tmem_base, p.tmem_cols); }
 }
+
+constexpr int kEpSplit = EP_F32OUT | EP_BIAS | EP_BIAS2D | EP_SCALE | EP_RESID | EP_RELU | EP_DROPOUT;
 
 // ---------------------------------------------------------------------------
 // host side
@@ -474,10 +520,14 @@ bool umma_conv_gemm_supported(const ConvGeom& g) {
   return true;
 }
 
-int32_t launch_conv_gemm_umma(const ConvGeom& g, const bf16* in, const bf16* w, const GemmEpilogue& ep, bf16* out, cudaStream_t st) {
+static int32_t launch_conv_gemm_impl(const ConvGeom& g, const bf16* in, const bf16* w, const GemmEpilogue& ep, bf16* out, float* out_f32,
+                                     cudaStream_t st) {
   KernelTimer kt_(KC_UMMA_GEMM, conv_algorithmic_flops(g), st);
+  const int nterms = out_f32 ? kSplitTerms : 0;     // fp32 path: operands are [hi | mid | lo] bf16 triples, six products per channel block
+  const int parts = out_f32 ? kSplitParts : 1;
   if (!umma_conv_gemm_supported(g)) { set_error("umma conv-gemm: unsupported geometry"); return STGCN_ERR_UNSUPPORTED; }
-  if (ep.accumulate) { set_error("umma conv-gemm: accumulate epilogue unsupported"); return STGCN_ERR_UNSUPPORTED; }
+  if (ep.accumulate && !out_f32) { set_error("umma conv-gemm: accumulate epilogue unsupported"); return STGCN_ERR_UNSUPPORTED; }
+  if (out_f32 && (ep.stat_partials || ep.vsum)) { set_error("umma conv-gemm: statistics epilogues need the bf16 output"); return STGCN_ERR_UNSUPPORTED; }
   if (((uintptr_t)ep.bias | (uintptr_t)ep.scale | (uintptr_t)ep.shift) & 15) {
     set_error("umma conv-gemm: bias / scale / shift must be 16-byte aligned"); return STGCN_ERR_INVALID;
   }
@@ -485,7 +535,8 @@ int32_t launch_conv_gemm_umma(const ConvGeom& g, const bf16* in, const bf16* w, 
   p.rev = next_direction();
   const int s = g.stride;
   p.nb = g.nb; p.v = g.v; p.ft = 128 / g.v; p.t_out = g.t_out; p.n_out = g.n_out;
-  p.bn = pick_bn(g.n_out); p.n_tiles = g.n_out / p.bn; p.kblocks_c = g.c / 64;
+  p.bn = pick_bn(g.n_out); p.n_tiles = g.n_out / p.bn; p.c_log = g.c / 64; p.nterms = nterms; p.kblocks_c = p.c_log * (nterms ? nterms : 1);
+  p.out_f32 = out_f32; p.accumulate = ep.accumulate; p.residual_f32 = out_f32 ? reinterpret_cast<const float*>(ep.residual) : nullptr;
   p.phases = g.dgrad ? s : 1;
   p.t_out_ph = g.t_out / p.phases;
   p.m_tiles_per_b = cdiv(p.t_out_ph, p.ft);
@@ -563,7 +614,7 @@ int32_t launch_conv_gemm_umma(const ConvGeom& g, const bf16* in, const bf16* w, 
   p.dropout_p = ep.dropout_p; p.inv_keep = ep.dropout_p > 0.f ? 1.f / (1.f - ep.dropout_p) : 1.f; p.seed = ep.seed; p.offset = ep.offset; p.rng = ep.rng;
 
   CUtensorMap map_in, map_w, map_out;
-  const uint64_t C = g.c, V = g.v, N = g.n_out;
+  const uint64_t C = (uint64_t)g.c * parts, V = g.v, N = g.n_out;
   {
     // input viewed as {C, V, sp, T_in/sp, NB}; sp = conv stride in forward mode, 1 for dgrad
     const uint64_t sp = g.dgrad ? 1 : s;
@@ -578,7 +629,8 @@ int32_t launch_conv_gemm_umma(const ConvGeom& g, const bf16* in, const bf16* w, 
     uint32_t box[3] = {64, (uint32_t)p.bn, 1};
     STGCN_TRY(make_tmap_bf16(&map_w, w, 3, dims, str, box));
   }
-  {
+  if (out_f32) map_out = map_in;       // unused: the epilogue stores fp32 rows itself
+  else {
     const uint64_t ph = p.phases;
     uint64_t dims[5] = {N, V, ph, (uint64_t)g.t_out / ph, (uint64_t)g.nb};
     uint64_t str[4] = {N * 2, V * N * 2, ph * V * N * 2, (uint64_t)g.t_out * V * N * 2};
@@ -590,7 +642,7 @@ int32_t launch_conv_gemm_umma(const ConvGeom& g, const bf16* in, const bf16* w, 
     cudaError_t e = cudaSuccess;
 #define STGCN_CG_ATTR(M) if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_gemm_umma_kernel<M>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     STGCN_CG_ATTR(0) STGCN_CG_ATTR(EP_BIAS2D) STGCN_CG_ATTR(EP_BIAS | EP_STATS) STGCN_CG_ATTR(EP_SCALE | EP_RELU)
-    STGCN_CG_ATTR(EP_BIAS | EP_SCALE | EP_RELU) STGCN_CG_ATTR(EP_ALL)
+    STGCN_CG_ATTR(EP_BIAS | EP_SCALE | EP_RELU) STGCN_CG_ATTR(EP_ALL) STGCN_CG_ATTR(kEpSplit)
 #undef STGCN_CG_ATTR
     if (e != cudaSuccess) { set_error("cudaFuncSetAttribute(smem) failed: %s", cudaGetErrorString(e)); return STGCN_ERR_CUDA; }
     attr_set = true;
@@ -598,6 +650,11 @@ int32_t launch_conv_gemm_umma(const ConvGeom& g, const bf16* in, const bf16* w, 
   const int grid = std::min(p.total_tiles, num_sms());
   const int need = (ep.bias ? EP_BIAS : 0) | (ep.bias2d ? EP_BIAS2D : 0) | (ep.scale ? EP_SCALE : 0) | (ep.residual ? EP_RESID : 0) |
                    (ep.relu ? EP_RELU : 0) | (ep.dropout_p > 0.f ? EP_DROPOUT : 0) | (ep.stat_partials ? EP_STATS : 0) | (ep.vsum ? EP_VSUM : 0);
+  if (out_f32) {
+    launch_k(conv_gemm_umma_kernel<kEpSplit>, grid, kUmmaThreads, smem, st, map_in, map_w, map_out, p);
+    STGCN_CHECK_LAUNCH("conv_gemm_umma(split)");
+    return STGCN_OK;
+  }
   // the leanest instantiation that keeps every requested option
 #define STGCN_CG_TRY(M) if ((need & ~(M)) == 0) { launch_k(conv_gemm_umma_kernel<M>, grid, kUmmaThreads, smem, st, map_in, map_w, map_out, p); } else
   STGCN_CG_TRY(0) STGCN_CG_TRY(EP_BIAS2D) STGCN_CG_TRY(EP_BIAS | EP_STATS) STGCN_CG_TRY(EP_SCALE | EP_RELU)
@@ -605,6 +662,15 @@ int32_t launch_conv_gemm_umma(const ConvGeom& g, const bf16* in, const bf16* w, 
 #undef STGCN_CG_TRY
   STGCN_CHECK_LAUNCH("conv_gemm_umma");
   return STGCN_OK;
+}
+
+int32_t launch_conv_gemm_umma(const ConvGeom& g, const bf16* in, const bf16* w, const GemmEpilogue& ep, bf16* out, cudaStream_t st) {
+  return launch_conv_gemm_impl(g, in, w, ep, out, nullptr, st);
+}
+// fp32 path: in3 [rows_in][3c] and w3 [taps][n_out][3c] hold (hi | mid | lo) bf16 splits of the fp32 operands; out is fp32 [rows_out][n_out]
+int32_t launch_conv_gemm_umma_split(const ConvGeom& g, const bf16* in3, const bf16* w3, const GemmEpilogue& ep, float* out, cudaStream_t st) {
+  if (!out) { set_error("umma conv-gemm (split): null output"); return STGCN_ERR_INVALID; }
+  return launch_conv_gemm_impl(g, in3, w3, ep, nullptr, out, st);
 }
 
 }  // namespace stgcn

@@ -40,7 +40,11 @@ struct WgParams {
   int b_slab;                        // bytes of one 64-channel input slab (rows * 128, rows % 8 == 0)
   WgGroup groups[kWgMaxGroups];
   float* packed;                     // [taps][n_out][c] fp32, zeroed by the host
+  int terms;                         // 1, or 6 for split-bf16 fp32 operands: dout is [rows][3 n_out] = [hi | mid | lo], in is [rows][3 c];
+                                     // every reduction step runs the six significant part products into the same accumulator
 };
+__device__ __constant__ int c_wg_term_d[6] = {1, 0, 2, 0, 1, 0};      // dout part of term i (smallest products first)
+__device__ __constant__ int c_wg_term_i[6] = {1, 2, 0, 1, 0, 0};      // input part of term i
 
 __global__ void __launch_bounds__(kWgThreads, 1)
 wgrad_umma_kernel(const __grid_constant__ CUtensorMap map_dout, const __grid_constant__ CUtensorMap map_in,
@@ -98,15 +102,18 @@ wgrad_umma_kernel(const __grid_constant__ CUtensorMap map_dout, const __grid_con
         const WgGroup& G = p.groups[g];
         for (int kb = kb0; kb < kb1; ++kb) {
           const int b = kb / p.jblocks, j0 = (kb % p.jblocks) * p.fj;
-          mbar_wait(empty_bar + stage, phase ^ 1);
-          mbar_expect_tx_e(full_bar + stage, p.a_bytes + p.b_bytes);
-          for (int s = 0; s < p.n_slabs; ++s)
-            tma_load_5d_e(&map_dout, smem_a + (size_t)stage * a_stage + s * kATile, full_bar + stage,
-                          p.stacked ? 0 : n_t * 128 + s * 64, 0, 0, p.stacked ? j0 - s : j0, b);
-          for (int s = 0; s < p.c_tile / 64; ++s)
-            tma_load_5d_e(&map_in, smem_b + (size_t)stage * b_stage + s * p.b_slab, full_bar + stage, c_t * p.c_tile + s * 64, 0,
-                        G.parity, j0 + G.h_min, b);
-          if (++stage == p.stages) { stage = 0; phase ^= 1; }
+          for (int term = 0; term < p.terms; ++term) {
+            const int dcol = p.terms > 1 ? c_wg_term_d[term] * p.n_out : 0, icol = p.terms > 1 ? c_wg_term_i[term] * p.c : 0;
+            mbar_wait(empty_bar + stage, phase ^ 1);
+            mbar_expect_tx_e(full_bar + stage, p.a_bytes + p.b_bytes);
+            for (int s = 0; s < p.n_slabs; ++s)
+              tma_load_5d_e(&map_dout, smem_a + (size_t)stage * a_stage + s * kATile, full_bar + stage,
+                            dcol + (p.stacked ? 0 : n_t * 128 + s * 64), 0, 0, p.stacked ? j0 - s : j0, b);
+            for (int s = 0; s < p.c_tile / 64; ++s)
+              tma_load_5d_e(&map_in, smem_b + (size_t)stage * b_stage + s * p.b_slab, full_bar + stage, icol + c_t * p.c_tile + s * 64, 0,
+                          G.parity, j0 + G.h_min, b);
+            if (++stage == p.stages) { stage = 0; phase ^= 1; }
+          }
         }
       }
     }
@@ -120,7 +127,8 @@ wgrad_umma_kernel(const __grid_constant__ CUtensorMap map_dout, const __grid_con
         const WgGroup& G = p.groups[g];
         mbar_wait(tempty_bar, tphase ^ 1);
         tc_fence_after();
-        for (int kb = kb0; kb < kb1; ++kb) {
+        for (int kbt = kb0 * p.terms; kbt < kb1 * p.terms; ++kbt) {
+          const int kb = kbt > kb0 * p.terms ? kb0 + 1 : kb0;      // only "first step of the item or not" matters below
           mbar_wait(full_bar + stage, phase);
           tc_fence_after();
           const uint32_t a_addr = smem_u32(smem_a + (size_t)stage * a_stage);
@@ -208,7 +216,7 @@ static int num_sms_wg() {
 }
 
 int32_t launch_wgrad_umma(const ConvGeom& g, const bf16* dout, const bf16* in, const WIndex& wi, float* packed_ws, float* dw,
-                          cudaStream_t st, int c_valid, bool packed_is_zero, cudaStream_t unpack_st, cudaEvent_t unpack_ev) {
+                          cudaStream_t st, int c_valid, bool packed_is_zero, cudaStream_t unpack_st, cudaEvent_t unpack_ev, int split) {
   KernelTimer kt_(KC_UMMA_WGRAD, 2.0 * g.nb * g.t_out * g.v * (double)(c_valid >= 0 ? c_valid : g.c) * g.n_out * g.taps, st);
   if (!umma_wgrad_supported(g)) { set_error("umma wgrad: unsupported geometry"); return STGCN_ERR_UNSUPPORTED; }
   WgParams p; memset(&p, 0, sizeof(p));
@@ -279,10 +287,11 @@ int32_t launch_wgrad_umma(const ConvGeom& g, const bf16* dout, const bf16* in, c
   uint32_t cols = 32; while (cols < (uint32_t)(maxt * p.c_tile)) cols <<= 1;
   p.tmem_cols = cols;
   p.packed = packed_ws;
+  p.terms = split ? 6 : 1;
   if (!packed_is_zero) cudaMemsetAsync(packed_ws, 0, sizeof(float) * umma_wgrad_workspace_floats(g), st);
 
   CUtensorMap map_dout, map_in;
-  const uint64_t C = g.c, V = g.v, N = g.n_out;
+  const uint64_t C = (uint64_t)g.c * (split ? 3 : 1), V = g.v, N = (uint64_t)g.n_out * (split ? 3 : 1);   // split: [hi | mid | lo] column thirds
   {
     uint64_t dims[5] = {N, V, 1, (uint64_t)g.t_out, (uint64_t)g.nb};
     uint64_t str[4] = {N * 2, V * N * 2, V * N * 2, (uint64_t)g.t_out * V * N * 2};

@@ -56,9 +56,12 @@ def test_cfg2_block_full_frames_matches_oracle(case, dtype):
     assert rel_err(y, y_ref) < tol
     if dtype == torch.bfloat16:
         y_ref, dx_ref, g_ref, _ = oracle_block(x, gy, p, cfg, True, bf16=True)
-    kinks = check_dx_kink_tolerant(dx, dx_ref, tol * 2)
+    # ReLU-kink flips are counted on the output mask first (a pre-activation within rounding noise of zero takes the other branch:
+    # ~1e-6 of the elements on the fp32 tensor-core path, whose six-product split carries ~1e-6 relative error against ~1e-7 for a
+    # plain fp32 sum); each flip reaches the 9 input frames of its temporal taps, so that many dx frames may be off per flip
     flips = int(((y > 0) != (y_ref > 0)).sum())
     assert flips <= max(2, int(1e-4 * y.numel())), flips
+    kinks = check_dx_kink_tolerant(dx, dx_ref, tol * 2, max_frames=9 * max(2, flips + 1))
     ptol = tol * 2 if (kinks == 0 and flips == 0) else 5e-2
     for k, v in grads.items():
         if k == 'temporalConv.bias':            # a bias in front of a batch-statistics BatchNorm has zero gradient
