@@ -84,6 +84,9 @@ typedef struct StgcnBlockParams {
    * CUDA graph of the step draws a fresh mask per replay; the state used is kept in `saved` and replayed by backward.  NULL: the
    * descriptor's seed / offset values are used. */
   uint64_t* rng_state;
+  /* Optional (NULL = derive inside the call): the block's weight-only training operands as written by stgcn_train_prep_multi --
+   * valid for as long as A and temporalConv.weight are unchanged.  Pass the same pointer to forward and backward. */
+  const void* train_prep;
 } StgcnBlockParams;
 
 /* Parameter gradients (fp32, overwritten).  Same shapes as the parameters. */
@@ -136,6 +139,17 @@ size_t stgcn_block_prepared_bytes(const StgcnBlockDesc* desc);
 int32_t stgcn_block_prepare(const StgcnBlockDesc* desc, const StgcnBlockParams* params, void* prepared, void* stream);
 int32_t stgcn_block_forward_prepared(const StgcnBlockDesc* desc, const void* x, const StgcnBlockParams* params, const void* prepared,
                                      void* y, void* workspace, size_t workspace_bytes, void* stream);
+
+/* Weight-only operands of the training chain for a whole stack of blocks in ONE launch (no reference counterpart: the reference
+ * calls cuDNN per layer).  For each block i: the temporal weights (st_graphconv.py:41-43) packed as bf16 for the forward GEMM and
+ * for its data gradient, and the block-diagonal bf16 expansions of A (st_graphconv.py:129) the tensor-core aggregation uses, written
+ * to preps[i] (a device buffer of stgcn_train_prep_bytes(&descs[i]) bytes; 0 = this block has no such operands: fp32, CUDA-core
+ * shapes).  Call it once after the parameters changed (after the optimizer step / at the start of a training forward) and hand
+ * preps[i] to the block calls through StgcnBlockParams.train_prep; the ~40 small launches those operands otherwise cost per step
+ * (measured: 0.33 ms of a 6.09 ms cfg4 step) collapse into one.  descs / params / preps are HOST arrays. */
+size_t stgcn_train_prep_bytes(const StgcnBlockDesc* desc);
+int32_t stgcn_train_prep_multi(int32_t count, const StgcnBlockDesc* descs, const StgcnBlockParams* params, void* const* preps,
+                               void* stream);
 
 /* Autograd of the above (reference: torch autograd over st_graphconv.py:85-109).
  *   dy (n,t_out,v,c_out) -> dx (n,t,v,c_in) (may be NULL: first block) + grads. */
@@ -207,6 +221,13 @@ int32_t stgcn_collate_pad_augment(int32_t dtype, int32_t n, int32_t t_out, int32
 /* Keep-scale of nn.Dropout(p) as the library draws it (Philox4x32-10): out[i] = 1/(1-p) if element i of the block output
  * (flat index over (n,t_out,v,c_out)) is kept under state {seed, offset}, else 0.  For replaying a mask in tests / oracles. */
 int32_t stgcn_dropout_mask(uint64_t seed, uint64_t offset, float p, size_t count, float* out, void* stream);
+
+/* Adjacency normalisation of the model constructor on the device (normalize, src/data/adjacency.py:161-183):
+ * out[k] = L . raw[k] . L with L = (diag(rowsum(raw[k])) + alpha) ** expo, alpha added to EVERY entry of the diagonal matrix when
+ * dense_alpha != 0 (what the reference computes: a dense result with entries ~1e4..1e5) or to the diagonal only (dense_alpha = 0:
+ * the D^-1/2 A D^-1/2 its comment intends).  raw, out: (k, v, v) fp32 device tensors of 0/1 partition matrices, v <= 32. */
+int32_t stgcn_adjacency_normalize(int32_t k, int32_t v, const float* raw, float alpha, float expo, int32_t dense_alpha, float* out,
+                                  void* stream);
 
 /* Layout helpers: fp32 (n,t,v,c) <-> dtype (n,t,v,c) casts on device. */
 int32_t stgcn_cast(int32_t src_dtype, int32_t dst_dtype, const void* src, void* dst, size_t count, void* stream);

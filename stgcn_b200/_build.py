@@ -15,7 +15,7 @@ CSRC = os.path.join(HERE, 'csrc')
 OBJ = os.path.join(CSRC, 'build')
 LIB = os.path.join(HERE, 'libstgcn_b200.so')
 SOURCES = ['block.cu', 'bn_kernels.cu', 'agg_kernels.cu', 'gemm_simt.cu', 'head_kernels.cu', 'umma_gemm.cu',
-           'umma_probe.cu', 'timing.cu', 'umma_wgrad.cu', 'umma_agg.cu', 'umma_spatial.cu', 'train_kernels.cu', 'input_kernels.cu']
+           'umma_probe.cu', 'timing.cu', 'umma_wgrad.cu', 'umma_agg.cu', 'umma_spatial.cu', 'train_kernels.cu', 'input_kernels.cu', 'train_prep.cu']
 NVCC_FLAGS = ['-std=c++17', '-O3', '-gencode', 'arch=compute_100a,code=sm_100a', '-lineinfo',
               '-Xcompiler', '-fPIC', '--expt-relaxed-constexpr']
 

@@ -30,7 +30,7 @@ class BlockParams(C.Structure):
     _fields_ = [(n, _P) for n in ('bn1_weight', 'bn1_bias', 'bn1_running_mean', 'bn1_running_var',
                                   'bn1_num_batches_tracked', 'A', 'W', 'W_bias', 'Wt', 'Wt_bias', 'bn2_weight',
                                   'bn2_bias', 'bn2_running_mean', 'bn2_running_var', 'bn2_num_batches_tracked',
-                                  'Wr', 'Wr_bias', 'rng_state')]
+                                  'Wr', 'Wr_bias', 'rng_state', 'train_prep')]
 
 
 class BlockGrads(C.Structure):
@@ -58,6 +58,9 @@ def _declare(lib):
     lib.stgcn_block_prepare.argtypes = [D, C.POINTER(BlockParams), _P, _P]
     lib.stgcn_block_forward_prepared.restype = i32
     lib.stgcn_block_forward_prepared.argtypes = [D, _P, C.POINTER(BlockParams), _P, _P, _P, sz, _P]
+    lib.stgcn_train_prep_bytes.restype = sz; lib.stgcn_train_prep_bytes.argtypes = [D]
+    lib.stgcn_train_prep_multi.restype = i32
+    lib.stgcn_train_prep_multi.argtypes = [i32, D, C.POINTER(BlockParams), C.POINTER(_P), _P]
     lib.stgcn_block_backward.restype = i32
     lib.stgcn_block_backward.argtypes = [D, _P, _P, C.POINTER(BlockParams), _P, _P, _P, C.POINTER(BlockGrads), _P, sz, _P]
     lib.stgcn_spatial_workspace_bytes.restype = sz; lib.stgcn_spatial_workspace_bytes.argtypes = [D, i32]
@@ -81,6 +84,8 @@ def _declare(lib):
     lib.stgcn_collate_pad_augment.restype = i32
     lib.stgcn_collate_pad_augment.argtypes = [i32] * 5 + [_P] * 5 + [_P]
     lib.stgcn_cast.restype = i32; lib.stgcn_cast.argtypes = [i32, i32, _P, _P, sz, _P]
+    lib.stgcn_adjacency_normalize.restype = i32
+    lib.stgcn_adjacency_normalize.argtypes = [i32, i32, _P, C.c_float, C.c_float, i32, _P, _P]
     lib.stgcn_dropout_mask.restype = i32; lib.stgcn_dropout_mask.argtypes = [u64, u64, C.c_float, sz, _P, _P]
     lib.stgcn_umma_conv_gemm.restype = i32
     lib.stgcn_umma_conv_gemm.argtypes = [i32] * 9 + [_P] * 4 + [_P]

@@ -693,4 +693,46 @@ int32_t launch_bn1_fold_grads(const float* W, float* dW, const float* stats, con
   return STGCN_OK;
 }
 
+// ---------------------------------------------------------------------------
+// adjacency normalisation on the device (reference: normalize, src/data/adjacency.py:161-183):
+//   Lambda = (diag(rowsum(A_k)) + alpha) ** expo     -- alpha added to EVERY entry (dense_alpha, the reference) or to the
+//                                                       diagonal only (the textbook D^-1/2 A D^-1/2)
+//   out_k  = Lambda . A_k . Lambda
+// One CTA per partition, V <= 32: the three V x V matrices live in shared memory; fp32, sums in index order.
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(1024) adjacency_normalize_kernel(const float* __restrict__ raw, int V, float alpha, float expo,
+                                                                    int dense_alpha, float* __restrict__ out) {
+  pdl_enter();
+  __shared__ float As[32 * 32], Ls[32 * 32], Ts[32 * 32];
+  __shared__ float rs[32];
+  const int k = blockIdx.x, i = threadIdx.x / 32, j = threadIdx.x % 32;
+  const bool in = i < V && j < V;
+  As[i * 32 + j] = in ? raw[((size_t)k * V + i) * V + j] : 0.f;
+  __syncthreads();
+  if (j == 0 && i < V) { float s = 0.f; for (int w = 0; w < V; ++w) s += As[i * 32 + w]; rs[i] = s; }
+  __syncthreads();
+  float lam = 0.f;
+  if (in) {
+    if (dense_alpha) lam = powf((i == j ? rs[i] : 0.f) + alpha, expo);
+    else lam = i == j ? powf(rs[i] + alpha, expo) : 0.f;
+  }
+  Ls[i * 32 + j] = lam;
+  __syncthreads();
+  float t = 0.f;
+  if (in) for (int w = 0; w < V; ++w) t = fmaf(Ls[i * 32 + w], As[w * 32 + j], t);
+  Ts[i * 32 + j] = t;
+  __syncthreads();
+  if (in) {
+    float o = 0.f;
+    for (int w = 0; w < V; ++w) o = fmaf(Ts[i * 32 + w], Ls[w * 32 + j], o);
+    out[((size_t)k * V + i) * V + j] = o;
+  }
+}
+int32_t launch_adjacency_normalize(const float* raw, int K, int V, float alpha, float expo, int dense_alpha, float* out, cudaStream_t st) {
+  if (K < 1 || V < 1 || V > 32) { set_error("adjacency_normalize: K=%d V=%d unsupported (V <= 32)", K, V); return STGCN_ERR_UNSUPPORTED; }
+  launch_k(adjacency_normalize_kernel, K, 1024, 0, st, raw, V, alpha, expo, dense_alpha, out);
+  STGCN_CHECK_LAUNCH("adjacency_normalize");
+  return STGCN_OK;
+}
+
 }  // namespace stgcn

@@ -8,9 +8,27 @@
 
 #include <mutex>
 
+#include <nvtx3/nvToolsExt.h>      // header-only (dlopens the tools' injection library when a profiler is attached)
+
 #include "kernels.cuh"
 
 namespace stgcn {
+
+// NVTX range around one library call ("stgcn fwd 64->128 s2 T300 N64"), on when STGCN_NVTX=1: nsys / ncu --nvtx then show the
+// kernels grouped per ST-GCN block and direction.  Off by default (no call into the tools library at all).
+struct NvtxRange {
+  bool on;
+  NvtxRange(const char* what, const StgcnBlockDesc* d) {
+    static const bool enabled = getenv("STGCN_NVTX") != nullptr;
+    on = enabled && d != nullptr;
+    if (!on) return;
+    char buf[96];
+    snprintf(buf, sizeof(buf), "stgcn %s %d->%d s%d T%d V%d N%d %s", what, d->c_in, d->c_out, d->stride, d->t, d->v, d->n,
+             d->dtype == STGCN_BF16 ? "bf16" : "f32");
+    nvtxRangePushA(buf);
+  }
+  ~NvtxRange() { if (on) nvtxRangePop(); }
+};
 
 std::atomic<uint64_t> g_launches{0};
 int next_direction() {
@@ -111,6 +129,18 @@ template <class T> static Saved<T> carve_saved(Arena& a, const StgcnBlockDesc& d
   s.fp.valid = false;
   if (fold_ok_desc(d, m)) s.fp = carve_fold_prep(a, m);
   return s;
+}
+
+// weight-only operands produced ahead of the step by stgcn_train_prep_multi (train_prep.cu)
+struct TrainPrep { bf16* wt_f; bf16* wt_d; void* big; bool has_big; };
+static bool train_prep_supported(const StgcnBlockDesc& d, const Dims& m);
+static TrainPrep carve_train_prep(Arena& a, const Dims& m) {
+  TrainPrep t;
+  t.wt_f = a.get<bf16>((size_t)m.gamma * m.co * m.co);
+  t.wt_d = a.get<bf16>((size_t)m.gamma * m.co * m.co);
+  t.has_big = umma_agg_supported(m.v, m.ci, m.k);
+  t.big = t.has_big ? a.get<uint8_t>(umma_agg_prep_bytes(m.k)) : nullptr;
+  return t;
 }
 
 // ---- side lane: a second stream per device for work that is off the data-gradient path of a chain (per-joint sums, weight-gradient
@@ -239,6 +269,11 @@ static WIndex widx(int ndiv, long long snh, long long snl, int cdiv_, long long 
   WIndex w; w.ndiv = ndiv; w.snh = snh; w.snl = snl; w.cdiv = cdiv_; w.sch = sch; w.scl = scl; w.st = st; return w;
 }
 constexpr int kNoDiv = 1 << 30;
+static bool train_prep_supported(const StgcnBlockDesc& d, const Dims& m) {
+  if (d.dtype != STGCN_BF16 || (d.flags & STGCN_FLAG_FORCE_SIMT) || d.residual != STGCN_RES_NONE) return false;
+  return umma_conv_gemm_supported(geom(m.n, m.t, m.to, m.v, m.co, m.co, m.gamma, m.stride, m.pad, 0)) &&
+         umma_conv_gemm_supported(geom(m.n, m.to, m.t, m.v, m.co, m.co, m.gamma, m.stride, m.pad, 1));
+}
 
 // ---------------------------------------------------------------------------
 // spatial graph convolution:  S = sum_k (A_k h) W_k^T + bias through A
@@ -285,7 +320,8 @@ template <class T> struct Bn1Fold {      // backward of the folded BatchNorm-1 (
 template <class T>
 static int32_t spatial_fwd(Engine<T>& e, const Dims& m, const T* x, const float* aff_a, const float* aff_b, int relu1,
                            const float* A, const float* W, const float* Wb, T* S, T* xa_keep = nullptr,
-                           const FoldPrep* keep_prep = nullptr, const float* b2d_ready = nullptr) {
+                           const FoldPrep* keep_prep = nullptr, const float* b2d_ready = nullptr, void* big_ext = nullptr) {
+  // big_ext: block-diagonal adjacency operand already built for this step (stgcn_train_prep_multi); folded path only
   Arena& ws = e.ws;
   T* XA = xa_keep ? xa_keep : ws.template get<T>(m.rows_in * m.k * m.ci);
   float* b2d = ws.template get<float>((size_t)m.v * m.co);
@@ -314,7 +350,7 @@ static int32_t spatial_fwd(Engine<T>& e, const Dims& m, const T* x, const float*
       // BatchNorm-1 folded into the 1x1 weights: aggregate the RAW input, GEMM-1 against W.diag(a), shift through bias2d
       const int KCi = m.k * m.ci;
       const FoldPrep fp = (keep_prep && keep_prep->valid) ? *keep_prep : carve_fold_prep(ws, m);
-      void* prep = fp.prep; bf16* w2p = fp.w2p; bf16* w2pT = fp.w2pT; float* wb = fp.wb; float* wbb = fp.wbb;
+      void* prep = big_ext ? big_ext : fp.prep; bf16* w2p = fp.w2p; bf16* w2pT = fp.w2pT; float* wb = fp.wb; float* wbb = fp.wbb;
       float* rsum2 = ws.template get<float>((size_t)2 * m.k * m.v);
       float* bvec2 = ws.template get<float>((size_t)2 * m.k * m.co);
       if (ws.dry) return STGCN_OK;
@@ -326,7 +362,7 @@ static int32_t spatial_fwd(Engine<T>& e, const Dims& m, const T* x, const float*
       const bool want_fused = fused_env ? (fused_env[0] != '0') : (xa_keep == nullptr);
       const bool fused = want_fused && umma_spatial_supported(m.v, m.ci, m.co, m.k);
       if (!b2d_ready) {
-        STGCN_TRY(launch_build_big_adjacency(A, m.k, m.v, prep, e.st));
+        if (!big_ext) STGCN_TRY(launch_build_big_adjacency(A, m.k, m.v, prep, e.st));
         STGCN_TRY(launch_bn1_fold(W, Wb, A, umma_agg_rowsum_q(prep, m.k), aff_a, aff_b, m.k, m.v, m.co, m.ci, w2p, w2pT, wb, wbb, b2d, e.st, 0,
                                   rsum2, bvec2));
       }
@@ -533,14 +569,20 @@ static int32_t block_forward_t(const StgcnBlockDesc& d, const T* x, const StgcnB
   // training chain on the tcgen05 engine: the temporal weights are packed on the side lane while BatchNorm-1 and the spatial
   // convolution run
   const bool pre_wt = !res && (d.training || keep) && e.gemm_on_umma(gt);
-  SideLane* lane = (pre_wt && !ws.dry) ? side_lane() : nullptr;
+  TrainPrep tp{}; bool have_tp = false;
+  if (P.train_prep && !ws.dry && train_prep_supported(d, m)) {
+    Arena ta(const_cast<void*>(P.train_prep), ~(size_t)0); tp = carve_train_prep(ta, m); have_tp = true;
+  }
+  SideLane* lane = (pre_wt && !have_tp && !ws.dry) ? side_lane() : nullptr;
   bf16* wt_pre = nullptr;
-  if (pre_wt) {
+  if (pre_wt && have_tp) wt_pre = tp.wt_f;          // packed ahead of the step
+  else if (pre_wt) {
     int32_t rc = STGCN_OK;
     wt_pre = e.prepack(gt, P.Wt, wiT, lane, lane ? lane->ev[0] : nullptr, lane ? lane->ev[1] : nullptr, &rc);
     STGCN_TRY(rc);
   }
-  STGCN_TRY(spatial_fwd<T>(e, m, x, S.stats1 + 2 * m.ci, S.stats1 + 3 * m.ci, relu1, P.A, P.W, P.W_bias, S.S, saved_mem ? S.XA : nullptr, saved_mem ? &S.fp : nullptr));
+  STGCN_TRY(spatial_fwd<T>(e, m, x, S.stats1 + 2 * m.ci, S.stats1 + 3 * m.ci, relu1, P.A, P.W, P.W_bias, S.S, saved_mem ? S.XA : nullptr, saved_mem ? &S.fp : nullptr,
+                           nullptr, (have_tp && tp.has_big && !res) ? tp.big : nullptr));
   if (!res) {
     if (d.training || keep) {
       T* U = S.U ? S.U : ws.get<T>(m.rows_out * m.co);
@@ -665,10 +707,20 @@ static int32_t block_backward_t(const StgcnBlockDesc& d, const T* x, const T* y,
   const ConvGeom gd = geom(m.n, m.to, m.t, m.v, m.co, m.co, m.gamma, m.stride, m.pad, 1);
   const WIndex wiD = widx(kNoDiv, 0, m.gamma, kNoDiv, 0, (long long)m.co * m.gamma, 1);
   bf16* wd_pre = nullptr;
+  TrainPrep tp{}; bool have_tp = false;
+  if (P.train_prep && !ws.dry && train_prep_supported(d, m)) {
+    Arena ta(const_cast<void*>(P.train_prep), ~(size_t)0); tp = carve_train_prep(ta, m); have_tp = true;
+    if (S.fp.valid && tp.has_big) S.fp.prep = tp.big;        // forward put the block-diagonal adjacency there, not in `saved`
+  }
+  bool wd_on_lane = false;
   if (!res && folded && packed_t && e.gemm_on_umma(gd)) {
-    int32_t rc = STGCN_OK;
-    wd_pre = e.prepack(gd, P.Wt, wiD, lane, lane ? lane->ev[4] : nullptr, lane ? lane->ev[5] : nullptr, &rc);
-    STGCN_TRY(rc);
+    if (have_tp) wd_pre = tp.wt_d;                            // packed ahead of the step
+    else {
+      int32_t rc = STGCN_OK;
+      wd_pre = e.prepack(gd, P.Wt, wiD, lane, lane ? lane->ev[4] : nullptr, lane ? lane->ev[5] : nullptr, &rc);
+      STGCN_TRY(rc);
+      wd_on_lane = lane != nullptr;
+    }
   }
   ZeroJobs zj;
   if (!res) {
@@ -712,7 +764,7 @@ static int32_t block_backward_t(const StgcnBlockDesc& d, const T* x, const T* y,
       ep.vsum = t1; t1_ready = true;
     }
     if (wd_pre) {
-      if (lane && !ws.dry) cudaStreamWaitEvent(st, lane->ev[5], 0);
+      if (wd_on_lane && !ws.dry) cudaStreamWaitEvent(st, lane->ev[5], 0);
       STGCN_TRY(e.gemm_packed(gd, dU, wd_pre, ep, dTin));
     } else STGCN_TRY(e.gemm(gd, dU, P.Wt, wiD, ep, dTin));
   }
@@ -831,6 +883,7 @@ static int32_t check_ptrs(const void* a, const void* b, const void* c) {
 
 int32_t stgcn_block_forward(const StgcnBlockDesc* d, const void* x, const StgcnBlockParams* P, void* y, void* saved,
                             void* workspace, size_t workspace_bytes, void* stream) {
+  NvtxRange nvtx_("fwd", d);
   STGCN_TRY(validate(d));
   STGCN_TRY(check_ptrs(x, P, y));
   if (!workspace) { set_error("null workspace"); return STGCN_ERR_WORKSPACE; }
@@ -846,6 +899,7 @@ size_t stgcn_colstats_bytes(int32_t channels) { return channels > 0 ? stat_parti
 int32_t stgcn_block_forward_chain(const StgcnBlockDesc* d, const void* x, const StgcnBlockParams* P, void* y, void* saved,
                                   void* workspace, size_t workspace_bytes, const float* x_colstats, int32_t x_colstats_nblk,
                                   float* y_colstats, int32_t* y_colstats_nblk, void* stream) {
+  NvtxRange nvtx_("fwd", d);
   STGCN_TRY(validate(d));
   STGCN_TRY(check_ptrs(x, P, y));
   if (!workspace) { set_error("null workspace"); return STGCN_ERR_WORKSPACE; }
@@ -880,6 +934,7 @@ int32_t stgcn_block_prepare(const StgcnBlockDesc* d, const StgcnBlockParams* P, 
 
 int32_t stgcn_block_forward_prepared(const StgcnBlockDesc* d, const void* x, const StgcnBlockParams* P, const void* prepared, void* y,
                                      void* workspace, size_t workspace_bytes, void* stream) {
+  NvtxRange nvtx_("fwd-prepared", d);
   STGCN_TRY(validate(d));
   STGCN_TRY(check_ptrs(x, P, y));
   if (!prepared) { set_error("null prepared buffer"); return STGCN_ERR_INVALID; }
@@ -888,9 +943,48 @@ int32_t stgcn_block_forward_prepared(const StgcnBlockDesc* d, const void* x, con
   return block_forward_prepared(*d, (const bf16*)x, *P, prepared, (bf16*)y, ws, (cudaStream_t)stream);
 }
 
+size_t stgcn_train_prep_bytes(const StgcnBlockDesc* d) {
+  if (validate(d) != STGCN_OK) return 0;
+  const Dims m = dims_of(*d);
+  if (!train_prep_supported(*d, m)) return 0;
+  Arena dry(nullptr, 0);
+  carve_train_prep(dry, m);
+  return dry.off + 256;
+}
+
+int32_t stgcn_train_prep_multi(int32_t count, const StgcnBlockDesc* descs, const StgcnBlockParams* params, void* const* preps,
+                               void* stream) {
+  if (count < 0 || (count > 0 && (!descs || !params || !preps))) { set_error("train_prep_multi: null argument"); return STGCN_ERR_INVALID; }
+  PrepTable tab; tab.count = 0;
+  cudaStream_t st = (cudaStream_t)stream;
+  for (int i = 0; i < count; ++i) {
+    STGCN_TRY(validate(&descs[i]));
+    const Dims m = dims_of(descs[i]);
+    if (!preps[i] || !train_prep_supported(descs[i], m)) continue;
+    if (!params[i].Wt || !params[i].A) { set_error("train_prep_multi: block %d has no parameters", i); return STGCN_ERR_INVALID; }
+    Arena ta(preps[i], ~(size_t)0);
+    const TrainPrep tp = carve_train_prep(ta, m);
+    if (tab.count + 3 > kMaxPrepJobs) { STGCN_TRY(launch_train_prep_multi(tab, st)); tab.count = 0; }
+    PrepJob j; memset(&j, 0, sizeof(j));
+    j.kind = 0; j.taps = m.gamma; j.n_out = m.co; j.c = m.co; j.src = params[i].Wt;
+    j.wi = widx(kNoDiv, 0, (long long)m.co * m.gamma, kNoDiv, 0, m.gamma, 1); j.dst = tp.wt_f;          // [tap][n=co][c=ci]  (forward)
+    tab.jobs[tab.count++] = j;
+    j.wi = widx(kNoDiv, 0, m.gamma, kNoDiv, 0, (long long)m.co * m.gamma, 1); j.dst = tp.wt_d;          // [tap][n=ci][c=co]  (data gradient)
+    tab.jobs[tab.count++] = j;
+    if (tp.has_big) {
+      PrepJob a; memset(&a, 0, sizeof(a));
+      a.kind = 1; a.K = m.k; a.V = m.v; a.FT = 128 / m.v; a.src = params[i].A;
+      umma_agg_prep_pointers(tp.big, m.k, &a.big, &a.bigT, &a.rowsum);
+      tab.jobs[tab.count++] = a;
+    }
+  }
+  return launch_train_prep_multi(tab, st);
+}
+
 int32_t stgcn_block_backward(const StgcnBlockDesc* d, const void* x, const void* y, const StgcnBlockParams* P, const void* saved,
                              const void* dy, void* dx, const StgcnBlockGrads* G, void* workspace, size_t workspace_bytes,
                              void* stream) {
+  NvtxRange nvtx_("bwd", d);
   STGCN_TRY(validate(d));
   STGCN_TRY(check_ptrs(x, P, dy));
   STGCN_TRY(check_ptrs(saved, G, y));
@@ -952,6 +1046,12 @@ int32_t stgcn_head_backward(int32_t dtype, int32_t n, int32_t t, int32_t v, int3
   STGCN_TRY(check_ptrs(pooled, fcw, dlogits));
   STGCN_TRY(check_ptrs(dfeat, dfcw, dfcb));
   return head_backward(dtype, n, t, v, c, classes, pooled, fcw, dlogits, dfeat, dfcw, dfcb, (cudaStream_t)stream);
+}
+
+int32_t stgcn_adjacency_normalize(int32_t k, int32_t v, const float* raw, float alpha, float expo, int32_t dense_alpha, float* out,
+                                  void* stream) {
+  STGCN_TRY(check_ptrs(raw, out, out));
+  return launch_adjacency_normalize(raw, k, v, alpha, expo, dense_alpha, out, (cudaStream_t)stream);
 }
 
 int32_t stgcn_cast(int32_t sd, int32_t dd, const void* src, void* dst, size_t count, void* stream) {

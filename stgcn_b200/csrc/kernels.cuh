@@ -87,6 +87,7 @@ template <class T> int32_t launch_agg_dA(const T* dxa, const T* x, long long fra
 template <class T> int32_t launch_agg_small_fwd(const T* x, long long frames, int V, int C, int K, int ld, const float* A, T* xa,
                                                cudaStream_t st);
 int32_t launch_adjacency_rowsum(const float* A, int K, int V, float* rs, cudaStream_t st);
+int32_t launch_adjacency_normalize(const float* raw, int K, int V, float alpha, float expo, int dense_alpha, float* out, cudaStream_t st);
 template <class T> int32_t launch_vcolsum(const T* ds, long long frames, int V, int C, float* t1, cudaStream_t st);
 int32_t launch_bias2d(const float* A, const float* bias, int K, int V, int Co, float* out, cudaStream_t st);
 int32_t launch_spatial_bias_grads(const float* t1, const float* A, const float* bias, int K, int V, int Co, float* dbias, float* dA,
@@ -137,6 +138,20 @@ bool umma_spatial_supported(int v, int ci, int co, int k);
 int32_t launch_spatial_fused(const bf16* x, int nb, int t, int v, int ci, int co, int k, const bf16* big, const bf16* w2p,
                              const float* b2d, bf16* xa, bf16* s_out, cudaStream_t st);
 const bf16* umma_agg_big(const void* prep, int k);
+
+// train_prep.cu  (weight-only operands of every block of a stack in one launch)
+struct PrepJob {
+  int kind;                                  // 0: weight pack, 1: block-diagonal adjacency
+  int taps, n_out, c; WIndex wi;             // kind 0
+  int K, V, FT;                              // kind 1
+  const float* src; bf16* dst;               // kind 0: weights -> packed; kind 1: src = A
+  bf16* big; bf16* bigT; float* rowsum;      // kind 1
+};
+constexpr int kMaxPrepJobs = 48;
+struct PrepTable { int count; PrepJob jobs[kMaxPrepJobs]; };
+int32_t launch_train_prep_multi(const PrepTable& tab, cudaStream_t st);
+// where the three parts of an aggregation prep buffer (umma_agg_prep_bytes) live
+void umma_agg_prep_pointers(void* prep, int K, bf16** big, bf16** bigT, float** rowsum);
 
 // head_kernels.cu
 int32_t head_forward(int dtype, int n, int t, int v, int c, int classes, const void* feat, const float* fcw, const float* fcb,

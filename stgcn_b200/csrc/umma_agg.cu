@@ -15,6 +15,9 @@
 //   agg_bwd : dh   = sum_k BigA_k^T . dXA_k                 (optionally masked by ReLU(h) > 0)
 //   agg_dA  : G_k += dXA_k tile . h tile^T  accumulated in TMEM over all tiles of the CTA;
 //             dA[k] = sum of the FT diagonal V x V blocks of G_k
+#include <stdlib.h>
+#include <string.h>
+
 #include "kernels.cuh"
 #include "umma_common.cuh"
 
@@ -63,8 +66,14 @@ AggPrep carve_agg_prep(void* mem, int K) {
   return a;
 }
 
+void umma_agg_prep_pointers(void* prep, int K, bf16** big, bf16** bigT, float** rowsum) {
+  const AggPrep a = carve_agg_prep(prep, K);
+  *big = a.big; *bigT = a.bigT; *rowsum = a.rowsum;
+}
+
 int32_t launch_build_big_adjacency(const float* A, int K, int V, void* prep_mem, cudaStream_t st) {
   KernelTimer kt_(KC_PACK, 0.0, st);
+  { static const char* x = getenv("STGCN_X_SKIP"); if (x && strchr(x, 'a')) return STGCN_OK; }     // timing experiment only (results invalid)
   AggPrep a = carve_agg_prep(prep_mem, K);
   launch_k(build_big_adjacency_kernel, cdiv(K * 128 * 128, 256), 256, 0, st, A, K, V, 128 / V, a.big, a.bigT, a.rowsum);
   STGCN_CHECK_LAUNCH("build_big_adjacency");

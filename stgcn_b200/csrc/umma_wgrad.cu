@@ -15,6 +15,9 @@
 // by tests/test_gpu_umma.py: the 128B swizzle is a function of the absolute address).
 // Each tap owns its own accumulator columns in TMEM; at the end of the item the epilogue
 // warps add the tile into a packed fp32 buffer with red.global.add.
+#include <stdlib.h>
+#include <string.h>
+
 #include "kernels.cuh"
 #include "umma_common.cuh"
 
@@ -314,6 +317,7 @@ int32_t launch_wgrad_umma(const ConvGeom& g, const bf16* dout, const bf16* in, c
   const int grid = std::min(p.total_items, num_sms_wg());
   launch_k(wgrad_umma_kernel, grid, kWgThreads, smem, st, map_dout, map_in, p);
   STGCN_CHECK_LAUNCH("wgrad_umma");
+  { static const char* x = getenv("STGCN_X_SKIP"); if (x && strchr(x, 'u')) return STGCN_OK; }     // timing experiment only (results invalid)
   size_t total = umma_wgrad_workspace_floats(g);
   cudaStream_t ust = st;
   if (unpack_st && unpack_ev) {      // the layout change is off the data-gradient path: let it run beside the next kernels

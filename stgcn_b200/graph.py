@@ -106,9 +106,24 @@ def normalize(matrices, expo=-0.5, alpha=0.001, dense_alpha=True):
     return out
 
 
+def normalize_on_device(matrices, device, expo=-0.5, alpha=0.001, dense_alpha=True):
+    """`normalize` executed by the library on `device` (stgcn_adjacency_normalize): (K,V,V) fp32 CUDA tensor, V <= 32."""
+    from . import _lib as L
+    raw = torch.stack([m.float() for m in matrices]).contiguous().to(device)
+    out = torch.empty_like(raw)
+    L.check(L.lib().stgcn_adjacency_normalize(raw.shape[0], raw.shape[1], L.ptr(raw), float(alpha), float(expo), int(bool(dense_alpha)),
+                                              L.ptr(out), L.stream_ptr(out.device)), 'adjacency_normalize')
+    return out
+
+
 def get_normalized_adjacency_matrices(strat=Strategy.UNI_LABELING, d=1, alpha=0.001, distance_file=None,
-                                      distances=None, skeleton='body25', dense_alpha=True):
+                                      distances=None, skeleton='body25', dense_alpha=True, device=None):
+    """device=None: host arithmetic as in the reference (bit-for-bit, tests/test_oracle_golden.py); a CUDA device: the
+    normalisation runs in the library on that device (same formula, fp32, within 1e-6 of the host result)."""
     if distances is None and distance_file:
         import numpy as np
         distances = np.load(distance_file)
-    return normalize(create_adjacency_matrices(strat, d, distances, skeleton), alpha=alpha, dense_alpha=dense_alpha)
+    mats = create_adjacency_matrices(strat, d, distances, skeleton)
+    if device is not None:
+        return normalize_on_device(mats, device, alpha=alpha, dense_alpha=dense_alpha)
+    return normalize(mats, alpha=alpha, dense_alpha=dense_alpha)

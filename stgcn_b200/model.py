@@ -8,10 +8,16 @@ import torch.nn as nn
 
 from . import functional as Fn
 from . import graph
-from .modules import SpatialTemporalConv
+from .modules import SpatialTemporalConv, prepare_training_operands
 
 LAYERS = [(None, 64, 1), (64, 64, 1), (64, 64, 1), (64, 64, 1), (64, 128, 2), (128, 128, 1), (128, 128, 1),
           (128, 256, 2), (256, 256, 1), (256, 256, 1)]          # lightning_model.py:65-86
+
+
+def _prepare(conv, x):
+    """Before a forward that will be differentiated: the weight-only operands of all ten blocks in one launch."""
+    if torch.is_grad_enabled() and x.is_cuda and any(p.requires_grad for p in conv[0].parameters()):
+        prepare_training_operands(list(conv), x.shape[0], x.shape[2], x.device)
 
 
 def _stack(c_in, A, masks, gamma, pad, compute_dtype, **kw):
@@ -49,6 +55,7 @@ class L_STGCN(nn.Module):
 
     def forward(self, x):
         x = x.permute(0, 3, 1, 2)                 # (N,T,V,C) -> logical (N,C,T,V): already channels-last in memory
+        _prepare(self.conv, x)
         x = self.conv(x)
         return Fn.head_forward(x, self.fc_layer.weight, self.fc_layer.bias)
 
@@ -77,6 +84,7 @@ class STGCN(nn.Module):
 
     def forward(self, x):
         x = x.permute(0, 3, 1, 2)
+        _prepare(self.conv, x)
         x = self.conv(x)
         x = Fn.head_forward(x, self.fc_layer.weight, self.fc_layer.bias)
         return self.softmax(x)

@@ -22,6 +22,53 @@ def _momentum(bn):
     return float(bn.momentum)
 
 
+def prepare_training_operands(blocks, n, t, device):
+    """Weight-only operands of a chain of SpatialTemporalConv blocks (packed temporal weights in both layouts, block-diagonal
+    adjacency) in ONE launch (stgcn_train_prep_multi) instead of ~4 small launches per block inside the step.  `n`, `t`: batch
+    and frame count of the input of blocks[0]; later blocks see the frame counts the chain produces.  Marks each block so that
+    its next forward uses the operands; called by the models at the start of a training forward and by a stand-alone block for
+    itself.  Must run after the last change of the parameters and before the forward that uses them (both are per forward)."""
+    import ctypes as C
+    import os
+    # Off unless STGCN_TRAIN_PREP=1: measured on B200 (cfg4, same box, alternating runs) the step takes 6.12 ms with the batched
+    # launch and 6.08-6.10 ms without it although 27 launches disappear -- the per-block packs already hide behind programmatic
+    # dependent launch and the side lane, while the batched kernel sits at the head of the forward chain.
+    if os.environ.get('STGCN_TRAIN_PREP', '0') in ('', '0'):
+        for b in blocks:
+            b._train_prep = None
+            b._tp_fresh = True
+        return
+    lib = L.lib()
+    k = len(blocks)
+    descs = (L.BlockDesc * k)()
+    params = (L.BlockParams * k)()
+    preps = (C.c_void_p * k)()
+    any_prep = False
+    for i, b in enumerate(blocks):
+        sc = b.spatialConv
+        d = L.BlockDesc(n=n, c_in=b.C_in, c_out=b.C_out, t=t, v=sc.V, k=sc.K, gamma=b.gamma, stride=b.temporal_stride,
+                        pad=b.temporal_padding, dtype=L.dtype_code(b.compute_dtype), training=1, residual=b._res_mode,
+                        flags=b.flags, dropout_p=0.0, bn_eps=1e-5, bn_momentum=0.1, seed=0, offset=0)
+        descs[i] = d
+        nbytes = lib.stgcn_train_prep_bytes(C.byref(d)) if (sc.A.is_cuda and sc.A.device == device) else 0
+        if nbytes:
+            if b._train_prep is None or b._train_prep.numel() != nbytes or b._train_prep.device != device:
+                b._train_prep = torch.empty(nbytes, dtype=torch.uint8, device=device)
+            params[i].A = sc.A.data_ptr()
+            params[i].Wt = b.temporalConv.weight.data_ptr()
+            preps[i] = b._train_prep.data_ptr()
+            b._tp_fresh = True
+            any_prep = True
+        else:
+            b._train_prep = None
+            b._tp_fresh = True          # nothing to prepare for this block (fp32 / CUDA-core shapes): do not ask again this forward
+        t = (t + 2 * b.temporal_padding - b.gamma) // b.temporal_stride + 1
+        if t < 1:
+            break
+    if any_prep:
+        L.check(lib.stgcn_train_prep_multi(k, descs, params, preps, L.stream_ptr(device)), 'train_prep_multi')
+
+
 class SpatialConv(nn.Module):
     """Spatial graph convolution, reference st_graphconv.py:111-152.
 
@@ -77,6 +124,8 @@ class SpatialTemporalConv(nn.Module):
         # non-persistent: the state_dict keeps the reference's keys
         self.register_buffer('_rng_state', None, persistent=False)
         self._prep_cache = {}      # frozen-parameter inference operands (functional._BlockFn), keyed by tensor versions
+        self._train_prep = None    # weight-only training operands (prepare_training_operands), refreshed every training forward
+        self._tp_fresh = False
 
     def _ensure_rng(self, device):
         """Create the device-resident dropout generator on first use: seeded once from torch's CPU generator (so
@@ -109,6 +158,11 @@ class SpatialTemporalConv(nn.Module):
                'rng_state': self._rng_state if p_drop > 0 else None,
                'grad_bufs': [Fn.grad_buf_of(q) for q in raw],
                'flags': self.flags, 'prep_cache': self._prep_cache}
+        if need_grad and f_in.is_cuda:
+            if not self._tp_fresh:          # stand-alone use: prepare for this block alone (models do it for the whole stack)
+                prepare_training_operands([self], f_in.shape[0], f_in.shape[2], f_in.device)
+            self._tp_fresh = False
+            cfg['train_prep'] = self._train_prep
         buffers = (b1.running_mean, b1.running_var, b1.num_batches_tracked,
                    b2.running_mean, b2.running_var, b2.num_batches_tracked)
         # chained blocks: the block that produced f_in may have left its column statistics on the tensor (valid only for this

@@ -310,6 +310,55 @@ def test_captured_step_refuses_when_an_older_autograd_graph_is_alive():
     torch.empty(4, device='cuda').uniform_()          # torch's CUDA generator is not stuck in capture mode
 
 
+def test_batched_training_operands_give_the_same_step(monkeypatch):
+    """stgcn_train_prep_multi (opt-in, STGCN_TRAIN_PREP=1): the weight-only operands of all ten blocks from one launch must give
+    the same logits and gradients as every block deriving them inside its own call, also after the weights changed."""
+    from stgcn_b200 import L_STGCN, cross_entropy
+    monkeypatch.setenv('STGCN_NO_PINGPONG', '1')       # same tile order in both runs (bf16 run-to-run noise, tools/gpu_determinism.py)
+    torch.manual_seed(0)
+    A = torch.randn(3, 25, 25) * 0.15
+    model = L_STGCN(_hp(), compute_dtype=torch.bfloat16, A=A).cuda().train()
+    state = {k: v.detach().clone() for k, v in model.state_dict().items()}
+    x = torch.randn(4, 40, 25, 3).cuda(); y = torch.tensor([1, 5, 30, 59]).cuda()
+
+    def run(flag):
+        monkeypatch.setenv('STGCN_TRAIN_PREP', flag)
+        model.load_state_dict(state)
+        outs = []
+        for it in range(2):                              # the second pass runs on modified weights: operands must follow
+            model.zero_grad(set_to_none=True)
+            lg = model(x)
+            cross_entropy(lg, y).backward()
+            outs.append((lg.detach().float().cpu(), torch.cat([p.grad.flatten().float().cpu() for p in model.parameters()])))
+            del lg
+            with torch.no_grad():
+                for b in model.conv:
+                    b.temporalConv.weight.mul_(1.25); b.spatialConv.A.mul_(0.8)
+        return outs
+    off, on = run('0'), run('1')
+    assert all(b._train_prep is not None for b in model.conv)            # the batched path really ran
+    for (l0, g0), (l1, g1) in zip(off, on):
+        assert rel_err(l1, l0) < 2e-2
+        assert float((g1 - g0).abs().max() / g0.abs().max()) < 2e-2
+    assert rel_err(off[1][0], off[0][0]) > 1e-3                          # the weight change was visible
+
+
+@pytest.mark.parametrize('skeleton,V', [('body25', 25), ('openpose18', 18)])
+@pytest.mark.parametrize('dense_alpha', [True, False], ids=['reference-dense-alpha', 'diagonal-alpha'])
+def test_device_adjacency_normalisation_matches_host(skeleton, V, dense_alpha):
+    """stgcn_adjacency_normalize against graph.normalize (which reproduces the reference's adjacency.py bit for bit on the golden
+    fixture): every strategy, d = 1 and 2, both skeletons."""
+    from stgcn_b200 import graph
+    dist = np.random.RandomState(0).rand(V)
+    for strat in range(4):
+        for d in (1, 2):
+            host = graph.get_normalized_adjacency_matrices(strat, d, distances=dist, skeleton=skeleton, dense_alpha=dense_alpha)
+            dev = graph.get_normalized_adjacency_matrices(strat, d, distances=dist, skeleton=skeleton, dense_alpha=dense_alpha,
+                                                          device=torch.device('cuda'))
+            assert dev.is_cuda and dev.shape == host.shape
+            assert rel_err(dev, host) < 1e-5, (strat, d)
+
+
 def test_cross_entropy_out_of_range_label_poisons_loss_without_oob():
     import stgcn_b200
     logits = torch.randn(6, 10).cuda().requires_grad_(True)
