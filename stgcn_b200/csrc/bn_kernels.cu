@@ -482,7 +482,7 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const T* __restrict__
                                                            const float* __restrict__ stats, const float* __restrict__ sums,
                                                            long long total, int C, int relu, int training, float inv_m,
                                                            float p, float inv_keep, uint64_t seed, uint64_t offset,
-                                                           T* __restrict__ dz, const uint64_t* __restrict__ rng) {
+                                                           T* __restrict__ dz, const uint64_t* __restrict__ rng, const ResAddend<T> ra) {
   pdl_enter();
   if (rng) { seed = rng[0]; offset = rng[1]; }
   long long i = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * VEC;
@@ -500,6 +500,15 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const T* __restrict__
       if (training) r = r - sums[c + j] * inv_m - (zz[j] - mean) * invstd * sums[C + c + j] * inv_m;
       g[j] = a * r;
     }
+    if (ra.ptr) {
+      const long long src = ra.source(i, C);
+      if (src >= 0) {
+        float ad[VEC];
+        if constexpr (VEC == 4) ld4(ra.ptr + src, ad); else ad[0] = ldf(ra.ptr + src);
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) g[j] += ad[j];
+      }
+    }
     if constexpr (VEC == 4) st4(dz + i, g); else stf(dz + i, g[0]);
   }
 }
@@ -508,7 +517,7 @@ template <class T>
 __global__ void __launch_bounds__(256, 3) bn_bwd_apply_fast_kernel(const T* __restrict__ dy, const T* __restrict__ z,
                                                                 const float* __restrict__ stats, const float* __restrict__ sums,
                                                                 long long total, int C, int relu, int training, float inv_m,
-                                                                T* __restrict__ dz, int rev) {
+                                                                T* __restrict__ dz, int rev, const ResAddend<T> ra) {
   pdl_enter();
   constexpr int VEC = VecN<T>::N;
   long long i = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * VEC;
@@ -534,19 +543,30 @@ __global__ void __launch_bounds__(256, 3) bn_bwd_apply_fast_kernel(const T* __re
       g[j] = ca[j] * r;
     }
   };
+  auto addend = [&](float (&g)[VEC], long long e) {          // skip connection's gradient rides in this pass
+    if (!ra.ptr) return;
+    const long long src = ra.source(e, C);
+    if (src < 0) return;
+    float ad[VEC];
+    ldv(ra.ptr + src, ad);
+#pragma unroll
+    for (int j = 0; j < VEC; ++j) g[j] += ad[j];
+  };
   for (; i + step < total; i += 2 * step) {
     float g0[VEC], z0[VEC], g1[VEC], z1[VEC];
     ldv(dy + P(i), g0); ldv(z + P(i), z0); ldv(dy + P(i + step), g1); ldv(z + P(i + step), z1);
     apply(g0, z0); apply(g1, z1);
+    addend(g0, P(i)); addend(g1, P(i + step));
     stv(dz + P(i), g0); stv(dz + P(i + step), g1);
   }
-  if (i < total) { float g0[VEC], z0[VEC]; ldv(dy + P(i), g0); ldv(z + P(i), z0); apply(g0, z0); stv(dz + P(i), g0); }
+  if (i < total) { float g0[VEC], z0[VEC]; ldv(dy + P(i), g0); ldv(z + P(i), z0); apply(g0, z0); addend(g0, P(i)); stv(dz + P(i), g0); }
 }
 
 template <class T>
 int32_t launch_bn_bwd_apply(const T* dy, const T* z, const float* stats, const float* sums, long long rows, int C,
                             int relu, int training, float p, uint64_t seed, uint64_t offset, T* dz, cudaStream_t st,
-                            const uint64_t* rng) {
+                            const uint64_t* rng, const ResAddend<T>* addend) {
+  const ResAddend<T> ra = addend ? *addend : ResAddend<T>();
   KernelTimer kt_(KC_ELEMWISE, (double)rows * C, st);
   long long total = rows * C;
   float inv_keep = p > 0.f ? 1.f / (1.f - p) : 1.f;
@@ -556,19 +576,19 @@ int32_t launch_bn_bwd_apply(const T* dy, const T* z, const float* stats, const f
     // (measured on B200: 444 CTAs 0.666 ms per step for the ten launches, 888: 0.681, 1184: 0.702)
     const int apply_cap = 148 * 3;
     launch_k(bn_bwd_apply_fast_kernel<T>, std::min(elementwise_blocks(total, VecN<T>::N), apply_cap), 256, 0, st, dy, z, stats, sums, total, C, relu, training,
-                                                                                         inv_m, dz, next_direction());
+                                                                                         inv_m, dz, next_direction(), ra);
   } else if (C % 4 == 0) {
     int blocks = (int)std::min<long long>((total / 4 + 255) / 256, 148 * 16);
-    launch_k(bn_bwd_apply_kernel<T, 4>, blocks, 256, 0, st, dy, z, stats, sums, total, C, relu, training, inv_m, p, inv_keep, seed, offset, dz, rng);
+    launch_k(bn_bwd_apply_kernel<T, 4>, blocks, 256, 0, st, dy, z, stats, sums, total, C, relu, training, inv_m, p, inv_keep, seed, offset, dz, rng, ra);
   } else {
     int blocks = (int)std::min<long long>((total + 255) / 256, 148 * 16);
-    launch_k(bn_bwd_apply_kernel<T, 1>, blocks, 256, 0, st, dy, z, stats, sums, total, C, relu, training, inv_m, p, inv_keep, seed, offset, dz, rng);
+    launch_k(bn_bwd_apply_kernel<T, 1>, blocks, 256, 0, st, dy, z, stats, sums, total, C, relu, training, inv_m, p, inv_keep, seed, offset, dz, rng, ra);
   }
   STGCN_CHECK_LAUNCH("bn_bwd_apply");
   return STGCN_OK;
 }
-template int32_t launch_bn_bwd_apply<float>(const float*, const float*, const float*, const float*, long long, int, int, int, float, uint64_t, uint64_t, float*, cudaStream_t, const uint64_t*);
-template int32_t launch_bn_bwd_apply<bf16>(const bf16*, const bf16*, const float*, const float*, long long, int, int, int, float, uint64_t, uint64_t, bf16*, cudaStream_t, const uint64_t*);
+template int32_t launch_bn_bwd_apply<float>(const float*, const float*, const float*, const float*, long long, int, int, int, float, uint64_t, uint64_t, float*, cudaStream_t, const uint64_t*, const ResAddend<float>*);
+template int32_t launch_bn_bwd_apply<bf16>(const bf16*, const bf16*, const float*, const float*, long long, int, int, int, float, uint64_t, uint64_t, bf16*, cudaStream_t, const uint64_t*, const ResAddend<bf16>*);
 
 // ---------------------------------------------------------------------------
 // dz = dy * [out > 0] * (1/(1-p) if dropout)    -- backward of the trailing

@@ -53,6 +53,20 @@ struct ZeroJobs {
   void add(float* ptr, size_t floats) { if (ptr && floats && count < 6) { p[count] = ptr; n[count] = (unsigned)floats; ++count; } }
 };
 
+// Gradient of a skip connection added inside the last element-wise backward pass of a residual block: element e of the
+// (n, t, v, C) tensor being written receives ptr[((n*t_src + t/stride)*v + v_)*C + c] when t % stride == 0 (stride 1, t_src = t:
+// the identity skip; stride 2: the strided 1x1 conv skip, whose data gradient only reaches the frames it sampled).
+template <class T> struct ResAddend {
+  const T* ptr = nullptr; int stride = 1, t = 1, t_src = 1, v = 1;
+  __device__ __forceinline__ long long source(long long e, int C) const {      // element index in ptr, or -1: nothing to add
+    const long long row = e / C; const int c = (int)(e - row * C);
+    const long long frame = row / v; const int vv = (int)(row - frame * v);
+    const long long n = frame / t; const int tt = (int)(frame - n * t);
+    if (tt % stride != 0) return -1;
+    return ((n * t_src + tt / stride) * v + vv) * (long long)C + c;
+  }
+};
+
 // bn_kernels.cu
 size_t stat_partials_bytes(int C);
 template <class T> int32_t launch_colstats(const T* x, long long rows, int C, float* partials, int* nblk, cudaStream_t st);
@@ -70,7 +84,7 @@ template <class T> int32_t launch_bn_bwd_reduce(const T* dy, const T* z, const f
 int32_t launch_bn_bwd_finalize(const float* partials, int nblk, int C, float* sums, float* dgamma, float* dbeta, cudaStream_t st);
 template <class T> int32_t launch_bn_bwd_apply(const T* dy, const T* z, const float* stats, const float* sums, long long rows, int C,
                                               int relu, int training, float p, uint64_t seed, uint64_t offset, T* dz, cudaStream_t st,
-                                              const uint64_t* rng = nullptr);
+                                              const uint64_t* rng = nullptr, const ResAddend<T>* addend = nullptr);
 int32_t launch_rng_fetch(uint64_t* state, uint64_t seed, uint64_t offset, uint64_t advance, uint64_t* slot, cudaStream_t st);
 int32_t launch_dropout_mask(uint64_t seed, uint64_t offset, float p, size_t n, float* out, cudaStream_t st);
 template <class T> int32_t launch_relu_bwd(const T* dy, const T* out, long long total, float p, T* dz, cudaStream_t st);
