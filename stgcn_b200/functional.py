@@ -12,8 +12,19 @@ from . import _lib as L
 
 
 def _to_ntvc(x, dtype):
-    """logical (N,C,T,V) -> contiguous physical (N,T,V,C) of `dtype` (no copy when already so)."""
-    return x.permute(0, 2, 3, 1).to(dtype).contiguous()
+    """logical (N,C,T,V) -> contiguous physical (N,T,V,C) of `dtype` (no copy when already so).  A dtype change of an already
+    channels-last CUDA tensor (block 0's fp32 input on the bf16 path) is done by the library's own cast kernel, so that no torch
+    kernel runs on the block path; anything that needs a real transpose falls back to torch (outside the benchmarked chain)."""
+    xp = x.permute(0, 2, 3, 1)
+    if xp.dtype == dtype:
+        return xp.contiguous()
+    if xp.is_cuda and xp.is_contiguous() and not (torch.is_grad_enabled() and x.requires_grad) \
+            and xp.dtype in (torch.float32, torch.bfloat16) and dtype in (torch.float32, torch.bfloat16):
+        out = torch.empty(xp.shape, dtype=dtype, device=xp.device)
+        L.check(L.lib().stgcn_cast(L.dtype_code(xp.dtype), L.dtype_code(dtype), L.ptr(xp), L.ptr(out), xp.numel(),
+                                   L.stream_ptr(xp.device)), 'cast')
+        return out
+    return xp.to(dtype).contiguous()
 
 
 def _from_ntvc(y):
