@@ -47,7 +47,12 @@ def _grad_out(param, buf):
 
 
 def grad_buf_of(p):
-    return getattr(p, '_stgcn_grad_buf', None) if p is not None else None
+    """The data-parallel reducer's bucket slice for parameter `p`, when backward may write the gradient straight into it: only
+    while `p.grad is None` (zero_grad(set_to_none=True), torch's default).  If `p.grad` exists it already aliases that slice, and
+    autograd would add the freshly written gradient to ITSELF; a separate tensor is used then and accumulates correctly."""
+    if p is None or p.grad is not None:
+        return None
+    return getattr(p, '_stgcn_grad_buf', None)
 
 
 class _BlockFn(torch.autograd.Function):

@@ -116,3 +116,27 @@ def test_bucket_reducer_on_the_real_model_with_edge_importance_masks():
         p.join(120)
         assert p.exitcode == 0
     assert err < 1e-5
+
+
+def test_bucket_slices_are_not_handed_out_while_a_gradient_exists():
+    """functional.grad_buf_of: with zero_grad(set_to_none=False) p.grad aliases the bucket slice; writing the new gradient into
+    that slice and letting autograd accumulate would double it, so no slice is handed out then."""
+    from stgcn_b200.functional import grad_buf_of
+    from stgcn_b200.parallel import GradBucketReducer
+    lin = torch.nn.Linear(4, 3)
+    red = GradBucketReducer(lin.parameters(), num_buckets=1)
+    assert all(grad_buf_of(p) is p._stgcn_grad_buf for p in lin.parameters())
+    lin(torch.randn(2, 4)).sum().backward()
+    red.finish()
+    g1 = [p.grad.clone() for p in lin.parameters()]
+    assert all(p.grad.data_ptr() == p._stgcn_grad_buf.data_ptr() for p in lin.parameters())        # adopted into the bucket
+    assert all(grad_buf_of(p) is None for p in lin.parameters())                                    # a gradient exists now
+    lin.zero_grad(set_to_none=False)
+    assert all(grad_buf_of(p) is None for p in lin.parameters())
+    lin(torch.randn(2, 4)).sum().backward()
+    red.finish()
+    assert all(torch.isfinite(p.grad).all() for p in lin.parameters())
+    lin.zero_grad(set_to_none=True)
+    assert all(grad_buf_of(p) is p._stgcn_grad_buf for p in lin.parameters())
+    red.remove()
+    assert all(grad_buf_of(p) is None for p in lin.parameters()) and g1 is not None
