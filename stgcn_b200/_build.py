@@ -34,9 +34,11 @@ def have_nvcc():
 
 
 def _digest(paths):
+    # file NAMES and contents only: the repository sits under a different absolute path on the GPU box, and a digest over
+    # absolute paths made every process there consider the shipped library stale and rebuild it (8 ranks at once)
     h = hashlib.sha256()
-    for p in sorted(paths):
-        h.update(p.encode())
+    for p in sorted(paths, key=os.path.basename):
+        h.update(os.path.basename(p).encode())
         with open(p, 'rb') as f:
             h.update(f.read())
     h.update(' '.join(NVCC_FLAGS).encode())
@@ -62,10 +64,24 @@ def is_fresh():
 
 
 def build(force=False, verbose=False):
-    """Compile every .cu for sm_100a and link the shared library. Returns its path."""
+    """Compile every .cu for sm_100a and link the shared library. Returns its path.  Safe against concurrent callers (the
+    ranks of one torchrun job): one process builds under a file lock, the others wait and find the result fresh; the library is
+    linked to a temporary name and moved into place atomically."""
     if not force and is_fresh():
         return LIB
+    import fcntl
     os.makedirs(OBJ, exist_ok=True)
+    with open(os.path.join(OBJ, '.build.lock'), 'w') as lockf:
+        fcntl.flock(lockf, fcntl.LOCK_EX)
+        try:
+            if not force and is_fresh():          # somebody else built it while we waited
+                return LIB
+            return _build_locked(verbose)
+        finally:
+            fcntl.flock(lockf, fcntl.LOCK_UN)
+
+
+def _build_locked(verbose):
     nvcc = _nvcc()
 
     def compile_one(src):
@@ -80,10 +96,12 @@ def build(force=False, verbose=False):
 
     with cf.ThreadPoolExecutor(max_workers=min(8, os.cpu_count() or 1)) as ex:
         objs = list(ex.map(compile_one, sources()))
-    cmd = [nvcc, '-shared', '-gencode', 'arch=compute_100a,code=sm_100a', '-o', LIB] + objs
+    tmp = LIB + '.tmp.%d' % os.getpid()
+    cmd = [nvcc, '-shared', '-gencode', 'arch=compute_100a,code=sm_100a', '-o', tmp] + objs
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError('link failed:\n%s\n%s' % (r.stdout, r.stderr))
+    os.replace(tmp, LIB)                        # atomic: a process loading the library never sees a half-written file
     with open(LIB + '.stamp', 'w') as f:
         f.write(_digest(sources() + headers()))
     return LIB

@@ -108,3 +108,20 @@ def test_training_tail_and_input_entry_points_validate_arguments_without_gpu():
     assert lib.stgcn_collate_pad_augment(_lib.F32, 2, 10, 25, 3, None, None, None, None, None, None) != 0
     assert b'collate_pad_augment' in lib.stgcn_last_error()
     assert lib.stgcn_collate_pad_augment(_lib.F32, 0, 10, 25, 3, None, None, None, None, None, None) == 0
+
+
+def test_build_digest_does_not_depend_on_where_the_repository_lives(tmp_path):
+    """The GPU box unpacks the repository under another path; a digest over absolute paths made every process there rebuild the
+    shipped library (8 torchrun ranks at once).  Same file names + contents => same digest, wherever they are."""
+    from stgcn_b200 import _build
+    a, b = tmp_path / 'a', tmp_path / 'b' / 'deeper'
+    a.mkdir(); b.mkdir(parents=True)
+    for d in (a, b):
+        (d / 'k.cu').write_text('__global__ void k() {}\n')
+        (d / 'h.cuh').write_text('#pragma once\n')
+    da = _build._digest([str(a / 'k.cu'), str(a / 'h.cuh')])
+    db = _build._digest([str(b / 'h.cuh'), str(b / 'k.cu')])
+    assert da == db
+    (b / 'k.cu').write_text('__global__ void k() { }\n')
+    assert _build._digest([str(b / 'h.cuh'), str(b / 'k.cu')]) != da
+    assert _build.is_fresh()          # the library in the tree matches its sources (built by __graft_entry__.build())
