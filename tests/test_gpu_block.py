@@ -13,7 +13,7 @@ import numpy as np
 import pytest
 import torch
 
-from _helpers import block_case_names, check_dx_kink_tolerant, load_golden, params_from_golden, rel_err
+from _helpers import bf16_grad_bound, block_case_names, check_dx_kink_tolerant, load_golden, params_from_golden, rel_err
 from oracle import stgcn_oracle as O
 
 pytestmark = pytest.mark.gpu
@@ -45,19 +45,18 @@ def test_fp32_block_matches_reference_golden(name):
     p = params_from_golden(g)
     m = build_block(ci, co, torch.tensor(g['A_init']), s, bool(res), p)
     y, dx, grads = run_block(m, torch.tensor(g['x']), torch.tensor(g['gy']), bool(training))
-    big_a = float(np.abs(g['A_init']).max()) > 100
-    tol = 2e-3 if big_a else TOL_F32
+    tol = TOL_F32            # also with the reference's own ~1e5-magnitude adjacency (measured on B200: 7e-6 .. 2.5e-5)
     assert rel_err(y, g['y']) < tol
-    assert rel_err(dx, g['dx']) < tol * 3
+    assert rel_err(dx, g['dx']) < tol
     for k, v in grads.items():
         ref = g['g.' + k]
         if training and not res and k == 'temporalConv.bias':
             assert float(v.abs().max()) < 1e-6 * float(np.abs(g['gy']).sum())
             continue
-        assert rel_err(v.reshape(ref.shape), ref) < tol * 3, k
+        assert rel_err(v.reshape(ref.shape), ref) < tol, k
     sd = m.state_dict()
     for k in ('batch_n.running_mean', 'batch_n.running_var', 'batch_n_2.running_mean', 'batch_n_2.running_var'):
-        assert rel_err(sd[k], g['post.' + k]) < (1e-3 if big_a else TOL_F32), k
+        assert rel_err(sd[k], g['post.' + k]) < TOL_F32, k
     if training:
         assert int(sd['batch_n.num_batches_tracked']) == int(g['post.batch_n.num_batches_tracked'])
 
@@ -106,6 +105,7 @@ def test_block_matches_oracle(case, training, dtype):
     gy = torch.randn(N, co, T_out, V)
     cfg = O.BlockCfg(ci, co, 9, s, 4, 0.0, res)
     y_ref, dx_ref, g_ref, p_after = oracle_block(x, gy, p, cfg, training)
+    g32, dx32 = g_ref, dx_ref
     y, dx, grads = run_block(m, x, gy, training)
     tol = TOL_F32 if dtype == torch.float32 else TOL_BF16
     assert rel_err(y, y_ref) < tol            # forward: against the plain fp32 oracle in both precisions
@@ -113,20 +113,26 @@ def test_block_matches_oracle(case, training, dtype):
         # gradients: against the oracle with bf16 storage emulation (matched ReLU masks, see oracle docstring)
         y_ref, dx_ref, g_ref, p_after = oracle_block(x, gy, p, cfg, training, bf16=True)
         assert rel_err(y, y_ref) < tol
-    kinks = check_dx_kink_tolerant(dx, dx_ref, tol * 2)
+    kinks = check_dx_kink_tolerant(dx, dx_ref, tol if dtype == torch.float32 else bf16_grad_bound(tol, dx_ref, dx32))
     # ReLU-kink flips seen directly on the output mask: a pre-activation within one bf16 ulp of zero may take the
     # other branch (fp32 accumulation order differs).  They must be rare (<= 1e-4 of the elements); each one moves a
     # whole (c_out, :, :) slice of the temporal weight gradient by |gy * S| / rows, which on these tiny test
     # tensors (a few hundred rows) is several percent of max|grad| -- measured 7e-2 with 2 flips of 82944.
     flips = int(((y > 0) != (y_ref > 0)).sum())
     assert flips <= max(2, int(1e-4 * y.numel())), flips
-    ptol = tol * 2 if (kinks == 0 and flips == 0) else (5e-2 if flips == 0 else 1e-1)
     for k, v in grads.items():
         ref = g_ref[k]
         if training and not res and k == 'temporalConv.bias':
             assert float(v.abs().max()) <= 1e-5 * float(gy.abs().sum())
             continue
-        assert rel_err(v.reshape(ref.shape), ref) < ptol, k
+        # fp32: the stated 1e-4.  bf16: the stated 2e-2, or this tensor's measured emulation-vs-fp32 distance if that is larger
+        # (_helpers.bf16_grad_bound); a ReLU flip on these tiny tensors moves a weight-gradient slice by several percent
+        bound = tol if dtype == torch.float32 else bf16_grad_bound(tol, ref, g32[k])
+        if dtype == torch.float32 and (kinks or flips):
+            # an fp32 kink flip (counted above: at most 2) moves one element's gradient by O(1); on these tensors of a few hundred
+            # rows that is percents of max|grad| (measured 2.0e-2 on spatialConv.A with T = 20); everything else stays at 1e-4
+            bound = 5e-2
+        assert rel_err(v.reshape(ref.shape), ref) < bound, (k, bound)
     if training:
         sd = m.state_dict()
         for k in ('batch_n.running_mean', 'batch_n.running_var', 'batch_n_2.running_mean', 'batch_n_2.running_var'):
@@ -182,10 +188,10 @@ def test_spatial_conv_module_matches_oracle():
     ref = O.spatial_conv(xr, Ar, W, b)
     (ref * go.cpu()).sum().backward()
     assert rel_err(out, ref) < TOL_F32
-    assert rel_err(xg.grad, xr.grad) < TOL_F32 * 2
-    assert rel_err(m.A.grad, Ar.grad) < TOL_F32 * 2
-    assert rel_err(m.W.weight.grad, W.grad) < TOL_F32 * 2
-    assert rel_err(m.W.bias.grad, b.grad) < TOL_F32 * 2
+    assert rel_err(xg.grad, xr.grad) < TOL_F32
+    assert rel_err(m.A.grad, Ar.grad) < TOL_F32
+    assert rel_err(m.W.weight.grad, W.grad) < TOL_F32
+    assert rel_err(m.W.bias.grad, b.grad) < TOL_F32
 
 
 @pytest.mark.parametrize('training', [True, False])
@@ -208,18 +214,18 @@ def test_first_block_without_input_gradient(training):
     (y.float() * gy.cuda()).sum().backward()
     grads = {k: v.grad.detach().cpu() for k, v in m.named_parameters() if v.grad is not None}
     cfg = O.BlockCfg(ci, co, 9, s, 4, 0.0, False)
+    _, _, g32, _ = oracle_block(x, gy, p, cfg, training)
     y_ref, _, g_ref, _ = oracle_block(x, gy, p, cfg, training, bf16=True)
     y = y.detach().float().cpu()
     assert rel_err(y, y_ref) < TOL_BF16
     flips = int(((y > 0) != (y_ref > 0)).sum())
     assert flips <= max(2, int(1e-4 * y.numel())), flips
-    ptol = TOL_BF16 * 2 if flips == 0 else 1e-1
     for k, v in grads.items():
         ref = g_ref[k]
         if training and k == 'temporalConv.bias':
             assert float(v.abs().max()) <= 1e-5 * float(gy.abs().sum())
             continue
-        assert rel_err(v.reshape(ref.shape), ref) < ptol, k
+        assert rel_err(v.reshape(ref.shape), ref) < bf16_grad_bound(TOL_BF16, ref, g32[k]), k
 
 
 def test_prepared_inference_tracks_parameter_changes():

@@ -14,7 +14,7 @@ import numpy as np
 import pytest
 import torch
 
-from _helpers import check_dx_kink_tolerant, rel_err
+from _helpers import bf16_grad_bound, check_dx_kink_tolerant, rel_err
 from oracle import stgcn_oracle as O
 from test_gpu_block import build_block, oracle_block, run_block
 
@@ -51,6 +51,7 @@ def test_cfg2_block_full_frames_matches_oracle(case, dtype):
     cfg = O.BlockCfg(ci, co, 9, s, 4, 0.0, False)
     tol = 1e-4 if dtype == torch.float32 else 2e-2
     y_ref, dx_ref, g_ref, _ = oracle_block(x, gy, p, cfg, True)
+    g32, dx32 = g_ref, dx_ref
     y, dx, grads = run_block(m, x, gy, True)
     assert y.shape == (N, co, T_out, V)
     assert rel_err(y, y_ref) < tol
@@ -61,13 +62,17 @@ def test_cfg2_block_full_frames_matches_oracle(case, dtype):
     # plain fp32 sum); each flip reaches the 9 input frames of its temporal taps, so that many dx frames may be off per flip
     flips = int(((y > 0) != (y_ref > 0)).sum())
     assert flips <= max(2, int(1e-4 * y.numel())), flips
-    kinks = check_dx_kink_tolerant(dx, dx_ref, tol * 2, max_frames=9 * max(2, flips + 1))
-    ptol = tol * 2 if (kinks == 0 and flips == 0) else 5e-2
+    kinks = check_dx_kink_tolerant(dx, dx_ref, tol if dtype == torch.float32 else bf16_grad_bound(tol, dx_ref, dx32),
+                                   max_frames=9 * max(2, flips + 1))
     for k, v in grads.items():
         if k == 'temporalConv.bias':            # a bias in front of a batch-statistics BatchNorm has zero gradient
             assert float(v.abs().max()) <= 1e-5 * float(gy.abs().sum())
             continue
-        assert rel_err(v.reshape(g_ref[k].shape), g_ref[k]) < ptol, k
+        if dtype == torch.float32:              # stated 1e-4; when kink flips were counted above (fp32 split path: ~1e-6 of the
+            bound = tol if (kinks == 0 and flips == 0) else 2e-2      # elements), the remainder is bounded at 2e-2 (measured 3.5e-3)
+        else:                                   # stated 2e-2, or this tensor's measured emulation-vs-fp32 distance if larger
+            bound = bf16_grad_bound(tol, g_ref[k], g32[k])
+        assert rel_err(v.reshape(g_ref[k].shape), g_ref[k]) < bound, (k, bound)
 
 
 def _hparams(classes, partitioning):
@@ -104,7 +109,7 @@ def test_full_size_inference_matches_oracle_and_is_batch_independent(V, K, class
     assert big.shape == (n_big, classes)
     ref = O.model_forward(x[:2], state, O.stack_cfgs(3, 9, 0.0, False), False)
     tol = 1e-4 if dtype == torch.float32 else 2e-2
-    assert rel_err(small, ref) < tol * (10 if dtype == torch.float32 else 2.5)     # same bound as the small-shape model test
+    assert rel_err(small, ref) < tol        # measured on B200: bf16 5.8e-4
     if dtype == torch.float32:
         assert np.array_equal(small.argmax(1).numpy(), ref.argmax(1).numpy())
     # eval-mode outputs do not depend on the batch a sequence is in (different tiling, same arithmetic per row)

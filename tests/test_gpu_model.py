@@ -65,7 +65,7 @@ def test_model_matches_oracle_sane_A(dtype, tol):
     cfgs = O.stack_cfgs(3, 9, 0.0, False)
     ref = O.model_forward(x, state, cfgs, True)
     got = model(x.cuda())
-    assert rel_err(got, ref) < tol * (1 if dtype == torch.float32 else 2.5)
+    assert rel_err(got, ref) < tol            # measured on B200: fp32 ~1e-6, bf16 4.8e-3
     if dtype == torch.float32:
         assert np.array_equal(got.argmax(1).cpu().numpy(), ref.argmax(1).numpy())
     # eval after the running stats moved once
@@ -73,7 +73,7 @@ def test_model_matches_oracle_sane_A(dtype, tol):
     with torch.no_grad():
         got_e = model(x.cuda())
         ref_e = O.model_forward(x, state, cfgs, False)
-    assert rel_err(got_e, ref_e) < tol * (10 if dtype == torch.float32 else 2.5)
+    assert rel_err(got_e, ref_e) < tol        # measured: bf16 6.4e-4
 
 
 def test_state_dict_round_trip_and_adam_step():

@@ -17,7 +17,7 @@ import numpy as np
 import pytest
 import torch
 
-from _helpers import assert_argmax_consistent, check_dx_kink_tolerant, rel_err
+from _helpers import assert_argmax_consistent, bf16_grad_bound, check_dx_kink_tolerant, rel_err
 from oracle import stgcn_oracle as O
 from test_gpu_block import build_block, oracle_block, run_block
 
@@ -76,21 +76,22 @@ def test_dropout_replayed_mask_matches_oracle(dtype, residual):
 
     tol = TOL[dtype]
     y_ref, dx_ref, g_ref = oracle(False)
+    g32, dx32 = g_ref, dx_ref
     assert rel_err(y, y_ref) < tol
     dropped_only = float(((y == 0) & (keep == 0)).float().sum() / (keep == 0).float().sum())
     assert dropped_only == 1.0
     if dtype == torch.bfloat16:
         y_ref, dx_ref, g_ref = oracle(True)
         assert rel_err(y, y_ref) < tol
-    kinks = check_dx_kink_tolerant(dx, dx_ref, tol * 2)
+    kinks = check_dx_kink_tolerant(dx, dx_ref, tol if dtype == torch.float32 else bf16_grad_bound(tol, dx_ref, dx32))
     flips = int((((y > 0) != (y_ref > 0)) & (keep > 0)).sum())
     assert flips <= max(2, int(1e-4 * y.numel())), flips
-    ptol = tol * 2 if (kinks == 0 and flips == 0) else 1e-1
     for k, v in grads.items():
         if not residual and k == 'temporalConv.bias':
             assert float(v.abs().max()) <= 1e-5 * float(gy.abs().sum())
             continue
-        assert rel_err(v.reshape(g_ref[k].shape), g_ref[k]) < ptol, k
+        bound = (tol if (kinks == 0 and flips == 0) else 5e-2) if dtype == torch.float32 else bf16_grad_bound(tol, g_ref[k], g32[k])
+        assert rel_err(v.reshape(g_ref[k].shape), g_ref[k]) < bound, (k, bound)
     # a second call draws a different mask; eval mode drops nothing
     y2, _, _ = run_block(m, x, gy, True)
     assert float(((y2 == 0) != (y == 0)).float().mean()) > 0.2
@@ -239,17 +240,18 @@ def test_residual_block_full_frames_matches_oracle(case, dtype):
     cfg = O.BlockCfg(ci, co, 9, s, 4, 0.0, True)
     tol = TOL[dtype]
     y_ref, dx_ref, g_ref, _ = oracle_block(x, gy, p, cfg, True)
+    g32, dx32 = g_ref, dx_ref
     y, dx, grads = run_block(m, x, gy, True)
     assert rel_err(y, y_ref) < tol
     if dtype == torch.bfloat16:
         y_ref, dx_ref, g_ref, _ = oracle_block(x, gy, p, cfg, True, bf16=True)
         assert rel_err(y, y_ref) < tol
-    kinks = check_dx_kink_tolerant(dx, dx_ref, tol * 2, max_frames=20)
+    kinks = check_dx_kink_tolerant(dx, dx_ref, tol if dtype == torch.float32 else bf16_grad_bound(tol, dx_ref, dx32), max_frames=20)
     flips = int(((y > 0) != (y_ref > 0)).sum())
     assert flips <= max(2, int(1e-4 * y.numel())), flips
-    ptol = tol * 2 if (kinks == 0 and flips == 0) else 5e-2
     for k, v in grads.items():
-        assert rel_err(v.reshape(g_ref[k].shape), g_ref[k]) < ptol, k
+        bound = (tol if (kinks == 0 and flips == 0) else 2e-2) if dtype == torch.float32 else bf16_grad_bound(tol, g_ref[k], g32[k])
+        assert rel_err(v.reshape(g_ref[k].shape), g_ref[k]) < bound, (k, bound)
 
 
 # ---------------------------------------------------------------------------------------------------------------------
