@@ -52,9 +52,26 @@ class L_STGCN(nn.Module):
         self.fc_layer = nn.Linear(256, hparams.nr_classes).float()
         self.softmax = nn.Softmax(dim=1)
         self.compute_dtype = compute_dtype
+        # Beyond the reference (its own TODO at lightning_model.py:52 / st_graphconv.py:129), opt-in with
+        # hparams.edge_importance_mode = 'learnable': the masks are what is learned -- every forward uses A_base * Masks[i] as the
+        # block's adjacency, Masks[i] receive dA (.) A_base, and spatialConv.A is a frozen base.  Default 'reference': A * Mask is
+        # baked into a detached trainable spatialConv.A at construction and the masks never get a gradient, as in the reference.
+        self.edge_importance_mode = getattr(hparams, 'edge_importance_mode', 'reference')
+        if self.edge_importance_mode == 'learnable':
+            if not hparams.use_edge_importance:
+                raise ValueError("edge_importance_mode='learnable' needs use_edge_importance=True")
+            with torch.no_grad():
+                for b in self.conv:
+                    b.spatialConv.A.copy_(A.float())          # the base graph, without the mask baked in
+                    b.spatialConv.A.requires_grad_(False)
+        elif self.edge_importance_mode != 'reference':
+            raise ValueError('edge_importance_mode must be "reference" or "learnable"')
 
     def forward(self, x):
         x = x.permute(0, 3, 1, 2)                 # (N,T,V,C) -> logical (N,C,T,V): already channels-last in memory
+        if self.edge_importance_mode == 'learnable':
+            for b, mk in zip(self.conv, self.Masks):
+                b._A_override = b.spatialConv.A.detach() * mk        # (K,V,V) element-wise: the only torch op, outside the chain
         _prepare(self.conv, x)
         x = self.conv(x)
         return Fn.head_forward(x, self.fc_layer.weight, self.fc_layer.bias)

@@ -54,7 +54,7 @@ def prepare_training_operands(blocks, n, t, device):
         if nbytes:
             if b._train_prep is None or b._train_prep.numel() != nbytes or b._train_prep.device != device:
                 b._train_prep = torch.empty(nbytes, dtype=torch.uint8, device=device)
-            params[i].A = sc.A.data_ptr()
+            params[i].A = (b._A_override if b._A_override is not None else sc.A).data_ptr()
             params[i].Wt = b.temporalConv.weight.data_ptr()
             preps[i] = b._train_prep.data_ptr()
             b._tp_fresh = True
@@ -124,6 +124,7 @@ class SpatialTemporalConv(nn.Module):
         # non-persistent: the state_dict keeps the reference's keys
         self.register_buffer('_rng_state', None, persistent=False)
         self._prep_cache = {}      # frozen-parameter inference operands (functional._BlockFn), keyed by tensor versions
+        self._A_override = None    # effective adjacency of this forward when the model learns edge-importance masks
         self._train_prep = None    # weight-only training operands (prepare_training_operands), refreshed every training forward
         self._tp_fresh = False
 
@@ -135,9 +136,12 @@ class SpatialTemporalConv(nn.Module):
 
     def forward(self, f_in):
         sc, tc, b1, b2 = self.spatialConv, self.temporalConv, self.batch_n, self.batch_n_2
-        params = [b1.weight, b1.bias, sc.A, sc.W.weight.view(sc.K * sc.C_out, sc.C_in), sc.W.bias,
+        # learnable edge importance (model.py, beyond the reference): the model hands in A_base * Mask for this forward
+        A_eff = self._A_override if self._A_override is not None else sc.A
+        params = [b1.weight, b1.bias, A_eff, sc.W.weight.view(sc.K * sc.C_out, sc.C_in), sc.W.bias,
                   tc.weight.view(self.C_out, self.C_out, self.gamma), tc.bias, b2.weight, b2.bias]
-        raw = [b1.weight, b1.bias, sc.A, sc.W.weight, sc.W.bias, tc.weight, tc.bias, b2.weight, b2.bias]
+        raw = [b1.weight, b1.bias, sc.A if self._A_override is None else None, sc.W.weight, sc.W.bias, tc.weight, tc.bias,
+               b2.weight, b2.bias]
         if self._res_mode == L.RES_CONV:
             params += [self.apply_residual.weight.view(self.C_out, self.C_in), self.apply_residual.bias]
             raw += [self.apply_residual.weight, self.apply_residual.bias]
