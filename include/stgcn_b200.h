@@ -253,6 +253,10 @@ int32_t stgcn_timing_classes(void);
 const char* stgcn_timing_class_name(int32_t cls);
 int32_t stgcn_timing_read(int32_t cls, double* ms, double* work, uint64_t* launches);
 
+/* sizeof of the library's own view of a boundary struct: which = 0 StgcnBlockDesc, 1 StgcnBlockParams, 2 StgcnBlockGrads (else 0).
+ * A binding compares it with its mirror of the struct at load time. */
+size_t stgcn_abi_sizeof(int32_t which);
+
 /* Number of CUDA kernels this library has launched in this process (bench's gpu_launches). */
 uint64_t stgcn_launch_count(void);
 const char* stgcn_last_error(void);

@@ -97,6 +97,11 @@ def _declare(lib):
     lib.stgcn_timing_class_name.restype = C.c_char_p; lib.stgcn_timing_class_name.argtypes = [i32]
     lib.stgcn_timing_read.restype = i32
     lib.stgcn_timing_read.argtypes = [i32, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_uint64)]
+    lib.stgcn_abi_sizeof.restype = sz; lib.stgcn_abi_sizeof.argtypes = [i32]
+    for which, struct in enumerate((BlockDesc, BlockParams, BlockGrads)):
+        if lib.stgcn_abi_sizeof(which) != C.sizeof(struct):
+            raise RuntimeError('stgcn_b200: %s is %d bytes here but %d in libstgcn_b200.so (stale library or binding)'
+                               % (struct.__name__, C.sizeof(struct), lib.stgcn_abi_sizeof(which)))
     lib.stgcn_launch_count.restype = u64; lib.stgcn_launch_count.argtypes = []
     lib.stgcn_last_error.restype = C.c_char_p; lib.stgcn_last_error.argtypes = []
     lib.stgcn_version.restype = C.c_char_p; lib.stgcn_version.argtypes = []

@@ -1150,6 +1150,9 @@ int32_t stgcn_spatial_forward_static(const StgcnBlockDesc* d, const void* x, con
   return spatial_only_fwd<bf16>(*d, (const bf16*)x, A, W, Wb, (bf16*)out, ws, st);
 }
 
+size_t stgcn_abi_sizeof(int32_t which) {
+  return which == 0 ? sizeof(StgcnBlockDesc) : which == 1 ? sizeof(StgcnBlockParams) : which == 2 ? sizeof(StgcnBlockGrads) : 0;
+}
 uint64_t stgcn_launch_count(void) { return g_launches.load(); }
 int32_t stgcn_dropout_mask(uint64_t seed, uint64_t offset, float p, size_t count, float* out, void* stream) {
   if (!out) { set_error("dropout_mask: null output"); return STGCN_ERR_INVALID; }

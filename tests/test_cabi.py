@@ -125,3 +125,12 @@ def test_build_digest_does_not_depend_on_where_the_repository_lives(tmp_path):
     (b / 'k.cu').write_text('__global__ void k() { }\n')
     assert _build._digest([str(b / 'h.cuh'), str(b / 'k.cu')]) != da
     assert _build.is_fresh()          # the library in the tree matches its sources (built by __graft_entry__.build())
+
+
+def test_ctypes_structs_have_the_library_s_sizes():
+    from stgcn_b200 import _lib
+    lib = _lib.lib()
+    assert lib.stgcn_abi_sizeof(0) == C.sizeof(_lib.BlockDesc) == 13 * 4 + 3 * 4 + 2 * 8
+    assert lib.stgcn_abi_sizeof(1) == C.sizeof(_lib.BlockParams) == 19 * 8
+    assert lib.stgcn_abi_sizeof(2) == C.sizeof(_lib.BlockGrads) == 11 * 8
+    assert lib.stgcn_abi_sizeof(7) == 0
