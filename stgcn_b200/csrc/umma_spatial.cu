@@ -11,13 +11,20 @@
 // and once per tile  S -> + bias2d' -> bf16 -> TMA store.  The N x K x C x T x V intermediate of the reference (and
 // the K*C_in-wide aggregated tensor of the unfused chain) never goes through HBM in inference.
 // Warp roles: 0 = TMA producer, 1 = MMA issuer (both products, software-pipelined), 2..5 / 6..9 = two epilogue groups.
+#include <stdlib.h>
+
 #include "kernels.cuh"
 #include "umma_common.cuh"
 
 namespace stgcn {
 using namespace umma;
 
-constexpr int kSpThreads = 320;          // TMA warp, MMA warp, 2 x 4 epilogue warps
+constexpr int kSpThreads = 320;          // TMA warp, MMA warp, 2 x 4 epilogue warps  (SUB = 1)
+// SUB = 2: every 64-column chunk is split between two sets of four warps (32 columns each), 2 x 8 epilogue warps.  The kernel is
+// bound by the LATENCY of the TMEM -> bf16 -> shared-memory conversion between its two products, which a
+// thread then does for 32 instead of 64 values.
+constexpr int sp_threads(int sub) { return 64 + 2 * 128 * sub; }
+constexpr int kSpDefaultSub = 1;
 constexpr int kSpTile = 128 * 128;          // one [128 rows][64 bf16] tile image
 
 struct SpParams {
@@ -32,7 +39,8 @@ struct SpParams {
   const float* b2d;            // [V][Co] joint bias table bias2d' (bias2d_fold_kernel)
 };
 
-__global__ void __launch_bounds__(kSpThreads, 1)
+template <int SUB>
+__global__ void __launch_bounds__(sp_threads(SUB), 1)
 spatial_fused_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_big,
                      const __grid_constant__ CUtensorMap map_w, const __grid_constant__ CUtensorMap map_xa,
                      const __grid_constant__ CUtensorMap map_out, const __grid_constant__ SpParams p) {
@@ -58,14 +66,14 @@ spatial_fused_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_con
   {  // padding rows of the activation tiles (never written by TMA) must be finite: they meet BigA's zero columns
     uint4* z = reinterpret_cast<uint4*>(smem_x);
     const int n16 = (p.xs + 2) * kSpTile / 16;
-    for (int i = threadIdx.x; i < n16; i += kSpThreads) z[i] = make_uint4(0, 0, 0, 0);
+    for (int i = threadIdx.x; i < n16; i += sp_threads(SUB)) z[i] = make_uint4(0, 0, 0, 0);
   }
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&map_x); prefetch_tmap(&map_big); prefetch_tmap(&map_w); prefetch_tmap(&map_xa); prefetch_tmap(&map_out);
     for (int s = 0; s < p.xs; ++s) { mbar_init(xfull + s, 1); mbar_init(xempty + s, 1); }
     for (int s = 0; s < p.wst; ++s) { mbar_init(wfull + s, 1); mbar_init(wempty + s, 1); }
-    for (int a = 0; a < 2; ++a) { mbar_init(tfull + a, 1); mbar_init(tempty + a, 128); mbar_init(pfull + a, 1); mbar_init(pempty + a, 1); }
-    for (int a = 0; a < 2; ++a) { mbar_init(sfull + a, 1); mbar_init(sempty + a, 256); }
+    for (int a = 0; a < 2; ++a) { mbar_init(tfull + a, 1); mbar_init(tempty + a, 128 * SUB); mbar_init(pfull + a, 1); mbar_init(pempty + a, 1); }
+    for (int a = 0; a < 2; ++a) { mbar_init(sfull + a, 1); mbar_init(sempty + a, 256 * SUB); }
     mbar_init(big_bar, 1);
     fence_barrier_init();
   }
@@ -166,13 +174,15 @@ spatial_fused_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_con
     // ===================== epilogue warps: group 0 = warps 2..5 (even chunks, T[0] / P[0]), group 1 = warps 6..9 (odd) ====
     // Two independent 128-thread pipelines, each owning one accumulator / operand buffer pair, so that the latencies of one
     // (TMEM load, proxy fence, barriers) hide behind the other.
-    const int grp = (warp - 2) / 4;
-    const int q = warp % 4, row = q * 32 + lane, et = threadIdx.x - 64 - grp * 128;
+    constexpr int GT = 128 * SUB;                    // threads per epilogue group
+    const int grp = (warp - 2) / (4 * SUB);
+    const int sub = ((warp - 2) / 4) % SUB;           // which 32-column half of a chunk this warp converts (SUB = 2)
+    const int q = warp % 4, row = q * 32 + lane, et = threadIdx.x - 64 - grp * GT;
     const int vv = row % p.v;
     const int bar_a = 1 + grp * 2, bar_b = 2 + grp * 2;
-    auto gsync = [&](int id) { asm volatile("bar.sync %0, 128;" ::"r"(id) : "memory"); };
+    auto gsync = [&](int id) { asm volatile("bar.sync %0, %1;" ::"r"(id), "n"(GT) : "memory"); };
     const int b2_ld = p.co + 4;                     // row pitch (floats): 16-byte rows, conflict-free across joints
-    for (int i = et; i < p.v * p.co; i += 128) b2_tab[(i / p.co) * b2_ld + (i % p.co)] = __ldg(p.b2d + i);   // both groups write the same values
+    for (int i = et; i < p.v * p.co; i += GT) b2_tab[(i / p.co) * b2_ld + (i % p.co)] = __ldg(p.b2d + i);   // both groups write the same values
     gsync(bar_a);
     const float* const my_b2 = b2_tab + (row < p.ft * p.v ? vv : 0) * b2_ld;
     int g = 0;
@@ -189,8 +199,12 @@ spatial_fused_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_con
         mbar_wait(tfull + grp, use);
         tc_fence_after();
         uint32_t r0[32], r1[32];
-        tmem_ld_32x32(t_tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(grp * 64), r0);
-        tmem_ld_32x32(t_tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(grp * 64 + 32), r1);
+        if (SUB == 1) {
+          tmem_ld_32x32(t_tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(grp * 64), r0);
+          tmem_ld_32x32(t_tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(grp * 64 + 32), r1);
+        } else {
+          tmem_ld_32x32(t_tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(grp * 64 + sub * 32), r0);
+        }
         tmem_ld_wait();
         tc_fence_before();
         mbar_arrive(tempty + grp);                              // the aggregation accumulator may be overwritten
@@ -199,8 +213,9 @@ spatial_fused_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_con
         mbar_wait(pempty + grp, use ^ 1);
         uint8_t* pb = my_p + row * 128;
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          const uint32_t* r = j < 4 ? r0 + j * 8 : r1 + (j - 4) * 8;
+        for (int jj = 0; jj < 8 / SUB; ++jj) {
+          const int j = SUB == 1 ? jj : sub * 4 + jj;          // 16-byte chunk of the row this thread writes
+          const uint32_t* r = SUB == 1 ? (jj < 4 ? r0 + jj * 8 : r1 + (jj - 4) * 8) : r0 + jj * 8;
           uint4 u;
           __nv_bfloat162 h0 = __floats2bfloat162_rn(__uint_as_float(r[0]), __uint_as_float(r[1]));
           __nv_bfloat162 h1 = __floats2bfloat162_rn(__uint_as_float(r[2]), __uint_as_float(r[3]));
@@ -227,18 +242,24 @@ spatial_fused_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_con
         if (et == 0) tma_store_wait_read<0>();                  // XA store / previous output chunk done reading the buffer
         gsync(bar_a);
         uint32_t r2[2][32];                                     // both 32-column halves in flight before the first use
-        tmem_ld_32x32(s_cur + ((uint32_t)(q * 32) << 16) + (uint32_t)(ch * 64), r2[0]);
-        tmem_ld_32x32(s_cur + ((uint32_t)(q * 32) << 16) + (uint32_t)(ch * 64 + 32), r2[1]);
+        if (SUB == 1) {
+          tmem_ld_32x32(s_cur + ((uint32_t)(q * 32) << 16) + (uint32_t)(ch * 64), r2[0]);
+          tmem_ld_32x32(s_cur + ((uint32_t)(q * 32) << 16) + (uint32_t)(ch * 64 + 32), r2[1]);
+        } else {
+          tmem_ld_32x32(s_cur + ((uint32_t)(q * 32) << 16) + (uint32_t)(ch * 64 + sub * 32), r2[0]);       // fixed slot: no dynamic register indexing
+        }
         tmem_ld_wait();
 #pragma unroll
         for (int half = 0; half < 2; ++half) {
+          if (SUB == 2 && half != sub) continue;
+          const uint32_t (&rr)[32] = r2[SUB == 1 ? half : 0];
           const float4* b2 = reinterpret_cast<const float4*>(my_b2 + ch * 64 + half * 32);
           float f[32];
 #pragma unroll
           for (int g4 = 0; g4 < 8; ++g4) {
             const float4 t4 = b2[g4];
-            f[g4 * 4 + 0] = __uint_as_float(r2[half][g4 * 4 + 0]) + t4.x; f[g4 * 4 + 1] = __uint_as_float(r2[half][g4 * 4 + 1]) + t4.y;
-            f[g4 * 4 + 2] = __uint_as_float(r2[half][g4 * 4 + 2]) + t4.z; f[g4 * 4 + 3] = __uint_as_float(r2[half][g4 * 4 + 3]) + t4.w;
+            f[g4 * 4 + 0] = __uint_as_float(rr[g4 * 4 + 0]) + t4.x; f[g4 * 4 + 1] = __uint_as_float(rr[g4 * 4 + 1]) + t4.y;
+            f[g4 * 4 + 2] = __uint_as_float(rr[g4 * 4 + 2]) + t4.z; f[g4 * 4 + 3] = __uint_as_float(rr[g4 * 4 + 3]) + t4.w;
           }
 #pragma unroll
           for (int g4 = 0; g4 < 4; ++g4) {
@@ -331,13 +352,18 @@ int32_t launch_spatial_fused(const bf16* x, int nb, int t, int v, int ci, int co
     uint64_t dims[2] = {(uint64_t)k * ci, (uint64_t)co}; uint64_t str[1] = {(uint64_t)k * ci * 2}; uint32_t box[2] = {64, (uint32_t)pl.wn};
     STGCN_TRY(make_tmap_bf16(&map_w, w2p, 2, dims, str, box));
   }
+  // STGCN_SPATIAL_SUB=1 | 2: epilogue warps per 64-column chunk (see sp_threads); default chosen by same-box A/B
+  static const int sub = [] { const char* v = getenv("STGCN_SPATIAL_SUB"); return (v && v[0] == '1') ? 1 : ((v && v[0] == '2') ? 2 : kSpDefaultSub); }();
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(spatial_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    cudaError_t e = cudaFuncSetAttribute(spatial_fused_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(spatial_fused_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     if (e != cudaSuccess) { set_error("cudaFuncSetAttribute failed: %s", cudaGetErrorString(e)); return STGCN_ERR_CUDA; }
     attr_set = true;
   }
-  launch_k(spatial_fused_kernel, std::min(p.total_tiles, num_sms_sp()), kSpThreads, pl.smem, st, map_x, map_big, map_w, map_xa, map_out, p);
+  const int grid = std::min(p.total_tiles, num_sms_sp());
+  if (sub == 2) launch_k(spatial_fused_kernel<2>, grid, sp_threads(2), pl.smem, st, map_x, map_big, map_w, map_xa, map_out, p);
+  else launch_k(spatial_fused_kernel<1>, grid, sp_threads(1), pl.smem, st, map_x, map_big, map_w, map_xa, map_out, p);
   STGCN_CHECK_LAUNCH("spatial_fused");
   return STGCN_OK;
 }

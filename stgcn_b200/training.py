@@ -47,10 +47,15 @@ class CapturedTrainStep:
         side = torch.cuda.Stream(device=dev)
         side.wait_stream(torch.cuda.current_stream(dev))
         import warnings
-        with torch.cuda.stream(side), warnings.catch_warnings(record=True) as caught:
-            warnings.simplefilter('always')
-            for _ in range(n_warm):
-                self._eager_step()
+        warn_always = torch.is_warn_always_enabled()
+        torch.set_warn_always(True)        # the stream-mismatch warning is a once-per-process C++ warning otherwise
+        try:
+            with torch.cuda.stream(side), warnings.catch_warnings(record=True) as caught:
+                warnings.simplefilter('always')
+                for _ in range(n_warm):
+                    self._eager_step()
+        finally:
+            torch.set_warn_always(warn_always)
         torch.cuda.current_stream(dev).wait_stream(side)
         stale = any('AccumulateGrad' in str(w.message) and 'stream' in str(w.message) for w in caught)
         for w in caught:
