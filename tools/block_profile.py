@@ -4,7 +4,7 @@ import torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from stgcn_b200 import SpatialTemporalConv, _lib
 ci, co, s, T, res = int(sys.argv[1]), int(sys.argv[2]), int(sys.argv[3]), int(sys.argv[4]), int(sys.argv[5])
-n, v, k = 128, 25, 3
+n, v, k = (int(sys.argv[6]) if len(sys.argv) > 6 else 128), 25, 3
 torch.manual_seed(0)
 with contextlib.redirect_stdout(io.StringIO()):
     m = SpatialTemporalConv(ci, co, torch.randn(k, v, v) * 0.2, 9, s, 4, dropout_rate=0, residual=bool(res), compute_dtype=torch.bfloat16).cuda().train()
@@ -20,6 +20,6 @@ l0 = _lib.launch_count()
 for _ in range(5): step()
 torch.cuda.synchronize(); _lib.timing_enable(False)
 prof = _lib.timing_read()
-print('block %d->%d s%d T%d res=%d: launches/step %d' % (ci, co, s, T, res, (_lib.launch_count() - l0) // 5))
+print('block %d->%d s%d T%d res=%d n=%d: launches/step %d' % (ci, co, s, T, res, n, (_lib.launch_count() - l0) // 5))
 for kname, (ms, work, cnt) in sorted(prof.items(), key=lambda kv: -kv[1][0]):
-    print('  %-16s %7.3f ms/step  %3d launches/step' % (kname, ms / 5, cnt // 5))
+    print('  %-16s %7.3f ms/step  %3d launches/step  %7.2f us per sample' % (kname, ms / 5, cnt // 5, ms / 5 * 1e3 / n))
