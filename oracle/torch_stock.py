@@ -11,7 +11,8 @@ as the product:
     L_STGCN.forward              /root/reference/src/lightning_model.py:91-112  (permute, 10 blocks, avg_pool2d, Linear)
 
 The reference itself cannot travel to the GPU box (/root/reference does not exist there); tests/test_oracle_golden.py pins
-THIS module's forward against the fixtures generated from the unmodified reference.  Nothing in stgcn_b200/ imports it.
+THIS module's forward against the fixtures generated from the unmodified reference.  Nothing in stgcn_b200/ imports it; its users are tests/test_oracle_golden.py (the pin), bench.py (`--impl reference`,
+`cpu_baseline`, `torch_gpu_baseline`) and tools/bench_block.py (the same comparator per block, BASELINE cfg2).
 """
 import torch
 import torch.nn as nn
