@@ -1,7 +1,7 @@
 """Model-level parity of the path bench.py times: bf16, the full 10-block stack, one TRAINING step at BASELINE cfg4's
-per-GPU shape (32 sequences x 2 persons = N_eff 64, T = 300, V = 25, K = 3, 60 classes), eager and through
-CapturedTrainStep, with a sane-magnitude adjacency and with the reference's own normalised adjacency (entries ~6e4,
-adjacency.py:161-183).
+per-GPU shape (32 sequences x 2 persons = N_eff 64, T = 300, V = 25, K = 3, 60 classes), with a sane-magnitude adjacency and
+with the reference's own normalised adjacency (entries ~6e4, adjacency.py:161-183), and at cfg5's per-GPU shape (128 sequences =
+N_eff 256, V = 18, 400 classes, the OpenPose-18 graph bench.py uses); eager and through CapturedTrainStep.
 
 Train-mode BatchNorm couples every row of the batch, so the oracle has to see the whole batch.  It is the same CPU
 restatement (oracle/stgcn_oracle.py: plain torch tensor formulas, device-agnostic), evaluated here on the GPU box's device
@@ -35,20 +35,27 @@ from _helpers import assert_argmax_consistent, rel_err
 from oracle import stgcn_oracle as O
 
 pytestmark = pytest.mark.gpu
-N_SEQ, M, T, V, K, CLASSES = 32, 2, 300, 25, 3, 60
+M, T, K = 2, 300, 3
 TOL = 2e-2
+# (sequences per GPU, V, classes): BASELINE cfg4 (NTU shape, 32 per GPU) and cfg5 (Kinetics-skeleton shape, V = 18, 400 classes,
+# 128 per GPU = N 1024 at 8 GPUs, with the OpenPose-18 graph bench.py uses)
+WORKLOADS = {'cfg4': (32, 25, 60), 'cfg5': (128, 18, 400)}
 
 
-def _hp():
+def _hp(V, CLASSES):
     return argparse.Namespace(C_in=3, nr_classes=CLASSES, gamma=9, dropout_rate=0.0, residual=False, use_edge_importance=False,
                               max_mask_jitter=0.001, partitioning=2, d=1, distance_file=None,
                               distances=np.random.RandomState(0).rand(V))
 
 
-def _adjacency(kind):
+def _adjacency(kind, V):
+    from stgcn_b200 import graph
     if kind == 'sane':
         return torch.randn(K, V, V, generator=torch.Generator().manual_seed(0)) * 0.2
-    from stgcn_b200 import graph
+    if kind == 'openpose18':
+        A = graph.get_normalized_adjacency_matrices(graph.Strategy.SPATIAL_CONFIGURATION, 1, distances=np.random.RandomState(0).rand(V),
+                                                    skeleton='openpose18', dense_alpha=False)
+        return A / A.abs().max()
     A = graph.get_normalized_adjacency_matrices(2, 1, distances=np.random.RandomState(0).rand(V))     # SPATIAL, d=1
     assert A.shape == (K, V, V) and float(A.abs().max()) > 1e4            # the reference's dense-alpha normalisation
     return A
@@ -69,15 +76,16 @@ def _oracle_step(x, labels, state, bf16):
     return float(loss), logits.detach().cpu(), {k: v.grad.detach().cpu() for k, v in leaves.items() if v.grad is not None}
 
 
-@pytest.mark.parametrize('adjacency', ['sane', 'reference'])
-def test_cfg4_bf16_training_step_matches_oracle(adjacency):
+@pytest.mark.parametrize('workload,adjacency', [('cfg4', 'sane'), ('cfg4', 'reference'), ('cfg5', 'openpose18')])
+def test_bf16_training_step_matches_oracle_at_full_shape(workload, adjacency):
     from stgcn_b200 import CapturedTrainStep, L_STGCN, cross_entropy
     from stgcn_b200.optim import Adam
+    N_SEQ, V, CLASSES = WORKLOADS[workload]
     torch.backends.cuda.matmul.allow_tf32 = False
     torch.backends.cudnn.allow_tf32 = False
     torch.manual_seed(0)
-    A = _adjacency(adjacency)
-    model = L_STGCN(_hp(), compute_dtype=torch.bfloat16, A=A).cuda().train()
+    A = _adjacency(adjacency, V)
+    model = L_STGCN(_hp(V, CLASSES), compute_dtype=torch.bfloat16, A=A).cuda().train()
     g = torch.Generator().manual_seed(100)
     x = torch.randn(N_SEQ * M, T, V, 3, generator=g).cuda()
     labels = torch.randint(0, CLASSES, (N_SEQ * M,), generator=g).cuda()
@@ -104,7 +112,7 @@ def test_cfg4_bf16_training_step_matches_oracle(adjacency):
     # ---- the checker -------------------------------------------------------------------------------------------------
     loss32, logits32, g32 = _oracle_step(x.float(), labels, state, bf16=False)
     loss16, logits16, g16 = _oracle_step(x.float(), labels, state, bf16=True)
-    report = {'adjacency': adjacency, 'max_abs_A': float(A.abs().max()),
+    report = {'workload': workload, 'n_eff': N_SEQ * M, 'V': V, 'classes': CLASSES, 'adjacency': adjacency, 'max_abs_A': float(A.abs().max()),
               'logits_vs_fp32': rel_err(got_logits, logits32), 'logits_vs_emulation': rel_err(got_logits, logits16),
               'emulation_logits_vs_fp32': rel_err(logits16, logits32),
               'loss': loss_eager, 'loss_fp32': loss32, 'loss_emulation': loss16, 'grads': {}}
@@ -160,7 +168,7 @@ def test_cfg4_bf16_training_step_matches_oracle(adjacency):
     report['captured_vs_eager_state'] = cap_err
 
     os.makedirs('gpurun_out', exist_ok=True)
-    with open(os.path.join('gpurun_out', 'cfg4_parity_%s.json' % adjacency), 'w') as f:
+    with open(os.path.join('gpurun_out', '%s_parity_%s.json' % (workload, adjacency)), 'w') as f:
         json.dump(report, f, indent=1)
     print(json.dumps({k: v for k, v in report.items() if k != 'grads'}))
     assert report['logits_vs_fp32'] < TOL, report['logits_vs_fp32']
