@@ -87,6 +87,18 @@ typedef struct StgcnBlockParams {
   /* Optional (NULL = derive inside the call): the block's weight-only training operands as written by stgcn_train_prep_multi --
    * valid for as long as A and temporalConv.weight are unchanged.  Pass the same pointer to forward and backward. */
   const void* train_prep;
+  /* Optional SyncBN (global-batch BatchNorm statistics under data parallel; no reference counterpart -- the reference is single
+   * process -- SURVEY.md 8(f)-4).  When sync_allreduce != NULL and sync_world > 1, every training-mode BatchNorm of the block uses
+   * the statistics of the batch over ALL ranks: at each of its four exchange points (BatchNorm-1 / -2, forward and backward) the
+   * library writes the 2*C local sums to sync_buf (device, >= 2 * max(C_in, C_out) floats), calls sync_allreduce(sync_user, stream)
+   * -- which must enqueue an in-place SUM all-reduce of sync_buf over the ranks on `stream` (e.g. ncclAllReduce, or
+   * torch.distributed.all_reduce with that stream current) and return without synchronising -- and continues from the global
+   * sums with sync_world times the local row count.  Parameter gradients stay local sums (the data-parallel gradient all-reduce
+   * completes them).  Every rank must make the same calls in the same order. */
+  float* sync_buf;
+  void (*sync_allreduce)(void* user, void* stream);
+  void* sync_user;
+  int64_t sync_world;
 } StgcnBlockParams;
 
 /* Parameter gradients (fp32, overwritten).  Same shapes as the parameters. */

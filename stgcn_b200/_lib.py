@@ -30,7 +30,14 @@ class BlockParams(C.Structure):
     _fields_ = [(n, _P) for n in ('bn1_weight', 'bn1_bias', 'bn1_running_mean', 'bn1_running_var',
                                   'bn1_num_batches_tracked', 'A', 'W', 'W_bias', 'Wt', 'Wt_bias', 'bn2_weight',
                                   'bn2_bias', 'bn2_running_mean', 'bn2_running_var', 'bn2_num_batches_tracked',
-                                  'Wr', 'Wr_bias', 'rng_state', 'train_prep')]
+                                  'Wr', 'Wr_bias', 'rng_state', 'train_prep', 'sync_buf', 'sync_allreduce', 'sync_user')] \
+        + [('sync_world', C.c_int64)]
+
+    def set_sync(self, sync):
+        """Fill the optional SyncBN fields from a parallel.SyncBatchNormLink (None: leave them zero = local statistics)."""
+        if sync is not None:
+            self.sync_buf, self.sync_allreduce, self.sync_user, self.sync_world = sync.buf.data_ptr(), sync.fn_ptr, None, sync.world
+        return self
 
 
 class BlockGrads(C.Structure):

@@ -164,6 +164,37 @@ static SideLane* side_lane() {
   return l.ok ? &l : nullptr;
 }
 
+// ---- SyncBN: global-batch BatchNorm sums through the caller's all-reduce (StgcnBlockParams.sync_*) --------------------------------
+struct SyncCtx {
+  float* buf = nullptr; void (*fn)(void*, void*) = nullptr; void* user = nullptr; int world = 1; cudaStream_t st = nullptr;
+  bool on() const { return fn != nullptr && buf != nullptr && world > 1; }
+  void allreduce() const { fn(user, (void*)st); }          // enqueues on st, does not synchronise
+};
+static SyncCtx sync_of(const StgcnBlockDesc& d, const StgcnBlockParams& P, cudaStream_t st, bool dry) {
+  SyncCtx s;
+  if (!dry && d.training && P.sync_allreduce && P.sync_buf && P.sync_world > 1) {
+    s.buf = P.sync_buf; s.fn = P.sync_allreduce; s.user = P.sync_user; s.world = (int)P.sync_world; s.st = st;
+  }
+  return s;
+}
+// training-mode statistics -> coefficient table; over all ranks when sync is on
+static int32_t finalize_stats(const SyncCtx& sy, const float* partials, int nblk, int C, double rows, const float* gamma, const float* beta,
+                              float* rm, float* rv, long long* nbt, float eps, float momentum, float* stats, cudaStream_t st) {
+  if (!sy.on()) return launch_bn_finalize(partials, nblk, C, rows, gamma, beta, rm, rv, nbt, eps, momentum, stats, st);
+  STGCN_TRY(launch_reduce_partials(partials, nblk, C, sy.buf, st));
+  sy.allreduce();
+  return launch_bn_finalize(sy.buf, 1, C, rows * sy.world, gamma, beta, rm, rv, nbt, eps, momentum, stats, st);
+}
+// BatchNorm-backward sums: parameter gradients from the LOCAL sums, the sums the apply pass uses over all ranks when sync is on
+static int32_t finalize_bwd_sums(const SyncCtx& sy, const float* partials, int nblk, int C, float* sums_local, float* dgamma, float* dbeta,
+                                 cudaStream_t st, const float** sums_use, double* count_scale) {
+  float* dst = sy.on() ? sy.buf : sums_local;
+  STGCN_TRY(launch_bn_bwd_finalize(partials, nblk, C, dst, dgamma, dbeta, st));
+  if (sy.on()) sy.allreduce();
+  *sums_use = dst; *count_scale = sy.on() ? (double)sy.world : 1.0;
+  return STGCN_OK;
+}
+
 // ---- GEMM dispatch: tcgen05 engine for bf16 when the shape fits, else CUDA cores ----
 template <class T> struct Engine {
   const StgcnBlockDesc& d; Arena& ws; cudaStream_t st;
@@ -316,6 +347,7 @@ template <class T> struct Bn1Fold {      // backward of the folded BatchNorm-1 (
   float* packed_m = nullptr;    // split-K accumulator of the mixing weight gradient carved by the caller (folded path)
   bool zeroed = false;          // dA, t1_buf and packed_m were already cleared by an earlier kernel of the chain
   bool bias_grads_done = false; // dW_bias and the rank-1 part of dA were already issued by the caller (side lane)
+  const SyncCtx* sync = nullptr; // SyncBN: the dx-correction coefficients come from sums over all ranks
 };
 template <class T>
 static int32_t spatial_fwd(Engine<T>& e, const Dims& m, const T* x, const float* aff_a, const float* aff_b, int relu1,
@@ -476,6 +508,11 @@ static int32_t spatial_bwd(Engine<T>& e, const Dims& m, const T* x, const float*
       if (!merged) STGCN_TRY(launch_agg_dA_umma(dXA, x, m.n, m.t, m.v, m.ci, m.k, dA, e.st));
       STGCN_TRY(launch_bn1_fold_grads(W, dW, bf->stats, t1, umma_agg_rowsum_q(prep, m.k), m.k, m.v, m.co, m.ci, bf->training,
                                       (double)m.rows_in, bf->dgamma, bf->dbeta, coef, e.st));
+      if (bf->sync && bf->sync->on() && bf->dx) {      // dbeta / dgamma stay local; the coefficients use their sums over all ranks
+        STGCN_TRY(launch_pack2(bf->dbeta, bf->dgamma, m.ci, bf->sync->buf, e.st));
+        bf->sync->allreduce();
+        STGCN_TRY(launch_bn1_coef_global(bf->stats, bf->sync->buf, m.ci, (double)m.rows_in * bf->sync->world, coef, e.st));
+      }
       if (bf->dx) STGCN_TRY(launch_agg_bwd_umma(dXA, m.n, m.t, m.v, m.ci, m.k, prep, nullptr, bf->dx, e.st, x, coef, merged ? dA : nullptr));
       if (!bf->bias_grads_done) STGCN_TRY(launch_spatial_bias_grads(t1, A, Wb, m.k, m.v, m.co, dWb, dA, e.st, wbb));
       return STGCN_OK;
@@ -547,6 +584,7 @@ static int32_t block_forward_t(const StgcnBlockDesc& d, const T* x, const StgcnB
   const bool res = d.residual != STGCN_RES_NONE;
   const int relu1 = res ? 1 : 0;
   int nblk = 0;
+  const SyncCtx sy = sync_of(d, P, st, ws.dry);
   const bool drop = d.training && d.dropout_p > 0.f;
   if (!ws.dry) {
     if (!ws.ok()) { set_error("workspace too small"); return STGCN_ERR_WORKSPACE; }
@@ -557,8 +595,8 @@ static int32_t block_forward_t(const StgcnBlockDesc& d, const T* x, const StgcnB
       const float* part1 = partials;
       if (x_cs && x_cs_n > 0) { part1 = x_cs; nblk = x_cs_n; }
       else STGCN_TRY(launch_colstats<T>(x, m.rows_in, m.ci, partials, &nblk, st));
-      STGCN_TRY(launch_bn_finalize(part1, nblk, m.ci, (double)m.rows_in, P.bn1_weight, P.bn1_bias, P.bn1_running_mean,
-                                   P.bn1_running_var, (long long*)P.bn1_num_batches_tracked, d.bn_eps, d.bn_momentum, S.stats1, st));
+      STGCN_TRY(finalize_stats(sy, part1, nblk, m.ci, (double)m.rows_in, P.bn1_weight, P.bn1_bias, P.bn1_running_mean,
+                               P.bn1_running_var, (long long*)P.bn1_num_batches_tracked, d.bn_eps, d.bn_momentum, S.stats1, st));
     } else {
       STGCN_TRY(launch_bn_eval_coeffs(m.ci, P.bn1_weight, P.bn1_bias, P.bn1_running_mean, P.bn1_running_var, d.bn_eps, S.stats1, st));
     }
@@ -599,8 +637,8 @@ static int32_t block_forward_t(const StgcnBlockDesc& d, const T* x, const StgcnB
       if (d.training) {
         if (fused_stats) nblk = umma_conv_gemm_grid(gt);
         else STGCN_TRY(launch_colstats<T>(U, m.rows_out, m.co, partials, &nblk, st));
-        STGCN_TRY(launch_bn_finalize(partials, nblk, m.co, (double)m.rows_out, P.bn2_weight, P.bn2_bias, P.bn2_running_mean,
-                                     P.bn2_running_var, (long long*)P.bn2_num_batches_tracked, d.bn_eps, d.bn_momentum, S.stats2, st));
+        STGCN_TRY(finalize_stats(sy, partials, nblk, m.co, (double)m.rows_out, P.bn2_weight, P.bn2_bias, P.bn2_running_mean,
+                                 P.bn2_running_var, (long long*)P.bn2_num_batches_tracked, d.bn_eps, d.bn_momentum, S.stats2, st));
       } else {
         STGCN_TRY(launch_bn_eval_coeffs(m.co, P.bn2_weight, P.bn2_bias, P.bn2_running_mean, P.bn2_running_var, d.bn_eps, S.stats2, st));
       }
@@ -619,8 +657,8 @@ static int32_t block_forward_t(const StgcnBlockDesc& d, const T* x, const StgcnB
     if (!ws.ok()) { set_error("workspace too small"); return STGCN_ERR_WORKSPACE; }
     if (d.training) {
       STGCN_TRY(launch_colstats<T>(S.S, m.rows_in, m.co, partials, &nblk, st));
-      STGCN_TRY(launch_bn_finalize(partials, nblk, m.co, (double)m.rows_in, P.bn2_weight, P.bn2_bias, P.bn2_running_mean,
-                                   P.bn2_running_var, (long long*)P.bn2_num_batches_tracked, d.bn_eps, d.bn_momentum, S.stats2, st));
+      STGCN_TRY(finalize_stats(sy, partials, nblk, m.co, (double)m.rows_in, P.bn2_weight, P.bn2_bias, P.bn2_running_mean,
+                               P.bn2_running_var, (long long*)P.bn2_num_batches_tracked, d.bn_eps, d.bn_momentum, S.stats2, st));
     } else {
       STGCN_TRY(launch_bn_eval_coeffs(m.co, P.bn2_weight, P.bn2_bias, P.bn2_running_mean, P.bn2_running_var, d.bn_eps, S.stats2, st));
     }
@@ -722,6 +760,8 @@ static int32_t block_backward_t(const StgcnBlockDesc& d, const T* x, const T* y,
       wd_on_lane = lane != nullptr;
     }
   }
+  const SyncCtx sy = sync_of(d, P, st, ws.dry);
+  const float* sums_use = nullptr; double cscale = 1.0;
   ZeroJobs zj;
   if (!res) {
     if (packed_t) zj.add(packed_t, umma_wgrad_workspace_floats(g_wt));
@@ -735,8 +775,9 @@ static int32_t block_backward_t(const StgcnBlockDesc& d, const T* x, const T* y,
       static const bool no_zj = getenv("STGCN_NO_ZEROJOBS") != nullptr;      // A/B switch: one memset node per accumulator
       STGCN_TRY(launch_bn_bwd_reduce<T>(dy, S.U, S.stats2, m.rows_out, m.co, 1, p, 0, 0, partials, &nblk, st, no_zj ? nullptr : &zj, p > 0.f ? S.rng : nullptr));
       if (!zj.done) for (int j = 0; j < zj.count; ++j) cudaMemsetAsync(zj.p[j], 0, sizeof(float) * zj.n[j], st);
-      STGCN_TRY(launch_bn_bwd_finalize(partials, nblk, m.co, sums2, G.bn2_weight, G.bn2_bias, st));
-      STGCN_TRY(launch_bn_bwd_apply<T>(dy, S.U, S.stats2, sums2, m.rows_out, m.co, 1, d.training, p, 0, 0, dU, st, p > 0.f ? S.rng : nullptr));
+      STGCN_TRY(finalize_bwd_sums(sy, partials, nblk, m.co, sums2, G.bn2_weight, G.bn2_bias, st, &sums_use, &cscale));
+      STGCN_TRY(launch_bn_bwd_apply<T>(dy, S.U, S.stats2, sums_use, m.rows_out, m.co, 1, d.training, p, 0, 0, dU, st, p > 0.f ? S.rng : nullptr,
+                                       nullptr, cscale));
       if (!d.training) STGCN_TRY(launch_colsum<T>(dU, m.rows_out, m.co, partials, G.Wt_bias, st));
     } else {
       STGCN_TRY(launch_relu_bwd<T>(dy, y, m.rows_out * m.co, p, dU, st));
@@ -786,10 +827,11 @@ static int32_t block_backward_t(const StgcnBlockDesc& d, const T* x, const T* y,
   }
   if (res && !ws.dry) {
     STGCN_TRY(launch_bn_bwd_reduce<T>(dTin, S.S, S.stats2, m.rows_in, m.co, 1, 0.f, 0, 0, partials, &nblk, st));
-    STGCN_TRY(launch_bn_bwd_finalize(partials, nblk, m.co, sums2, G.bn2_weight, G.bn2_bias, st));
-    STGCN_TRY(launch_bn_bwd_apply<T>(dTin, S.S, S.stats2, sums2, m.rows_in, m.co, 1, d.training, 0.f, 0, 0, dS, st));
+    STGCN_TRY(finalize_bwd_sums(sy, partials, nblk, m.co, sums2, G.bn2_weight, G.bn2_bias, st, &sums_use, &cscale));
+    STGCN_TRY(launch_bn_bwd_apply<T>(dTin, S.S, S.stats2, sums_use, m.rows_in, m.co, 1, d.training, 0.f, 0, 0, dS, st, nullptr, nullptr, cscale));
   }
   Bn1Fold<T> bf{S.stats1, d.training, G.bn1_weight, G.bn1_bias, dx, false, S.XA, &S.fp, t1_ready ? t1 : nullptr};
+  bf.sync = &sy;
   bf.t1_buf = t1; bf.packed_m = packed_m; bf.zeroed = folded && !t1_from_epilogue; bf.bias_grads_done = side_bias_grads;      // (with STGCN_FUSED_VSUM t1 is cleared right before its producer)
   STGCN_TRY(spatial_bwd<T>(e, m, x, S.stats1 + 2 * m.ci, S.stats1 + 3 * m.ci, relu1, P.A, P.W, P.W_bias, dS, dh, G.A, G.W, G.W_bias, &bf));
   // Gradient of the skip connection (st_graphconv.py:71,81): it reaches dx as an addend of the last BatchNorm-1 backward pass
@@ -812,9 +854,9 @@ static int32_t block_backward_t(const StgcnBlockDesc& d, const T* x, const T* y,
   }
   if (!ws.dry && own_pass) {
     STGCN_TRY(launch_bn_bwd_reduce<T>(dh, x, S.stats1, m.rows_in, m.ci, 0, 0.f, 0, 0, partials, &nblk, st));
-    STGCN_TRY(launch_bn_bwd_finalize(partials, nblk, m.ci, sums1, G.bn1_weight, G.bn1_bias, st));
-    if (dx) STGCN_TRY(launch_bn_bwd_apply<T>(dh, x, S.stats1, sums1, m.rows_in, m.ci, 0, d.training, 0.f, 0, 0, dx, st, nullptr,
-                                             ra.ptr ? &ra : nullptr));
+    STGCN_TRY(finalize_bwd_sums(dx ? sy : SyncCtx{}, partials, nblk, m.ci, sums1, G.bn1_weight, G.bn1_bias, st, &sums_use, &cscale));
+    if (dx) STGCN_TRY(launch_bn_bwd_apply<T>(dh, x, S.stats1, sums_use, m.rows_in, m.ci, 0, d.training, 0.f, 0, 0, dx, st, nullptr,
+                                             ra.ptr ? &ra : nullptr, cscale));
   } else if (!ws.dry && dx && ra.ptr) {              // (not reached today: the folded path excludes residual blocks)
     set_error("block_backward: skip-connection gradient without a BatchNorm-1 backward pass"); return STGCN_ERR_UNSUPPORTED;
   }

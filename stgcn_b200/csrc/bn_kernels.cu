@@ -565,12 +565,12 @@ __global__ void __launch_bounds__(256, 3) bn_bwd_apply_fast_kernel(const T* __re
 template <class T>
 int32_t launch_bn_bwd_apply(const T* dy, const T* z, const float* stats, const float* sums, long long rows, int C,
                             int relu, int training, float p, uint64_t seed, uint64_t offset, T* dz, cudaStream_t st,
-                            const uint64_t* rng, const ResAddend<T>* addend) {
+                            const uint64_t* rng, const ResAddend<T>* addend, double count_scale) {
   const ResAddend<T> ra = addend ? *addend : ResAddend<T>();
   KernelTimer kt_(KC_ELEMWISE, (double)rows * C, st);
   long long total = rows * C;
   float inv_keep = p > 0.f ? 1.f / (1.f - p) : 1.f;
-  float inv_m = 1.0f / (float)rows;
+  float inv_m = (float)(1.0 / ((double)rows * count_scale));      // count_scale = ranks when `sums` are global (SyncBN)
   if (p == 0.f && elementwise_fast_ok<T>(total, C)) {
     // one wave: the kernel keeps 3 CTAs per SM (launch bounds), and every extra wave repeats the per-column constant loads
     // (measured on B200: 444 CTAs 0.666 ms per step for the ten launches, 888: 0.681, 1184: 0.702)
@@ -587,8 +587,8 @@ int32_t launch_bn_bwd_apply(const T* dy, const T* z, const float* stats, const f
   STGCN_CHECK_LAUNCH("bn_bwd_apply");
   return STGCN_OK;
 }
-template int32_t launch_bn_bwd_apply<float>(const float*, const float*, const float*, const float*, long long, int, int, int, float, uint64_t, uint64_t, float*, cudaStream_t, const uint64_t*, const ResAddend<float>*);
-template int32_t launch_bn_bwd_apply<bf16>(const bf16*, const bf16*, const float*, const float*, long long, int, int, int, float, uint64_t, uint64_t, bf16*, cudaStream_t, const uint64_t*, const ResAddend<bf16>*);
+template int32_t launch_bn_bwd_apply<float>(const float*, const float*, const float*, const float*, long long, int, int, int, float, uint64_t, uint64_t, float*, cudaStream_t, const uint64_t*, const ResAddend<float>*, double);
+template int32_t launch_bn_bwd_apply<bf16>(const bf16*, const bf16*, const float*, const float*, long long, int, int, int, float, uint64_t, uint64_t, bf16*, cudaStream_t, const uint64_t*, const ResAddend<bf16>*, double);
 
 // ---------------------------------------------------------------------------
 // dz = dy * [out > 0] * (1/(1-p) if dropout)    -- backward of the trailing
@@ -663,6 +663,50 @@ int32_t launch_add_inplace(T* d, const T* s, size_t n, cudaStream_t st) {
 }
 template int32_t launch_add_inplace<float>(float*, const float*, size_t, cudaStream_t);
 template int32_t launch_add_inplace<bf16>(bf16*, const bf16*, size_t, cudaStream_t);
+
+// ---------------------------------------------------------------------------
+// SyncBN support (global-batch BatchNorm statistics under data parallel; no reference counterpart): the sums a
+// BatchNorm needs are brought into ONE [2][C] row that the caller's callback all-reduces over the ranks.
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(kFinThreads) reduce_partials_kernel(const float* __restrict__ partials, int nblk, int C, float* __restrict__ out) {
+  pdl_enter();
+  double s1, s2;
+  if (!reduce_partials_32x32(partials, nblk, C, s1, s2)) return;
+  const int c = blockIdx.x * 32 + (threadIdx.x & 31);
+  out[c] = (float)s1; out[C + c] = (float)s2;
+}
+int32_t launch_reduce_partials(const float* partials, int nblk, int C, float* out, cudaStream_t st) {
+  launch_k(reduce_partials_kernel, cdiv(C, 32), kFinThreads, 0, st, partials, nblk, C, out);
+  STGCN_CHECK_LAUNCH("reduce_partials");
+  return STGCN_OK;
+}
+// out = [a | b]  (two C-vectors side by side)
+__global__ void pack2_kernel(const float* __restrict__ a, const float* __restrict__ b, int C, float* __restrict__ out) {
+  pdl_enter();
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c < C) { out[c] = a[c]; out[C + c] = b[c]; }
+}
+int32_t launch_pack2(const float* a, const float* b, int C, float* out, cudaStream_t st) {
+  launch_k(pack2_kernel, cdiv(C, 128), 128, 0, st, a, b, C, out);
+  STGCN_CHECK_LAUNCH("pack2");
+  return STGCN_OK;
+}
+// folded BatchNorm-1 backward (agg_kernels.cu, bn1_fold_grads): the dx-correction coefficients from GLOBAL sums
+//   g = [sum dbeta | sum dgamma] over all ranks, inv_m = 1 / global row count:  coef = { mean, a*db/m, a*invstd*dg/m }
+__global__ void bn1_coef_global_kernel(const float* __restrict__ stats, const float* __restrict__ g, int C, float inv_m, float* __restrict__ coef) {
+  pdl_enter();
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  const float a = stats[2 * C + c], invstd = stats[C + c];
+  coef[c] = stats[c];
+  coef[C + c] = a * g[c] * inv_m;
+  coef[2 * C + c] = a * invstd * g[C + c] * inv_m;
+}
+int32_t launch_bn1_coef_global(const float* stats, const float* g, int C, double rows_global, float* coef, cudaStream_t st) {
+  launch_k(bn1_coef_global_kernel, cdiv(C, 128), 128, 0, st, stats, g, C, (float)(1.0 / rows_global), coef);
+  STGCN_CHECK_LAUNCH("bn1_coef_global");
+  return STGCN_OK;
+}
 
 // ---------------------------------------------------------------------------
 // fp32 -> split bf16: x = hi + mid + lo with hi = bf16(x), mid = bf16(x - hi), lo = bf16(x - hi - mid) (24 significand bits

@@ -84,7 +84,10 @@ template <class T> int32_t launch_bn_bwd_reduce(const T* dy, const T* z, const f
 int32_t launch_bn_bwd_finalize(const float* partials, int nblk, int C, float* sums, float* dgamma, float* dbeta, cudaStream_t st);
 template <class T> int32_t launch_bn_bwd_apply(const T* dy, const T* z, const float* stats, const float* sums, long long rows, int C,
                                               int relu, int training, float p, uint64_t seed, uint64_t offset, T* dz, cudaStream_t st,
-                                              const uint64_t* rng = nullptr, const ResAddend<T>* addend = nullptr);
+                                              const uint64_t* rng = nullptr, const ResAddend<T>* addend = nullptr, double count_scale = 1.0);
+int32_t launch_reduce_partials(const float* partials, int nblk, int C, float* out, cudaStream_t st);
+int32_t launch_pack2(const float* a, const float* b, int C, float* out, cudaStream_t st);
+int32_t launch_bn1_coef_global(const float* stats, const float* g, int C, double rows_global, float* coef, cudaStream_t st);
 int32_t launch_rng_fetch(uint64_t* state, uint64_t seed, uint64_t offset, uint64_t advance, uint64_t* slot, cudaStream_t st);
 int32_t launch_dropout_mask(uint64_t seed, uint64_t offset, float p, size_t n, float* out, cudaStream_t st);
 template <class T> int32_t launch_relu_bwd(const T* dy, const T* out, long long total, float p, T* dz, cudaStream_t st);

@@ -81,7 +81,7 @@ class _BlockFn(torch.autograd.Function):
         P = L.BlockParams(L.ptr(_f32(bn1_w)), L.ptr(_f32(bn1_b)), L.ptr(rm1), L.ptr(rv1), L.ptr(nbt1),
                           L.ptr(_f32(A)), L.ptr(_f32(W)), L.ptr(_f32(Wb)), L.ptr(_f32(Wt)), L.ptr(_f32(bt)),
                           L.ptr(_f32(bn2_w)), L.ptr(_f32(bn2_b)), L.ptr(rm2), L.ptr(rv2), L.ptr(nbt2),
-                          L.ptr(_f32(Wr)), L.ptr(_f32(Wrb)), L.ptr(cfg.get('rng_state')), L.ptr(cfg.get('train_prep')))
+                          L.ptr(_f32(Wr)), L.ptr(_f32(Wrb)), L.ptr(cfg.get('rng_state')), L.ptr(cfg.get('train_prep'))).set_sync(cfg.get('sync'))
         y = torch.empty((n, t_out, v, cfg['c_out']), dtype=dt, device=x.device)
         saved = None
         if need_grad:
@@ -125,6 +125,7 @@ class _BlockFn(torch.autograd.Function):
         if need_grad:
             ctx.d = d
             ctx.grad_bufs = cfg.get('grad_bufs')
+            ctx.sync = cfg.get('sync')                    # SyncBN link (parallel.enable_sync_batchnorm): backward exchanges sums too
             ctx.train_prep = cfg.get('train_prep')        # the same weight-only operands must reach backward (and stay alive)
             ctx.buffers = buffers
             ctx.x_dtype = x.dtype
@@ -141,7 +142,7 @@ class _BlockFn(torch.autograd.Function):
         dyp = _to_ntvc(gy, y.dtype)
         P = L.BlockParams(L.ptr(bn1_w), L.ptr(bn1_b), L.ptr(rm1), L.ptr(rv1), L.ptr(nbt1), L.ptr(A), L.ptr(W),
                           L.ptr(Wb), L.ptr(Wt), L.ptr(bt), L.ptr(bn2_w), L.ptr(bn2_b), L.ptr(rm2), L.ptr(rv2),
-                          L.ptr(nbt2), L.ptr(Wr), L.ptr(Wrb), None, L.ptr(ctx.train_prep))
+                          L.ptr(nbt2), L.ptr(Wr), L.ptr(Wrb), None, L.ptr(ctx.train_prep)).set_sync(ctx.sync)
         # gradients go straight into the data-parallel reducer's bucket slices when there are any (parallel.GradBucketReducer)
         gb = ctx.grad_bufs or [None] * 11
         g = {k: _grad_out(v, gb[i]) for i, (k, v) in enumerate((('bn1_w', bn1_w), ('bn1_b', bn1_b), ('A', A), ('W', W), ('Wb', Wb),

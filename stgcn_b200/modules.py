@@ -127,6 +127,7 @@ class SpatialTemporalConv(nn.Module):
         self._A_override = None    # effective adjacency of this forward when the model learns edge-importance masks
         self._train_prep = None    # weight-only training operands (prepare_training_operands), refreshed every training forward
         self._tp_fresh = False
+        self._sync = None          # SyncBN link (parallel.enable_sync_batchnorm): training statistics over all ranks
 
     def _ensure_rng(self, device):
         """Create the device-resident dropout generator on first use: seeded once from torch's CPU generator (so
@@ -162,6 +163,8 @@ class SpatialTemporalConv(nn.Module):
                'rng_state': self._rng_state if p_drop > 0 else None,
                'grad_bufs': [Fn.grad_buf_of(q) for q in raw],
                'flags': self.flags, 'prep_cache': self._prep_cache}
+        if self._sync is not None and self.training:
+            cfg['sync'] = self._sync.on(f_in.device, max(self.C_in, self.C_out))
         if need_grad and f_in.is_cuda:
             if not self._tp_fresh:          # stand-alone use: prepare for this block alone (models do it for the whole stack)
                 prepare_training_operands([self], f_in.shape[0], f_in.shape[2], f_in.device)

@@ -7,11 +7,14 @@ blocks 9-7, which finish first), the last one holds only the early blocks (~7 %)
 when backward ends is small.  The library's backward writes each gradient straight into its slice of a bucket
 (`p.grad` IS the slice -- no pack / unpack copies); as soon as every gradient of a bucket has been produced the
 bucket is all-reduced on a side stream (NCCL `AVG`, so no separate divide) while the remaining backward
-kernels keep running.  BatchNorm statistics stay per replica (PyTorch DDP default).  Inference needs no
+kernels keep running.  BatchNorm statistics stay per replica by default (PyTorch DDP default);
+enable_sync_batchnorm() switches the blocks to global-batch statistics (SyncBN).  Inference needs no
 collective.  Works with backend 'gloo' on CPU tensors for tests (SUM + divide there).
 
 Constraint: a parameter must be used once per step (no weight sharing between calls inside one backward).
 """
+import ctypes
+
 import torch
 import torch.distributed as dist
 
@@ -122,3 +125,52 @@ def shard_batch(x, y, rank, world):
     n = x.shape[0]
     per = n // world
     return x[rank * per:(rank + 1) * per], y[rank * per:(rank + 1) * per]
+
+
+class SyncBatchNormLink:
+    """Global-batch BatchNorm statistics for the blocks of a data-parallel replica (SyncBN; the reference is single-process and
+    has no counterpart).
+
+    The library does the arithmetic; this object is the exchange step it calls back into (StgcnBlockParams.sync_*,
+    include/stgcn_b200.h): at each of a block's BatchNorm exchange points the library writes 2*C local sums into `buf` and calls
+    `allreduce`, which must enqueue an in-place SUM over the ranks on the CURRENT stream (the library is always called on
+    torch's current stream) and return without a host synchronisation.  Default: torch.distributed.all_reduce on `group`
+    (NCCL: stream-ordered).  All ranks must run the same blocks in the same order (they do: one model, replicated).
+    """
+
+    def __init__(self, world=None, group=None, allreduce=None):
+        self.world = int(world if world is not None else dist.get_world_size(group))
+        self.group = group
+        self.buf = None
+        self._allreduce = allreduce or (lambda buf: dist.all_reduce(buf, op=dist.ReduceOp.SUM, group=self.group))
+        self.calls = 0
+
+        def _cb(user, stream):
+            self.calls += 1
+            self._allreduce(self.buf)
+        self._cfn = ctypes.CFUNCTYPE(None, ctypes.c_void_p, ctypes.c_void_p)(_cb)      # kept alive with the link
+        self.fn_ptr = ctypes.cast(self._cfn, ctypes.c_void_p).value
+
+    def on(self, device, channels):
+        """The link with its exchange buffer on `device`, at least 2*channels floats (called by the block every forward)."""
+        if self.buf is None or self.buf.device != device or self.buf.numel() < 2 * channels:
+            self.buf = torch.zeros(2 * max(channels, 256), dtype=torch.float32, device=device)
+        return self
+
+
+def enable_sync_batchnorm(model, group=None, world=None, allreduce=None):
+    """Switch every SpatialTemporalConv of `model` to global-batch BatchNorm statistics in training mode; returns the link
+    (keep it, or call disable_sync_batchnorm).  With world == 1 the blocks keep their local path."""
+    from .modules import SpatialTemporalConv
+    link = SyncBatchNormLink(world, group, allreduce)
+    for m in model.modules():
+        if isinstance(m, SpatialTemporalConv):
+            m._sync = link if link.world > 1 else None
+    return link
+
+
+def disable_sync_batchnorm(model):
+    from .modules import SpatialTemporalConv
+    for m in model.modules():
+        if isinstance(m, SpatialTemporalConv):
+            m._sync = None

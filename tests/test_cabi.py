@@ -131,6 +131,6 @@ def test_ctypes_structs_have_the_library_s_sizes():
     from stgcn_b200 import _lib
     lib = _lib.lib()
     assert lib.stgcn_abi_sizeof(0) == C.sizeof(_lib.BlockDesc) == 13 * 4 + 3 * 4 + 2 * 8
-    assert lib.stgcn_abi_sizeof(1) == C.sizeof(_lib.BlockParams) == 19 * 8
+    assert lib.stgcn_abi_sizeof(1) == C.sizeof(_lib.BlockParams) == 23 * 8
     assert lib.stgcn_abi_sizeof(2) == C.sizeof(_lib.BlockGrads) == 11 * 8
     assert lib.stgcn_abi_sizeof(7) == 0

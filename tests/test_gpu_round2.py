@@ -411,3 +411,62 @@ def test_batchnorm_momentum_none_is_rejected():
     m.batch_n.momentum = None
     with pytest.raises(RuntimeError):
         m(torch.randn(2, 8, 12, 25).cuda())
+
+
+# ---- SyncBN plumbing on one GPU: a world of two IDENTICAL ranks ----------------------------------------------------------------
+SYNC_CASES = [
+    # ci, co, T, stride, residual, dtype
+    (16, 24, 20, 1, False, torch.float32),       # CUDA-core / split path, BatchNorm-1 backward as its own pass
+    (64, 64, 20, 1, False, torch.bfloat16),      # tcgen05 path: BatchNorm-1 backward folded into the spatial weights
+    (64, 128, 20, 2, False, torch.bfloat16),
+    (64, 64, 14, 1, True, torch.bfloat16),       # residual block: BatchNorm-2 sits between the convolutions
+    (16, 32, 20, 2, True, torch.float32),
+]
+
+
+@pytest.mark.parametrize('case', SYNC_CASES, ids=lambda c: '%d-%d-T%d-s%d-%s-%s' % (c[0], c[1], c[2], c[3], 'res' if c[4] else 'def', str(c[5])[6:]))
+def test_sync_batchnorm_with_two_identical_ranks_equals_local_statistics(case):
+    """StgcnBlockParams.sync_* (include/stgcn_b200.h): with an exchange step that doubles the sums (= SUM over two ranks holding
+    the same shard) and world = 2, every mean / variance / backward correction is that of the local batch, so outputs, dx and
+    all gradients must equal the local-statistics run; only the running variance differs, by the unbiased-count factor
+    (2m/(2m-1)) / (m/(m-1)).  All exchange points must have fired: 2 forward + 2 backward per block (+1 when the folded
+    BatchNorm-1 backward is its own exchange)."""
+    from stgcn_b200.parallel import SyncBatchNormLink
+    ci, co, T, s, res, dtype = case
+    V, K, N = 25, 3, 4
+    torch.manual_seed(99)
+    A = torch.randn(K, V, V) * 0.2
+    with contextlib.redirect_stdout(io.StringIO()):
+        m = build_block(ci, co, A, s, res, dtype=dtype)
+    _rand_bn(m)
+    state = {k: v.detach().clone() for k, v in m.state_dict().items()}
+    x = torch.randn(N, ci, T, V)
+    gy = torch.randn(N, co, (T - 1) // s + 1, V)
+    y0, dx0, g0 = run_block(m, x, gy, True)
+    sd0 = {k: v.detach().clone() for k, v in m.state_dict().items()}
+    m.load_state_dict(state)
+    m.zero_grad(set_to_none=True)
+    link = SyncBatchNormLink(world=2, allreduce=lambda buf: buf.mul_(2.0))
+    m._sync = link
+    y1, dx1, g1 = run_block(m, x, gy, True)
+    sd1 = m.state_dict()
+    assert link.calls in (4, 5), link.calls
+    tol = 1e-5 if dtype == torch.float32 else 2e-2            # fp32: same kernels, sums doubled and halved; bf16: rounding of y re-drawn
+    assert rel_err(y1, y0) < tol
+    assert rel_err(dx1, dx0) < (1e-4 if dtype == torch.float32 else 2e-2)
+    for k in g0:
+        assert rel_err(g1[k], g0[k]) < (1e-4 if dtype == torch.float32 else 2e-2), k
+    rows = {'batch_n': N * T * V, 'batch_n_2': N * (T if res else (T - 1) // s + 1) * V}
+    for bn, mrows in rows.items():
+        assert rel_err(sd1[bn + '.running_mean'], sd0[bn + '.running_mean']) < 1e-5
+        # running_var = 0.9 * start + 0.1 * unbiased batch variance: undo the blend, compare the batch parts
+        b0 = (sd0[bn + '.running_var'] - 0.9 * state[bn + '.running_var']) / 0.1
+        b1 = (sd1[bn + '.running_var'] - 0.9 * state[bn + '.running_var']) / 0.1
+        factor = (2 * mrows / (2 * mrows - 1)) / (mrows / (mrows - 1))
+        assert rel_err(b1, b0 * factor) < 1e-4, bn
+        assert int(sd1[bn + '.num_batches_tracked']) == int(sd0[bn + '.num_batches_tracked'])
+    # eval mode never exchanges
+    m.eval(); n_before = link.calls
+    with torch.no_grad():
+        m(x.cuda())
+    assert link.calls == n_before
