@@ -211,7 +211,6 @@ __global__ void __launch_bounds__(256) pack_weights_kernel(const float* __restri
 template <class TD>
 int32_t launch_pack_weights(const float* src, const WIndex& wi, int taps, int n_out, int c, TD* dst, cudaStream_t st, int round_bf16) {
   KernelTimer kt_(KC_PACK, 0.0, st);
-  { static const char* x = getenv("STGCN_X_SKIP"); if (x && strchr(x, 'p')) return STGCN_OK; }     // timing experiment only (results invalid)
   size_t total = (size_t)taps * n_out * c;
   int blocks = (int)std::min<size_t>((total + 255) / 256, 148 * 4);
   launch_k(pack_weights_kernel<TD>, blocks, 256, 0, st, src, wi, taps, n_out, c, round_bf16, dst);

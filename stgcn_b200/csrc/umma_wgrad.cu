@@ -317,7 +317,6 @@ int32_t launch_wgrad_umma(const ConvGeom& g, const bf16* dout, const bf16* in, c
   const int grid = std::min(p.total_items, num_sms_wg());
   launch_k(wgrad_umma_kernel, grid, kWgThreads, smem, st, map_dout, map_in, p);
   STGCN_CHECK_LAUNCH("wgrad_umma");
-  { static const char* x = getenv("STGCN_X_SKIP"); if (x && strchr(x, 'u')) return STGCN_OK; }     // timing experiment only (results invalid)
   size_t total = umma_wgrad_workspace_floats(g);
   cudaStream_t ust = st;
   if (unpack_st && unpack_ev) {      // the layout change is off the data-gradient path: let it run beside the next kernels
