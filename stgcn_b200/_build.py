@@ -18,6 +18,9 @@ SOURCES = ['block.cu', 'bn_kernels.cu', 'agg_kernels.cu', 'gemm_simt.cu', 'head_
            'umma_probe.cu', 'timing.cu', 'umma_wgrad.cu', 'umma_agg.cu', 'umma_spatial.cu', 'train_kernels.cu', 'input_kernels.cu', 'train_prep.cu']
 NVCC_FLAGS = ['-std=c++17', '-O3', '-gencode', 'arch=compute_100a,code=sm_100a', '-lineinfo',
               '-Xcompiler', '-fPIC', '--expt-relaxed-constexpr']
+# development builds (e.g. STGCN_NVCC_EXTRA=-DSTGCN_SP_TRACE, umma_spatial.cu): part of the freshness digest, so a library built
+# with extra flags is stale for a process that does not set the same variable
+NVCC_FLAGS += os.environ.get('STGCN_NVCC_EXTRA', '').split()
 
 
 def _nvcc():

@@ -150,7 +150,7 @@ agg_umma_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_constan
   __syncthreads();
   tc_fence_after();
   pdl_wait();                       // everything above (barriers, TMEM, descriptor prefetch) overlaps the previous kernel's tail
-  const uint32_t tmem_base = *tmem_slot;
+  const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);      // warp-uniform for the compiler: the MMA operands stay in uniform registers (no R2UR per tcgen05.mma)
 
   auto decode = [&](int item, int& cch, int& j0, int& b) {
     if (p.rev) item = p.total_items - 1 - item;
@@ -431,7 +431,7 @@ agg_dA_umma_kernel(const __grid_constant__ CUtensorMap map_dxa, const __grid_con
   __syncthreads();
   tc_fence_after();
   pdl_wait();                       // everything above (barriers, TMEM, descriptor prefetch) overlaps the previous kernel's tail
-  const uint32_t tmem_base = *tmem_slot;
+  const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);      // warp-uniform for the compiler: the MMA operands stay in uniform registers (no R2UR per tcgen05.mma)
   const int cbs = p.c / 64;
   const bool have_work = (int)blockIdx.x < p.total_tiles;
 

@@ -39,6 +39,7 @@ struct SpParams {
   const float* b2d;            // [V][Co] joint bias table bias2d' (bias2d_fold_kernel)
   const bf16* big_g;           // block-diagonal adjacency in global memory (tensor-memory-resident variant)
   int wres;                    // all weight chunks stay resident in shared memory (loaded once; wst = their count)
+  bf16* xa_g;                  // tensor-memory variant, training: the aggregated rows are ALSO stored (nb,t,v,k*ci) for backward's weight gradient
   long long* trace;            // per-role segment timers of CTA 0 (builds with -DSTGCN_SP_TRACE only; null otherwise)
 };
 
@@ -86,7 +87,7 @@ spatial_fused_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_con
   __syncthreads();
   tc_fence_after();
   pdl_wait();                       // everything above (barriers, TMEM, descriptor prefetch) overlaps the previous kernel's tail
-  const uint32_t tmem_base = *tmem_slot;
+  const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);      // warp-uniform for the compiler: the MMA operands stay in uniform registers (no R2UR per tcgen05.mma)
   const uint32_t t_tmem = tmem_base;                 // 2 x 64 columns: aggregation accumulators
   const uint32_t s_tmem = tmem_base + 128;           // Co columns: the output tile
   const int chunks = p.cblocks * p.k;                // (cc, k) pairs per tile, cc outer
@@ -296,15 +297,26 @@ spatial_fused_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_con
 }
 
 // ---------------------------------------------------------------------------
-// Variant for inference (no XA store): the aggregated chunk never leaves tensor memory.
+// Tensor-memory variant (the default for inference): the aggregated chunk never leaves tensor memory.
 //
-// The kernel above is bound by a LATENCY chain, not by a throughput: MMA-1 -> (TMEM -> registers -> bf16 -> swizzled shared
-// memory -> proxy fence -> CTA-group barrier) -> MMA-2, with only two chunks in flight (measured: ~5.7 k cycles per 125-row tile
-// at C = 64 against ~1.4 k for the tile's HBM bytes and ~1.2 k for its MMAs).  Here the bf16 chunk is written back to TENSOR
-// MEMORY (tcgen05.st, 32 columns of packed pairs) and the mixing product reads its A operand from there
-// (tcgen05.mma ... [d], [a_tmem], b_desc): no shared-memory tile, no proxy fence, no barrier between the threads of a group --
-// each of the 128 threads arrives on the mbarrier by itself.  G conversion groups (G T accumulators and G P operands in TMEM)
-// keep G chunks in flight, and a separate output group owns the S -> bias -> bf16 -> TMA-store leg with two staging buffers.
+// The kernel above has ONE warp issuing both products and a shared-memory round trip between them.  Per-role cycle counters
+// (-DSTGCN_SP_TRACE below) showed that warp busy ~900 cycles per chunk for 384 cycles of tensor work -- every barrier wait it
+// passes costs ~50 cycles even when already satisfied -- while the conversion warps idled; and a stand-alone issue-rate
+// benchmark (tools/mma_rate.cu, profiles/r2_mma_issue_rate.txt) gave the hardware floors: a 128x64x16 MMA with both operands in
+// shared memory takes 48 cycles (6 KB of operand reads at 128 B/clk), with A in tensor memory 32.  Hence:
+//   * the bf16 chunk is written back to TENSOR MEMORY (tcgen05.st, 32 columns of packed pairs) and the mixing product takes its A
+//     operand from there (tcgen05.mma [d], [a_tmem], b_desc): no shared-memory tile, no proxy fence, no barrier among the
+//     threads of a group -- each of the 128 threads arrives on the mbarrier by itself;
+//   * TWO issuer warps, one per product, and two TMA producer warps (activation tiles / weight chunks), so no instruction stream
+//     waits behind another one's barriers;
+//   * G conversion groups (G accumulators T and G operands P in tensor memory) keep G chunks in flight; a separate output group
+//     owns the S -> bias -> bf16 -> TMA-store leg with two staging buffers;
+//   * BT: the block-diagonal adjacency itself (k x 64 packed columns) is the tensor-memory A operand of the aggregation product
+//     when the columns allow (C_out = 64), which frees 96 KB of shared memory; all weight chunks then stay resident.
+// Measured (N_eff = 128, one B200, tools/spatial_probe.py): 136 -> 69 us (64->64, T = 300), 145 -> 75 us (128->128, T = 150),
+// 187 -> 133 us (256->256, T = 75); cfg3 inference 22.8 k -> 27.4 k sequences/s.  For training (XA wanted by the weight gradient)
+// the rows can be stored straight from the conversion registers (STGCN_FUSED_SPATIAL=1), but that measured 6.20 against 6.03 ms
+// per step for the two-kernel pair, which stays the default there.
 // Warp roles: 0 / 3 = TMA producers (activation tiles / weight chunks), 1 / 2 = MMA issuers (aggregation / mixing products),
 // 4..7 = output group, 8.. = G conversion groups of four warps.
 // ---------------------------------------------------------------------------
@@ -316,10 +328,13 @@ constexpr int sp_ts_threads(int g) { return 128 + 128 + 128 * g; }
 __device__ __forceinline__ uint32_t sp_clk() { uint32_t c; asm volatile("mov.u32 %0, %%clock;" : "=r"(c)); return c; }
 #define SPSEG(i) do { if (tr) { const uint32_t now_ = sp_clk(); acc[i] += now_ - last_; last_ = now_; } } while (0)
 #define SPSTART() do { if (tr) last_ = sp_clk(); } while (0)
+__device__ __forceinline__ long long sp_ns() { long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
+#define SPNS(slot, cond) do { if (tr && (cond)) p.trace[slot] = sp_ns(); } while (0)
 #define SPDUMP(cond, first, count, base) do { if (tr && (cond)) { for (int i_ = 0; i_ < (count); ++i_) p.trace[(base) + i_] = acc[(first) + i_]; } } while (0)
 #else
 #define SPSEG(i) do { } while (0)
 #define SPSTART() do { } while (0)
+#define SPNS(slot, cond) do { } while (0)
 #define SPDUMP(cond, first, count, base) do { } while (0)
 #endif
 
@@ -349,6 +364,7 @@ spatial_fused_ts_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_
 #ifdef STGCN_SP_TRACE
   const bool tr = p.trace != nullptr && blockIdx.x == 0; uint32_t acc[8] = {0, 0, 0, 0, 0, 0, 0, 0}, last_ = 0;
 #endif
+  SPNS(10, threadIdx.x == 0);
 
   {  // padding rows of the activation tiles (never written by TMA) must be finite: they meet BigA's zero columns
     uint4* z = reinterpret_cast<uint4*>(smem_x);
@@ -369,8 +385,10 @@ spatial_fused_ts_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  SPNS(11, threadIdx.x == 0);
   pdl_wait();
-  const uint32_t tmem_base = *tmem_slot;
+  SPNS(12, threadIdx.x == 0);
+  const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);      // warp-uniform for the compiler: the MMA operands stay in uniform registers (no R2UR per tcgen05.mma)
   const uint32_t t_tmem = tmem_base;                        // G x 64 columns: aggregation accumulators (fp32)
   const uint32_t p_tmem = tmem_base + 64 * G;               // G x 32 columns: the same chunks as packed bf16 pairs (A operand of MMA-2)
   const uint32_t s_tmem = tmem_base + 96 * G;               // ns x Co columns: output tiles
@@ -451,6 +469,7 @@ spatial_fused_ts_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_
       SPSEG(2);
     }
     SPDUMP(lane == 0, 0, 3, 0);
+    SPNS(13, lane == 0);
   } else if (warp == 2) {
     // ===================== issuer B: mixing products S[sb] += P[pb] . W2'(k, cc) =====================
     const uint32_t idesc2 = make_idesc_bf16(128, p.wn, 0, 0);      // A = P (tensor memory), B = weights (K-major)
@@ -552,6 +571,7 @@ spatial_fused_ts_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_
     }
     SPDUMP(et == 0, 0, 6, 24);
     if (et == 0) tma_store_wait<0>();
+    SPNS(14, et == 0);
   } else {
     // ===================== conversion groups: T (fp32) -> packed bf16 pairs -> P (tensor memory) =====================
     const int grp = (warp - 8) / 4, q = warp % 4;
@@ -592,6 +612,21 @@ spatial_fused_ts_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_
         __nv_bfloat162 h1 = __floats2bfloat162_rn(__uint_as_float(r1[2 * j]), __uint_as_float(r1[2 * j + 1]));
         pk[j] = *reinterpret_cast<uint32_t*>(&h0); pk[16 + j] = *reinterpret_cast<uint32_t*>(&h1);
       }
+      if (p.xa_g) {      // training: this thread's row of the chunk (64 bf16 = 128 contiguous bytes of XA) straight from registers
+        const int tix = g / chunks, c = g - tix * chunks, cc = c / p.k, kq = c - cc * p.k;
+        const int tile = blockIdx.x + tix * (int)gridDim.x;
+        const int tl = p.rev ? p.total_tiles - 1 - tile : tile;
+        const int j0 = (tl % p.m_tiles_per_b) * p.ft, b = tl / p.m_tiles_per_b;
+        const int row = q * 32 + lane, fr = j0 + row / p.v;
+        if (row < p.ft * p.v && fr < p.t) {
+          uint4* dst = reinterpret_cast<uint4*>(p.xa_g + ((size_t)(b * p.t + fr) * p.v + row % p.v) * ((size_t)p.k * p.ci) + (size_t)kq * p.ci + cc * 64);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {      // pk[0..15] = columns 0..31, pk[16..31] = columns 32..63
+            dst[j] = make_uint4(pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
+            dst[4 + j] = make_uint4(pk[16 + 4 * j], pk[16 + 4 * j + 1], pk[16 + 4 * j + 2], pk[16 + 4 * j + 3]);
+          }
+        }
+      }
       mbar_wait(pempty + grp, par ^ 1);                         // the mixing product that last read this operand has retired
       SPSEG(2);
       tc_fence_after();
@@ -606,6 +641,7 @@ spatial_fused_ts_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_
   tc_fence_before();
   __syncthreads();
   if (warp == 1) { tc_fence_after(); tmem_dealloc(tmem_base, p.tmem_cols); }
+  SPNS(15, threadIdx.x == 0);
 }
 
 // ---------------------------------------------------------------------------
@@ -707,7 +743,8 @@ int32_t launch_spatial_fused(const bf16* x, int nb, int t, int v, int ci, int co
   // inference (no XA store): the tensor-memory variant; STGCN_SPATIAL_TS=0 keeps the shared-memory kernel for A/B runs
   static const bool use_ts = [] { const char* e = getenv("STGCN_SPATIAL_TS"); return !(e && e[0] == '0'); }();
   const SpTsPlan tpl = sp_ts_plan(v, ci, co, k);
-  if (use_ts && !xa && tpl.ok) {
+  static const bool ts_train = [] { const char* e = getenv("STGCN_SPATIAL_TS_TRAIN"); return !(e && e[0] == '0'); }();
+  if (use_ts && (!xa || ts_train) && tpl.ok) {
 #ifdef STGCN_SP_TRACE
     static long long* trace_buf = nullptr;
     if (getenv("STGCN_SPATIAL_TRACE")) { if (!trace_buf) cudaMalloc(&trace_buf, 32 * 8); cudaMemsetAsync(trace_buf, 0, 32 * 8, st); p.trace = trace_buf; }
@@ -723,7 +760,7 @@ int32_t launch_spatial_fused(const bf16* x, int nb, int t, int v, int ci, int co
       ts_attr_set = true;
     }
     const int grid_ts = std::min(p.total_tiles, num_sms_sp());
-    p.big_g = big;
+    p.big_g = big; p.xa_g = xa;
     if (tpl.g == 3 && tpl.bt) launch_k(spatial_fused_ts_kernel<3, true>, grid_ts, sp_ts_threads(3), tpl.smem, st, map_x, map_big, map_w, map_out, p);
     else if (tpl.g == 3) launch_k(spatial_fused_ts_kernel<3, false>, grid_ts, sp_ts_threads(3), tpl.smem, st, map_x, map_big, map_w, map_out, p);
     else if (tpl.bt) launch_k(spatial_fused_ts_kernel<2, true>, grid_ts, sp_ts_threads(2), tpl.smem, st, map_x, map_big, map_w, map_out, p);
@@ -735,10 +772,11 @@ int32_t launch_spatial_fused(const bf16* x, int nb, int t, int v, int ci, int co
       long long h[32];
       cudaMemcpy(h, p.trace, sizeof(h), cudaMemcpyDeviceToHost);
       const double n = (double)(cdiv(p.total_tiles - 0, grid_ts)) * (ci / 64) * k;      // chunks of CTA 0
-      fprintf(stderr, "[sp trace %d->%d G=%d bt=%d ns=%d xs=%d wst=%d] per chunk (cycles): MMA warp: tempty %.0f xfull %.0f issue1 %.0f | sempty %.0f pfull %.0f wfull %.0f mix %.0f other %.0f = %.0f ; conv0 (per own chunk): tfull %.0f ld %.0f pempty %.0f cvt+st %.0f ; O per tile: sfull %.0f loop %.0f ld %.0f bar1 %.0f bias+sts %.0f fence+bar2+store %.0f (wres %d)\n",
+      fprintf(stderr, "[sp trace %d->%d G=%d bt=%d ns=%d xs=%d wst=%d] per chunk (cycles): MMA warp: tempty %.0f xfull %.0f issue1 %.0f | sempty %.0f pfull %.0f wfull %.0f mix %.0f other %.0f = %.0f ; conv0 (per own chunk): tfull %.0f ld %.0f pempty %.0f cvt+st %.0f ; O per tile: sfull %.0f loop %.0f ld %.0f bar1 %.0f bias+sts %.0f fence+bar2+store %.0f (wres %d) | ns: prologue %lld pdl_wait %lld issuerA-end %lld O-end %lld exit %lld\n",
               ci, co, tpl.g, (int)tpl.bt, tpl.ns, tpl.xs, tpl.wst, h[0] / n, h[1] / n, h[2] / n, h[3] / n, h[4] / n, h[5] / n, h[6] / n, h[7] / n,
               (h[0] + h[1] + h[2] + h[3] + h[4] + h[5] + h[6] + h[7]) / n, h[16] / (n / tpl.g), h[17] / (n / tpl.g), h[18] / (n / tpl.g), h[19] / (n / tpl.g),
-              h[24] / (n / (ci / 64 * k)), h[25] / (n / (ci / 64 * k)), h[26] / (n / (ci / 64 * k)), h[27] / (n / (ci / 64 * k)), h[28] / (n / (ci / 64 * k)), h[29] / (n / (ci / 64 * k)), (int)tpl.wres);
+              h[24] / (n / (ci / 64 * k)), h[25] / (n / (ci / 64 * k)), h[26] / (n / (ci / 64 * k)), h[27] / (n / (ci / 64 * k)), h[28] / (n / (ci / 64 * k)), h[29] / (n / (ci / 64 * k)), (int)tpl.wres,
+              h[11] - h[10], h[12] - h[11], h[13] - h[12], h[14] - h[12], h[15] - h[12]);
     }
 #endif
     return STGCN_OK;

@@ -85,7 +85,7 @@ wgrad_umma_kernel(const __grid_constant__ CUtensorMap map_dout, const __grid_con
   __syncthreads();
   tc_fence_after();
   pdl_wait();                       // everything above (barriers, TMEM, descriptor prefetch) overlaps the previous kernel's tail
-  const uint32_t tmem_base = *tmem_slot;
+  const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);      // warp-uniform for the compiler: the MMA operands stay in uniform registers (no R2UR per tcgen05.mma)
 
   // item -> (n_t, c_t, group, split)
   auto decode = [&](int item, int& n_t, int& c_t, int& g, int& kb0, int& kb1) {

@@ -12,6 +12,7 @@ Tolerances: fp32 1e-4, bf16 2e-2 (max|got-ref| / max|ref| per tensor), structura
 import argparse
 import contextlib
 import io
+import os
 
 import numpy as np
 import pytest
@@ -470,3 +471,17 @@ def test_sync_batchnorm_with_two_identical_ranks_equals_local_statistics(case):
     with torch.no_grad():
         m(x.cuda())
     assert link.calls == n_before
+
+
+def test_fused_spatial_kernel_with_aggregate_store_in_training():
+    """STGCN_FUSED_SPATIAL=1 routes the training forward through the tensor-memory spatial kernel, which then also stores the
+    aggregated rows for backward's weight gradient straight from its conversion registers (umma_spatial.cu).  The switch is read
+    once per process, so the block parity cases run in a child process with it set."""
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, STGCN_FUSED_SPATIAL='1')
+    r = subprocess.run([sys.executable, '-m', 'pytest', os.path.join(root, 'tests', 'test_gpu_block.py'), '-q', '-x', '-m', 'gpu',
+                        '-k', 'test_block_matches_oracle and bfloat16'], env=env, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-1000:]
+    assert ' passed' in r.stdout and 'failed' not in r.stdout
