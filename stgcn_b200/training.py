@@ -162,3 +162,57 @@ class CapturedForward:
         self.x.copy_(x, non_blocking=True)
         self.graph.replay()
         return self.out
+
+    def stream(self, host_batches, out_host=None):
+        """Serving loop over an iterable of PINNED host batches: the host->device copy of batch i+1 runs on a copy stream while the
+        graph computes batch i (two device staging buffers), and each batch's logits go to a pinned host buffer.  Generator: yields
+        the host logits of batch i once they have arrived, while batch i+1 is already running; the yielded buffer is valid until
+        the generator is advanced again (it is one of two that alternate) unless `out_host`, a list of pinned buffers, provides
+        one per batch."""
+        dev = self.x.device
+        main = torch.cuda.current_stream(dev)
+        if not hasattr(self, '_copy_stream'):
+            self._copy_stream = torch.cuda.Stream(device=dev)
+            self._stage = [torch.empty_like(self.x) for _ in range(2)]
+            self._ev_in = [torch.cuda.Event() for _ in range(2)]
+            self._ev_free = [torch.cuda.Event() for _ in range(2)]
+            self._ev_out = [torch.cuda.Event() for _ in range(2)]
+            self._out_host = [torch.empty(self.out.shape, dtype=torch.float32).pin_memory() for _ in range(2)]
+            self._used = [False, False]
+
+        def prefetch(hx, j):
+            if hx.shape != self.x.shape or not hx.is_pinned():
+                raise RuntimeError('stgcn_b200.CapturedForward.stream: batches must be pinned host tensors of the captured shape')
+            with torch.cuda.stream(self._copy_stream):
+                if self._used[j]:
+                    self._copy_stream.wait_event(self._ev_free[j])       # the graph input took over this staging buffer's last batch
+                self._stage[j].copy_(hx, non_blocking=True)
+                self._ev_in[j].record(self._copy_stream)
+            self._used[j] = True
+
+        it = iter(host_batches)
+        nxt = next(it, None)
+        if nxt is not None:
+            prefetch(nxt, 0)
+        i = 0
+        pending = None
+        while nxt is not None:
+            j = i & 1
+            cur, nxt = nxt, next(it, None)
+            if nxt is not None:
+                prefetch(nxt, j ^ 1)
+            main.wait_event(self._ev_in[j])
+            self.x.copy_(self._stage[j], non_blocking=True)
+            self._ev_free[j].record(main)
+            self.graph.replay()
+            dst = out_host[i] if out_host is not None else self._out_host[j]
+            dst.copy_(self.out, non_blocking=True)
+            self._ev_out[j].record(main)
+            if pending is not None:                    # hand out batch i-1 while batch i computes
+                pending[0].synchronize()
+                yield pending[1]
+            pending = (self._ev_out[j], dst)
+            i += 1
+        if pending is not None:
+            pending[0].synchronize()
+            yield pending[1]

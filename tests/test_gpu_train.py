@@ -158,3 +158,28 @@ def test_captured_forward_equals_eager_eval_forward():
         assert float((got - ref).abs().max() / ref.abs().max()) < 1e-2        # same kernels; tiles may be walked the other way round
     with pytest.raises(RuntimeError):
         fwd(torch.randn(2, 40, 25, 3).cuda())
+
+
+def test_captured_forward_serving_loop_matches_single_calls():
+    """CapturedForward.stream: pinned host batches in, pinned host logits out, the copy of the next batch on a copy stream while the
+    graph runs -- same numbers as one call per batch, in order, for an odd and an even number of batches and across two runs."""
+    import stgcn_b200
+    model = _small_model(torch.bfloat16)
+    g = torch.Generator().manual_seed(4)
+    hosts = [torch.randn(4, 40, 25, 3, generator=g).pin_memory() for _ in range(5)]
+    with torch.no_grad():
+        model(hosts[0].cuda())
+    model.eval()
+    fwd = stgcn_b200.CapturedForward(model, hosts[0].cuda())
+    refs = [fwd(h.cuda()).float().cpu().clone() for h in hosts]
+    for n in (5, 2, 1):
+        got = [o.clone() for o in fwd.stream(hosts[:n])]
+        assert len(got) == n
+        for a, b in zip(got, refs):
+            assert float((a - b).abs().max() / b.abs().max()) < 1e-2
+    outs = [torch.empty(refs[0].shape).pin_memory() for _ in range(3)]
+    res = list(fwd.stream(hosts[:3], out_host=outs))
+    assert all(r is o for r, o in zip(res, outs))
+    assert float((outs[2] - refs[2]).abs().max() / refs[2].abs().max()) < 1e-2
+    with pytest.raises(RuntimeError):
+        list(fwd.stream([torch.randn(4, 40, 25, 3)]))           # not pinned
