@@ -485,3 +485,44 @@ def test_fused_spatial_kernel_with_aggregate_store_in_training():
                         '-k', 'test_block_matches_oracle and bfloat16'], env=env, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-1000:]
     assert ' passed' in r.stdout and 'failed' not in r.stdout
+
+
+# ---- tensor-memory spatial kernel (inference default): shapes beyond the model's own ----------------------------------------------
+TS_SHAPES = [
+    # ci, co, V, K, T, stride   (T chosen so that the last tile of frames is ragged; every tensor-memory plan is visited:
+    #                            adjacency in tensor memory + resident weights, weight ring, one / two output accumulators, 64- and
+    #                            128-wide weight stages, 1..3 partitions, 4..7 frames per tile)
+    (64, 64, 25, 3, 23, 1),
+    (64, 192, 25, 3, 13, 1),
+    (128, 64, 18, 2, 20, 1),
+    (192, 256, 20, 1, 9, 1),
+    (256, 128, 32, 3, 11, 2),
+    (64, 128, 16, 3, 30, 2),
+    (256, 256, 25, 3, 7, 1),
+]
+
+
+@pytest.mark.parametrize('shape', TS_SHAPES, ids=lambda s: '%d-%d-V%d-K%d-T%d-s%d' % s)
+def test_inference_block_on_the_tensor_memory_spatial_kernel_matches_oracle(shape):
+    """Eval-mode, no-grad bf16 block (the path CapturedForward replays): spatial_fused_ts_kernel (aggregation and channel mixing with
+    the intermediate in tensor memory, umma_spatial.cu) followed by the temporal GEMM with BatchNorm-2 + ReLU in its epilogue,
+    against the fp32 oracle block (st_graphconv.py:85-109) at the bf16 tolerance; a second call must give the same bits."""
+    ci, co, V, K, T, s = shape
+    torch.manual_seed(ci + co + V + K)
+    A = torch.randn(K, V, V) * 0.2
+    with contextlib.redirect_stdout(io.StringIO()):
+        m = build_block(ci, co, A, s, False, dtype=torch.bfloat16).eval()
+    _rand_bn(m)
+    p = {k: v.detach().cpu().clone() for k, v in m.state_dict().items()}
+    x = torch.randn(3, ci, T, V)
+    from stgcn_b200 import _lib
+    with torch.no_grad():
+        y = m(x.cuda())
+        _lib.timing_reset(); _lib.timing_enable(True)
+        y2 = m(x.cuda())
+        torch.cuda.synchronize(); _lib.timing_enable(False)
+        y_ref = O.block_forward(x, p, O.BlockCfg(ci, co, 9, s, 4, 0.0, False), False)
+    assert _lib.timing_read().get('umma_spatial', (0, 0, 0))[2] == 1, 'the fused spatial kernel did not run for this shape'
+    assert rel_err(y.float(), y_ref) < TOL[torch.bfloat16]
+    assert float(y_ref.abs().max()) > 0.1
+    assert rel_err(y2.float(), y.float()) < 1e-2          # (bitwise only with the traversal direction fixed)
