@@ -170,6 +170,12 @@ struct SyncCtx {
   bool on() const { return fn != nullptr && buf != nullptr && world > 1; }
   void allreduce() const { fn(user, (void*)st); }          // enqueues on st, does not synchronise
 };
+// a half-filled link is a caller bug that would silently fall back to per-replica statistics on SOME ranks: refuse it
+static int32_t sync_check(const StgcnBlockParams& P) {
+  if (P.sync_allreduce && P.sync_world > 1 && !P.sync_buf) { set_error("SyncBN link: sync_allreduce is set but sync_buf is null"); return STGCN_ERR_INVALID; }
+  if (P.sync_world < 0) { set_error("SyncBN link: negative sync_world"); return STGCN_ERR_INVALID; }
+  return STGCN_OK;
+}
 static SyncCtx sync_of(const StgcnBlockDesc& d, const StgcnBlockParams& P, cudaStream_t st, bool dry) {
   SyncCtx s;
   if (!dry && d.training && P.sync_allreduce && P.sync_buf && P.sync_world > 1) {
@@ -584,6 +590,7 @@ static int32_t block_forward_t(const StgcnBlockDesc& d, const T* x, const StgcnB
   const bool res = d.residual != STGCN_RES_NONE;
   const int relu1 = res ? 1 : 0;
   int nblk = 0;
+  STGCN_TRY(sync_check(P));
   const SyncCtx sy = sync_of(d, P, st, ws.dry);
   const bool drop = d.training && d.dropout_p > 0.f;
   if (!ws.dry) {
@@ -760,6 +767,7 @@ static int32_t block_backward_t(const StgcnBlockDesc& d, const T* x, const T* y,
       wd_on_lane = lane != nullptr;
     }
   }
+  STGCN_TRY(sync_check(P));
   const SyncCtx sy = sync_of(d, P, st, ws.dry);
   const float* sums_use = nullptr; double cscale = 1.0;
   ZeroJobs zj;

@@ -526,3 +526,18 @@ def test_inference_block_on_the_tensor_memory_spatial_kernel_matches_oracle(shap
     assert rel_err(y.float(), y_ref) < TOL[torch.bfloat16]
     assert float(y_ref.abs().max()) > 0.1
     assert rel_err(y2.float(), y.float()) < 1e-2          # (bitwise only with the traversal direction fixed)
+
+
+def test_sync_batchnorm_link_without_a_buffer_is_refused():
+    """A half-filled SyncBN link (callback but no exchange buffer) must fail loudly, not fall back to per-replica statistics."""
+    from stgcn_b200.parallel import SyncBatchNormLink
+    torch.manual_seed(0)
+    with contextlib.redirect_stdout(io.StringIO()):
+        m = build_block(16, 16, torch.randn(2, 25, 25) * 0.2, 1, False).train()
+    link = SyncBatchNormLink(world=2, allreduce=lambda buf: None)
+    link.buf = torch.empty(0, device='cuda')            # data_ptr() == 0
+    link.on = lambda device, channels: link
+    m._sync = link
+    with pytest.raises(RuntimeError, match='sync_buf is null'):
+        m(torch.randn(2, 16, 12, 25).cuda())
+    assert link.calls == 0
