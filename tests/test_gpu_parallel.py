@@ -334,6 +334,38 @@ def _sync_body(rank, world, port, out):
                         'running_stats': max(rel_err(sd_sync[k], sd1[k]) for k in sd1 if 'running' in k),
                         'calls': link.calls}
         del lg1
+    # the whole synced training step as one CUDA graph (the all-reduces of the sums are captured with it) == the eager step
+    try:
+        from stgcn_b200 import CapturedTrainStep
+        from stgcn_b200.optim import Adam
+        from stgcn_b200.parallel import GradBucketReducer
+        xs2, ys2 = x[rank * per:(rank + 1) * per].to(dev), yl[rank * per:(rank + 1) * per].to(dev)
+        model.load_state_dict(state); model.zero_grad(set_to_none=True)
+        link2 = enable_sync_batchnorm(model)
+        reducer = GradBucketReducer(model.parameters(), 3)
+        opt = Adam(model.parameters(), lr=1e-4)
+        step = CapturedTrainStep(model, opt, xs2, ys2, reducer=reducer)
+        calls_before = link2.calls
+        l_cap = float(step(xs2, ys2))
+        cap_state = {k: v.detach().clone() for k, v in model.state_dict().items()}
+        step.close()
+        model.load_state_dict(state)
+        opt2 = Adam(model.parameters(), lr=1e-4)
+        opt2.zero_grad(set_to_none=True)
+        l_e = cross_entropy(model(xs2), ys2); l_e.backward(); reducer.finish(); opt2.step()
+        cs = {'loss_diff': abs(l_cap - float(l_e)),
+              'param_absdiff': max(float((cap_state[k] - v).abs().max()) for k, v in model.state_dict().items()
+                                   if v.dtype.is_floating_point and 'running' not in k),
+              'running_stats': max(float((cap_state[k] - v).abs().max() / v.abs().max().clamp_min(1e-6)) for k, v in model.state_dict().items() if 'running' in k),
+              'host_calls_after_capture': link2.calls - calls_before}
+        w = torch.cat([q.detach().flatten() for q in model.parameters()])
+        w0 = w.clone(); dist.broadcast(w0, src=0)
+        cs['replica_weight_diff'] = float((w - w0).abs().max())
+        res['captured_sync'] = cs
+        del l_e
+    except BaseException:
+        import traceback
+        res['captured_sync'] = {'error': traceback.format_exc()[-1200:]}
     torch.cuda.synchronize()
     out.put((rank, res))
 
@@ -362,7 +394,7 @@ def test_two_rank_sync_batchnorm_equals_full_batch():
         assert 'error' not in results[r], results[r]['error']
     res = results[0]
     for tag, r in res.items():
-        if tag == 'model':
+        if tag in ('model', 'captured_sync'):
             continue
         assert r['calls'] in (4, 5), (tag, r)
         assert r['y'] < (1e-4 if tag.endswith('float32') else 2e-2), (tag, r)
@@ -371,4 +403,9 @@ def test_two_rank_sync_batchnorm_equals_full_batch():
     assert md['logits_vs_full_batch'] < TOL and md['logits_vs_oracle'] < TOL, md
     assert md['running_stats'] < TOL, md
     assert md['grad_l2_vs_full_batch'] < 0.5, md       # bf16 model-level gradient noise floor is 0.2-0.9 in this measure
+    for r in range(2):
+        cs = results[r]['captured_sync']
+        assert 'error' not in cs, cs['error']
+        assert cs['loss_diff'] < 1e-2 and cs['param_absdiff'] <= 2.5e-4 and cs['running_stats'] < 2e-2, cs
+        assert cs['replica_weight_diff'] == 0.0, cs
     assert md['calls'] >= 30, md                      # ~4 exchanges per block (the first block has no dx, so no BatchNorm-1 backward exchange)
